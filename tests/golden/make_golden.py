@@ -1,0 +1,247 @@
+"""Generate tests/golden/*.pt from the REFERENCE's own Python reference functions.
+
+Run in the build container only (needs /root/reference, which does not exist
+on the GPU box):   python tests/golden/make_golden.py
+
+The reference's torch reference implementations live inside its test modules,
+which import the XPU extension modules at import time and hard-code
+``device="xpu"``.  This script stubs those extension modules with empty ones,
+redirects the "xpu" device to the CPU, imports the test modules from
+/root/reference unmodified, and calls their reference functions on seeded
+inputs.  Inputs and outputs are stored (fp8 as uint8 views) so that
+tests/test_oracle_golden.py can pin oracle/ to them without the reference.
+"""
+import os
+import sys
+import types
+
+import torch
+
+REF = "/root/reference"
+OUT = os.path.dirname(os.path.abspath(__file__))
+
+
+def _stub_reference_extensions():
+    pkg = types.ModuleType("vllm_xpu_kernels")
+    pkg.__path__ = []  # namespace-like: no real submodules are imported
+    sys.modules["vllm_xpu_kernels"] = pkg
+    for name in ("_C", "_moe_C", "_xpu_C", "_vllm_fa2_C"):
+        m = types.ModuleType(f"vllm_xpu_kernels.{name}")
+        sys.modules[f"vllm_xpu_kernels.{name}"] = m
+        setattr(pkg, name, m)
+    sys.path.insert(0, REF)
+
+
+def u8(t):
+    return t.contiguous().view(torch.uint8).clone()
+
+
+def main():
+    _stub_reference_extensions()
+    import tests.test_fp8_quant as t_fp8
+    import tests.test_fused_norm_quant as t_norm
+    import tests.test_fused_quant_activation as t_act
+    import tests.test_fused_silu_mul_block_quant as t_silu_blk
+    import tests.test_fused_silu_mul_mxfp4_quant as t_silu_fp4
+    from tests.ops import fp8_quant_op, mx_utils
+
+    # device="xpu" -> cpu
+    t_fp8.as_float32_tensor = lambda x: torch.as_tensor(x, dtype=torch.float32)
+
+    E4, E5 = torch.float8_e4m3fn, torch.float8_e5m2
+    g = {}
+
+    # ---- exhaustive E2M1 table over every bf16 bit pattern (mx_utils :152-266)
+    allbits = torch.arange(0, 65536, dtype=torch.int32).to(torch.int16)
+    allbf16 = allbits.view(torch.bfloat16)
+    finite = torch.isfinite(allbf16.float())
+    codes = mx_utils._f32_to_floatx_unpacked(
+        torch.where(finite, allbf16.float(), torch.zeros(())), 2, 1)
+    g["e2m1_all_bf16"] = {"codes": codes, "finite": finite}
+    dec = mx_utils._floatx_unpacked_to_f32(torch.arange(16, dtype=torch.uint8), 2, 1)
+    g["e2m1_decode"] = {"values": dec}
+
+    # ---- a1 dynamic per-token (test_fp8_quant.py:270-304 inputs)
+    cases = []
+    for dtype in (torch.bfloat16, torch.float16, torch.float32):
+        for qd in (E4, E5):
+            for (T, H) in ((7, 67), (5, 1024), (3, 1031)):
+                for use_ub in (False, True):
+                    torch.manual_seed(0)
+                    x = torch.rand(T, H, dtype=dtype) + 1e-6
+                    ub = torch.mean(x).to(torch.float32) if use_ub else None
+                    q, s = t_fp8.ref_dynamic_per_token_quant(x, qd, ub)
+                    cases.append(dict(x=x, qdtype=str(qd), ub=ub, q=u8(q), s=s))
+    g["a1_dynamic_per_token"] = cases
+
+    # ---- a3 dynamic per-tensor / a2 static with that scale (:28-45, :401-425)
+    cases = []
+    for dtype in (torch.bfloat16, torch.float16, torch.float32):
+        for qd in (E4, E5):
+            torch.manual_seed(0)
+            x = torch.rand(11, 520, dtype=dtype)
+            q, s = t_fp8.ref_dynamic_per_tensor_fp8_quant(x, qd)
+            cases.append(dict(x=x, qdtype=str(qd), q=u8(q), s=s))
+    g["a3_dynamic_per_tensor"] = cases
+
+    # ---- a2 static group shapes via scaled_quantize (fp8_quant_op.py:301-348)
+    cases = []
+    for gs in ((-1, -1), (-1, 1), (1, -1), (1, 128), (128, 128), (4, 256)):
+        torch.manual_seed(0)
+        x = torch.rand(128, 256, dtype=torch.bfloat16)
+        q, s = fp8_quant_op.scaled_quantize(x, gs, E4, compute_dtype=torch.float32)
+        cases.append(dict(x=x, group_shape=gs, q=u8(q), s=s))
+    g["a2_static_scaled_quantize"] = cases
+
+    # ---- a4 per-token-group (ref_per_block_quant :86-142; to_mxfp for ue8m0)
+    cases = []
+    for dtype in (torch.float32, torch.bfloat16, torch.float16):
+        for G in (32, 64, 128):
+            torch.manual_seed(0)
+            x = torch.rand(9, 256, dtype=dtype) + 1e-6
+            q, s = t_fp8.ref_per_block_quant(x, 1, G)
+            cases.append(dict(x=x, G=G, q=u8(q), s=s))
+    g["a4_per_block"] = cases
+    cases = []
+    for dtype in (torch.float32, torch.bfloat16):
+        torch.manual_seed(0)
+        x = torch.rand(9, 256, dtype=dtype) + 1e-6
+        s, q = mx_utils.to_mxfp(x)
+        cases.append(dict(x=x, q=u8(q), s_e8m0=u8(s)))
+    g["a4_mxfp8"] = cases
+
+    # ---- a5 mxfp4 (to_mxfp mxfp4; known values test_mxfp4_quant.py:113-142)
+    cases = []
+    for dtype in (torch.float32, torch.bfloat16):
+        for (T, H) in ((4, 64), (8, 512)):
+            torch.manual_seed(0)
+            x = torch.rand(T, H, dtype=dtype) + 1e-6
+            s, q = mx_utils.to_mxfp(x, block_size=32, format="mxfp4")
+            cases.append(dict(x=x, q=u8(q), s_e8m0=u8(s)))
+        torch.manual_seed(1)
+        x = (torch.randn(16, 256, dtype=dtype) * 3.0)
+        s, q = mx_utils.to_mxfp(x, block_size=32, format="mxfp4")
+        cases.append(dict(x=x, q=u8(q), s_e8m0=u8(s)))
+    for val in (0.0, 0.5, 1.0, 1.5, 2.0, 3.0, 4.0, 6.0):
+        x = torch.zeros(1, 32, dtype=torch.float32)
+        x[0, 0] = val if val > 0 else 0.5
+        s, q = mx_utils.to_mxfp(x, block_size=32, format="mxfp4")
+        cases.append(dict(x=x, q=u8(q), s_e8m0=u8(s)))
+    # mid-points and an all-zero group
+    x = torch.zeros(2, 64, dtype=torch.float32)
+    x[0, :9] = torch.tensor([6.0, 0.25, 0.75, 1.25, 1.75, 2.5, 3.5, 5.0, -5.0])
+    x[1, 32:40] = torch.tensor([-6.0, -0.25, 0.1, 7e-3, 3.0, -3.5, 4.5, 5.5])
+    s, q = mx_utils.to_mxfp(x, block_size=32, format="mxfp4")
+    cases.append(dict(x=x, q=u8(q), s_e8m0=u8(s)))
+    g["a5_mxfp4"] = cases
+
+    # ---- a6..a9 fused rms-norm (test_fused_norm_quant.py:37-125,448-456)
+    class Layer:
+        pass
+
+    cases = []
+    for dtype in (torch.bfloat16, torch.float16):
+        for (T, H) in ((7, 128), (5, 1024)):
+            for add_res in (False, True):
+                torch.manual_seed(0)
+                layer = Layer()
+                layer.variance_epsilon = 1e-6
+                layer.weight = torch.empty(H, dtype=dtype).normal_(mean=1.0, std=0.1)
+                x = torch.randn(T, H, dtype=dtype) * (1.0 / H)
+                res = torch.randn_like(x) * (1.0 / H) if add_res else None
+                normed, res_out = t_norm._ref_rms_norm(layer, x, res)
+                c = dict(x=x, w=layer.weight, res=res, res_out=res_out, normed=normed)
+                for qd in (E4, torch.int8):
+                    q, s = t_norm._ref_per_token_quant(normed, qd)
+                    c[f"tok_{qd}"] = (u8(q), s)
+                    for G in (64, 128):
+                        q, s = t_norm._ref_per_group_quant(normed, G, qd)
+                        c[f"grp{G}_{qd}"] = (u8(q), s)
+                q, s = t_norm._ref_per_group_quant(normed, 32, E4, scale_ue8m0=True)
+                c["grp32_ue8m0"] = (u8(q), s)
+                ub = torch.tensor(0.9 * float(normed.abs().max()))
+                q, s = t_norm._ref_per_token_quant(normed, E4, ub)
+                c["tok_ub"] = (ub, u8(q), s)
+                c["static"] = u8(t_norm._ref_static_fp8_quant(normed, torch.tensor(1.0)))
+                c["static_0p02"] = u8(t_norm._ref_static_fp8_quant(normed, torch.tensor(0.02)))
+                s, q = mx_utils.to_mxfp(normed.float().contiguous(), block_size=32,
+                                        format="mxfp4")
+                c["mxfp4"] = (u8(q), u8(s))
+                cases.append(c)
+    g["a6_a9_rms_norm"] = cases
+
+    # ---- a10 silu_and_mul_quant (test_fused_quant_activation.py:28-40)
+    cases = []
+    for dtype in (torch.bfloat16, torch.float16):
+        for qd in (E4, E5):
+            torch.manual_seed(0)
+            x = torch.randn(7, 2 * 128, dtype=dtype)
+            scale = torch.tensor([0.5], dtype=torch.float32)
+            q = t_act.ref_silu_and_mul_quant(x, scale, qd)
+            cases.append(dict(x=x, scale=scale, qdtype=str(qd), q=u8(q)))
+    g["a10_silu_static"] = cases
+
+    # ---- a11 silu_and_mul_per_block_quant (test_fused_silu_mul_block_quant.py:49-79)
+    cases = []
+    for dtype in (torch.bfloat16, torch.float16):
+        for qd in (E4, torch.int8):
+            for G in (64, 128):
+                torch.manual_seed(0)
+                H = 1024
+                x = torch.randn(16, 2 * H, dtype=dtype) * (1.0 / H)
+                q, s = t_silu_blk.ref_silu_and_mul_per_block_quant(x, qd, G)
+                cases.append(dict(x=x, G=G, qdtype=str(qd), q=u8(q), s=s))
+    g["a11_silu_block"] = cases
+
+    # ---- a12 silu_and_mul_mxfp4_quant (test_fused_silu_mul_mxfp4_quant.py:22-41)
+    cases = []
+    for dtype in (torch.bfloat16, torch.float16):
+        torch.manual_seed(0)
+        H = 1024
+        x = torch.randn(7, 2 * H, dtype=dtype) * (1.0 / H)
+        q, s_f32, _ = t_silu_fp4._ref_silu_and_mul_mxfp4_quant(x)
+        cases.append(dict(x=x, q=u8(q), s=s_f32))
+    g["a12_silu_mxfp4"] = cases
+
+    # ---- weight-side helpers used to build GEMM operands
+    cases = []
+    for ue in (False, True):
+        torch.manual_seed(1234)
+        w = torch.randn(256, 512, dtype=torch.bfloat16) / 10.0
+        q, s = fp8_quant_op.fp8_block_quant_2d(w, 128, 128, use_ue8m0=ue)
+        deq = fp8_quant_op.fp8_block_dequant_2d(q, s, 128, 128, torch.bfloat16)
+        cases.append(dict(w=w, ue8m0=ue, q=u8(q), s=u8(s) if ue else s, deq=deq))
+    g["fp8_block_quant_2d"] = cases
+
+    # ---- a13 / a14 GEMM: the reference tests' expected outputs
+    # (test_fp8_gemm_onednn.py:172-214 per-channel; test_fp4_gemm_onednn.py:49-78)
+    torch.manual_seed(1234)
+    m, n, k = 8, 64, 256
+    a = torch.randn(m, k, dtype=torch.bfloat16) / 10.0
+    w = torch.randn(n, k, dtype=torch.bfloat16) / 10.0
+    aq, asc = t_fp8.ref_dynamic_per_token_quant(a, E4)
+    wq, wsc = t_fp8.ref_dynamic_per_token_quant(w, E4)
+    a_hp = aq.to(torch.bfloat16) * asc.to(torch.bfloat16)
+    w_hp = wq.to(torch.bfloat16) * wsc.to(torch.bfloat16)
+    g["a13_fp8_gemm_per_channel"] = dict(aq=u8(aq), asc=asc, wq=u8(wq), wsc=wsc,
+                                         out=torch.matmul(a_hp, w_hp.t()))
+    torch.manual_seed(1234)
+    a = torch.randn(m, k, dtype=torch.bfloat16) * 0.01
+    w = torch.randn(n, k, dtype=torch.bfloat16) * 0.01
+    sa, qa = mx_utils.to_mxfp(a, format="mxfp4")
+    sw, qw = mx_utils.to_mxfp(w, format="mxfp4")
+    a_hp = mx_utils.from_blocked_format(
+        mx_utils._floatx_unpacked_to_f32(mx_utils.unpack_uint4(qa), 2, 1), sa, 32)
+    w_hp = mx_utils.from_blocked_format(
+        mx_utils._floatx_unpacked_to_f32(mx_utils.unpack_uint4(qw), 2, 1), sw, 32)
+    g["a14_fp4_gemm"] = dict(qa=u8(qa), sa=u8(sa), qw=u8(qw), sw=u8(sw),
+                             a_hp=a_hp, w_hp=w_hp,
+                             out=torch.matmul(a_hp, w_hp.t()))
+
+    for name, obj in g.items():
+        torch.save(obj, os.path.join(OUT, name + ".pt"))
+        print(f"{name}: {os.path.getsize(os.path.join(OUT, name + '.pt'))/1024:.1f} KiB")
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,197 @@
+"""Pins oracle/ to the reference: every oracle function is compared bit for
+bit with outputs of the reference's own Python reference functions, captured
+by tests/golden/make_golden.py (which imports them from /root/reference)."""
+import os
+
+import pytest
+import torch
+
+from oracle import formats, gemm, quant
+
+G = os.path.join(os.path.dirname(__file__), "golden")
+E4, E5 = torch.float8_e4m3fn, torch.float8_e5m2
+QD = {str(E4): E4, str(E5): E5, str(torch.int8): torch.int8}
+
+
+def load(name):
+    return torch.load(os.path.join(G, name + ".pt"), weights_only=False)
+
+
+def u8(t):
+    return t.contiguous().view(torch.uint8)
+
+
+def test_e2m1_encode_matches_reference_on_every_bf16():
+    g = load("e2m1_all_bf16")
+    allbf16 = torch.arange(0, 65536, dtype=torch.int32).to(torch.int16).view(torch.bfloat16)
+    v = torch.where(g["finite"], allbf16.float(), torch.zeros(()))
+    assert torch.equal(formats.e2m1_encode(v), g["codes"])
+
+
+def test_e2m1_decode_table():
+    g = load("e2m1_decode")
+    assert torch.equal(formats.e2m1_decode(torch.arange(16, dtype=torch.uint8)), g["values"])
+
+
+def test_pack_unpack_roundtrip():
+    c = torch.randint(0, 16, (5, 64), dtype=torch.uint8)
+    assert torch.equal(formats.unpack_nibbles(formats.pack_nibbles(c)), c)
+
+
+def test_rceil_exponent_exact_vs_log2():
+    # exact powers of two and generic values agree; the log2 form only differs
+    # within a few ulp above 2^k (DESIGN.md "ceil(log2)")
+    k = torch.arange(-126, 128, dtype=torch.float32)
+    p = torch.exp2(k)
+    assert torch.equal(formats.rceil_exponent(p), formats.rceil_exponent_exact(p))
+    torch.manual_seed(0)
+    x = torch.rand(1 << 16) * torch.exp2(torch.randint(-40, 40, (1 << 16,)).float())
+    a, b = formats.rceil_exponent(x), formats.rceil_exponent_exact(x)
+    assert (a != b).float().mean() < 1e-4
+    up = torch.nextafter(p[:-1], torch.tensor(float("inf")))
+    assert torch.equal(formats.rceil_exponent_exact(up).int(),
+                       (k[:-1] + 1 + 127).clamp(0, 254).int())
+    z = torch.tensor([0.0, 2.0 ** -127, 2.0 ** -126.5, 2.0 ** -149])
+    assert formats.rceil_exponent_exact(z).tolist() == [0, 0, 1, 0]
+    assert formats.rceil_exponent(z).tolist() == [0, 0, 1, 0]
+
+
+def test_a1_dynamic_per_token():
+    for c in load("a1_dynamic_per_token"):
+        q, s = quant.dynamic_per_token_scaled_fp8_quant(c["x"], QD[c["qdtype"]], c["ub"])
+        assert torch.equal(s, c["s"])
+        assert torch.equal(u8(q), c["q"])
+
+
+def test_a3_dynamic_per_tensor_and_a2_static():
+    for c in load("a3_dynamic_per_tensor"):
+        qd = QD[c["qdtype"]]
+        q, s = quant.dynamic_scaled_fp8_quant(c["x"], qd)
+        assert torch.equal(s, c["s"])
+        assert torch.equal(u8(q), c["q"])
+        q2 = quant.static_scaled_fp8_quant(c["x"], c["s"], qd)
+        assert torch.equal(u8(q2), c["q"])
+
+
+def test_a2_static_group_shapes_reference_tolerance():
+    # scaled_quantize multiplies by fp8max/amax; the op multiplies by 1/(1/that):
+    # the reference only pins this to rtol 0.12 (test_fp8_quant.py:464-470)
+    for c in load("a2_static_scaled_quantize"):
+        s = c["s"]
+        q = quant.static_scaled_fp8_quant(c["x"], s, E4, tuple(c["group_shape"]))
+        ref = c["q"].view(E4).float()
+        torch.testing.assert_close(q.float(), ref, rtol=0.12, atol=1e-5)
+        # 1-D scale path
+        gs = tuple(c["group_shape"])
+        if gs in ((1, -1), (-1, 1)):
+            q1 = quant.static_scaled_fp8_quant(c["x"], s.flatten(), E4, gs)
+            assert torch.equal(u8(q1), u8(q))
+
+
+def test_a4_per_block():
+    for c in load("a4_per_block"):
+        x, Gs = c["x"], c["G"]
+        ql, sl = quant.per_token_group_fp8_quant_literal(x, Gs)
+        assert torch.equal(u8(ql), c["q"]) and torch.equal(sl, c["s"])
+        q, s = quant.per_token_group_fp8_quant(x, Gs)
+        if x.dtype == torch.float32:   # fp32 input: literal == exact
+            assert torch.equal(u8(q), c["q"]) and torch.equal(s, c["s"])
+        else:                          # reference's own tolerance (:338-345)
+            assert torch.allclose(q.float(), c["q"].view(E4).float(), atol=0.15, rtol=0.15)
+            assert torch.allclose(s, c["s"], atol=0.01, rtol=0.01)
+
+
+def test_a4_mxfp8():
+    for c in load("a4_mxfp8"):
+        e, q = formats.mx_quantize(c["x"], "mxfp8")
+        assert torch.equal(u8(e), c["s_e8m0"]) and torch.equal(u8(q), c["q"])
+        q2, s2 = quant.per_token_group_fp8_quant(c["x"], 32, scale_ue8m0=True)
+        assert torch.equal(u8(q2), c["q"])
+        assert torch.equal(u8(s2.to(torch.float8_e8m0fnu)), c["s_e8m0"])
+
+
+def test_a5_mxfp4():
+    for c in load("a5_mxfp4"):
+        for exact in (False, True):
+            q, s, e = quant.per_token_group_quant_mxfp4(c["x"], 32, exact_exponent=exact)
+            assert torch.equal(e, c["s_e8m0"])
+            assert torch.equal(q, c["q"])
+            assert torch.equal(u8(s.to(torch.float8_e8m0fnu)), c["s_e8m0"])
+
+
+def test_a6_a9_rms_norm():
+    for c in load("a6_a9_rms_norm"):
+        x, w, res = c["x"], c["w"], c["res"]
+        normed, res_out = quant.rms_norm_f32(x, w, 1e-6, res)
+        assert torch.equal(normed, c["normed"])
+        if res is not None:
+            assert torch.equal(res_out, c["res_out"])
+        for qd in (E4, torch.int8):
+            q, s, _ = quant.rms_norm_dynamic_per_token_quant(x, w, 1e-6, qd, None, res)
+            gq, gs = c[f"tok_{qd}"]
+            assert torch.equal(u8(q), gq) and torch.equal(s, gs)
+            for Gs in (64, 128):
+                q, s, _ = quant.rms_norm_per_block_quant(x, w, 1e-6, Gs, qd, res)
+                gq, gs = c[f"grp{Gs}_{qd}"]
+                assert torch.equal(u8(q), gq) and torch.equal(s, gs)
+        q, s, _ = quant.rms_norm_per_block_quant(x, w, 1e-6, 32, E4, res, scale_ue8m0=True)
+        gq, gs = c["grp32_ue8m0"]
+        assert torch.equal(u8(q), gq) and torch.equal(s, gs)
+        ub, gq, gs = c["tok_ub"]
+        q, s, _ = quant.rms_norm_dynamic_per_token_quant(x, w, 1e-6, E4, ub, res)
+        assert torch.equal(u8(q), gq) and torch.equal(s, gs)
+        q, _ = quant.rms_norm_static_fp8_quant(x, w, torch.tensor(1.0), 1e-6, res)
+        assert torch.equal(u8(q), c["static"])
+        q, _ = quant.rms_norm_static_fp8_quant(x, w, torch.tensor(0.02), 1e-6, res)
+        assert torch.equal(u8(q), c["static_0p02"])
+        gq, ge = c["mxfp4"]
+        for exact in (False, True):
+            q, s, _ = quant.rms_norm_mxfp4_quant(x, w, 1e-6, res, exact_exponent=exact)
+            assert torch.equal(q, gq)
+            assert torch.equal(u8(s.to(torch.float8_e8m0fnu)), ge)
+
+
+def test_a10_silu_static():
+    for c in load("a10_silu_static"):
+        q = quant.silu_and_mul_quant(c["x"], c["scale"], QD[c["qdtype"]])
+        assert torch.equal(u8(q), c["q"])
+
+
+def test_a11_silu_block():
+    for c in load("a11_silu_block"):
+        q, s = quant.silu_and_mul_per_block_quant(c["x"], c["G"], QD[c["qdtype"]])
+        assert torch.equal(s, c["s"]) and torch.equal(u8(q), c["q"])
+
+
+def test_a12_silu_mxfp4():
+    for c in load("a12_silu_mxfp4"):
+        for exact in (False, True):
+            q, s = quant.silu_and_mul_mxfp4_quant(c["x"], exact_exponent=exact)
+            assert torch.equal(q, c["q"])
+            # the reference test turns byte 0 into 1.0; no zero groups here
+            assert torch.equal(s, c["s"])
+
+
+def test_fp8_block_quant_2d_helper():
+    for c in load("fp8_block_quant_2d"):
+        q, s = gemm.fp8_block_quant_2d(c["w"], 128, 128, use_ue8m0=c["ue8m0"])
+        assert torch.equal(u8(q), c["q"])
+        assert torch.equal(u8(s) if c["ue8m0"] else s, c["s"])
+
+
+def test_a13_fp8_gemm_reference_tolerance():
+    g = load("a13_fp8_gemm_per_channel")
+    A = g["aq"].view(E4)
+    W = g["wq"].view(E4)
+    out = gemm.fp8_gemm_ref(A, W.t(), torch.bfloat16, g["asc"], g["wsc"])
+    torch.testing.assert_close(out, g["out"], atol=6e-2, rtol=6e-2)
+
+
+def test_a14_fp4_gemm_reference_tolerance():
+    g = load("a14_fp4_gemm")
+    A = g["qa"].view(torch.float4_e2m1fn_x2)
+    W = g["qw"].view(torch.float4_e2m1fn_x2)
+    assert torch.equal(formats.mx_dequantize(A, g["sa"].view(torch.float8_e8m0fnu)), g["a_hp"])
+    out = gemm.fp4_gemm_ref(A, W.t(), g["sa"].view(torch.float8_e8m0fnu),
+                            g["sw"].view(torch.float8_e8m0fnu), torch.bfloat16)
+    torch.testing.assert_close(out.float(), g["out"].float(), atol=5e-2, rtol=5e-2)
