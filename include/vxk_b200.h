@@ -1,0 +1,180 @@
+/*
+ * vxk_b200.h -- C ABI of libvxk_b200.so, the B200 (sm_100a) implementation of
+ * the quantized-linear hot path of vllm-xpu-kernels.
+ *
+ * One entry point per reference operator on the path.  Every pointer is a
+ * DEVICE pointer unless stated otherwise; no torch / C++ types cross this
+ * boundary.  All calls are asynchronous on `stream` and allocate nothing
+ * (the GEMMs take their output buffer from the caller).  Return value: 0 on
+ * success, a negative VXK_ERR_* otherwise; vxk_last_error() returns a
+ * thread-local message for the last failure on the calling thread.
+ *
+ * "ref:" lines cite the reference interface each function replaces
+ * (paths relative to the reference repository root).
+ */
+#ifndef VXK_B200_H_
+#define VXK_B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define VXK_ABI_VERSION 1
+
+typedef struct CUstream_st* vxk_stream_t; /* == cudaStream_t */
+
+/* activation element types (ref: VLLM_DISPATCH_FLOATING_TYPES, csrc/dispatch_utils.h) */
+enum { VXK_F32 = 0, VXK_F16 = 1, VXK_BF16 = 2 };
+/* quantised element types (ref: VLLM_DISPATCH_FP8_TYPES + int8 of the fused kernels) */
+enum { VXK_Q_E4M3 = 0, VXK_Q_E5M2 = 1, VXK_Q_INT8 = 2 };
+/* GEMM scale element types */
+enum { VXK_S_F32 = 0, VXK_S_E8M0 = 1 };
+
+enum {
+  VXK_OK = 0,
+  VXK_ERR_INVALID = -1,     /* bad argument (the torch shim turns it into RuntimeError) */
+  VXK_ERR_UNSUPPORTED = -2, /* valid in the reference but not implemented here */
+  VXK_ERR_CUDA = -3         /* CUDA runtime / driver error */
+};
+
+int vxk_abi_version(void);
+const char* vxk_last_error(void);
+/* number of kernels this library has launched in this process (bench "gpu_launches") */
+uint64_t vxk_launch_count(void);
+/* silu evaluation in the fused silu_and_mul_* kernels: 0 (default) = expf + IEEE divide,
+ * 1 = ex2.approx / rcp.approx.  Returns the previous setting.  Process-wide. */
+int vxk_set_silu_fast(int on);
+
+/* ---------------------------------------------------------------- a1 ----
+ * ref: dynamic_per_token_scaled_fp8_quant  csrc/quantization/fp8/fp8_quant.cpp:842-881
+ *      schema csrc/torch_bindings.cpp:160-163
+ * in [T,H] contiguous, out [T,H] contiguous fp8, scales [T] fp32,
+ * scale_ub: nullable pointer to ONE fp32 on the device. */
+int vxk_dynamic_per_token_scaled_fp8_quant(void* out, const void* in, float* scales,
+                                           const float* scale_ub, int64_t T, int64_t H,
+                                           int in_dtype, int q_dtype, vxk_stream_t stream);
+
+/* ---------------------------------------------------------------- a2 ----
+ * ref: static_scaled_fp8_quant  fp8_quant.cpp:481-665, schema torch_bindings.cpp:147-149
+ * scale element for (row, col) is scale[(row/group_m)*ss_i + (col/group_n)*ss_j]. */
+int vxk_static_scaled_fp8_quant(void* out, const void* in, const float* scale, int64_t T,
+                                int64_t H, int64_t in_row_stride, int64_t out_row_stride,
+                                int64_t group_m, int64_t group_n, int64_t ss_i, int64_t ss_j,
+                                int in_dtype, int q_dtype, vxk_stream_t stream);
+
+/* ---------------------------------------------------------------- a3 ----
+ * ref: dynamic_scaled_fp8_quant  fp8_quant.cpp:667-722, schema torch_bindings.cpp:153-156
+ * scale: ONE fp32, written (amax / fp8_max). */
+int vxk_dynamic_scaled_fp8_quant(void* out, const void* in, float* scale, int64_t T, int64_t H,
+                                 int64_t in_row_stride, int64_t out_row_stride, int in_dtype,
+                                 int q_dtype, vxk_stream_t stream);
+
+/* ---------------------------------------------------------------- a4 ----
+ * ref: per_token_group_quant_fp8  fp8_quant.cpp:724-840, schema torch_bindings.cpp:170-177
+ * scales element (t, g) at out_s[t*ss0 + g*ss1] (row-major, column-major and
+ * TMA-aligned column-major are all stride pairs). */
+int vxk_per_token_group_fp8_quant(const void* in, void* out_q, float* out_s, int64_t T, int64_t H,
+                                  int64_t group_size, double eps, int scale_ue8m0, int64_t ss0,
+                                  int64_t ss1, int in_dtype, int q_dtype, vxk_stream_t stream);
+
+/* ---------------------------------------------------------------- a5 ----
+ * ref: per_token_group_quant_mxfp4  csrc/quantization/fp4/mxfp4_quant.cpp:24-126,
+ *      schema torch_bindings.cpp:180-182.  out_q [T,H/2] bytes (even element in the
+ * low nibble), out_s fp32 power of two 2^(e-127) at out_s[t*ss0 + g*ss1]. */
+int vxk_per_token_group_quant_mxfp4(const void* in, void* out_q, float* out_s, int64_t T, int64_t H,
+                                    int64_t group_size, double eps, int64_t ss0, int64_t ss1,
+                                    int in_dtype, vxk_stream_t stream);
+
+/* ---------------------------------------------------------------- a6 ----
+ * ref: rms_norm_dynamic_per_token_quant  csrc/layernorm_quant.cpp:988-1045,
+ *      schema torch_bindings.cpp:39-42.  residual (nullable) is updated in place. */
+int vxk_rms_norm_dynamic_per_token_quant(void* out, const void* in, const void* weight, float* scales,
+                                         double epsilon, const float* scale_ub, void* residual,
+                                         int64_t T, int64_t H, int in_dtype, int q_dtype,
+                                         vxk_stream_t stream);
+
+/* ---------------------------------------------------------------- a7 ----
+ * ref: rms_norm_per_block_quant  layernorm_quant.cpp:1047-1114, schema torch_bindings.cpp:49-53 */
+int vxk_rms_norm_per_block_quant(void* out, const void* in, const void* weight, float* scales,
+                                 double epsilon, void* residual, int64_t T, int64_t H,
+                                 int64_t in_row_stride, int64_t group_size, int64_t ss0, int64_t ss1,
+                                 int scale_ue8m0, int in_dtype, int q_dtype, vxk_stream_t stream);
+
+/* ---------------------------------------------------------------- a8 ----
+ * ref: rms_norm_mxfp4_quant  layernorm_quant.cpp:1172-1219, schema torch_bindings.cpp:56-59 */
+int vxk_rms_norm_mxfp4_quant(void* out, const void* in, const void* weight, float* scales,
+                             double epsilon, void* residual, int64_t T, int64_t H,
+                             int64_t group_size, int64_t ss0, int64_t ss1, int in_dtype,
+                             vxk_stream_t stream);
+
+/* ---------------------------------------------------------------- a9 ----
+ * ref: rms_norm_static_fp8_quant / fused_add_rms_norm_static_fp8_quant
+ *      layernorm_quant.cpp:1116-1170, schema torch_bindings.cpp:63-73.
+ * residual nullable: non-null selects the fused_add variant (updated in place). */
+int vxk_rms_norm_static_fp8_quant(void* out, const void* in, const void* weight, const float* scale,
+                                  double epsilon, void* residual, int64_t T, int64_t H,
+                                  int64_t in_row_stride, int in_dtype, int q_dtype,
+                                  vxk_stream_t stream);
+
+/* ---------------------------------------------------------------- a10 ---
+ * ref: silu_and_mul_quant  csrc/activation.cpp:552-566, schema torch_bindings.cpp:84-85
+ * in [T, 2*d] (gate || up), out [T, d] fp8, scale ONE fp32. */
+int vxk_silu_and_mul_quant(void* out, const void* in, const float* scale, int64_t T, int64_t d,
+                           int in_dtype, int q_dtype, vxk_stream_t stream);
+
+/* ---------------------------------------------------------------- a11 ---
+ * ref: silu_and_mul_per_block_quant  csrc/quantization/fused_kernels/fused_silu_mul_block_quant.cpp:141-239,
+ *      schema torch_bindings.cpp:89-97 */
+int vxk_silu_and_mul_per_block_quant(void* out, const void* in, float* scales, int64_t T, int64_t H,
+                                     int64_t group_size, const float* scale_ub, int64_t ss0,
+                                     int64_t ss1, int scale_ue8m0, int in_dtype, int q_dtype,
+                                     vxk_stream_t stream);
+
+/* ---------------------------------------------------------------- a12 ---
+ * ref: silu_and_mul_mxfp4_quant  fused_silu_mul_mxfp4_quant.cpp:134-209,
+ *      schema torch_bindings.cpp:103-106 */
+int vxk_silu_and_mul_mxfp4_quant(void* out, const void* in, float* scales, int64_t T, int64_t H,
+                                 int64_t group_size, double eps, int64_t ss0, int64_t ss1,
+                                 int in_dtype, vxk_stream_t stream);
+
+/* ---------------------------------------------------------------- a13 ---
+ * ref: fp8_gemm  csrc/xpu/onednn/onednn_matmul.cpp:54-79 -> dnnl_matmul_w8a8_fp8
+ *      csrc/xpu/onednn/fp8_gemm_w8a8.h:12-184, schema csrc/xpu/torch_bindings.cpp:14-16
+ *
+ * D[M,N] (ldd) = (A o sA) (B o sB) + bias,  fp32 accumulate, D bf16 or f16.
+ *   A: [M,K] fp8, row stride lda (K contiguous).
+ *   B: element (k,n) at B[k*b_stride_k + n*b_stride_n]; one of the strides is 1
+ *      ("nt": b_stride_k == 1, i.e. a transposed view of W[N,K]; "nn": b_stride_n == 1).
+ *   a_scale_mode / b_scale_mode: 0 = one scalar, 1 = per row of A ([M]) / per
+ *      column of B ([N]), 2 = block: sA[m, k/gk] at sA[m*sa0 + kb*sa1],
+ *      sB[k/gk, n/gn] at sB[kb*sb0 + nb*sb1].
+ *   scale_dtype: VXK_S_F32 or VXK_S_E8M0 (block mode only).
+ *   bias: nullable, [N], bias_dtype VXK_F32/F16/BF16.
+ */
+int vxk_fp8_gemm(void* D, const void* A, const void* B, const void* a_scale, const void* b_scale,
+                 const void* bias, int64_t M, int64_t N, int64_t K, int64_t lda,
+                 int64_t b_stride_k, int64_t b_stride_n, int64_t ldd, int a_scale_mode,
+                 int b_scale_mode, int64_t group_k, int64_t group_n, int64_t sa0, int64_t sa1,
+                 int64_t sb0, int64_t sb1, int scale_dtype, int fp8_dtype, int out_dtype,
+                 int bias_dtype, vxk_stream_t stream);
+
+/* ---------------------------------------------------------------- a14 ---
+ * ref: fp4_gemm  onednn_matmul.cpp:101-123 -> dnnl_matmul_w4a4_fp4
+ *      csrc/xpu/onednn/fp4_gemm_w4a4.h:12-167, schema csrc/xpu/torch_bindings.cpp:24-26
+ *
+ *   A: [M, K/2] packed E2M1 bytes, row stride lda_bytes.
+ *   B: W[N, K/2] packed bytes, row stride ldb_bytes (the op receives it as the
+ *      transposed view [K/2, N]; only this K-major layout exists for FP4).
+ *   sA: [M, K/32] e8m0 bytes at sA[m*sa0 + kb*sa1]; sB: [N, K/32] at sB[n*sb0 + kb*sb1].
+ */
+int vxk_fp4_gemm(void* D, const void* A, const void* B, const void* a_scale, const void* b_scale,
+                 const void* bias, int64_t M, int64_t N, int64_t K, int64_t lda_bytes,
+                 int64_t ldb_bytes, int64_t ldd, int64_t sa0, int64_t sa1, int64_t sb0, int64_t sb1,
+                 int out_dtype, int bias_dtype, vxk_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* VXK_B200_H_ */

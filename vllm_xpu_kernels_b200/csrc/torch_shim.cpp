@@ -1,0 +1,638 @@
+// PyTorch operator surface of the quantized-linear hot path, registered under
+// the CUDA dispatch key.  Schemas are the reference's, verbatim:
+//   library _C      <- /root/reference/csrc/torch_bindings.cpp:38-107,146-184
+//   library _xpu_C  <- /root/reference/csrc/xpu/torch_bindings.cpp:14-27
+// Each implementation replicates the reference launcher's argument checks
+// (TORCH_CHECK -> RuntimeError), takes the current CUDA stream and calls the
+// C ABI of libvxk_b200.so (include/vxk_b200.h).  No kernels live here and
+// there is no CPU or library fallback: a failing C-ABI call raises.
+#include <ATen/cuda/CUDAContext.h>
+#include <c10/cuda/CUDAGuard.h>
+#include <ATen/ATen.h>
+#include <torch/library.h>
+
+#include <optional>
+#include <tuple>
+
+#include "../../include/vxk_b200.h"
+
+namespace {
+
+using at::Tensor;
+
+inline vxk_stream_t cur_stream() {
+  return reinterpret_cast<vxk_stream_t>(at::cuda::getCurrentCUDAStream().stream());
+}
+
+inline void check_rc(int rc, const char* op) {
+  TORCH_CHECK(rc == 0, op, ": ", vxk_last_error());
+}
+
+inline int in_dtype_of(const Tensor& t, const char* op) {
+  switch (t.scalar_type()) {
+    case at::kFloat: return VXK_F32;
+    case at::kHalf: return VXK_F16;
+    case at::kBFloat16: return VXK_BF16;
+    default: TORCH_CHECK(false, op, ": unsupported input dtype ", t.scalar_type());
+  }
+}
+
+inline int q_dtype_of(const Tensor& t, const char* op, bool allow_int8) {
+  switch (t.scalar_type()) {
+    case at::kFloat8_e4m3fn: return VXK_Q_E4M3;
+    case at::kFloat8_e5m2: return VXK_Q_E5M2;
+    case at::kChar:
+      TORCH_CHECK(allow_int8, op, ": int8 output is not supported by this op");
+      return VXK_Q_INT8;
+    default: TORCH_CHECK(false, op, ": unsupported output dtype ", t.scalar_type());
+  }
+}
+
+inline void check_cuda(const Tensor& t, const char* name) {
+  TORCH_CHECK(t.is_cuda(), name, " must be a CUDA tensor");
+}
+
+inline const float* opt_f32(const std::optional<Tensor>& t, const char* name) {
+  if (!t.has_value() || !t->defined()) return nullptr;
+  TORCH_CHECK(t->scalar_type() == at::kFloat, name, " must be float32");
+  check_cuda(*t, name);
+  return t->data_ptr<float>();
+}
+
+// ------------------------------------------------------------------- _C ops
+
+// ref: csrc/quantization/fp8/fp8_quant.cpp:842-881
+void dynamic_per_token_scaled_fp8_quant(Tensor& out, const Tensor& input, Tensor& scales,
+                                        const std::optional<Tensor>& scale_ub) {
+  TORCH_CHECK(input.is_contiguous());
+  TORCH_CHECK(out.is_contiguous());
+  TORCH_CHECK(scales.scalar_type() == at::kFloat, "scales must be float32");
+  check_cuda(input, "input");
+  const int64_t H = input.size(-1);
+  const int64_t T = H ? input.numel() / H : 0;
+  TORCH_CHECK(scales.numel() >= T && scales.is_contiguous(), "scales must hold one fp32 per token");
+  const c10::cuda::CUDAGuard guard(input.device());
+  check_rc(vxk_dynamic_per_token_scaled_fp8_quant(
+               out.data_ptr(), input.data_ptr(), scales.data_ptr<float>(),
+               opt_f32(scale_ub, "scale_ub"), T, H, in_dtype_of(input, "dynamic_per_token_scaled_fp8_quant"),
+               q_dtype_of(out, "dynamic_per_token_scaled_fp8_quant", false), cur_stream()),
+           "dynamic_per_token_scaled_fp8_quant");
+}
+
+// ref: fp8_quant.cpp:481-665 (scale-shape logic :502-623)
+void static_scaled_fp8_quant(Tensor& out, const Tensor& input, const Tensor& scale,
+                             std::optional<std::tuple<int64_t, int64_t>> opt_group_shape) {
+  TORCH_CHECK(input.stride(-1) == 1, "last dimension of input must be contiguous");
+  TORCH_CHECK(out.stride(-1) == 1, "last dimension of output must be contiguous");
+  TORCH_CHECK(scale.scalar_type() == at::kFloat, "scale must be float32");
+  check_cuda(input, "input");
+  const int64_t hidden_size = input.size(-1);
+  const int64_t num_tokens = hidden_size ? input.numel() / hidden_size : 0;
+  int64_t group_m, group_n, ss_i, ss_j;
+  if (scale.dim() == 0 || scale.numel() == 1) {
+    group_m = num_tokens; group_n = hidden_size; ss_i = 0; ss_j = 0;
+  } else if (scale.dim() == 1) {
+    TORCH_CHECK(opt_group_shape.has_value(),
+                "1D scale requires explicit group_shape to disambiguate per-channel vs per-token "
+                "quantization. Use group_shape=(-1, 1) for per-channel or group_shape=(1, -1) for "
+                "per-token.");
+    const auto [ogm, ogn] = opt_group_shape.value();
+    group_m = ogm == -1 ? num_tokens : ogm;
+    group_n = ogn == -1 ? hidden_size : ogn;
+    TORCH_CHECK(group_m > 0 && group_n > 0, "invalid group_shape");
+    const int64_t em = num_tokens / group_m, en = hidden_size / group_n;
+    TORCH_CHECK(scale.numel() == em * en, "1D scale length (", scale.numel(),
+                ") does not match expected size (", em * en, ") for group_shape (", ogm, ", ", ogn,
+                ") with input shape (", num_tokens, ", ", hidden_size, ")");
+    if (em == 1) { ss_i = 0; ss_j = scale.stride(0); }
+    else if (en == 1) { ss_i = scale.stride(0); ss_j = 0; }
+    else TORCH_CHECK(false, "1D scale can only be used when one of the scale dimensions is 1. "
+                            "For 2D group scaling, use a 2D scale tensor.");
+  } else if (scale.dim() == 2) {
+    const int64_t s0 = scale.size(0), s1 = scale.size(1);
+    TORCH_CHECK(s0 > 0 && num_tokens % s0 == 0, "num_tokens (", num_tokens,
+                ") must be divisible by scale.size(0) (", s0, ")");
+    TORCH_CHECK(s1 > 0 && hidden_size % s1 == 0, "hidden_size (", hidden_size,
+                ") must be divisible by scale.size(1) (", s1, ")");
+    const int64_t igm = num_tokens / s0, ign = hidden_size / s1;
+    if (opt_group_shape.has_value()) {
+      const auto [ogm, ogn] = opt_group_shape.value();
+      group_m = ogm == -1 ? num_tokens : ogm;
+      group_n = ogn == -1 ? hidden_size : ogn;
+      TORCH_CHECK(group_m == igm && group_n == ign, "Explicit group_shape (", ogm, ", ", ogn,
+                  ") does not match inferred group shape (", igm, ", ", ign,
+                  ") from 2D scale tensor shape (", s0, ", ", s1, ")");
+    } else {
+      group_m = igm; group_n = ign;
+    }
+    ss_i = scale.stride(0); ss_j = scale.stride(1);
+  } else {
+    TORCH_CHECK(false, "scale must be 0D, 1D, or 2D tensor, but got ", scale.dim(), "D");
+  }
+  const int64_t in_rs = input.dim() >= 2 ? input.stride(-2) : hidden_size;
+  const int64_t out_rs = out.dim() >= 2 ? out.stride(-2) : hidden_size;
+  const c10::cuda::CUDAGuard guard(input.device());
+  check_rc(vxk_static_scaled_fp8_quant(out.data_ptr(), input.data_ptr(), scale.data_ptr<float>(),
+                                       num_tokens, hidden_size, in_rs, out_rs, group_m, group_n, ss_i,
+                                       ss_j, in_dtype_of(input, "static_scaled_fp8_quant"),
+                                       q_dtype_of(out, "static_scaled_fp8_quant", false), cur_stream()),
+           "static_scaled_fp8_quant");
+}
+
+// ref: fp8_quant.cpp:667-722
+void dynamic_scaled_fp8_quant(Tensor& out, const Tensor& input, Tensor& scale) {
+  TORCH_CHECK(scale.scalar_type() == at::kFloat, "scale must be a float tensor");
+  TORCH_CHECK(scale.numel() == 1, "scale must be a single-element tensor");
+  TORCH_CHECK(input.stride(-1) == 1, "last dimension of input must be contiguous");
+  TORCH_CHECK(out.stride(-1) == 1, "last dimension of output must be contiguous");
+  check_cuda(input, "input");
+  const int64_t H = input.size(-1);
+  const int64_t T = H ? input.numel() / H : 0;
+  const int64_t in_rs = input.dim() >= 2 ? input.stride(-2) : H;
+  const int64_t out_rs = out.dim() >= 2 ? out.stride(-2) : H;
+  const c10::cuda::CUDAGuard guard(input.device());
+  check_rc(vxk_dynamic_scaled_fp8_quant(out.data_ptr(), input.data_ptr(), scale.data_ptr<float>(), T, H,
+                                        in_rs, out_rs, in_dtype_of(input, "dynamic_scaled_fp8_quant"),
+                                        q_dtype_of(out, "dynamic_scaled_fp8_quant", false), cur_stream()),
+           "dynamic_scaled_fp8_quant");
+}
+
+// ref: fp8_quant.cpp:724-840.  fp8_min / fp8_max are ignored like in the reference
+// (the type's max is used); the two dummy flags are ignored too: the scale layout
+// is read off output_s's strides (:763-765).
+void per_token_group_fp8_quant(const Tensor& input, Tensor& output_q, Tensor& output_s, int64_t group_size,
+                               double eps, double /*fp8_min*/, double /*fp8_max*/, bool scale_ue8m0,
+                               bool /*dummy_is_scale_transposed*/, bool /*dummy_is_tma_aligned*/) {
+  TORCH_CHECK(input.is_contiguous());
+  TORCH_CHECK(output_q.is_contiguous());
+  TORCH_CHECK(group_size > 0 && input.numel() % group_size == 0);
+  TORCH_CHECK(output_s.dim() == 2);
+  TORCH_CHECK(output_s.scalar_type() == at::kFloat, "output_s must be float32");
+  check_cuda(input, "input");
+  const int64_t T = output_s.size(0);
+  if (T == 0 || input.numel() == 0) return;
+  const int64_t H = input.numel() / T;
+  TORCH_CHECK(H % group_size == 0 && output_s.size(1) == H / group_size,
+              "output_s must have shape [num_tokens, hidden / group_size]");
+  const c10::cuda::CUDAGuard guard(input.device());
+  check_rc(vxk_per_token_group_fp8_quant(input.data_ptr(), output_q.data_ptr(), output_s.data_ptr<float>(),
+                                         T, H, group_size, eps, scale_ue8m0 ? 1 : 0, output_s.stride(0),
+                                         output_s.stride(1), in_dtype_of(input, "per_token_group_fp8_quant"),
+                                         q_dtype_of(output_q, "per_token_group_fp8_quant", false),
+                                         cur_stream()),
+           "per_token_group_fp8_quant");
+}
+
+// ref: csrc/quantization/fp4/mxfp4_quant.cpp:24-126
+void per_token_group_quant_mxfp4(const Tensor& input, Tensor& output_q, Tensor& output_s, int64_t group_size,
+                                 double eps) {
+  TORCH_CHECK(input.is_contiguous(), "input must be contiguous");
+  TORCH_CHECK(output_q.is_contiguous(), "output_q must be contiguous");
+  TORCH_CHECK(group_size == 32, "MXFP4 requires group_size == 32, got ", group_size);
+  TORCH_CHECK(input.numel() % group_size == 0, "input numel must be divisible by group_size");
+  TORCH_CHECK(output_s.dim() == 2, "output_s must be 2-D");
+  TORCH_CHECK(output_q.scalar_type() == at::kByte, "output_q must be uint8");
+  TORCH_CHECK(output_s.scalar_type() == at::kFloat, "output_s must be float32");
+  if (input.numel() / group_size == 0) {
+    TORCH_CHECK(output_q.numel() == 0, "output_q must be empty when input is empty");
+    TORCH_CHECK(output_s.numel() == 0, "output_s must be empty when input is empty");
+    return;
+  }
+  check_cuda(input, "input");
+  const int64_t T = output_s.size(0);
+  const int64_t H = input.numel() / T;
+  TORCH_CHECK(H % group_size == 0 && output_s.size(1) == H / group_size,
+              "output_s must have shape [num_tokens, hidden / 32]");
+  const c10::cuda::CUDAGuard guard(input.device());
+  check_rc(vxk_per_token_group_quant_mxfp4(input.data_ptr(), output_q.data_ptr(), output_s.data_ptr<float>(),
+                                           T, H, group_size, eps, output_s.stride(0), output_s.stride(1),
+                                           in_dtype_of(input, "per_token_group_quant_mxfp4"), cur_stream()),
+           "per_token_group_quant_mxfp4");
+}
+
+void check_residual(const std::optional<Tensor>& residual, const Tensor& input) {
+  if (residual.has_value()) {
+    TORCH_CHECK(residual->scalar_type() == input.scalar_type(), "residual and input must have the same dtype");
+    TORCH_CHECK(residual->is_contiguous(), "residual must be contiguous");
+    TORCH_CHECK(residual->numel() == input.numel(), "residual and input must have the same size");
+  }
+}
+
+// ref: csrc/layernorm_quant.cpp:988-1045
+void rms_norm_dynamic_per_token_quant(Tensor& out, const Tensor& input, const Tensor& weight, Tensor& scales,
+                                      double epsilon, std::optional<Tensor> scale_ub,
+                                      std::optional<Tensor> residual) {
+  TORCH_CHECK(input.is_contiguous(), "input must be contiguous");
+  TORCH_CHECK(out.is_contiguous(), "out must be contiguous");
+  TORCH_CHECK(weight.dtype() == input.dtype(), "weight and input must have the same dtype");
+  TORCH_CHECK(scales.dtype() == at::kFloat, "scales must be float32");
+  TORCH_CHECK(out.dtype() == at::kFloat8_e4m3fn || out.dtype() == at::kChar,
+              "output must be float8_e4m3fn or int8");
+  if (scale_ub.has_value())
+    TORCH_CHECK(out.dtype() == at::kFloat8_e4m3fn, "scale_ub is only supported for FP8 output");
+  check_residual(residual, input);
+  check_cuda(input, "input");
+  const int64_t H = input.size(-1);
+  const int64_t T = H ? input.numel() / H : 0;
+  TORCH_CHECK(weight.numel() == H && weight.is_contiguous(), "weight must be a contiguous [hidden] tensor");
+  TORCH_CHECK(scales.numel() >= T && scales.is_contiguous(), "scales must hold one fp32 per token");
+  const c10::cuda::CUDAGuard guard(input.device());
+  check_rc(vxk_rms_norm_dynamic_per_token_quant(
+               out.data_ptr(), input.data_ptr(), weight.data_ptr(), scales.data_ptr<float>(), epsilon,
+               opt_f32(scale_ub, "scale_ub"), residual.has_value() ? residual->data_ptr() : nullptr, T, H,
+               in_dtype_of(input, "rms_norm_dynamic_per_token_quant"),
+               q_dtype_of(out, "rms_norm_dynamic_per_token_quant", true), cur_stream()),
+           "rms_norm_dynamic_per_token_quant");
+}
+
+// ref: layernorm_quant.cpp:1047-1114.  scale_ub is accepted and ignored, as in the reference (:1088-1097).
+void rms_norm_per_block_quant(Tensor& out, const Tensor& input, const Tensor& weight, Tensor& scales,
+                              double epsilon, std::optional<Tensor> /*scale_ub*/, std::optional<Tensor> residual,
+                              int64_t group_size, bool is_scale_transposed, bool scale_ue8m0) {
+  TORCH_CHECK(input.stride(-1) == 1, "input must be contiguous in the last dimension");
+  TORCH_CHECK(out.is_contiguous(), "out must be contiguous");
+  TORCH_CHECK(weight.dtype() == input.dtype(), "weight and input must have the same dtype");
+  TORCH_CHECK(scales.dtype() == at::kFloat, "scales must be float32");
+  TORCH_CHECK(out.dtype() == at::kFloat8_e4m3fn || out.dtype() == at::kChar,
+              "output must be float8_e4m3fn or int8");
+  TORCH_CHECK(group_size > 0 && input.size(-1) % group_size == 0, "hidden_size must be divisible by group_size");
+  check_residual(residual, input);
+  if (scale_ue8m0)
+    TORCH_CHECK(out.dtype() == at::kFloat8_e4m3fn,
+                "scale_ue8m0 (MX FP8) is only supported for float8_e4m3fn output");
+  check_cuda(input, "input");
+  const int64_t H = input.size(-1);
+  const int64_t T = H ? input.numel() / H : 0;
+  const int64_t G = H / group_size;
+  TORCH_CHECK(input.dim() <= 2 || input.is_contiguous(), "only 2-D inputs may be row-strided");
+  const int64_t in_rs = input.dim() >= 2 ? input.stride(-2) : H;
+  TORCH_CHECK(weight.numel() == H && weight.is_contiguous(), "weight must be a contiguous [hidden] tensor");
+  TORCH_CHECK(scales.numel() >= T * G, "scales too small");
+  // reference addressing: transposed -> tok + g * T, else tok * G + g  (:751-753)
+  const int64_t ss0 = is_scale_transposed ? 1 : G;
+  const int64_t ss1 = is_scale_transposed ? T : 1;
+  const c10::cuda::CUDAGuard guard(input.device());
+  check_rc(vxk_rms_norm_per_block_quant(out.data_ptr(), input.data_ptr(), weight.data_ptr(),
+                                        scales.data_ptr<float>(), epsilon,
+                                        residual.has_value() ? residual->data_ptr() : nullptr, T, H, in_rs,
+                                        group_size, ss0, ss1, scale_ue8m0 ? 1 : 0,
+                                        in_dtype_of(input, "rms_norm_per_block_quant"),
+                                        q_dtype_of(out, "rms_norm_per_block_quant", true), cur_stream()),
+           "rms_norm_per_block_quant");
+}
+
+// ref: layernorm_quant.cpp:1172-1219
+void rms_norm_mxfp4_quant(Tensor& out, const Tensor& input, const Tensor& weight, Tensor& scales,
+                          double epsilon, std::optional<Tensor> residual, int64_t group_size) {
+  TORCH_CHECK(input.is_contiguous(), "input must be contiguous");
+  TORCH_CHECK(out.is_contiguous(), "out must be contiguous");
+  TORCH_CHECK(weight.dtype() == input.dtype(), "weight and input must have the same dtype");
+  TORCH_CHECK(scales.dtype() == at::kFloat, "scales must be float32");
+  TORCH_CHECK(out.scalar_type() == at::ScalarType::Byte, "output must be uint8 (packed FP4)");
+  TORCH_CHECK(group_size == 32, "MXFP4 requires group_size == 32, got ", group_size);
+  TORCH_CHECK(input.size(-1) % group_size == 0, "hidden_size must be divisible by group_size");
+  TORCH_CHECK(input.size(-1) % 2 == 0, "hidden_size must be even for FP4 packing");
+  TORCH_CHECK(scales.dim() == 2, "scales must be 2-D");
+  check_residual(residual, input);
+  check_cuda(input, "input");
+  const int64_t H = input.size(-1);
+  const int64_t T = H ? input.numel() / H : 0;
+  TORCH_CHECK(scales.size(0) == T && scales.size(1) == H / group_size, "scales must be [num_tokens, hidden/32]");
+  TORCH_CHECK(weight.numel() == H && weight.is_contiguous(), "weight must be a contiguous [hidden] tensor");
+  const c10::cuda::CUDAGuard guard(input.device());
+  check_rc(vxk_rms_norm_mxfp4_quant(out.data_ptr(), input.data_ptr(), weight.data_ptr(), scales.data_ptr<float>(),
+                                    epsilon, residual.has_value() ? residual->data_ptr() : nullptr, T, H,
+                                    group_size, scales.stride(0), scales.stride(1),
+                                    in_dtype_of(input, "rms_norm_mxfp4_quant"), cur_stream()),
+           "rms_norm_mxfp4_quant");
+}
+
+void rms_norm_static_impl(Tensor& out, const Tensor& input, Tensor* residual, const Tensor& weight,
+                          const Tensor& scale, double epsilon, const char* op) {
+  TORCH_CHECK(out.is_contiguous(), "out must be contiguous");
+  TORCH_CHECK(weight.scalar_type() == input.scalar_type(), "weight and input must have the same dtype");
+  TORCH_CHECK(input.stride(-1) == 1, "input must be contiguous in the last dimension");
+  TORCH_CHECK(scale.scalar_type() == at::kFloat && scale.numel() == 1, "scale must be one float32");
+  check_cuda(input, "input");
+  const int64_t H = input.size(-1);
+  const int64_t T = H ? input.numel() / H : 0;
+  TORCH_CHECK(input.dim() <= 2 || input.is_contiguous(), "only 2-D inputs may be row-strided");
+  const int64_t in_rs = input.dim() >= 2 ? input.stride(-2) : H;
+  TORCH_CHECK(weight.numel() == H && weight.is_contiguous(), "weight must be a contiguous [hidden] tensor");
+  const c10::cuda::CUDAGuard guard(input.device());
+  check_rc(vxk_rms_norm_static_fp8_quant(out.data_ptr(), input.data_ptr(), weight.data_ptr(),
+                                         scale.data_ptr<float>(), epsilon,
+                                         residual ? residual->data_ptr() : nullptr, T, H, in_rs,
+                                         in_dtype_of(input, op), q_dtype_of(out, op, false), cur_stream()),
+           op);
+}
+
+// ref: layernorm_quant.cpp:1116-1136
+void rms_norm_static_fp8_quant(Tensor& out, const Tensor& input, const Tensor& weight, const Tensor& scale,
+                               double epsilon) {
+  rms_norm_static_impl(out, input, nullptr, weight, scale, epsilon, "rms_norm_static_fp8_quant");
+}
+
+// ref: layernorm_quant.cpp:1138-1170
+void fused_add_rms_norm_static_fp8_quant(Tensor& out, const Tensor& input, Tensor& residual, const Tensor& weight,
+                                         const Tensor& scale, double epsilon) {
+  TORCH_CHECK(residual.is_contiguous(), "residual must be contiguous");
+  TORCH_CHECK(residual.scalar_type() == input.scalar_type(), "residual and input must have the same dtype");
+  TORCH_CHECK(residual.numel() == input.numel(), "residual and input must have the same size");
+  rms_norm_static_impl(out, input, &residual, weight, scale, epsilon, "fused_add_rms_norm_static_fp8_quant");
+}
+
+// ref: csrc/activation.cpp:552-566
+void silu_and_mul_quant(Tensor& out, const Tensor& input, const Tensor& scale) {
+  TORCH_CHECK(out.dtype() == at::kFloat8_e4m3fn || out.dtype() == at::kFloat8_e5m2);
+  TORCH_CHECK(input.dtype() == at::kHalf || input.dtype() == at::kBFloat16);
+  TORCH_CHECK(input.size(-1) % 2 == 0);
+  TORCH_CHECK(input.is_contiguous() && out.is_contiguous(), "input and out must be contiguous");
+  TORCH_CHECK(scale.scalar_type() == at::kFloat && scale.numel() >= 1, "scale must be float32");
+  const int64_t d = input.size(-1) / 2;
+  const int64_t T = input.size(-1) ? input.numel() / input.size(-1) : 0;
+  if (T == 0) return;
+  check_cuda(input, "input");
+  const c10::cuda::CUDAGuard guard(input.device());
+  check_rc(vxk_silu_and_mul_quant(out.data_ptr(), input.data_ptr(), scale.data_ptr<float>(), T, d,
+                                  in_dtype_of(input, "silu_and_mul_quant"),
+                                  q_dtype_of(out, "silu_and_mul_quant", false), cur_stream()),
+           "silu_and_mul_quant");
+}
+
+// ref: csrc/quantization/fused_kernels/fused_silu_mul_block_quant.cpp:141-239
+void silu_and_mul_per_block_quant(Tensor& out, const Tensor& input, Tensor& scales, int64_t group_size,
+                                  std::optional<Tensor> scale_ub, bool is_scale_transposed, bool scale_ue8m0) {
+  TORCH_CHECK(out.dtype() == at::kFloat8_e4m3fn || out.dtype() == at::kFloat8_e5m2 ||
+                  out.dtype() == at::kChar,
+              "out must be float8_e4m3fn, float8_e5m2, or int8");
+  TORCH_CHECK(input.dtype() == at::kHalf || input.dtype() == at::kBFloat16,
+              "input must be float16 or bfloat16");
+  TORCH_CHECK(out.is_contiguous(), "out must be contiguous");
+  TORCH_CHECK(input.is_contiguous(), "input must be contiguous");
+  TORCH_CHECK(scales.dtype() == at::kFloat, "scales must be float32");
+  TORCH_CHECK(group_size == 32 || group_size == 64 || group_size == 128,
+              "group_size must be 32, 64, or 128, got ", group_size);
+  if (scale_ub.has_value())
+    TORCH_CHECK(out.dtype() == at::kFloat8_e4m3fn || out.dtype() == at::kFloat8_e5m2,
+                "scale_ub is only supported for FP8 output");
+  if (scale_ue8m0)
+    TORCH_CHECK(out.dtype() != at::kChar, "scale_ue8m0 is only supported for FP8 output");
+  TORCH_CHECK(input.dim() == 2, "input must be 2-dimensional");
+  TORCH_CHECK(out.dim() == 2, "out must be 2-dimensional");
+  TORCH_CHECK(scales.dim() == 2, "scales must be 2-dimensional");
+  const int64_t T = input.size(0);
+  const int64_t H = out.size(1);
+  const int64_t G = H / group_size;
+  TORCH_CHECK(input.size(-1) == H * 2, "input last dim must be 2 * hidden_size");
+  TORCH_CHECK(H % group_size == 0, "hidden_size must be divisible by group_size");
+  TORCH_CHECK(out.size(0) == T, "out.size(0) must equal num_tokens (input.size(0))");
+  TORCH_CHECK(scales.size(0) == T && scales.size(1) == G, "scales must have logical shape [num_tokens, num_groups]");
+  if (T == 0) return;
+  check_cuda(input, "input");
+  const int64_t ss0 = is_scale_transposed ? 1 : G;
+  const int64_t ss1 = is_scale_transposed ? T : 1;
+  const c10::cuda::CUDAGuard guard(input.device());
+  check_rc(vxk_silu_and_mul_per_block_quant(out.data_ptr(), input.data_ptr(), scales.data_ptr<float>(), T, H,
+                                            group_size, opt_f32(scale_ub, "scale_ub"), ss0, ss1,
+                                            scale_ue8m0 ? 1 : 0, in_dtype_of(input, "silu_and_mul_per_block_quant"),
+                                            q_dtype_of(out, "silu_and_mul_per_block_quant", true), cur_stream()),
+           "silu_and_mul_per_block_quant");
+}
+
+// ref: fused_silu_mul_mxfp4_quant.cpp:134-209
+void silu_and_mul_mxfp4_quant(Tensor& out, const Tensor& input, Tensor& scales, int64_t group_size, double eps) {
+  TORCH_CHECK(input.dtype() == at::kHalf || input.dtype() == at::kBFloat16,
+              "input must be float16 or bfloat16");
+  TORCH_CHECK(out.scalar_type() == at::ScalarType::Byte, "out must be uint8 (packed FP4)");
+  TORCH_CHECK(out.is_contiguous(), "out must be contiguous");
+  TORCH_CHECK(input.is_contiguous(), "input must be contiguous");
+  TORCH_CHECK(scales.dtype() == at::kFloat, "scales must be float32");
+  TORCH_CHECK(group_size == 32, "MXFP4 requires group_size == 32, got ", group_size);
+  TORCH_CHECK(input.dim() == 2, "input must be 2-dimensional");
+  TORCH_CHECK(out.dim() == 2, "out must be 2-dimensional");
+  TORCH_CHECK(scales.dim() == 2, "scales must be 2-dimensional");
+  const int64_t T = input.size(0);
+  const int64_t H = input.size(-1) / 2;
+  const int64_t G = H / group_size;
+  TORCH_CHECK(input.size(-1) == H * 2, "input last dim must be 2 * hidden_size");
+  TORCH_CHECK(H % group_size == 0, "hidden_size must be divisible by group_size");
+  TORCH_CHECK(out.size(0) == T && out.size(1) == H / 2, "out must have shape [num_tokens, hidden_size / 2]");
+  TORCH_CHECK(scales.size(0) == T && scales.size(1) == G, "scales must have logical shape [num_tokens, num_groups]");
+  if (T == 0) return;
+  check_cuda(input, "input");
+  const c10::cuda::CUDAGuard guard(input.device());
+  check_rc(vxk_silu_and_mul_mxfp4_quant(out.data_ptr(), input.data_ptr(), scales.data_ptr<float>(), T, H,
+                                        group_size, eps, scales.stride(0), scales.stride(1),
+                                        in_dtype_of(input, "silu_and_mul_mxfp4_quant"), cur_stream()),
+           "silu_and_mul_mxfp4_quant");
+}
+
+// --------------------------------------------------------------- _xpu_C ops
+
+// ref: csrc/xpu/onednn/onednn_matmul.cpp:17-52
+Tensor check_and_create_output_tensor(const Tensor& A, const Tensor& B, std::optional<c10::ScalarType> out_dtype) {
+  TORCH_CHECK(A.dim() == 2 || A.dim() == 3, "Matmul only support 2D and 3D inputs!\n");
+  TORCH_CHECK(B.dim() == 2, "Matmul only support 2D weights!\n");
+  std::vector<int64_t> result_shape;
+  if (A.dim() == 2) result_shape = {A.size(0), B.size(1)};
+  else result_shape = {A.size(0), A.size(1), B.size(1)};
+  const auto k = A.size(A.dim() - 1);
+  const auto n = result_shape.back();
+  auto res_stride = A.strides().vec();
+  for (size_t i = 0; i + 1 < res_stride.size(); i++) res_stride[i] = res_stride[i] / k * n;
+  const auto out_dtype_ = out_dtype.value_or(at::kHalf);  // reference default (:49)
+  return at::empty_strided(result_shape, res_stride, A.options().dtype(out_dtype_));
+}
+
+struct ARows {  // A viewed as M rows of K contiguous elements with ONE row stride
+  int64_t M, lda, ldd;
+};
+ARows flatten_rows(const Tensor& A, const Tensor& D) {
+  TORCH_CHECK(A.stride(-1) == 1, "A must be contiguous in its last dimension");
+  if (A.dim() == 2) return {A.size(0), A.stride(0), D.stride(0)};
+  // [b, m, k]: rows must be expressible with one stride (contiguous [b,m,k], or b == 1 / m == 1)
+  const int64_t b = A.size(0), m = A.size(1);
+  if (b == 1) return {m, A.stride(1), D.stride(1)};
+  if (m == 1) return {b, A.stride(0), D.stride(0)};
+  TORCH_CHECK(A.stride(0) == m * A.stride(1),
+              "3-D A must have uniformly strided rows ([b,m,k] contiguous); got strides ", A.strides());
+  return {b * m, A.stride(1), D.stride(1)};
+}
+
+int bias_dtype_of(const Tensor& b) {
+  switch (b.scalar_type()) {
+    case at::kFloat: return VXK_F32;
+    case at::kHalf: return VXK_F16;
+    case at::kBFloat16: return VXK_BF16;
+    default: TORCH_CHECK(false, "Unsupported data type for bias in matmul: ", b.scalar_type());
+  }
+}
+
+// ref: onednn_matmul.cpp:54-79, fp8_gemm_w8a8.h:12-184
+Tensor fp8_gemm(const Tensor& A, const Tensor& B, std::optional<c10::ScalarType> out_dtype,
+                const std::optional<Tensor>& A_scale_, const std::optional<Tensor>& B_scale_,
+                const std::optional<Tensor>& bias_) {
+  const c10::cuda::CUDAGuard guard(A.device());
+  Tensor result = check_and_create_output_tensor(A, B, out_dtype);
+  const auto a_st = A.scalar_type(), b_st = B.scalar_type();
+  TORCH_CHECK((a_st == at::kFloat8_e5m2 || a_st == at::kFloat8_e4m3fn) && a_st == b_st,
+              "input and weight must be f8_e5m2 or f8_e4m3fn for fp8 matmul");
+  TORCH_CHECK(result.scalar_type() == at::kHalf || result.scalar_type() == at::kBFloat16,
+              "output must be float16 or bfloat16 for fp8 matmul");
+  TORCH_CHECK(B.stride(0) == 1 || B.stride(1) == 1, "B must be contiguous along K or along N");
+  const ARows r = flatten_rows(A, result);
+  const int64_t K = A.size(-1), N = B.size(1);
+  TORCH_CHECK(B.size(0) == K, "A and B have mismatched K: ", K, " vs ", B.size(0));
+  if (r.M == 0 || N == 0) return result;
+
+  // missing scales default to 1.0 (onednn_matmul.cpp:75-76)
+  Tensor A_scale = A_scale_.has_value() && A_scale_->defined() && A_scale_->numel() > 0
+                       ? *A_scale_ : at::ones({1}, A.options().dtype(at::kFloat));
+  Tensor B_scale = B_scale_.has_value() && B_scale_->defined() && B_scale_->numel() > 0
+                       ? *B_scale_ : at::ones({1}, A.options().dtype(at::kFloat));
+  check_cuda(A_scale, "A_scale");
+  check_cuda(B_scale, "B_scale");
+
+  const bool is_block = A_scale.dim() == 2 && A_scale.size(1) > 1;  // fp8_gemm_w8a8.h:28
+  int a_mode, b_mode, scale_dtype = VXK_S_F32;
+  int64_t gk = 0, gn = 0, sa0 = 0, sa1 = 0, sb0 = 0, sb1 = 0;
+  if (is_block) {
+    TORCH_CHECK(B_scale.dim() == 2, "block-quantised weights need a 2-D [K/gk, N/gn] scale");
+    TORCH_CHECK(A_scale.size(1) == B_scale.size(0), "Mismatch group size in input and weight.",
+                A_scale.size(1), " vs ", B_scale.size(0));
+    TORCH_CHECK(A_scale.size(0) == r.M, "A_scale must have one row per row of A");
+    TORCH_CHECK(K % B_scale.size(0) == 0 && N % B_scale.size(1) == 0,
+                "K and N must be divisible by the scale grid");
+    gk = K / B_scale.size(0);
+    gn = N / B_scale.size(1);
+    a_mode = b_mode = 2;
+    sa0 = A_scale.stride(0); sa1 = A_scale.stride(1);
+    sb0 = B_scale.stride(0); sb1 = B_scale.stride(1);
+    TORCH_CHECK(A_scale.scalar_type() == B_scale.scalar_type(), "A_scale / B_scale dtype mismatch");
+    if (A_scale.scalar_type() == at::kFloat8_e8m0fnu) scale_dtype = VXK_S_E8M0;
+    else TORCH_CHECK(A_scale.scalar_type() == at::kFloat, "block scales must be float32 or float8_e8m0fnu");
+  } else {
+    TORCH_CHECK(A_scale.scalar_type() == at::kFloat && B_scale.scalar_type() == at::kFloat,
+                "per-tensor / per-token / per-channel scales must be float32");
+    a_mode = A_scale.numel() == 1 ? 0 : 1;
+    b_mode = B_scale.numel() == 1 ? 0 : 1;
+    if (a_mode == 1) TORCH_CHECK(A_scale.numel() == r.M && A_scale.is_contiguous(), "A_scale must be [M] / [M,1]");
+    if (b_mode == 1) TORCH_CHECK(B_scale.numel() == N && B_scale.is_contiguous(), "B_scale must be [N] / [N,1]");
+  }
+  const void* bias = nullptr;
+  int bias_dtype = VXK_F32;
+  if (bias_.has_value() && bias_->defined() && bias_->numel() > 0) {  // empty tensor == no bias (onednn_ext.h:317-318)
+    TORCH_CHECK(bias_->numel() == N && bias_->is_contiguous(), "only a contiguous [N] bias is supported, got ",
+                bias_->sizes());
+    check_cuda(*bias_, "bias");
+    bias = bias_->data_ptr();
+    bias_dtype = bias_dtype_of(*bias_);
+  }
+  check_rc(vxk_fp8_gemm(result.data_ptr(), A.data_ptr(), B.data_ptr(), A_scale.data_ptr(), B_scale.data_ptr(),
+                        bias, r.M, N, K, r.lda, B.stride(0), B.stride(1), r.ldd, a_mode, b_mode, gk, gn, sa0, sa1,
+                        sb0, sb1, scale_dtype, a_st == at::kFloat8_e4m3fn ? VXK_Q_E4M3 : VXK_Q_E5M2,
+                        result.scalar_type() == at::kBFloat16 ? VXK_BF16 : VXK_F16, bias_dtype, cur_stream()),
+           "fp8_gemm");
+  return result;
+}
+
+// ref: onednn_matmul.cpp:101-123, fp4_gemm_w4a4.h:12-167
+Tensor fp4_gemm(const Tensor& A, const Tensor& B, const Tensor& A_scale, const Tensor& B_scale,
+                std::optional<c10::ScalarType> out_dtype, const std::optional<Tensor>& bias_) {
+  const c10::cuda::CUDAGuard guard(A.device());
+  Tensor result = check_and_create_output_tensor(A, B, out_dtype);
+  const auto a_st = A.scalar_type(), b_st = B.scalar_type();
+  TORCH_CHECK(a_st == at::ScalarType::Float4_e2m1fn_x2 && a_st == b_st,
+              "input and weight must be f4_e2m1x2 or f4_e2m1x2 for fp4 matmul");
+  TORCH_CHECK(result.scalar_type() == at::kHalf || result.scalar_type() == at::kBFloat16,
+              "output must be float16 or bfloat16 for fp4 matmul");
+  TORCH_CHECK(A_scale.scalar_type() == at::kFloat8_e8m0fnu, "Unsupported scale type for fp4 matmul: ",
+              A_scale.scalar_type());
+  TORCH_CHECK(B_scale.scalar_type() == at::kFloat8_e8m0fnu, "Mismatched scale data types in mxfp4 matmul: ",
+              A_scale.scalar_type(), " vs ", B_scale.scalar_type());
+  TORCH_CHECK(B.stride(0) == 1, "FP4 weights must be K-major: pass W[N, K/2].transpose(0, 1)");
+  const ARows r = flatten_rows(A, result);
+  const int64_t K = 2 * A.size(-1), N = B.size(1);
+  TORCH_CHECK(B.size(0) * 2 == K, "A and B have mismatched K");
+  TORCH_CHECK(K % 32 == 0, "K must be a multiple of the MX block (32)");
+  TORCH_CHECK(A_scale.dim() == 2 && A_scale.size(0) == r.M && A_scale.size(1) == K / 32,
+              "A_scale must be [M, K/32]");
+  TORCH_CHECK(B_scale.dim() == 2 && B_scale.size(0) == N && B_scale.size(1) == K / 32,
+              "B_scale must be [N, K/32] (tests/test_fp4_gemm_onednn.py:65-71 convention)");
+  if (r.M == 0 || N == 0) return result;
+  const void* bias = nullptr;
+  int bias_dtype = VXK_F32;
+  if (bias_.has_value() && bias_->defined() && bias_->numel() > 0) {
+    TORCH_CHECK(bias_->numel() == N && bias_->is_contiguous(), "only a contiguous [N] bias is supported");
+    bias = bias_->data_ptr();
+    bias_dtype = bias_dtype_of(*bias_);
+  }
+  check_rc(vxk_fp4_gemm(result.data_ptr(), A.data_ptr(), B.data_ptr(), A_scale.data_ptr(), B_scale.data_ptr(), bias,
+                        r.M, N, K, r.lda, B.stride(1), r.ldd, A_scale.stride(0), A_scale.stride(1),
+                        B_scale.stride(0), B_scale.stride(1),
+                        result.scalar_type() == at::kBFloat16 ? VXK_BF16 : VXK_F16, bias_dtype, cur_stream()),
+           "fp4_gemm");
+  return result;
+}
+
+}  // namespace
+
+// Schemas verbatim from /root/reference/csrc/torch_bindings.cpp (line numbers in SURVEY.md 8b).
+TORCH_LIBRARY_FRAGMENT(_C, ops) {
+  ops.def("rms_norm_dynamic_per_token_quant(Tensor! result, Tensor input, Tensor weight, Tensor! scale, "
+          "float epsilon, Tensor? scale_ub, Tensor!? residual) -> ()");
+  ops.def("rms_norm_per_block_quant(Tensor! result, Tensor input, Tensor weight, Tensor! scale, float epsilon, "
+          "Tensor? scale_ub, Tensor!? residual, int group_size, bool is_scale_transposed, "
+          "bool scale_ue8m0=False) -> ()");
+  ops.def("rms_norm_mxfp4_quant(Tensor! result, Tensor input, Tensor weight, Tensor! scale, float epsilon, "
+          "Tensor!? residual, int group_size) -> ()");
+  ops.def("rms_norm_static_fp8_quant(Tensor! result, Tensor input, Tensor weight, Tensor scale, "
+          "float epsilon) -> ()");
+  ops.def("fused_add_rms_norm_static_fp8_quant(Tensor! result, Tensor input, Tensor! residual, Tensor weight, "
+          "Tensor scale, float epsilon) -> ()");
+  ops.def("silu_and_mul_quant(Tensor! result, Tensor input, Tensor scale) -> ()");
+  ops.def("silu_and_mul_per_block_quant(Tensor! out, Tensor input, Tensor! scales, int group_size, "
+          "Tensor? scale_ub=None, bool is_scale_transposed=False, bool scale_ue8m0=False) -> ()");
+  ops.def("silu_and_mul_mxfp4_quant(Tensor! out, Tensor input, Tensor! scales, int group_size, "
+          "float eps=1e-10) -> ()");
+  ops.def("static_scaled_fp8_quant(Tensor! result, Tensor input, Tensor scale, "
+          "(int, int)? group_shape=None) -> ()");
+  ops.def("dynamic_scaled_fp8_quant(Tensor! result, Tensor input, Tensor! scale) -> ()");
+  ops.def("dynamic_per_token_scaled_fp8_quant(Tensor! result, Tensor input, Tensor! scale, "
+          "Tensor? scale_ub) -> ()");
+  ops.def("per_token_group_fp8_quant(Tensor input, Tensor! output_q, Tensor! output_s, int group_size, "
+          "float eps, float fp8_min, float fp8_max, bool scale_ue8m0, bool dummy_is_scale_transposed, "
+          "bool dummy_is_tma_aligned ) -> ()");
+  ops.def("per_token_group_quant_mxfp4(Tensor input, Tensor! output_q, Tensor! output_s, int group_size, "
+          "float eps) -> ()");
+}
+
+TORCH_LIBRARY_IMPL(_C, CUDA, ops) {
+  ops.impl("rms_norm_dynamic_per_token_quant", &rms_norm_dynamic_per_token_quant);
+  ops.impl("rms_norm_per_block_quant", &rms_norm_per_block_quant);
+  ops.impl("rms_norm_mxfp4_quant", &rms_norm_mxfp4_quant);
+  ops.impl("rms_norm_static_fp8_quant", &rms_norm_static_fp8_quant);
+  ops.impl("fused_add_rms_norm_static_fp8_quant", &fused_add_rms_norm_static_fp8_quant);
+  ops.impl("silu_and_mul_quant", &silu_and_mul_quant);
+  ops.impl("silu_and_mul_per_block_quant", &silu_and_mul_per_block_quant);
+  ops.impl("silu_and_mul_mxfp4_quant", &silu_and_mul_mxfp4_quant);
+  ops.impl("static_scaled_fp8_quant", &static_scaled_fp8_quant);
+  ops.impl("dynamic_scaled_fp8_quant", &dynamic_scaled_fp8_quant);
+  ops.impl("dynamic_per_token_scaled_fp8_quant", &dynamic_per_token_scaled_fp8_quant);
+  ops.impl("per_token_group_fp8_quant", &per_token_group_fp8_quant);
+  ops.impl("per_token_group_quant_mxfp4", &per_token_group_quant_mxfp4);
+}
+
+// Schemas verbatim from /root/reference/csrc/xpu/torch_bindings.cpp:14-27.
+TORCH_LIBRARY_FRAGMENT(_xpu_C, xpu_ops) {
+  xpu_ops.def("fp8_gemm(Tensor A, Tensor B, ScalarType? out_dtype, Tensor? A_scale_, Tensor? B_scale_, "
+              "Tensor? bias_) -> Tensor");
+  xpu_ops.def("fp4_gemm(Tensor A, Tensor B, Tensor A_scale, Tensor B_scale, ScalarType? out_dtype, "
+              "Tensor? bias_) -> Tensor");
+}
+
+TORCH_LIBRARY_IMPL(_xpu_C, CUDA, xpu_ops) {
+  xpu_ops.impl("fp8_gemm", &fp8_gemm);
+  xpu_ops.impl("fp4_gemm", &fp4_gemm);
+}

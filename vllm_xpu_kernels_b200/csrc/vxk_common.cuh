@@ -1,0 +1,300 @@
+// Shared device/host helpers for the quantisation kernels (sm_100a only).
+//
+// Numerics contract (see DESIGN.md "Arithmetic"): this translation unit is
+// compiled with -fmad=false, so the only fused multiply-adds are the explicit
+// fmaf() calls below; every other float operation is a single IEEE
+// round-to-nearest-even op, which is what the torch CPU reference does.
+#pragma once
+
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <atomic>
+#include <cstdarg>
+#include <cstdio>
+
+#include "../../include/vxk_b200.h"
+
+namespace vxk {
+
+// ------------------------------------------------------------------ host side
+extern thread_local char g_last_error[512];
+extern std::atomic<uint64_t> g_launches;
+
+inline int fail(int code, const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_last_error, sizeof(g_last_error), fmt, ap);
+  va_end(ap);
+  return code;
+}
+
+#define VXK_REQUIRE(cond, ...)                                   \
+  do {                                                           \
+    if (!(cond)) return ::vxk::fail(VXK_ERR_INVALID, __VA_ARGS__); \
+  } while (0)
+
+inline int check_launch(const char* what) {
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess)
+    return fail(VXK_ERR_CUDA, "%s: %s", what, cudaGetErrorString(e));
+  g_launches.fetch_add(1, std::memory_order_relaxed);
+  return VXK_OK;
+}
+
+int sm_count();  // cached cudaDevAttrMultiProcessorCount of the current device
+
+inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
+
+// ---------------------------------------------------------------- device side
+constexpr int kVec = 8;  // elements handled per "vector" (16 B of bf16/f16, 32 B of f32)
+
+template <int Q> struct QTraits;
+template <> struct QTraits<VXK_Q_E4M3> { static constexpr float kMax = 448.0f; };
+template <> struct QTraits<VXK_Q_E5M2> { static constexpr float kMax = 57344.0f; };
+template <> struct QTraits<VXK_Q_INT8> { static constexpr float kMax = 127.0f; };
+
+__device__ __forceinline__ uint4 ldg_stream(const void* p) {
+  uint4 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+               : "l"(p));
+  return r;
+}
+__device__ __forceinline__ void stg_stream(void* p, uint2 v) {
+  asm volatile("st.global.L1::no_allocate.v2.u32 [%0], {%1,%2};" ::"l"(p), "r"(v.x), "r"(v.y)
+               : "memory");
+}
+__device__ __forceinline__ void stg_stream(void* p, uint32_t v) {
+  asm volatile("st.global.L1::no_allocate.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ void stg_stream(void* p, uint4 v) {
+  asm volatile("st.global.L1::no_allocate.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x),
+               "r"(v.y), "r"(v.z), "r"(v.w)
+               : "memory");
+}
+
+__device__ __forceinline__ float bf16_lo(uint32_t w) { return __uint_as_float(w << 16); }
+__device__ __forceinline__ float bf16_hi(uint32_t w) { return __uint_as_float(w & 0xffff0000u); }
+
+template <typename T> __device__ __forceinline__ float to_f32(T v);
+template <> __device__ __forceinline__ float to_f32<float>(float v) { return v; }
+template <> __device__ __forceinline__ float to_f32<__half>(__half v) { return __half2float(v); }
+template <> __device__ __forceinline__ float to_f32<__nv_bfloat16>(__nv_bfloat16 v) {
+  return __bfloat162float(v);
+}
+template <typename T> __device__ __forceinline__ T from_f32(float v);
+template <> __device__ __forceinline__ float from_f32<float>(float v) { return v; }
+template <> __device__ __forceinline__ __half from_f32<__half>(float v) { return __float2half_rn(v); }
+template <> __device__ __forceinline__ __nv_bfloat16 from_f32<__nv_bfloat16>(float v) {
+  return __float2bfloat16_rn(v);
+}
+// round an fp32 value to T and back (the "stored as orig dtype, read back" steps of the refs)
+template <typename T> __device__ __forceinline__ float round_to(float v) {
+  return to_f32<T>(from_f32<T>(v));
+}
+
+// 8 consecutive elements -> fp32.  STREAM selects the non-coherent streaming
+// load (read-only inputs); in-place tensors (residual) use plain loads.
+template <typename T, bool STREAM = true>
+__device__ __forceinline__ void load8(const T* __restrict__ p, float (&v)[8]) {
+  if constexpr (sizeof(T) == 2) {
+    uint4 r;
+    if constexpr (STREAM) r = ldg_stream(p);
+    else r = *reinterpret_cast<const uint4*>(p);
+    const uint32_t w[4] = {r.x, r.y, r.z, r.w};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      if constexpr (std::is_same<T, __nv_bfloat16>::value) {
+        v[2 * i] = bf16_lo(w[i]);
+        v[2 * i + 1] = bf16_hi(w[i]);
+      } else {
+        const __half2 h = *reinterpret_cast<const __half2*>(&w[i]);
+        const float2 f = __half22float2(h);
+        v[2 * i] = f.x;
+        v[2 * i + 1] = f.y;
+      }
+    }
+  } else {
+    uint4 a, b;
+    if constexpr (STREAM) {
+      a = ldg_stream(p);
+      b = ldg_stream(p + 4);
+    } else {
+      a = *reinterpret_cast<const uint4*>(p);
+      b = *reinterpret_cast<const uint4*>(p + 4);
+    }
+    v[0] = __uint_as_float(a.x); v[1] = __uint_as_float(a.y);
+    v[2] = __uint_as_float(a.z); v[3] = __uint_as_float(a.w);
+    v[4] = __uint_as_float(b.x); v[5] = __uint_as_float(b.y);
+    v[6] = __uint_as_float(b.z); v[7] = __uint_as_float(b.w);
+  }
+}
+
+// fp32 x8 -> T x8, one 16 B (or 2 x 16 B) store; used for the in-place residual
+template <typename T>
+__device__ __forceinline__ void store8(T* p, const float (&v)[8]) {
+  if constexpr (sizeof(T) == 2) {
+    uint32_t w[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      if constexpr (std::is_same<T, __nv_bfloat16>::value) {
+        __nv_bfloat162 h = __floats2bfloat162_rn(v[2 * i], v[2 * i + 1]);
+        w[i] = *reinterpret_cast<uint32_t*>(&h);
+      } else {
+        __half2 h = __floats2half2_rn(v[2 * i], v[2 * i + 1]);
+        w[i] = *reinterpret_cast<uint32_t*>(&h);
+      }
+    }
+    *reinterpret_cast<uint4*>(p) = make_uint4(w[0], w[1], w[2], w[3]);
+  } else {
+    *reinterpret_cast<float4*>(p) = make_float4(v[0], v[1], v[2], v[3]);
+    *reinterpret_cast<float4*>(p + 4) = make_float4(v[4], v[5], v[6], v[7]);
+  }
+}
+
+// ---- packed saturating conversions (RNE, saturate-to-finite) ----
+__device__ __forceinline__ uint32_t cvt_e4m3x2(float hi, float lo) {
+  uint16_t r;
+  asm("cvt.rn.satfinite.e4m3x2.f32 %0, %1, %2;" : "=h"(r) : "f"(hi), "f"(lo));
+  return r;
+}
+__device__ __forceinline__ uint32_t cvt_e5m2x2(float hi, float lo) {
+  uint16_t r;
+  asm("cvt.rn.satfinite.e5m2x2.f32 %0, %1, %2;" : "=h"(r) : "f"(hi), "f"(lo));
+  return r;
+}
+__device__ __forceinline__ uint32_t cvt_e2m1x2(float hi, float lo) {
+  uint16_t r;
+  asm("{ .reg .b8 t; cvt.rn.satfinite.e2m1x2.f32 t, %1, %2; cvt.u16.u8 %0, t; }"
+      : "=h"(r)
+      : "f"(hi), "f"(lo));
+  return r;
+}
+__device__ __forceinline__ uint32_t cvt_s8(float v) {
+  // round half to even, clamp to [-128, 127]  (torch .round().clamp(-128,127).to(int8))
+  int i = __float2int_rn(fminf(fmaxf(v, -128.0f), 127.0f));
+  return static_cast<uint32_t>(i) & 0xffu;
+}
+
+template <int Q>
+__device__ __forceinline__ uint2 pack_q8(const float (&v)[8]) {
+  uint32_t lo, hi;
+  if constexpr (Q == VXK_Q_E4M3) {
+    lo = cvt_e4m3x2(v[1], v[0]) | (cvt_e4m3x2(v[3], v[2]) << 16);
+    hi = cvt_e4m3x2(v[5], v[4]) | (cvt_e4m3x2(v[7], v[6]) << 16);
+  } else if constexpr (Q == VXK_Q_E5M2) {
+    lo = cvt_e5m2x2(v[1], v[0]) | (cvt_e5m2x2(v[3], v[2]) << 16);
+    hi = cvt_e5m2x2(v[5], v[4]) | (cvt_e5m2x2(v[7], v[6]) << 16);
+  } else {
+    lo = cvt_s8(v[0]) | (cvt_s8(v[1]) << 8) | (cvt_s8(v[2]) << 16) | (cvt_s8(v[3]) << 24);
+    hi = cvt_s8(v[4]) | (cvt_s8(v[5]) << 8) | (cvt_s8(v[6]) << 16) | (cvt_s8(v[7]) << 24);
+  }
+  return make_uint2(lo, hi);
+}
+template <int Q>
+__device__ __forceinline__ uint8_t pack_q1(float v) {
+  if constexpr (Q == VXK_Q_E4M3) return static_cast<uint8_t>(cvt_e4m3x2(0.0f, v) & 0xff);
+  else if constexpr (Q == VXK_Q_E5M2) return static_cast<uint8_t>(cvt_e5m2x2(0.0f, v) & 0xff);
+  else return static_cast<uint8_t>(cvt_s8(v));
+}
+// 8 fp32 -> 4 bytes of packed E2M1 (even element in the low nibble)
+__device__ __forceinline__ uint32_t pack_e2m1x8(const float (&v)[8]) {
+  return cvt_e2m1x2(v[1], v[0]) | (cvt_e2m1x2(v[3], v[2]) << 8) | (cvt_e2m1x2(v[5], v[4]) << 16) |
+         (cvt_e2m1x2(v[7], v[6]) << 24);
+}
+
+// ---- exact division by a row/group constant ----
+// r must be RN(1/s).  q0 = RN(x*r) is within 2 ulp of x/s; one FMA residual +
+// one FMA correction lands on RN(x/s) (Markstein).  3 ops instead of the ~10 of
+// div.rn.f32.  The select keeps +-inf when x*r overflows.
+__device__ __forceinline__ float div_by(float x, float s, float r) {
+  const float q0 = x * r;
+  const float rem = fmaf(-q0, s, x);
+  const float q1 = fmaf(rem, r, q0);
+  return (fabsf(q0) <= 3.0e38f) ? q1 : q0;
+}
+
+// ---- UE8M0 helpers (exact, from the bit pattern) ----
+// biased exponent byte of 2^ceil(log2(v)) clamped to [-127,127]; v >= 0
+__device__ __forceinline__ int rceil_e8m0(float v) {
+  const uint32_t b = __float_as_uint(v);
+  const int exp = static_cast<int>((b >> 23) & 0xff);
+  const uint32_t man = b & 0x7fffffu;
+  int e;
+  if (exp == 0) e = (man > 0x400000u) ? 1 : 0;  // subnormal / zero: 2^-126 or 2^-127
+  else e = exp + (man != 0 ? 1 : 0);
+  return min(e, 254);
+}
+// 2^(e-127) as fp32 (e = 0 -> the subnormal 2^-127)
+__device__ __forceinline__ float e8m0_scale(int e) {
+  return __uint_as_float(e == 0 ? 0x00400000u : (static_cast<uint32_t>(e) << 23));
+}
+// 2^(127-e) as fp32, 1.0 for e == 0 (mx_utils.to_mxfp :327-331)
+__device__ __forceinline__ float e8m0_descale(int e) {
+  if (e == 0) return 1.0f;
+  return __uint_as_float(e == 254 ? 0x00400000u : (static_cast<uint32_t>(254 - e) << 23));
+}
+// 2^ceil(log2(s)) for positive normal s
+__device__ __forceinline__ float exp2_ceil_log2(float s) {
+  const uint32_t b = __float_as_uint(s);
+  return __uint_as_float(((b >> 23) + ((b & 0x7fffffu) ? 1u : 0u)) << 23);
+}
+
+// ---- reductions ----
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+// max over `lanes` (power of two <= 32) consecutive lanes
+__device__ __forceinline__ float seg_max(float v, int lanes) {
+  for (int o = lanes >> 1; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+// CTA-wide reductions; `scratch` is >= 33 floats of shared memory; all threads get the result.
+template <bool IS_MAX>
+__device__ __forceinline__ float block_reduce(float v, float* scratch) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = (blockDim.x + 31) >> 5;
+  v = IS_MAX ? warp_max(v) : warp_sum(v);
+  if (nwarp == 1) return v;
+  __syncthreads();  // scratch may still be read from a previous reduction
+  if (lane == 0) scratch[warp] = v;
+  __syncthreads();
+  float r = (lane < nwarp) ? scratch[lane] : (IS_MAX ? 0.0f : 0.0f);
+  r = IS_MAX ? warp_max(r) : warp_sum(r);
+  return r;
+}
+
+// ---- silu ----
+// ACCURATE: expf (<= 2 ulp) and an IEEE divide, the same formula torch's CPU
+// kernels evaluate (x / (1 + exp(-x))).  FAST: ex2.approx / rcp.approx.
+template <bool FAST>
+__device__ __forceinline__ float sigmoid_f32(float x) {
+  if constexpr (FAST) {
+    const float e = exp2f(-x * 1.4426950408889634f);  // lowered to ex2.approx under -use_fast_math only
+    return __fdividef(1.0f, 1.0f + e);
+  } else {
+    return __fdiv_rn(1.0f, 1.0f + expf(-x));
+  }
+}
+template <bool FAST>
+__device__ __forceinline__ float silu_f32(float x) {
+  if constexpr (FAST) {
+    float e;
+    const float t = -x * 1.4426950408889634f;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(t));
+    return __fdividef(x, 1.0f + e);
+  } else {
+    return __fdiv_rn(x, 1.0f + expf(-x));
+  }
+}
+
+}  // namespace vxk

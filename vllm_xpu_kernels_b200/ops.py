@@ -1,0 +1,213 @@
+"""Python-side operator wrappers, mirroring the reference's
+tests/register_ops.py (:29-74, :297-415) and the allocation helpers of
+tests/ops/fp8_quant_op.py (:135-276) and tests/ops/mxfp4_quant_op.py (:8-63):
+same names, same arguments, same scale layouts -- on CUDA tensors.
+
+All compute goes through torch.ops._C.* / torch.ops._xpu_C.* (registered by the
+compiled shim); nothing here computes on its own.
+"""
+from __future__ import annotations
+
+from typing import Optional, Union
+
+import torch
+
+from . import _C, _xpu_C  # noqa: F401  (registers the operators; raises if not built)
+
+
+# ----------------------------------------------------------------- raw ops
+def static_scaled_fp8_quant(out, input, scale, group_shape=None) -> None:
+    torch.ops._C.static_scaled_fp8_quant(out, input, scale, group_shape)
+
+
+def dynamic_scaled_fp8_quant(out, input, scale) -> None:
+    torch.ops._C.dynamic_scaled_fp8_quant(out, input, scale)
+
+
+def dynamic_per_token_scaled_fp8_quant(out, input, scales, scale_ub=None) -> None:
+    torch.ops._C.dynamic_per_token_scaled_fp8_quant(out, input, scales, scale_ub)
+
+
+def silu_and_mul_quant(out, input, scale) -> None:
+    torch.ops._C.silu_and_mul_quant(out, input, scale)
+
+
+def fp8_gemm(input, weight, out_dtype, scale_act, scale_wei, bias=None):
+    return torch.ops._xpu_C.fp8_gemm(input, weight, out_dtype, scale_act, scale_wei, bias)
+
+
+def fp4_gemm(input, weight, scale_act, scale_wei, out_dtype, bias=None):
+    return torch.ops._xpu_C.fp4_gemm(input, weight, scale_act, scale_wei, out_dtype, bias)
+
+
+# ------------------------------------------------- allocation helpers (tests/ops)
+def scaled_fp8_quant(
+    input: torch.Tensor,
+    scale: Optional[torch.Tensor] = None,
+    num_token_padding: Optional[int] = None,
+    scale_ub: Optional[torch.Tensor] = None,
+    use_per_token_if_dynamic: bool = False,
+    output: Optional[torch.Tensor] = None,
+    fp8_dtype: torch.dtype = torch.float8_e5m2,
+    group_shape: tuple[int, int] | None = None,
+) -> tuple[torch.Tensor, torch.Tensor]:
+    """tests/ops/fp8_quant_op.py:135-194."""
+    assert input.ndim == 2
+    shape: Union[tuple[int, int], torch.Size] = input.shape
+    if num_token_padding:
+        shape = (max(num_token_padding, input.shape[0]), shape[1])
+    if output is None:
+        output = torch.empty(shape, device=input.device, dtype=fp8_dtype)
+    else:
+        assert num_token_padding is None, "padding not supported if output passed in"
+        assert output.dtype == fp8_dtype
+    if scale is None:
+        if use_per_token_if_dynamic:
+            scale = torch.zeros((shape[0], 1), device=input.device, dtype=torch.float32)
+            dynamic_per_token_scaled_fp8_quant(output, input.contiguous(), scale, scale_ub)
+        else:
+            scale = torch.empty(1, device=input.device, dtype=torch.float32)
+            dynamic_scaled_fp8_quant(output, input, scale)
+    else:
+        static_scaled_fp8_quant(output, input, scale, group_shape)
+    return output, scale
+
+
+def get_tma_aligned_size(x: int, element_size: int) -> int:
+    alignment = 16 // element_size
+    return (x + alignment - 1) // alignment * alignment
+
+
+def per_token_group_quant_fp8(
+    x: torch.Tensor,
+    group_size: int,
+    eps: float = 1e-10,
+    dtype: torch.dtype = torch.float8_e4m3fn,
+    out_q: torch.Tensor | None = None,
+    column_major_scales: bool = False,
+    tma_aligned_scales: bool = False,
+    use_ue8m0: bool | None = None,
+) -> tuple[torch.Tensor, torch.Tensor]:
+    """tests/ops/fp8_quant_op.py:206-276 (same scale allocation rules)."""
+    assert x.shape[-1] % group_size == 0
+    assert x.stride(-1) == 1, "`x` groups must be contiguous"
+    finfo = torch.finfo(dtype)
+    x_q = out_q if out_q is not None else torch.empty_like(x, dtype=dtype)
+    if column_major_scales:
+        if tma_aligned_scales:
+            m = x.shape[-2]
+            sf_k = x.shape[-1] // group_size
+            tma_m = get_tma_aligned_size(m, 4)
+            shape = x.shape[:-2] + (m, sf_k)
+            stride = (1, tma_m) if x.dim() == 2 else (tma_m * sf_k, 1, tma_m)
+            x_s = torch.empty_strided(shape, stride, device=x.device, dtype=torch.float32)
+        else:
+            shape = x.shape[:-2] + (x.shape[-1] // group_size, x.shape[-2])
+            x_s = torch.empty(shape, device=x.device, dtype=torch.float32).permute(-1, -2)
+    else:
+        shape = x.shape[:-1] + (x.shape[-1] // group_size,)
+        x_s = torch.empty(shape, device=x.device, dtype=torch.float32)
+    torch.ops._C.per_token_group_fp8_quant(x, x_q, x_s, group_size, eps, finfo.min, finfo.max,
+                                           bool(use_ue8m0), column_major_scales, tma_aligned_scales)
+    if use_ue8m0:
+        x_s = x_s.to(torch.float8_e8m0fnu)
+    return x_q, x_s
+
+
+def per_token_group_quant_mxfp4(
+    x: torch.Tensor,
+    group_size: int = 32,
+    eps: float = 1e-10,
+    column_major_scales: bool = False,
+) -> tuple[torch.Tensor, torch.Tensor]:
+    """tests/ops/mxfp4_quant_op.py:8-63: returns (float4_e2m1fn_x2 [M,N/2], float8_e8m0fnu [M,N/32])."""
+    assert x.ndim == 2 and x.shape[-1] % group_size == 0 and x.stride(-1) == 1
+    M, N = x.shape
+    out_q = torch.empty(M, N // 2, device=x.device, dtype=torch.uint8)
+    if column_major_scales:
+        out_s = torch.empty((N // group_size, M), device=x.device, dtype=torch.float32).permute(-1, -2)
+    else:
+        out_s = torch.empty(M, N // group_size, device=x.device, dtype=torch.float32)
+    torch.ops._C.per_token_group_quant_mxfp4(x.contiguous(), out_q, out_s, group_size, eps)
+    out_q = out_q.view(torch.float4_e2m1fn_x2)
+    out_s = out_s.to(dtype=torch.float8_e8m0fnu, memory_format=torch.preserve_format)
+    return out_q, out_s
+
+
+def silu_and_mul_per_block_quant(
+    input: torch.Tensor,
+    group_size: int,
+    quant_dtype: torch.dtype,
+    scale_ub: Optional[torch.Tensor] = None,
+    is_scale_transposed: bool = False,
+    scale_ue8m0: bool = False,
+) -> tuple[torch.Tensor, torch.Tensor]:
+    """tests/register_ops.py:34-74."""
+    assert input.ndim == 2
+    num_tokens = input.shape[0]
+    hidden_size = input.shape[-1] // 2
+    num_groups = hidden_size // group_size
+    out = torch.empty((num_tokens, hidden_size), device=input.device, dtype=quant_dtype)
+    if is_scale_transposed:
+        scales = torch.empty((num_groups, num_tokens), device=input.device, dtype=torch.float32).t()
+    else:
+        scales = torch.empty((num_tokens, num_groups), device=input.device, dtype=torch.float32)
+    torch.ops._C.silu_and_mul_per_block_quant(out, input, scales, group_size, scale_ub,
+                                              is_scale_transposed, scale_ue8m0)
+    return out, scales
+
+
+def silu_and_mul_mxfp4_quant(input: torch.Tensor, group_size: int = 32, eps: float = 1e-10):
+    """tests/test_fused_silu_mul_mxfp4_quant.py:44-56: returns (uint8 [T,H/2], fp32 scales [T,H/32])."""
+    T = input.shape[0]
+    H = input.shape[-1] // 2
+    out = torch.empty(T, H // 2, dtype=torch.uint8, device=input.device)
+    scales = torch.empty(T, H // group_size, dtype=torch.float32, device=input.device)
+    torch.ops._C.silu_and_mul_mxfp4_quant(out, input.contiguous(), scales, group_size, eps)
+    return out, scales
+
+
+def rms_norm_dynamic_per_token_quant(x, weight, eps, quant_dtype, scale_ub=None, residual=None):
+    """tests/test_fused_norm_quant.py:128-144 (residual is updated in place)."""
+    x = x.contiguous()
+    out = torch.empty_like(x, dtype=quant_dtype)
+    T = x.numel() // x.shape[-1]
+    scales = torch.empty(T, dtype=torch.float32, device=x.device)
+    torch.ops._C.rms_norm_dynamic_per_token_quant(out, x, weight, scales, eps, scale_ub, residual)
+    return out, scales
+
+
+def rms_norm_per_block_quant(x, weight, eps, group_size, quant_dtype, residual=None,
+                             is_scale_transposed=False, scale_ue8m0=False):
+    """tests/test_fused_norm_quant.py:147-176."""
+    out = torch.empty(x.shape, dtype=quant_dtype, device=x.device)
+    T = x.numel() // x.shape[-1]
+    G = x.shape[-1] // group_size
+    if is_scale_transposed:
+        scales = torch.empty(G, T, dtype=torch.float32, device=x.device).t()
+    else:
+        scales = torch.empty(T, G, dtype=torch.float32, device=x.device)
+    torch.ops._C.rms_norm_per_block_quant(out, x, weight, scales, eps, None, residual, group_size,
+                                          is_scale_transposed, scale_ue8m0)
+    return out, scales
+
+
+def rms_norm_mxfp4_quant(x, weight, eps, residual=None, group_size: int = 32):
+    """tests/test_fused_norm_quant.py:645-663."""
+    x = x.contiguous()
+    T = x.numel() // x.shape[-1]
+    H = x.shape[-1]
+    out = torch.empty(T, H // 2, device=x.device, dtype=torch.uint8)
+    scales = torch.empty(T, H // group_size, device=x.device, dtype=torch.float32)
+    torch.ops._C.rms_norm_mxfp4_quant(out, x, weight, scales, eps, residual, group_size)
+    return out, scales
+
+
+def rms_norm_static_fp8_quant(x, weight, scale, eps, residual=None, quant_dtype=torch.float8_e4m3fn):
+    """tests/test_fused_norm_quant.py:424-445."""
+    out = torch.empty(x.shape, dtype=quant_dtype, device=x.device)
+    if residual is None:
+        torch.ops._C.rms_norm_static_fp8_quant(out, x, weight, scale, eps)
+    else:
+        torch.ops._C.fused_add_rms_norm_static_fp8_quant(out, x, residual, weight, scale, eps)
+    return out
