@@ -120,7 +120,9 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--quick", action="store_true")
     ap.add_argument("--json", default=None)
-    ap.add_argument("--silu-fast", type=int, default=0)
+    ap.add_argument("--silu-fast", type=int, default=1)
+    ap.add_argument("--only", default=None, help="comma-separated op names")
+    ap.add_argument("--T", type=int, default=None)
     args = ap.parse_args()
     peak = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"] \
         if os.path.exists(os.path.join(ROOT, "MEASURED_PEAKS.json")) else 6650.0
@@ -129,8 +131,12 @@ def main():
                "rms_token_fp8_res", "rms_block_fp8_128", "rms_mxfp4", "rms_static_fp8"]
     act_ops = ["silu_static_fp8", "silu_block_fp8_128", "silu_mxfp4"]
     Ts = [8192] if args.quick else [1, 16, 128, 1024, 4096, 8192]
+    if args.T:
+        Ts = [args.T]
     rows = []
     for op in row_ops + act_ops:
+        if args.only and op not in args.only.split(","):
+            continue
         Hs = ([4096] if args.quick else [4096, 8192]) if op in row_ops else ([14336] if args.quick else [14336, 28672])
         for H in Hs:
             for T in Ts:

@@ -29,11 +29,14 @@ NVCC_COMMON = ARCH + ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC",
 CU_SOURCES = {
     "vxk_api.cu": [],
     "quant_row.cu": ["-fmad=false"],
+    "quant_row_f32.cu": ["-fmad=false"],
+    "quant_row_f16.cu": ["-fmad=false"],
+    "quant_row_bf16.cu": ["-fmad=false"],
     "quant_flat.cu": ["-fmad=false"],
     "gemm_fp8.cu": [],
     "gemm_fp4.cu": [],
 }
-HEADERS = ["vxk_common.cuh", "gemm_common.cuh", os.path.join(ROOT, "include", "vxk_b200.h")]
+HEADERS = ["vxk_common.cuh", "gemm_common.cuh", "quant_row_impl.cuh", os.path.join(ROOT, "include", "vxk_b200.h")]
 
 
 def _digest(paths, extra=""):

@@ -20,7 +20,7 @@
 
 namespace vxk {
 
-std::atomic<int> g_silu_fast{0};
+std::atomic<int> g_silu_fast{1};  // see DESIGN.md "silu": approx by default, vxk_set_silu_fast(0) for expf + IEEE divide
 
 enum Pro { PRO_NONE = 0, PRO_SILU_T = 1, PRO_SILU_F32 = 2 };
 enum Fmt { FMT_FP8_DIV = 0, FMT_MX8 = 1, FMT_MXFP4 = 2, FMT_STATIC = 3 };
@@ -30,114 +30,203 @@ struct FlatParams {
   const void* in;        // [T, H] or [T, 2H] (gate || up)
   float* scales;         // (t*ss0 + g*ss1)
   const float* scale_in; // scale_ub or static scale
-  int64_t total;         // T * H / 8
+  int64_t T;
   int64_t ss0, ss1;
   int nvec;              // H / 8
-  int lanes;             // G / 8
+  int lanes_log2;        // log2(G / 8)
   int ue8m0;
   float eps;
+  // thread -> (row-in-block, column) mapping: tx column threads, rpb rows per block
+  int tx, rpb;
+  int ncb;               // column blocks per row = ceil(nvec / (tx * U))
+  unsigned tiles;        // ceil(T / rpb) * ncb
 };
 
-template <typename T, int PRO, bool FAST>
-__device__ __forceinline__ void load_act(const FlatParams& p, int64_t t, int c, float (&v)[8]) {
-  if constexpr (PRO == PRO_NONE) {
-    load8<T, true>(static_cast<const T*>(p.in) + (t * p.nvec + c) * kVec, v);
+// ---- packed 16-bit helpers (bf16x2 / half2 held in a 32-bit register) ----
+template <typename T> struct Pair;
+template <> struct Pair<__nv_bfloat16> {
+  using V = __nv_bfloat162;
+  static __device__ __forceinline__ float2 unpack(uint32_t w) { return make_float2(bf16_lo(w), bf16_hi(w)); }
+  static __device__ __forceinline__ V pack(float lo, float hi) { return __floats2bfloat162_rn(lo, hi); }
+};
+template <> struct Pair<__half> {
+  using V = __half2;
+  static __device__ __forceinline__ float2 unpack(uint32_t w) {
+    return __half22float2(*reinterpret_cast<const __half2*>(&w));
+  }
+  static __device__ __forceinline__ V pack(float lo, float hi) { return __floats2half2_rn(lo, hi); }
+};
+
+template <typename T> struct RawV { uint4 a; };
+template <> struct RawV<float> { uint4 a, b; };
+template <typename T>
+__device__ __forceinline__ RawV<T> ldg_raw(const T* p) {
+  RawV<T> r;
+  r.a = ldg_stream(p);
+  if constexpr (sizeof(T) == 4) r.b = ldg_stream(p + 4);
+  return r;
+}
+template <typename T>
+__device__ __forceinline__ void raw_to_f32(const RawV<T>& r, float (&v)[8]) {
+  if constexpr (sizeof(T) == 2) {
+    const uint32_t w[4] = {r.a.x, r.a.y, r.a.z, r.a.w};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const float2 f = Pair<T>::unpack(w[i]);
+      v[2 * i] = f.x;
+      v[2 * i + 1] = f.y;
+    }
   } else {
-    const T* g = static_cast<const T*>(p.in) + (t * 2 * p.nvec + c) * kVec;
+    v[0] = __uint_as_float(r.a.x); v[1] = __uint_as_float(r.a.y);
+    v[2] = __uint_as_float(r.a.z); v[3] = __uint_as_float(r.a.w);
+    v[4] = __uint_as_float(r.b.x); v[5] = __uint_as_float(r.b.y);
+    v[6] = __uint_as_float(r.b.z); v[7] = __uint_as_float(r.b.w);
+  }
+}
+
+// gate/up vectors -> the fp32 values to quantise.
+//  PRO_SILU_T  : y = T(T(silu(gate)) * up)  -- the product and its rounding are one packed
+//                HMUL2 (a product of two 8/11-bit significands is exact before the rounding)
+//  PRO_SILU_F32: y = (gate * sigmoid(gate)) * up in fp32
+template <typename T, int PRO, bool FAST>
+__device__ __forceinline__ void prologue(const RawV<T>& g, const RawV<T>& up, float (&v)[8]) {
+  if constexpr (PRO == PRO_NONE) {
+    raw_to_f32<T>(g, v);
+  } else if constexpr (PRO == PRO_SILU_T && sizeof(T) == 2) {
+    const uint32_t gw[4] = {g.a.x, g.a.y, g.a.z, g.a.w};
+    const uint32_t uw[4] = {up.a.x, up.a.y, up.a.z, up.a.w};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const float2 f = Pair<T>::unpack(gw[i]);
+      const typename Pair<T>::V s2 = Pair<T>::pack(silu_f32<FAST>(f.x), silu_f32<FAST>(f.y));
+      const typename Pair<T>::V y2 = __hmul2(s2, *reinterpret_cast<const typename Pair<T>::V*>(&uw[i]));
+      const float2 y = Pair<T>::unpack(*reinterpret_cast<const uint32_t*>(&y2));
+      v[2 * i] = y.x;
+      v[2 * i + 1] = y.y;
+    }
+  } else {
     float u[8];
-    load8<T, true>(g, v);
-    load8<T, true>(g + static_cast<int64_t>(p.nvec) * kVec, u);
+    raw_to_f32<T>(g, v);
+    raw_to_f32<T>(up, u);
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
-      if constexpr (PRO == PRO_SILU_T) {
-        // F.silu(gate) * up evaluated in T: silu rounded to T, product rounded to T
-        v[j] = round_to<T>(round_to<T>(silu_f32<FAST>(v[j])) * u[j]);
-      } else {
-        // gate_f32 * sigmoid(gate_f32) * up_f32, no intermediate rounding to T
-        if constexpr (FAST) v[j] = silu_f32<true>(v[j]) * u[j];
-        else v[j] = (v[j] * __fdiv_rn(1.0f, 1.0f + expf(-v[j]))) * u[j];
-      }
+      if constexpr (PRO == PRO_SILU_T) v[j] = round_to<T>(round_to<T>(silu_f32<FAST>(v[j])) * u[j]);
+      else if constexpr (FAST) v[j] = silu_f32<true>(v[j]) * u[j];
+      else v[j] = (v[j] * __fdiv_rn(1.0f, 1.0f + expf(-v[j]))) * u[j];
     }
   }
 }
 
+// Tiles of (rpb rows) x (tx*U column vectors), persistent grid-stride over tiles; no
+// per-element integer division (one 32-bit division per tile).  All 128-bit loads of a
+// tile (U vectors, x2 for gate/up) are issued before the first use.  Like the row
+// kernels these are instruction-issue bound on B200, so the body is kept minimal:
+// packed 16-bit multiply for silu*up, constant-divisor and reciprocal-based exact
+// divisions, unrolled segmented shuffles.
 template <typename T, int Q, int PRO, int FMT, bool FAST, int U>
 __global__ void __launch_bounds__(256) flat_quant_kernel(const FlatParams p) {
   constexpr float kQMax = QTraits<Q>::kMax;
-  const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
-  const int64_t first = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
-  const int lanes = p.lanes;
+  constexpr bool kGated = PRO != PRO_NONE;
+  const int ry = threadIdx.x / p.tx;            // once per thread
+  const int cx = threadIdx.x - ry * p.tx;
+  const int lanes_log2 = p.lanes_log2;
+  const int lane_mask = (1 << lanes_log2) - 1;
+  const bool sat = p.scale_in != nullptr;
   float r_static = 0.0f;
-  if constexpr (FMT == FMT_STATIC) r_static = __fdiv_rn(1.0f, __ldg(p.scale_in));
+  if constexpr (FMT == FMT_STATIC) r_static = __frcp_rn(__ldg(p.scale_in));
+  const int64_t in_row = static_cast<int64_t>(p.nvec) * kVec * (kGated ? 2 : 1);
+  constexpr int kOutVecBytes = (FMT == FMT_MXFP4) ? 4 : kVec;
 
-  // warp-uniform trip count: lane 0's index decides, every lane runs the shuffles
-  for (int64_t base = first - (threadIdx.x & 31); base < p.total; base += stride * U) {
-    float v[U][8];
-    int64_t jj[U];
+  for (unsigned tile = blockIdx.x; tile < p.tiles; tile += gridDim.x) {
+    const unsigned rb = tile / static_cast<unsigned>(p.ncb);
+    const int cb = static_cast<int>(tile - rb * p.ncb);
+    const int64_t t = static_cast<int64_t>(rb) * p.rpb + ry;
+    const int c0 = cb * U * p.tx + cx;
+    const bool row_ok = t < p.T;
+    const T* __restrict__ xrow = static_cast<const T*>(p.in) + t * in_row;
+
+    RawV<T> g[U], up[kGated ? U : 1];
 #pragma unroll
     for (int u = 0; u < U; ++u) {
-      jj[u] = base + (threadIdx.x & 31) + u * stride;
-      if (jj[u] < p.total) {
-        load_act<T, PRO, FAST>(p, jj[u] / p.nvec, static_cast<int>(jj[u] % p.nvec), v[u]);
+      const int c = c0 + u * p.tx;
+      if (row_ok && c < p.nvec) {
+        g[u] = ldg_raw<T>(xrow + c * kVec);
+        if constexpr (kGated) up[u] = ldg_raw<T>(xrow + (p.nvec + c) * kVec);
       } else {
-#pragma unroll
-        for (int j = 0; j < 8; ++j) v[u][j] = 0.0f;
+        g[u] = RawV<T>{};
+        if constexpr (kGated) up[u] = RawV<T>{};
       }
     }
+    uint8_t* orow = static_cast<uint8_t*>(p.out) + t * p.nvec * kOutVecBytes;
+    float* srow = p.scales + t * p.ss0;
 #pragma unroll
     for (int u = 0; u < U; ++u) {
-      const int64_t j = jj[u];
-      const bool valid = j < p.total;
-      const int64_t t = j / p.nvec;
-      const int c = static_cast<int>(j % p.nvec);
-      float q[8];
+      const int c = c0 + u * p.tx;
+      const bool valid = row_ok && c < p.nvec;
+      float v[8], q[8];
+      prologue<T, PRO, FAST>(g[u], up[kGated ? u : 0], v);
       if constexpr (FMT == FMT_STATIC) {
 #pragma unroll
-        for (int k = 0; k < 8; ++k) q[k] = v[u][k] * r_static;
-        if (valid) stg_stream(static_cast<uint8_t*>(p.out) + j * kVec, pack_q8<Q>(q));
+        for (int k = 0; k < 8; ++k) q[k] = v[k] * r_static;
+        if (valid) stg_stream(orow + c * kVec, pack_q8<Q>(q));
       } else {
         float gmax = 0.0f;
 #pragma unroll
-        for (int k = 0; k < 8; ++k) gmax = fmaxf(gmax, fabsf(v[u][k]));
-        gmax = seg_max(gmax, lanes);
-        const bool leader = valid && (c % lanes == 0);
-        float* sp = p.scales + t * p.ss0 + (c / lanes) * p.ss1;
+        for (int k = 0; k < 8; ++k) gmax = fmaxf(gmax, fabsf(v[k]));
+        gmax = seg_max_pow2(gmax, lanes_log2);   // every lane takes part (invalid ones carry 0)
+        const bool leader = valid && ((c & lane_mask) == 0);
+        float* sp = srow + (c >> lanes_log2) * p.ss1;
         if constexpr (FMT == FMT_MXFP4) {
-          const int e = rceil_e8m0(__fdiv_rn(gmax, 6.0f));
+          const int e = rceil_e8m0(div_const<6>(gmax));
           const float d = e8m0_descale(e);
           if (leader) *sp = e8m0_scale(e);
 #pragma unroll
-          for (int k = 0; k < 8; ++k) {
-            const float cl = fminf(fmaxf(v[u][k] * d, -6.0f), 6.0f);
-            // bf16 inputs scaled by a power of two are already bf16 values
-            q[k] = (PRO == PRO_NONE && std::is_same<T, __nv_bfloat16>::value)
-                       ? cl : __bfloat162float(__float2bfloat16_rn(cl));
+          for (int k = 0; k < 8; ++k) q[k] = fminf(fmaxf(v[k] * d, -6.0f), 6.0f);
+          // bf16 inputs scaled by a power of two are already bf16 values; everything else
+          // takes the reference's intermediate rounding to bf16 (mx_utils.py:346)
+          if constexpr (!(PRO == PRO_NONE && std::is_same<T, __nv_bfloat16>::value)) {
+#pragma unroll
+            for (int k = 0; k < 8; k += 2) {
+              const __nv_bfloat162 b2 = __floats2bfloat162_rn(q[k], q[k + 1]);
+              const uint32_t w = *reinterpret_cast<const uint32_t*>(&b2);
+              q[k] = bf16_lo(w);
+              q[k + 1] = bf16_hi(w);
+            }
           }
-          if (valid) stg_stream(static_cast<uint8_t*>(p.out) + j * 4, pack_e2m1x8(q));
+          if (valid) stg_stream(orow + c * 4, pack_e2m1x8(q));
         } else if constexpr (FMT == FMT_MX8) {
-          const int e = rceil_e8m0(__fdiv_rn(gmax, kQMax));
+          const int e = rceil_e8m0(div_qmax<Q>(gmax));
           const float d = e8m0_descale(e);
           if (leader) *sp = e8m0_scale(e);
 #pragma unroll
-          for (int k = 0; k < 8; ++k) q[k] = v[u][k] * d;
-          if (valid) stg_stream(static_cast<uint8_t*>(p.out) + j * kVec, pack_q8<Q>(q));
+          for (int k = 0; k < 8; ++k) q[k] = v[k] * d;
+          if (valid) stg_stream(orow + c * kVec, pack_q8<Q>(q));
         } else {
           float s;
           if constexpr (PRO == PRO_NONE) {
-            // a4: s = max(amax / qmax, eps)
-            s = fmaxf(__fdiv_rn(gmax, kQMax), p.eps);
+            s = fmaxf(div_qmax<Q>(gmax), p.eps);            // a4: s = max(amax / qmax, eps)
           } else if constexpr (Q == VXK_Q_INT8) {
-            s = __fdiv_rn(fmaxf(gmax, 1e-10f), 127.0f);
+            s = div_qmax<Q>(fmaxf(gmax, 1e-10f));
           } else {
-            s = __fdiv_rn(fmaxf(gmax, FLT_MIN), kQMax);
-            if (p.scale_in != nullptr) s = fminf(s, __ldg(p.scale_in));
+            s = div_qmax<Q>(fmaxf(gmax, FLT_MIN));
+            if (sat) s = fminf(s, __ldg(p.scale_in));
             if (p.ue8m0) s = exp2_ceil_log2(fmaxf(s, 1e-10f));
           }
-          const float r = __fdiv_rn(1.0f, s);
+          const float r = __frcp_rn(s);
           if (leader) *sp = s;
+          if (!(r <= FLT_MAX)) {
+            // s is subnormal or zero (an all-zero / vanishing group): 1/s overflows, take the
+            // IEEE divide (0 / s = 0, matching the reference)
 #pragma unroll
-          for (int k = 0; k < 8; ++k) q[k] = div_by(v[u][k], s, r);
-          if (valid) stg_stream(static_cast<uint8_t*>(p.out) + j * kVec, pack_q8<Q>(q));
+            for (int k = 0; k < 8; ++k) q[k] = __fdiv_rn(v[k], s);
+          } else if (Q != VXK_Q_INT8 && sat) {
+#pragma unroll
+            for (int k = 0; k < 8; ++k) q[k] = div_by<true>(v[k], s, r, kQMax);
+          } else {
+#pragma unroll
+            for (int k = 0; k < 8; ++k) q[k] = div_by<false>(v[k], s, r);
+          }
+          if (valid) stg_stream(orow + c * kVec, pack_q8<Q>(q));
         }
       }
     }
@@ -213,7 +302,7 @@ __global__ void __launch_bounds__(256) flat_quant_generic(const FlatParams p, in
       uint8_t* o = static_cast<uint8_t*>(p.out) + t * H;
       for (int h = g * G + lane; h < (g + 1) * G; h += 32) {
         const float x = value(t, h);
-        o[h] = pack_q1<Q>(mul ? x * r : div_by(x, s, r));
+        o[h] = pack_q1<Q>(mul ? x * r : (!(r <= FLT_MAX) ? __fdiv_rn(x, s) : (Q == VXK_Q_INT8 ? div_by<false>(x, s, r) : div_by<true>(x, s, r, kQMax))));
       }
     }
   }
@@ -227,31 +316,35 @@ struct StaticParams {
   int64_t T, H, in_row_stride, out_row_stride, group_m, group_n, ss_i, ss_j;
 };
 
-// vector path: group_n % 8 == 0 so one scale per vector
+// vector path: group_n % 8 == 0 so one scale per vector; persistent CTAs over rows,
+// 32-bit index arithmetic only (host guarantees T < 2^32, H < 2^31)
 template <typename T, int Q>
 __global__ void __launch_bounds__(256) static_quant_vec_kernel(const StaticParams p) {
   const int nvec = static_cast<int>(p.H / kVec);
-  const int64_t total = p.T * nvec;
-  const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
-  for (int64_t j = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; j < total;
-       j += 2 * stride) {
-    float v[2][8];
-    const int64_t j1 = j + stride;
-    const int64_t t0 = j / nvec, t1 = j1 / nvec;
-    const int c0 = static_cast<int>(j % nvec), c1 = static_cast<int>(j1 % nvec);
-    load8<T, true>(static_cast<const T*>(p.in) + t0 * p.in_row_stride + c0 * kVec, v[0]);
-    if (j1 < total) load8<T, true>(static_cast<const T*>(p.in) + t1 * p.in_row_stride + c1 * kVec, v[1]);
+  const unsigned gm = static_cast<unsigned>(p.group_m), gnv = static_cast<unsigned>(p.group_n / kVec);
+  for (int64_t t = blockIdx.x; t < p.T; t += gridDim.x) {
+    const T* __restrict__ xrow = static_cast<const T*>(p.in) + t * p.in_row_stride;
+    uint8_t* orow = static_cast<uint8_t*>(p.out) + t * p.out_row_stride;
+    const float* srow = p.scale + static_cast<int64_t>(static_cast<unsigned>(t) / gm) * p.ss_i;
+    for (int c0 = threadIdx.x; c0 < nvec; c0 += 4 * blockDim.x) {
+      float v[4][8];
 #pragma unroll
-    for (int u = 0; u < 2; ++u) {
-      const int64_t t = u ? t1 : t0;
-      const int c = u ? c1 : c0;
-      if (u == 1 && j1 >= total) break;
-      const float s = __ldg(p.scale + (t / p.group_m) * p.ss_i + ((c * kVec) / p.group_n) * p.ss_j);
-      const float r = __fdiv_rn(1.0f, s);
-      float q[8];
+      for (int u = 0; u < 4; ++u) {
+        const int c = c0 + u * blockDim.x;
+        if (c < nvec) load8<T, true>(xrow + c * kVec, v[u]);
+      }
 #pragma unroll
-      for (int k = 0; k < 8; ++k) q[k] = v[u][k] * r;
-      stg_stream(static_cast<uint8_t*>(p.out) + t * p.out_row_stride + c * kVec, pack_q8<Q>(q));
+      for (int u = 0; u < 4; ++u) {
+        const int c = c0 + u * blockDim.x;
+        if (c < nvec) {
+          const float s = __ldg(srow + static_cast<int64_t>(static_cast<unsigned>(c) / gnv) * p.ss_j);
+          const float r = __fdiv_rn(1.0f, s);
+          float q[8];
+#pragma unroll
+          for (int k = 0; k < 8; ++k) q[k] = v[u][k] * r;
+          stg_stream(orow + c * kVec, pack_q8<Q>(q));
+        }
+      }
     }
   }
 }
@@ -275,21 +368,29 @@ __global__ void __launch_bounds__(256) tensor_amax_kernel(const T* __restrict__ 
                                                           bool vec) {
   __shared__ float scratch[33];
   float amax = 0.0f;
-  const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
-  const int64_t i0 = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
-  if (vec) {
-    const int nvec = static_cast<int>(H / kVec);
-    const int64_t total = T_ * nvec;
-    for (int64_t j = i0; j < total; j += stride) {
-      float v[8];
-      load8<T, true>(in + (j / nvec) * in_row_stride + (j % nvec) * kVec, v);
+  for (int64_t t = blockIdx.x; t < T_; t += gridDim.x) {
+    const T* __restrict__ xrow = in + t * in_row_stride;
+    if (vec) {
+      const int nvec = static_cast<int>(H / kVec);
+      for (int c0 = threadIdx.x; c0 < nvec; c0 += 4 * blockDim.x) {
+        float v[4][8];
 #pragma unroll
-      for (int k = 0; k < 8; ++k) amax = fmaxf(amax, fabsf(v[k]));
+        for (int u = 0; u < 4; ++u) {
+          const int c = c0 + u * blockDim.x;
+          if (c < nvec) load8<T, true>(xrow + c * kVec, v[u]);
+          else {
+#pragma unroll
+            for (int k = 0; k < 8; ++k) v[u][k] = 0.0f;
+          }
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+#pragma unroll
+          for (int k = 0; k < 8; ++k) amax = fmaxf(amax, fabsf(v[u][k]));
+      }
+    } else {
+      for (int h = threadIdx.x; h < H; h += blockDim.x) amax = fmaxf(amax, fabsf(to_f32<T>(xrow[h])));
     }
-  } else {
-    const int64_t total = T_ * H;
-    for (int64_t i = i0; i < total; i += stride)
-      amax = fmaxf(amax, fabsf(to_f32<T>(in[(i / H) * in_row_stride + (i % H)])));
   }
   amax = block_reduce<true>(amax, scratch);
   if (threadIdx.x == 0) {
@@ -311,14 +412,27 @@ template <typename T, int Q, int PRO, int FMT>
 static int launch_flat(FlatParams p, int64_t T_, int64_t H, int G, bool vec_ok, cudaStream_t st) {
   if (T_ == 0 || H == 0) return VXK_OK;
   const bool fast = (PRO != PRO_NONE) && g_silu_fast.load(std::memory_order_relaxed) != 0;
+  p.T = T_;
   if (vec_ok) {
+    constexpr int U = (PRO == PRO_NONE) ? 4 : 2;   // 4 x 16 B loads in flight per thread either way
     p.nvec = static_cast<int>(H / kVec);
-    p.total = T_ * p.nvec;
-    p.lanes = G / kVec;
-    constexpr int U = (PRO == PRO_NONE) ? 2 : 1;
-    const int grid = flat_grid(p.total, 256 * U);
-    if (fast) flat_quant_kernel<T, Q, PRO, FMT, (PRO != PRO_NONE), U><<<grid, 256, 0, st>>>(p);
-    else flat_quant_kernel<T, Q, PRO, FMT, false, U><<<grid, 256, 0, st>>>(p);
+    const int lanes = G / kVec;
+    p.lanes_log2 = 0;
+    while ((1 << p.lanes_log2) < lanes) ++p.lanes_log2;
+    // columns per block: a multiple of 32 (and so of `lanes`); short rows share a block
+    int per_thread = (p.nvec + U - 1) / U;                   // column threads wanted for one row
+    p.tx = per_thread >= 256 ? 256 : (per_thread + 31) / 32 * 32;
+    p.rpb = 256 / p.tx;
+    p.ncb = (p.nvec + p.tx * U - 1) / (p.tx * U);
+    const int64_t row_blocks = (T_ + p.rpb - 1) / p.rpb;
+    const int64_t tiles = row_blocks * p.ncb;
+    if (tiles > 0xffffffffLL) return fail(VXK_ERR_INVALID, "problem too large (%lld tiles)", (long long)tiles);
+    p.tiles = static_cast<unsigned>(tiles);
+    const int threads = p.tx * p.rpb;
+    const int64_t cap = static_cast<int64_t>(sm_count()) * 8;
+    const unsigned grid = static_cast<unsigned>(tiles < cap ? tiles : cap);
+    if (fast) flat_quant_kernel<T, Q, PRO, FMT, (PRO != PRO_NONE), U><<<grid, threads, 0, st>>>(p);
+    else flat_quant_kernel<T, Q, PRO, FMT, false, U><<<grid, threads, 0, st>>>(p);
   } else {
     const int64_t ngroups = T_ * (H / G);
     const int grid = flat_grid(ngroups, 8);
@@ -454,8 +568,10 @@ extern "C" int vxk_silu_and_mul_mxfp4_quant(void* out, const void* in, float* sc
 template <typename T, int Q>
 static int launch_static(const StaticParams& p, bool vec, cudaStream_t st) {
   if (vec) {
-    const int grid = flat_grid(p.T * (p.H / kVec), 512);
-    static_quant_vec_kernel<T, Q><<<grid, 256, 0, st>>>(p);
+    const int64_t cap = static_cast<int64_t>(sm_count()) * 8;
+    const int nvec = static_cast<int>(p.H / kVec);
+    const int threads = nvec >= 1024 ? 256 : (nvec >= 512 ? 128 : 64);
+    static_quant_vec_kernel<T, Q><<<static_cast<unsigned>(p.T < cap ? p.T : cap), threads, 0, st>>>(p);
   } else {
     const int grid = flat_grid(p.T * p.H, 1024);
     static_quant_scalar_kernel<T, Q><<<grid, 256, 0, st>>>(p);
@@ -465,7 +581,7 @@ static int launch_static(const StaticParams& p, bool vec, cudaStream_t st) {
 
 static bool static_vec_ok(const StaticParams& p, int in_dtype) {
   const size_t es = in_dtype == VXK_F32 ? 4 : 2;
-  return p.H % kVec == 0 && p.group_n % kVec == 0 && aligned16(p.in) &&
+  return p.H % kVec == 0 && p.group_n % kVec == 0 && p.T < 0xffffffffLL && p.H < 0x7fffffffLL && aligned16(p.in) &&
          (p.in_row_stride * es) % 16 == 0 && reinterpret_cast<uintptr_t>(p.out) % 8 == 0 &&
          p.out_row_stride % 8 == 0;
 }
@@ -480,6 +596,14 @@ extern "C" int vxk_static_scaled_fp8_quant(void* out, const void* in, const floa
   VXK_REQUIRE(group_m > 0 && group_n > 0, "group shape must be positive");
   StaticParams p{out, in, scale, T_, H, in_row_stride, out_row_stride, group_m, group_n, ss_i, ss_j};
   const bool v = static_vec_ok(p, in_dtype);
+  if (v && ss_i == 0 && ss_j == 0 && in_row_stride == H && out_row_stride == H) {
+    // per-tensor scale on contiguous rows: the flat streaming kernel
+    FlatParams f{};
+    f.out = out; f.in = in; f.scale_in = scale;
+    VXK_DISPATCH_T(in_dtype,
+      if (q_dtype == VXK_Q_E4M3) return launch_flat<T, VXK_Q_E4M3, PRO_NONE, FMT_STATIC>(f, T_, H, kVec, true, stream);
+      return launch_flat<T, VXK_Q_E5M2, PRO_NONE, FMT_STATIC>(f, T_, H, kVec, true, stream));
+  }
   VXK_DISPATCH_T(in_dtype,
     if (q_dtype == VXK_Q_E4M3) return launch_static<T, VXK_Q_E4M3>(p, v, stream);
     return launch_static<T, VXK_Q_E5M2>(p, v, stream));
@@ -495,7 +619,8 @@ extern "C" int vxk_dynamic_scaled_fp8_quant(void* out, const void* in, float* sc
   if (T_ == 0 || H == 0) return VXK_OK;
   StaticParams p{out, in, scale, T_, H, in_row_stride, out_row_stride, T_, H, 0, 0};
   const bool v = static_vec_ok(p, in_dtype);
-  const int grid = flat_grid(v ? T_ * (H / kVec) : T_ * H, v ? 1024 : 2048);
+  const int64_t cap = static_cast<int64_t>(sm_count()) * 8;
+  const unsigned grid = static_cast<unsigned>(T_ < cap ? T_ : cap);
   VXK_DISPATCH_T(in_dtype, {
     int rc;
     if (q_dtype == VXK_Q_E4M3) {

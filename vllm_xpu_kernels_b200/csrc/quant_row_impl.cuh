@@ -1,0 +1,476 @@
+// Row-resident quantisation kernels (templates).  See quant_row.cu for the op list.
+#pragma once
+#include "vxk_common.cuh"
+
+#include <cstdlib>
+
+namespace vxk {
+
+enum RowMode { MODE_TOKEN_DIV = 0, MODE_TOKEN_MUL = 1, MODE_GROUP = 2, MODE_MXFP4 = 3, MODE_STATIC = 4 };
+
+struct RowParams {
+  void* out;            // [T, H] codes (or [T, H/2] packed fp4)
+  const void* in;       // [T, H], row stride in_row_stride
+  const void* weight;   // [H] (rms only)
+  void* residual;       // [T, H] in/out, nullable
+  float* scales;        // per-token [T] or per-group (t*ss0 + g*ss1)
+  const float* scale_in;  // scale_ub (token modes) or the static scale
+  int64_t H, in_row_stride, ss0, ss1;
+  int nvec;             // H / 8
+  int group;            // group size (MODE_GROUP / MODE_MXFP4)
+  int lanes_log2;       // log2(group / 8) on the vector path
+  int ue8m0;
+  float eps;
+};
+
+// Raw (still packed) copy of 8 input elements: 4 registers for bf16/f16, 8 for f32.
+template <typename T> struct Raw8 { uint4 a; };
+template <> struct Raw8<float> { uint4 a, b; };
+
+template <typename T, bool STREAM>
+__device__ __forceinline__ Raw8<T> load_raw(const T* p) {
+  Raw8<T> r;
+  if constexpr (STREAM) r.a = ldg_stream(p);
+  else r.a = *reinterpret_cast<const uint4*>(p);
+  if constexpr (sizeof(T) == 4) {
+    if constexpr (STREAM) r.b = ldg_stream(p + 4);
+    else r.b = *reinterpret_cast<const uint4*>(p + 4);
+  }
+  return r;
+}
+template <typename T>
+__device__ __forceinline__ void unpack_raw(const Raw8<T>& r, float (&v)[8]) {
+  if constexpr (sizeof(T) == 2) {
+    const uint32_t w[4] = {r.a.x, r.a.y, r.a.z, r.a.w};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      if constexpr (std::is_same<T, __nv_bfloat16>::value) {
+        v[2 * i] = bf16_lo(w[i]);
+        v[2 * i + 1] = bf16_hi(w[i]);
+      } else {
+        const float2 f = __half22float2(*reinterpret_cast<const __half2*>(&w[i]));
+        v[2 * i] = f.x;
+        v[2 * i + 1] = f.y;
+      }
+    }
+  } else {
+    v[0] = __uint_as_float(r.a.x); v[1] = __uint_as_float(r.a.y);
+    v[2] = __uint_as_float(r.a.z); v[3] = __uint_as_float(r.a.w);
+    v[4] = __uint_as_float(r.b.x); v[5] = __uint_as_float(r.b.y);
+    v[6] = __uint_as_float(r.b.z); v[7] = __uint_as_float(r.b.w);
+  }
+}
+// fp32 x8 -> T x8 (RNE), packed
+template <typename T>
+__device__ __forceinline__ Raw8<T> pack_raw(const float (&v)[8]) {
+  Raw8<T> r;
+  if constexpr (sizeof(T) == 2) {
+    uint32_t w[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      if constexpr (std::is_same<T, __nv_bfloat16>::value) {
+        __nv_bfloat162 h = __floats2bfloat162_rn(v[2 * i], v[2 * i + 1]);
+        w[i] = *reinterpret_cast<uint32_t*>(&h);
+      } else {
+        __half2 h = __floats2half2_rn(v[2 * i], v[2 * i + 1]);
+        w[i] = *reinterpret_cast<uint32_t*>(&h);
+      }
+    }
+    r.a = make_uint4(w[0], w[1], w[2], w[3]);
+  } else {
+    r.a = make_uint4(__float_as_uint(v[0]), __float_as_uint(v[1]), __float_as_uint(v[2]), __float_as_uint(v[3]));
+    r.b = make_uint4(__float_as_uint(v[4]), __float_as_uint(v[5]), __float_as_uint(v[6]), __float_as_uint(v[7]));
+  }
+  return r;
+}
+template <typename T>
+__device__ __forceinline__ void store_raw(T* p, const Raw8<T>& r) {
+  *reinterpret_cast<uint4*>(p) = r.a;
+  if constexpr (sizeof(T) == 4) *reinterpret_cast<uint4*>(p + 4) = r.b;
+}
+
+// Opaque to the optimiser: stops it from keeping the 8 unpacked fp32 values of every
+// vector live between the amax pass and the quantise pass (that would cost 8 registers
+// per vector instead of 4 and halve the resident CTAs).
+template <typename T>
+__device__ __forceinline__ void keep_packed(Raw8<T>& r) {
+  asm volatile("" : "+r"(r.a.x), "+r"(r.a.y), "+r"(r.a.z), "+r"(r.a.w));
+  if constexpr (sizeof(T) == 4) asm volatile("" : "+r"(r.b.x), "+r"(r.b.y), "+r"(r.b.z), "+r"(r.b.w));
+}
+
+__device__ __forceinline__ double block_sum_f64(double v, double* scratch) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = (blockDim.x + 31) >> 5;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  if (nwarp == 1) return v;
+  __syncthreads();
+  if (lane == 0) scratch[warp] = v;
+  __syncthreads();
+  double r = (lane < nwarp) ? scratch[lane] : 0.0;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) r += __shfl_xor_sync(0xffffffffu, r, o);
+  return r;
+}
+
+// Persistent CTAs (grid = min(T, resident CTAs)), each loops over rows.  A thread owns
+// VPT vectors of a row (tid + i * blockDim); all of its 128-bit loads are issued before
+// the first use and the row then lives in registers as fp32, so every element is
+// converted, normalised and scaled exactly once.  These kernels are instruction-issue
+// bound on B200 (HBM delivers one bf16 element per ~14 issue slots), hence no value is
+// ever recomputed.  SAT: clamp the quotient before the conversion (only needed when a
+// scale upper bound can push |x / s| past the format maximum).
+template <typename T, int Q, int MODE, bool RMS, bool HAS_RES, int VPT>
+__global__ void __launch_bounds__(512) row_quant_kernel(const RowParams p, const int64_t T_rows) {
+  __shared__ float scratch[33];
+  const int tid = threadIdx.x, nthr = blockDim.x;
+  constexpr float kQMax = QTraits<Q>::kMax;
+  const T* __restrict__ w = static_cast<const T*>(p.weight);
+  const bool sat = p.scale_in != nullptr;
+
+  for (int64_t row = blockIdx.x; row < T_rows; row += gridDim.x) {
+    const T* __restrict__ xin = static_cast<const T*>(p.in) + row * p.in_row_stride;
+    float v[VPT][8];
+    {
+      Raw8<T> raw[VPT];
+#pragma unroll
+      for (int i = 0; i < VPT; ++i) {
+        const int idx = tid + i * nthr;
+        raw[i] = (idx < p.nvec) ? load_raw<T, true>(xin + idx * kVec) : Raw8<T>{};
+      }
+      if constexpr (RMS && HAS_RES) {
+        T* res = static_cast<T*>(p.residual) + row * p.H;
+        Raw8<T> rr[VPT];
+#pragma unroll
+        for (int i = 0; i < VPT; ++i) {
+          const int idx = tid + i * nthr;
+          rr[i] = (idx < p.nvec) ? load_raw<T, false>(res + idx * kVec) : Raw8<T>{};
+        }
+#pragma unroll
+        for (int i = 0; i < VPT; ++i) {
+          const int idx = tid + i * nthr;
+          float b[8];
+          unpack_raw<T>(raw[i], v[i]);
+          unpack_raw<T>(rr[i], b);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) v[i][j] = v[i][j] + b[j];
+          const Raw8<T> z = pack_raw<T>(v[i]);  // z = T(x + res): new residual and norm input
+          if (idx < p.nvec) store_raw<T>(res + idx * kVec, z);
+          unpack_raw<T>(z, v[i]);
+        }
+      } else {
+#pragma unroll
+        for (int i = 0; i < VPT; ++i) unpack_raw<T>(raw[i], v[i]);
+      }
+    }
+
+    if constexpr (RMS) {
+      float ss = 0.0f;
+#pragma unroll
+      for (int i = 0; i < VPT; ++i) {
+        float part = 0.0f;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) part = fmaf(v[i][j], v[i][j], part);
+        ss += part;
+      }
+      ss = block_reduce<false>(ss, scratch);
+      const float var = __fdiv_rn(ss, static_cast<float>(p.H));
+      const float inv_rms = __fdiv_rn(1.0f, __fsqrt_rn(var + p.eps));
+#pragma unroll
+      for (int i = 0; i < VPT; ++i) {
+        const int idx = tid + i * nthr;
+        float wv[8];
+        if (idx < p.nvec) load8<T, false>(w + idx * kVec, wv);
+        else {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) wv[j] = 0.0f;
+        }
+#pragma unroll
+        for (int j = 0; j < 8; ++j) v[i][j] = (v[i][j] * inv_rms) * wv[j];
+      }
+    }
+
+    if constexpr (MODE == MODE_TOKEN_DIV || MODE == MODE_TOKEN_MUL) {
+      float amax = 0.0f;
+#pragma unroll
+      for (int i = 0; i < VPT; ++i)
+#pragma unroll
+        for (int j = 0; j < 8; ++j) amax = fmaxf(amax, fabsf(v[i][j]));
+      amax = block_reduce<true>(amax, scratch);
+      float s;
+      if constexpr (Q == VXK_Q_INT8) {
+        s = amax > 0.0f ? div_qmax<Q>(amax) : 1.0f;
+      } else {
+        if (sat) amax = fminf(amax, __ldg(p.scale_in));
+        s = fmaxf(div_qmax<Q>(amax), 1.0f / (kQMax * 512.0f));
+      }
+      const float r = __frcp_rn(s);
+      if (tid == 0) p.scales[row] = s;
+      uint8_t* o = static_cast<uint8_t*>(p.out) + row * p.H;
+#pragma unroll
+      for (int i = 0; i < VPT; ++i) {
+        const int idx = tid + i * nthr;
+        float q[8];
+        if constexpr (Q == VXK_Q_INT8) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) q[j] = div_by<false>(v[i][j], s, r);
+        } else if constexpr (MODE == MODE_TOKEN_DIV) {
+          if (sat) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) q[j] = div_by<true>(v[i][j], s, r, kQMax);
+          } else {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) q[j] = div_by<false>(v[i][j], s, r);
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) q[j] = v[i][j] * r;
+        }
+        if (idx < p.nvec) stg_stream(o + idx * kVec, pack_q8<Q>(q));
+      }
+    } else if constexpr (MODE == MODE_STATIC) {
+      const float r = __frcp_rn(__ldg(p.scale_in));
+      uint8_t* o = static_cast<uint8_t*>(p.out) + row * p.H;
+#pragma unroll
+      for (int i = 0; i < VPT; ++i) {
+        const int idx = tid + i * nthr;
+        float q[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) q[j] = v[i][j] * r;
+        if (idx < p.nvec) stg_stream(o + idx * kVec, pack_q8<Q>(q));
+      }
+    } else {  // MODE_GROUP / MODE_MXFP4: 1 x G groups, G/8 consecutive lanes per group
+      const int lanes_log2 = p.lanes_log2;
+#pragma unroll
+      for (int i = 0; i < VPT; ++i) {
+        const int idx = tid + i * nthr;
+        const bool valid = idx < p.nvec;
+        float q[8];
+        float gmax = 0.0f;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) gmax = fmaxf(gmax, fabsf(v[i][j]));
+        gmax = seg_max_pow2(gmax, lanes_log2);  // all lanes participate (invalid ones carry 0)
+        const int g = idx >> lanes_log2;
+        const bool leader = valid && ((idx & ((1 << lanes_log2) - 1)) == 0);
+        if constexpr (MODE == MODE_MXFP4) {
+          const int e = rceil_e8m0(div_const<6>(gmax));
+          const float d = e8m0_descale(e);
+          if (leader) p.scales[row * p.ss0 + g * p.ss1] = e8m0_scale(e);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) q[j] = fminf(fmaxf(v[i][j] * d, -6.0f), 6.0f);
+#pragma unroll
+          for (int j = 0; j < 8; j += 2) {  // the reference's intermediate rounding to bf16
+            const __nv_bfloat162 b2 = __floats2bfloat162_rn(q[j], q[j + 1]);
+            const uint32_t wd = *reinterpret_cast<const uint32_t*>(&b2);
+            q[j] = bf16_lo(wd);
+            q[j + 1] = bf16_hi(wd);
+          }
+          uint8_t* o = static_cast<uint8_t*>(p.out) + row * (p.H / 2);
+          if (valid) stg_stream(o + idx * 4, pack_e2m1x8(q));
+        } else {
+          float s;
+          if constexpr (Q == VXK_Q_INT8) {
+            s = gmax > 0.0f ? div_qmax<Q>(gmax) : 1.0f;
+          } else {
+            s = fmaxf(div_qmax<Q>(gmax), 1.0f / (kQMax * 512.0f));
+            if (p.ue8m0) s = exp2_ceil_log2(fmaxf(fabsf(s), 1e-10f));
+          }
+          const float r = __frcp_rn(s);
+          if (leader) p.scales[row * p.ss0 + g * p.ss1] = s;
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            if constexpr (Q == VXK_Q_INT8) q[j] = div_by<false>(v[i][j], s, r);
+            else q[j] = v[i][j] * r;
+          }
+          uint8_t* o = static_cast<uint8_t*>(p.out) + row * p.H;
+          if (valid) stg_stream(o + idx * kVec, pack_q8<Q>(q));
+        }
+      }
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------
+// Generic fallback: any H, any alignment.  One CTA per row, scalar accesses,
+// the row is re-read from L2 for each pass.  Same arithmetic as above.
+// ---------------------------------------------------------------------------
+template <typename T, int Q, int MODE, bool RMS>
+__global__ void __launch_bounds__(256) row_quant_generic(const RowParams p) {
+  __shared__ double scratch64[32];
+  float* scratch = reinterpret_cast<float*>(scratch64);
+  const int64_t row = blockIdx.x;
+  const int tid = threadIdx.x, nthr = blockDim.x;
+  const T* __restrict__ xin = static_cast<const T*>(p.in) + row * p.in_row_stride;
+  T* res = p.residual ? static_cast<T*>(p.residual) + row * p.H : nullptr;
+  const T* __restrict__ w = static_cast<const T*>(p.weight);
+  const int H = static_cast<int>(p.H);
+  constexpr float kQMax = QTraits<Q>::kMax;
+
+  float inv_rms = 1.0f;
+  if constexpr (RMS) {
+    float ss = 0.0f;
+    for (int h = tid; h < H; h += nthr) {
+      float x = to_f32<T>(xin[h]);
+      if (res) {
+        x = round_to<T>(x + to_f32<T>(res[h]));
+        res[h] = from_f32<T>(x);
+      }
+      ss = fmaf(x, x, ss);
+    }
+    ss = block_reduce<false>(ss, scratch);
+    inv_rms = __fdiv_rn(1.0f, __fsqrt_rn(__fdiv_rn(ss, static_cast<float>(H)) + p.eps));
+  }
+  // value to quantise at column h (after the prologue)
+  auto value = [&](int h) -> float {
+    if constexpr (RMS) {
+      const float x = res ? to_f32<T>(res[h]) : to_f32<T>(xin[h]);
+      return (x * inv_rms) * to_f32<T>(w[h]);
+    } else {
+      return to_f32<T>(xin[h]);
+    }
+  };
+
+  if constexpr (MODE == MODE_TOKEN_DIV || MODE == MODE_TOKEN_MUL) {
+    float amax = 0.0f;
+    for (int h = tid; h < H; h += nthr) amax = fmaxf(amax, fabsf(value(h)));
+    amax = block_reduce<true>(amax, scratch);
+    float s;
+    if constexpr (Q == VXK_Q_INT8) {
+      s = amax > 0.0f ? __fdiv_rn(amax, 127.0f) : 1.0f;
+    } else {
+      if (p.scale_in != nullptr) amax = fminf(amax, __ldg(p.scale_in));
+      s = fmaxf(__fdiv_rn(amax, kQMax), __fdiv_rn(1.0f, kQMax * 512.0f));
+    }
+    const float r = __fdiv_rn(1.0f, s);
+    if (tid == 0) p.scales[row] = s;
+    uint8_t* o = static_cast<uint8_t*>(p.out) + row * p.H;
+    for (int h = tid; h < H; h += nthr) {
+      const float x = value(h);
+      const float q = (Q == VXK_Q_INT8) ? div_by<false>(x, s, r) : (MODE == MODE_TOKEN_DIV ? div_by<true>(x, s, r, kQMax) : x * r);
+      o[h] = pack_q1<Q>(q);
+    }
+  } else if constexpr (MODE == MODE_STATIC) {
+    const float r = __fdiv_rn(1.0f, __ldg(p.scale_in));
+    uint8_t* o = static_cast<uint8_t*>(p.out) + row * p.H;
+    for (int h = tid; h < H; h += nthr) o[h] = pack_q1<Q>(value(h) * r);
+  } else {
+    // one warp per group, round-robin over the row's groups
+    const int G = p.group, ngroups = H / G;
+    const int lane = tid & 31, warp = tid >> 5, nwarp = nthr >> 5;
+    for (int g = warp; g < ngroups; g += nwarp) {
+      float gmax = 0.0f;
+      for (int h = g * G + lane; h < (g + 1) * G; h += 32) gmax = fmaxf(gmax, fabsf(value(h)));
+      gmax = warp_max(gmax);
+      if constexpr (MODE == MODE_MXFP4) {
+        const int e = rceil_e8m0(__fdiv_rn(gmax, 6.0f));
+        const float d = e8m0_descale(e);
+        if (lane == 0) p.scales[row * p.ss0 + g * p.ss1] = e8m0_scale(e);
+        uint8_t* o = static_cast<uint8_t*>(p.out) + row * (p.H / 2);
+        for (int h2 = g * G / 2 + lane; h2 < (g + 1) * G / 2; h2 += 32) {
+          float c0 = fminf(fmaxf(value(2 * h2) * d, -6.0f), 6.0f);
+          float c1 = fminf(fmaxf(value(2 * h2 + 1) * d, -6.0f), 6.0f);
+          c0 = __bfloat162float(__float2bfloat16_rn(c0));
+          c1 = __bfloat162float(__float2bfloat16_rn(c1));
+          o[h2] = static_cast<uint8_t>(cvt_e2m1x2(c1, c0));
+        }
+      } else {
+        float s;
+        if constexpr (Q == VXK_Q_INT8) {
+          s = gmax > 0.0f ? __fdiv_rn(gmax, 127.0f) : 1.0f;
+        } else {
+          s = fmaxf(__fdiv_rn(gmax, kQMax), __fdiv_rn(1.0f, kQMax * 512.0f));
+          if (p.ue8m0) s = exp2_ceil_log2(fmaxf(fabsf(s), 1e-10f));
+        }
+        const float r = __fdiv_rn(1.0f, s);
+        if (lane == 0) p.scales[row * p.ss0 + g * p.ss1] = s;
+        uint8_t* o = static_cast<uint8_t*>(p.out) + row * p.H;
+        for (int h = g * G + lane; h < (g + 1) * G; h += 32) {
+          const float x = value(h);
+          o[h] = pack_q1<Q>(Q == VXK_Q_INT8 ? div_by<false>(x, s, r) : x * r);
+        }
+      }
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------
+// host dispatch
+// ---------------------------------------------------------------------------
+template <typename K>
+inline int resident_ctas(K kernel, int threads) {
+  int n = 0;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kernel, threads, 0) != cudaSuccess || n < 1) n = 1;
+  return n * sm_count();
+}
+
+template <typename T, int Q, int MODE, bool RMS, bool HAS_RES, int VPT>
+inline void launch_row_vpt2(const RowParams& p, int64_t T_rows, int threads, cudaStream_t st) {
+  auto kernel = row_quant_kernel<T, Q, MODE, RMS, HAS_RES, VPT>;
+  const int64_t cap = resident_ctas(kernel, threads);
+  const unsigned grid = static_cast<unsigned>(T_rows < cap ? T_rows : cap);
+  kernel<<<grid, threads, 0, st>>>(p, T_rows);
+}
+template <typename T, int Q, int MODE, bool RMS, int VPT>
+inline void launch_row_vpt(const RowParams& p, int64_t T_rows, int threads, cudaStream_t st) {
+  if constexpr (RMS) {
+    if (p.residual != nullptr) return launch_row_vpt2<T, Q, MODE, RMS, true, VPT>(p, T_rows, threads, st);
+  }
+  launch_row_vpt2<T, Q, MODE, RMS, false, VPT>(p, T_rows, threads, st);
+}
+
+template <typename T, int Q, int MODE, bool RMS>
+int launch_row(const RowParams& p_in, int64_t T_rows, bool vec_ok, cudaStream_t st) {
+  RowParams p = p_in;
+  p.lanes_log2 = 0;
+  while (p.group > 0 && (kVec << p.lanes_log2) < p.group) ++p.lanes_log2;
+  if (T_rows == 0 || p.H == 0) return VXK_OK;
+  const int nvec = p.nvec;
+  // per-thread vectors: enough to keep one warp busy, 4 by default (two register
+  // copies of the row are live: current + prefetched), more only for long rows
+  constexpr int kMaxVpt = 8;
+  static const int env_vpt = [] { const char* e = getenv("VXK_ROW_VPT"); return e ? atoi(e) : 0; }();
+  const int want = env_vpt > 0 ? env_vpt : 4;
+  int vpt = 1;
+  while (vpt < want && nvec > 32 * vpt) vpt *= 2;
+  while ((nvec + vpt - 1) / vpt > 256 && vpt < kMaxVpt) vpt *= 2;  // long rows: up to 8 x 512 threads
+  if (vpt > kMaxVpt) vpt = kMaxVpt;
+  const int threads = ((nvec + vpt - 1) / vpt + 31) / 32 * 32;
+  if (vec_ok && threads <= 512) {
+    switch (vpt) {
+      case 1: launch_row_vpt<T, Q, MODE, RMS, 1>(p, T_rows, threads, st); break;
+      case 2: launch_row_vpt<T, Q, MODE, RMS, 2>(p, T_rows, threads, st); break;
+      case 4: launch_row_vpt<T, Q, MODE, RMS, 4>(p, T_rows, threads, st); break;
+      default: launch_row_vpt<T, Q, MODE, RMS, 8>(p, T_rows, threads, st); break;
+    }
+  } else {
+    if (T_rows > 0x7fffffffLL) return fail(VXK_ERR_INVALID, "too many rows (%lld)", (long long)T_rows);
+    row_quant_generic<T, Q, MODE, RMS><<<static_cast<unsigned>(T_rows), 256, 0, st>>>(p);
+  }
+  return check_launch("row_quant");
+}
+
+
+// One entry per (op, quant dtype); instantiated per activation type in quant_row_<type>.cu
+enum RowOp { ROW_A1 = 0, ROW_A6 = 1, ROW_A7 = 2, ROW_A8 = 3, ROW_A9 = 4 };
+
+template <typename T>
+int row_launch(int op, int q_dtype, const RowParams& p, int64_t T_rows, bool vec_ok, cudaStream_t st) {
+  switch (op) {
+    case ROW_A1:
+      if (q_dtype == VXK_Q_E4M3) return launch_row<T, VXK_Q_E4M3, MODE_TOKEN_DIV, false>(p, T_rows, vec_ok, st);
+      return launch_row<T, VXK_Q_E5M2, MODE_TOKEN_DIV, false>(p, T_rows, vec_ok, st);
+    case ROW_A6:
+      if (q_dtype == VXK_Q_E4M3) return launch_row<T, VXK_Q_E4M3, MODE_TOKEN_MUL, true>(p, T_rows, vec_ok, st);
+      return launch_row<T, VXK_Q_INT8, MODE_TOKEN_MUL, true>(p, T_rows, vec_ok, st);
+    case ROW_A7:
+      if (q_dtype == VXK_Q_E4M3) return launch_row<T, VXK_Q_E4M3, MODE_GROUP, true>(p, T_rows, vec_ok, st);
+      return launch_row<T, VXK_Q_INT8, MODE_GROUP, true>(p, T_rows, vec_ok, st);
+    case ROW_A8:
+      return launch_row<T, VXK_Q_E4M3, MODE_MXFP4, true>(p, T_rows, vec_ok, st);
+    case ROW_A9:
+      if (q_dtype == VXK_Q_E4M3) return launch_row<T, VXK_Q_E4M3, MODE_STATIC, true>(p, T_rows, vec_ok, st);
+      return launch_row<T, VXK_Q_E5M2, MODE_STATIC, true>(p, T_rows, vec_ok, st);
+    default: return fail(VXK_ERR_INVALID, "bad row op %d", op);
+  }
+}
+
+}  // namespace vxk

@@ -207,14 +207,36 @@ __device__ __forceinline__ uint32_t pack_e2m1x8(const float (&v)[8]) {
 }
 
 // ---- exact division by a row/group constant ----
-// r must be RN(1/s).  q0 = RN(x*r) is within 2 ulp of x/s; one FMA residual +
-// one FMA correction lands on RN(x/s) (Markstein).  3 ops instead of the ~10 of
-// div.rn.f32.  The select keeps +-inf when x*r overflows.
-__device__ __forceinline__ float div_by(float x, float s, float r) {
+// r must be RN(1/s), s > 0.  q0 = RN(x*r) is within 2 ulp of x/s; one FMA residual +
+// one FMA correction lands on RN(x/s) (Markstein) -- 3 ops instead of the ~10 of
+// div.rn.f32.  The sign is re-applied from x (s > 0), which keeps -0 and tiny
+// negative quotients that round to zero on the right side; SAT_MAX > 0 also clamps
+// the magnitude (fminf drops the NaN that an overflowing x*r would produce, so the
+// result is the saturated value the reference's clamp gives).
+template <bool SAT>
+__device__ __forceinline__ float div_by(float x, float s, float r, float sat_max = 0.0f) {
   const float q0 = x * r;
   const float rem = fmaf(-q0, s, x);
-  const float q1 = fmaf(rem, r, q0);
-  return (fabsf(q0) <= 3.0e38f) ? q1 : q0;
+  float q1 = fabsf(fmaf(rem, r, q0));
+  if constexpr (SAT) q1 = fminf(q1, sat_max);
+  return copysignf(q1, x);
+}
+
+// x / C for a compile-time constant C > 0, correctly rounded (same Markstein step with
+// r = RN(1/C) folded at compile time).  Used for amax / fp8_max.
+template <int C_NUM>
+__device__ __forceinline__ float div_const(float x) {
+  constexpr float c = static_cast<float>(C_NUM);
+  constexpr float r = 1.0f / c;   // constant-folded by the host compiler: IEEE RN
+  const float q0 = x * r;
+  const float rem = fmaf(-q0, c, x);
+  return fmaf(rem, r, q0);
+}
+template <int Q>
+__device__ __forceinline__ float div_qmax(float x) {
+  if constexpr (Q == 0) return div_const<448>(x);
+  else if constexpr (Q == 1) return div_const<57344>(x);
+  else return div_const<127>(x);
 }
 
 // ---- UE8M0 helpers (exact, from the bit pattern) ----
@@ -259,6 +281,23 @@ __device__ __forceinline__ float seg_max(float v, int lanes) {
   for (int o = lanes >> 1; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
   return v;
 }
+template <int LANES>
+__device__ __forceinline__ float seg_max_c(float v) {
+#pragma unroll
+  for (int o = LANES >> 1; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+// runtime power-of-two lane count, dispatched to the unrolled versions
+__device__ __forceinline__ float seg_max_pow2(float v, int lanes_log2) {
+  switch (lanes_log2) {
+    case 0: return v;
+    case 1: return seg_max_c<2>(v);
+    case 2: return seg_max_c<4>(v);
+    case 3: return seg_max_c<8>(v);
+    case 4: return seg_max_c<16>(v);
+    default: return seg_max_c<32>(v);
+  }
+}
 // CTA-wide reductions; `scratch` is >= 33 floats of shared memory; all threads get the result.
 template <bool IS_MAX>
 __device__ __forceinline__ float block_reduce(float v, float* scratch) {
@@ -279,8 +318,12 @@ __device__ __forceinline__ float block_reduce(float v, float* scratch) {
 template <bool FAST>
 __device__ __forceinline__ float sigmoid_f32(float x) {
   if constexpr (FAST) {
-    const float e = exp2f(-x * 1.4426950408889634f);  // lowered to ex2.approx under -use_fast_math only
-    return __fdividef(1.0f, 1.0f + e);
+    float e, rc;
+    const float t = x * -1.4426950408889634f;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(t));
+    const float d = 1.0f + e;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(rc) : "f"(d));
+    return rc;
   } else {
     return __fdiv_rn(1.0f, 1.0f + expf(-x));
   }
@@ -288,10 +331,12 @@ __device__ __forceinline__ float sigmoid_f32(float x) {
 template <bool FAST>
 __device__ __forceinline__ float silu_f32(float x) {
   if constexpr (FAST) {
-    float e;
-    const float t = -x * 1.4426950408889634f;
+    float e, rc;
+    const float t = x * -1.4426950408889634f;
     asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(t));
-    return __fdividef(x, 1.0f + e);
+    const float d = 1.0f + e;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(rc) : "f"(d));
+    return x * rc;
   } else {
     return __fdiv_rn(x, 1.0f + expf(-x));
   }
