@@ -152,13 +152,24 @@ int vxk_silu_and_mul_mxfp4_quant(void* out, const void* in, float* scales, int64
  *      sB[k/gk, n/gn] at sB[kb*sb0 + nb*sb1].
  *   scale_dtype: VXK_S_F32 or VXK_S_E8M0 (block mode only).
  *   bias: nullable, [N], bias_dtype VXK_F32/F16/BF16.
+ *   workspace: device scratch of vxk_fp8_gemm_workspace_bytes(...) bytes (may be null when 0).
  */
 int vxk_fp8_gemm(void* D, const void* A, const void* B, const void* a_scale, const void* b_scale,
                  const void* bias, int64_t M, int64_t N, int64_t K, int64_t lda,
                  int64_t b_stride_k, int64_t b_stride_n, int64_t ldd, int a_scale_mode,
                  int b_scale_mode, int64_t group_k, int64_t group_n, int64_t sa0, int64_t sa1,
                  int64_t sb0, int64_t sb1, int scale_dtype, int fp8_dtype, int out_dtype,
-                 int bias_dtype, vxk_stream_t stream);
+                 int bias_dtype, void* workspace, int64_t workspace_bytes, vxk_stream_t stream);
+
+/* Scratch the caller must provide to vxk_fp8_gemm (device memory, any alignment); 0 when
+ * none is needed.  ref: the per-call scratchpad of fp8_gemm_w8a8.h:176-179. */
+int64_t vxk_fp8_gemm_workspace_bytes(int64_t M, int64_t N, int64_t K, int a_scale_mode, int scale_dtype);
+
+/* How many GEMM calls ran on the tcgen05 kernels / on the CUDA-core fallback so far. */
+void vxk_gemm_stats(uint64_t* tensor_core_calls, uint64_t* fallback_calls);
+/* Testing aid: route every GEMM to the CUDA-core fallback (also env VXK_GEMM_FORCE_FALLBACK=1).
+ * Returns the previous setting. */
+int vxk_set_gemm_force_fallback(int on);
 
 /* ---------------------------------------------------------------- a14 ---
  * ref: fp4_gemm  onednn_matmul.cpp:101-123 -> dnnl_matmul_w4a4_fp4

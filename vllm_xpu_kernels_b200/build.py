@@ -33,10 +33,10 @@ CU_SOURCES = {
     "quant_row_f16.cu": ["-fmad=false"],
     "quant_row_bf16.cu": ["-fmad=false"],
     "quant_flat.cu": ["-fmad=false"],
-    "gemm_fp8.cu": [],
-    "gemm_fp4.cu": [],
+    "gemm_fallback.cu": [],
+    "gemm_tc.cu": [],
 }
-HEADERS = ["vxk_common.cuh", "gemm_common.cuh", "quant_row_impl.cuh", os.path.join(ROOT, "include", "vxk_b200.h")]
+HEADERS = ["vxk_common.cuh", "gemm_common.cuh", "gemm_tc.cuh", "quant_row_impl.cuh", os.path.join(ROOT, "include", "vxk_b200.h")]
 
 
 def _digest(paths, extra=""):

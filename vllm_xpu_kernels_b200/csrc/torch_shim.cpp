@@ -529,10 +529,15 @@ Tensor fp8_gemm(const Tensor& A, const Tensor& B, std::optional<c10::ScalarType>
     bias = bias_->data_ptr();
     bias_dtype = bias_dtype_of(*bias_);
   }
+  // per-call scratch, like the reference's scratchpad tensor (fp8_gemm_w8a8.h:176-179)
+  const int64_t ws_bytes = vxk_fp8_gemm_workspace_bytes(r.M, N, K, a_mode, scale_dtype);
+  Tensor ws;
+  if (ws_bytes > 0) ws = at::empty({ws_bytes}, A.options().dtype(at::kByte));
   check_rc(vxk_fp8_gemm(result.data_ptr(), A.data_ptr(), B.data_ptr(), A_scale.data_ptr(), B_scale.data_ptr(),
                         bias, r.M, N, K, r.lda, B.stride(0), B.stride(1), r.ldd, a_mode, b_mode, gk, gn, sa0, sa1,
                         sb0, sb1, scale_dtype, a_st == at::kFloat8_e4m3fn ? VXK_Q_E4M3 : VXK_Q_E5M2,
-                        result.scalar_type() == at::kBFloat16 ? VXK_BF16 : VXK_F16, bias_dtype, cur_stream()),
+                        result.scalar_type() == at::kBFloat16 ? VXK_BF16 : VXK_F16, bias_dtype,
+                        ws_bytes > 0 ? ws.data_ptr() : nullptr, ws_bytes, cur_stream()),
            "fp8_gemm");
   return result;
 }
