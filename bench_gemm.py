@@ -1,0 +1,106 @@
+"""GEMM section of bench.py: FP8 W8A8 (per-token x per-channel) and MXFP4 scaled GEMMs on the
+Llama-3-70B shapes of the reference's benchmark table (benchmark/benchmark_gemm_onednn.py:88-116),
+column-parallel over the ranks (each rank owns W[n0:n1, :]), timed with CUDA events on the device.
+
+Reported per shape: whole-job TFLOP/s (2*M*N*K over the max-over-ranks time), the fraction of the
+dense tensor roofline (FP8 = 2x, FP4 = 4x the measured bf16 cuBLAS peak of MEASURED_PEAKS.json),
+and for one shape the time including the NCCL all-gather that reassembles the [M, N] output.
+"""
+from __future__ import annotations
+
+import ctypes
+
+import torch
+import torch.distributed as dist
+
+LLAMA70B_KN = [(8192, 10240), (8192, 8192), (8192, 57344), (28672, 8192)]
+E4 = torch.float8_e4m3fn
+E8 = torch.float8_e8m0fnu
+
+
+def _time(fn, steps, warmup=3):
+    for _ in range(warmup):
+        fn()
+    torch.cuda.synchronize()
+    s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    s.record()
+    for _ in range(steps):
+        fn()
+    e.record()
+    torch.cuda.synchronize()
+    return s.elapsed_time(e) / steps
+
+
+def bench_gemms(dev, rank, world, pk, steps=10, m_tokens=8192):
+    from vllm_xpu_kernels_b200 import _loader, ops, shard
+    lib = _loader.cdll()
+
+    def stats():
+        a, b = ctypes.c_uint64(), ctypes.c_uint64()
+        lib.vxk_gemm_stats(ctypes.byref(a), ctypes.byref(b))
+        return a.value, b.value
+
+    peak_fp8 = 2.0 * pk["bf16"]
+    peak_fp4 = 4.0 * pk["bf16"]
+    rows = []
+    torch.manual_seed(1234)
+    M = m_tokens
+    for (K, N) in LLAMA70B_KN:
+        n0, n1 = shard.column_shard(N, rank, world)
+        nloc = n1 - n0
+        for kind in ("fp8_w8a8", "mxfp4"):
+            if nloc == 0:
+                ms = 0.0
+            elif kind == "fp8_w8a8":
+                a = (torch.randn(M, K, device=dev) / 4).to(E4)
+                w = (torch.randn(nloc, K, device=dev) / 4).to(E4)
+                sa = torch.rand(M, 1, device=dev) * 0.01 + 0.001
+                sw = torch.rand(nloc, 1, device=dev) * 0.01 + 0.001
+                wt = w.t()
+                fn = lambda: torch.ops._xpu_C.fp8_gemm(a, wt, torch.bfloat16, sa, sw, None)  # noqa: E731
+                ms = _time(fn, steps)
+            else:
+                a = torch.randint(0, 256, (M, K // 2), dtype=torch.uint8, device=dev).view(torch.float4_e2m1fn_x2)
+                w = torch.randint(0, 256, (nloc, K // 2), dtype=torch.uint8, device=dev).view(torch.float4_e2m1fn_x2)
+                sa = torch.randint(118, 130, (M, K // 32), dtype=torch.uint8, device=dev).view(E8)
+                sw = torch.randint(118, 130, (nloc, K // 32), dtype=torch.uint8, device=dev).view(E8)
+                wt = w.t()
+                fn = lambda: torch.ops._xpu_C.fp4_gemm(a, wt, sa, sw, torch.bfloat16, None)  # noqa: E731
+                ms = _time(fn, steps)
+            t = torch.tensor([ms], dtype=torch.float64, device=dev)
+            if world > 1:
+                dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms_max = float(t.item())
+            tflops = 2.0 * M * N * K / (ms_max * 1e-3) / 1e12
+            peak = peak_fp8 if kind == "fp8_w8a8" else peak_fp4
+            rows.append({"kind": kind, "M": M, "N": N, "K": K, "n_per_gpu": nloc if world > 1 else N,
+                         "ms": ms_max, "tflops": tflops, "peak_tflops": peak * world,
+                         "frac_of_dense_peak": tflops / (peak * world)})
+            del a, w, sa, sw, wt
+            torch.cuda.empty_cache()
+
+    # reassembled output for one shape (gate_up of Llama-3-70B): GEMM + NCCL all-gather of the bf16 slabs
+    gather = None
+    if world > 1:
+        K, N = 8192, 57344
+        n0, n1 = shard.column_shard(N, rank, world)
+        a = (torch.randn(M, K, device=dev) / 4).to(E4)
+        w = (torch.randn(n1 - n0, K, device=dev) / 4).to(E4)
+        sa = torch.rand(M, 1, device=dev) * 0.01
+        sw = torch.rand(n1 - n0, 1, device=dev) * 0.01
+        wt = w.t()
+
+        def fn():
+            out = torch.ops._xpu_C.fp8_gemm(a, wt, torch.bfloat16, sa, sw, None)
+            return shard.all_gather_columns(out, N)
+
+        ms = _time(fn, max(2, steps // 2))
+        t = torch.tensor([ms], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        gather = {"shape": [M, N, K], "kind": "fp8_w8a8", "ms_gemm_plus_allgather": float(t.item()),
+                  "tflops_reassembled": 2.0 * M * N * K / (float(t.item()) * 1e-3) / 1e12}
+    tc, fb = stats()
+    best = max(rows, key=lambda r: r["frac_of_dense_peak"]) if rows else None
+    return {"shapes": "Llama-3-70B (K,N) x M=%d, N sharded over %d GPU(s)" % (M, world), "rows": rows,
+            "best": best, "reassembled": gather, "tensor_core_calls": tc, "fallback_calls": fb,
+            "peak_source": pk["src"] + " bf16 cuBLAS x2 (fp8) / x4 (fp4)"}

@@ -63,6 +63,9 @@ def _compile_cu(name, flags, force):
     tag = _digest([name] + HEADERS, " ".join(NVCC_COMMON + flags))
     obj = os.path.join(OBJDIR, f"{name}.{tag}.o")
     if force or not os.path.exists(obj):
+        for old in os.listdir(OBJDIR):          # drop stale objects of this source
+            if old.startswith(name + ".") and not old.startswith(f"{name}.{tag}."):
+                os.remove(os.path.join(OBJDIR, old))
         _run([NVCC] + NVCC_COMMON + flags + ["-c", src, "-o", obj], obj + ".log")
     return obj
 
