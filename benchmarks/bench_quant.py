@@ -40,6 +40,9 @@ def nsets(bytes_per_set):
     return max(2, min(16, int(300e6 // max(bytes_per_set, 1)) + 1))
 
 
+SCALE = 1.0
+
+
 def case(name, T, H):
     bf = torch.bfloat16
     if name == "dynamic_per_token_fp8":
@@ -95,19 +98,19 @@ def case(name, T, H):
     elif name == "silu_static_fp8":
         nb = T * H * 5
         def mk():
-            x = torch.randn(T, 2 * H, dtype=bf, device=DEV); o = torch.empty(T, H, dtype=E4, device=DEV)
+            x = torch.randn(T, 2 * H, dtype=bf, device=DEV) * SCALE; o = torch.empty(T, H, dtype=E4, device=DEV)
             s = torch.tensor([0.5], device=DEV)
             return lambda: torch.ops._C.silu_and_mul_quant(o, x, s)
     elif name == "silu_block_fp8_128":
         nb = T * H * 5 + 4 * T * H // 128
         def mk():
-            x = torch.randn(T, 2 * H, dtype=bf, device=DEV); o = torch.empty(T, H, dtype=E4, device=DEV)
+            x = torch.randn(T, 2 * H, dtype=bf, device=DEV) * SCALE; o = torch.empty(T, H, dtype=E4, device=DEV)
             s = torch.empty(T, H // 128, device=DEV)
             return lambda: torch.ops._C.silu_and_mul_per_block_quant(o, x, s, 128, None, False, False)
     elif name == "silu_mxfp4":
         nb = T * H * 4.5 + 4 * T * H // 32
         def mk():
-            x = torch.randn(T, 2 * H, dtype=bf, device=DEV); o = torch.empty(T, H // 2, dtype=torch.uint8, device=DEV)
+            x = torch.randn(T, 2 * H, dtype=bf, device=DEV) * SCALE; o = torch.empty(T, H // 2, dtype=torch.uint8, device=DEV)
             s = torch.empty(T, H // 32, device=DEV)
             return lambda: torch.ops._C.silu_and_mul_mxfp4_quant(o, x, s, 32, 1e-10)
     else:
@@ -123,7 +126,10 @@ def main():
     ap.add_argument("--silu-fast", type=int, default=1)
     ap.add_argument("--only", default=None, help="comma-separated op names")
     ap.add_argument("--T", type=int, default=None)
+    ap.add_argument("--scale", type=float, default=1.0, help="multiply the random inputs (activation magnitude)")
     args = ap.parse_args()
+    global SCALE
+    SCALE = args.scale
     peak = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"] \
         if os.path.exists(os.path.join(ROOT, "MEASURED_PEAKS.json")) else 6650.0
     _loader.cdll().vxk_set_silu_fast(args.silu_fast)

@@ -12,7 +12,7 @@ def report(name,out,ref):
     print(f"{name}: max abs {d.max():.4g} max rel {rel.max():.4g} mean abs {d.mean():.4g} ref absmean {ref.float().abs().mean():.4g} stats {stats()}", flush=True)
 torch.manual_seed(0)
 which=sys.argv[1] if len(sys.argv)>1 else "all"
-for (M,N,K) in ((128,128,128),(128,128,512),(256,384,1024),(100,200,2048),(8,512,2048),(1024,2048,2048)):
+for (M,N,K) in ((128,128,512),(100,200,2048),(1024,2048,2048),(2048,4224,1024),(1500,3000,1536)):
     a=torch.randn(M,K,dtype=torch.bfloat16)/10; w=torch.randn(N,K,dtype=torch.bfloat16)/10
     if which in ("all","f8"):
         aq,asc=oq.dynamic_per_token_scaled_fp8_quant(a,E4); wq,wsc=oq.dynamic_per_token_scaled_fp8_quant(w,E4)

@@ -160,12 +160,14 @@ extern "C" int vxk_fp8_gemm(void* D, const void* A, const void* B, const void* a
     canon_sf_kernel<<<blocks, 256, 0, st>>>(sfb, N, groups32, pitch, static_cast<const uint8_t*>(b_scale), group_n, sb1,
                                             group_k / 32, sb0);
     if ((rc = check_launch("canon_sfb"))) return rc;
-    tp.num_n_blocks = (int)((N + 127) / 128);
+    const bool wide = N >= 192 && (M * N) >= 148LL * 128 * 192;
+    const int bn = wide ? 192 : 128;
+    tp.num_n_blocks = (int)((N + bn - 1) / bn);
     if ((rc = make_map_2d_u8(&ma, A, K, M, lda, kBlockKBytes, kBlockM, true))) return rc;
-    if ((rc = make_map_2d_u8(&mb, B, K, N, b_stride_n, kBlockKBytes, 128, true))) return rc;
+    if ((rc = make_map_2d_u8(&mb, B, K, N, b_stride_n, kBlockKBytes, bn, true))) return rc;
     if ((rc = make_map_2d_u8(&msa, sfa, pitch, M, pitch, 16, kBlockM, false))) return rc;
-    if ((rc = make_map_2d_u8(&msb, sfb, pitch, N, pitch, 16, 128, false))) return rc;
-    return launch_tc<KIND_MXF8, 128>(tp, ma, mb, msa, msb, st);
+    if ((rc = make_map_2d_u8(&msb, sfb, pitch, N, pitch, 16, bn, false))) return rc;
+    return wide ? launch_tc<KIND_MXF8, 192>(tp, ma, mb, msa, msb, st) : launch_tc<KIND_MXF8, 128>(tp, ma, mb, msa, msb, st);
   }
   return launch_gemm_fallback(p, /*is_fp4=*/false, st);
 }
@@ -189,14 +191,16 @@ extern "C" int vxk_fp4_gemm(void* D, const void* A, const void* B, const void* a
   tp.D = D; tp.bias = bias; tp.M = (int)M; tp.N = (int)N; tp.K_bytes = (int)(K / 2); tp.ldd = ldd;
   tp.a_scale_mode = 2; tp.b_scale_mode = 2; tp.out_dtype = out_dtype; tp.bias_dtype = bias_dtype;
   tp.num_m_blocks = (int)((M + kBlockM - 1) / kBlockM);
-  tp.num_n_blocks = (int)((N + 127) / 128);
+  const bool wide = N >= 192 && (M * N) >= 148LL * 128 * 192;
+  const int bn = wide ? 192 : 128;
+  tp.num_n_blocks = (int)((N + bn - 1) / bn);
   tp.num_k_blocks = (int)((K / 2 + kBlockKBytes - 1) / kBlockKBytes);
   tp.vec_store_ok = aligned16(D) && (ldd * 2) % 16 == 0;
   CUtensorMap ma, mb, msa, msb;
   int rc;
   if ((rc = make_map_2d_u8(&ma, A, K / 2, M, lda_bytes, kBlockKBytes, kBlockM, true))) return rc;
-  if ((rc = make_map_2d_u8(&mb, B, K / 2, N, ldb_bytes, kBlockKBytes, 128, true))) return rc;
+  if ((rc = make_map_2d_u8(&mb, B, K / 2, N, ldb_bytes, kBlockKBytes, bn, true))) return rc;
   if ((rc = make_map_2d_u8(&msa, a_scale, K / 32, M, sa0, 16, kBlockM, false))) return rc;
-  if ((rc = make_map_2d_u8(&msb, b_scale, K / 32, N, sb0, 16, 128, false))) return rc;
-  return launch_tc<KIND_MXF4, 128>(tp, ma, mb, msa, msb, st);
+  if ((rc = make_map_2d_u8(&msb, b_scale, K / 32, N, sb0, 16, bn, false))) return rc;
+  return wide ? launch_tc<KIND_MXF4, 192>(tp, ma, mb, msa, msb, st) : launch_tc<KIND_MXF4, 128>(tp, ma, mb, msa, msb, st);
 }

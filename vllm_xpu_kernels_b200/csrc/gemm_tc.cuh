@@ -53,12 +53,13 @@ struct TcSmem {
   static constexpr int kABytes = kBlockM * kBlockKBytes;
   static constexpr int kBBytes = BLOCK_N * kBlockKBytes;
   static constexpr int kRawSfaBytes = kScaled ? kBlockM * 16 : 0;    // TMA box: 16 scale bytes per row
-  static constexpr int kRawSfbBytes = kScaled ? BLOCK_N * 16 : 0;
+  static constexpr int kNB = (BLOCK_N + 127) / 128;                  // 128-row scale blocks of the B tile
+  static constexpr int kRawSfbBytes = kScaled ? kNB * 128 * 16 : 0;  // sized for whole 128-row blocks
   static constexpr int kSfaTBytes = kScaled ? kSfWords * (kBlockM / 128) * 512 : 0;
-  static constexpr int kSfbTBytes = kScaled ? kSfWords * (BLOCK_N / 128) * 512 : 0;
+  static constexpr int kSfbTBytes = kScaled ? kSfWords * kNB * 512 : 0;
   static constexpr int kStageBytesRaw = kABytes + kBBytes + kRawSfaBytes + kRawSfbBytes + kSfaTBytes + kSfbTBytes;
   static constexpr int kStageBytes = (kStageBytesRaw + 1023) / 1024 * 1024;
-  static constexpr int kTxBytes = kABytes + kBBytes + kRawSfaBytes + kRawSfbBytes;
+  static constexpr int kTxBytes = kABytes + kBBytes + kRawSfaBytes + (kScaled ? BLOCK_N * 16 : 0);
   static constexpr int kStages = (200 * 1024) / kStageBytes > 8 ? 8 : (200 * 1024) / kStageBytes;
   static constexpr int kBarrierBytes = (3 * kStages + 4) * 8 + 16;
   static constexpr int kTotalBytes = kStages * kStageBytes + kBarrierBytes + 1024;  // + alignment slack
@@ -118,7 +119,8 @@ gemm_tc_kernel(const TcParams p, const __grid_constant__ CUtensorMap map_a, cons
   constexpr uint32_t kAccCols = BLOCK_N;                       // fp32 accumulator columns per buffer
   constexpr uint32_t kSfaCol = 2 * kAccCols;                   // SFA: kSfWords * 4 columns
   constexpr uint32_t kSfbCol = kSfaCol + 8;                    // SFB: kSfWords * 4 * (BLOCK_N/128) columns
-  static_assert(!kScaled || kSfbCol + 8 * (BLOCK_N / 128) <= kTmemCols, "TMEM budget");
+  constexpr int NB = L::kNB;
+  static_assert(!kScaled || kSfbCol + 8 * NB <= kTmemCols, "TMEM budget");
 
   const int num_tiles = p.num_m_blocks * p.num_n_blocks;
 
@@ -167,9 +169,9 @@ gemm_tc_kernel(const TcParams p, const __grid_constant__ CUtensorMap map_a, cons
             for (int w = 0; w < L::kSfWords; ++w) {
               utccp_32x128b_warpx4(tmem_base + kSfaCol + w * 4, make_sf_desc(smem_u32(stage_sfa_t(stage) + w * 512)));
 #pragma unroll
-              for (int j = 0; j < BLOCK_N / 128; ++j)
-                utccp_32x128b_warpx4(tmem_base + kSfbCol + (w * (BLOCK_N / 128) + j) * 4,
-                                     make_sf_desc(smem_u32(stage_sfb_t(stage) + (w * (BLOCK_N / 128) + j) * 512)));
+              for (int j = 0; j < NB; ++j)
+                utccp_32x128b_warpx4(tmem_base + kSfbCol + (w * NB + j) * 4,
+                                     make_sf_desc(smem_u32(stage_sfb_t(stage) + (w * NB + j) * 512)));
             }
           }
 #pragma unroll
@@ -187,7 +189,7 @@ gemm_tc_kernel(const TcParams p, const __grid_constant__ CUtensorMap map_a, cons
               // two SF bytes per row per MMA: bytes {0,1} or {2,3} of word k/2
               const uint32_t w = k >> 1, id = (k & 1) * 2;
               umma_mxf4(tmem_d, dak, dbk, idesc_with_sf_ids(idesc, id, id), acc, tmem_base + kSfaCol + w * 4,
-                        tmem_base + kSfbCol + w * (BLOCK_N / 128) * 4);
+                        tmem_base + kSfbCol + w * NB * 4);
             }
           }
           umma_commit(&empty_bar[stage]);                 // frees the ring slot when the MMAs retire
@@ -221,13 +223,13 @@ gemm_tc_kernel(const TcParams p, const __grid_constant__ CUtensorMap map_a, cons
             v.w = raw_a[(3 * 32 + lane) * 4 + wofs + w];
             out_a[w * 32 + lane] = v;
 #pragma unroll
-            for (int j = 0; j < BLOCK_N / 128; ++j) {
+            for (int j = 0; j < NB; ++j) {
               uint4 u;
               u.x = raw_b[(j * 128 + 0 * 32 + lane) * 4 + wofs + w];
               u.y = raw_b[(j * 128 + 1 * 32 + lane) * 4 + wofs + w];
               u.z = raw_b[(j * 128 + 2 * 32 + lane) * 4 + wofs + w];
               u.w = raw_b[(j * 128 + 3 * 32 + lane) * 4 + wofs + w];
-              out_b[(w * (BLOCK_N / 128) + j) * 32 + lane] = u;
+              out_b[(w * NB + j) * 32 + lane] = u;
             }
           }
           fence_proxy_async_smem();   // generic-proxy writes -> visible to tcgen05.cp (async proxy)

@@ -117,6 +117,11 @@ __device__ __forceinline__ void prologue(const RawV<T>& g, const RawV<T>& up, fl
   }
 }
 
+__device__ __noinline__ void slow_div8(const float (&v)[8], float s, float (&q)[8]) {
+#pragma unroll
+  for (int k = 0; k < 8; ++k) q[k] = __fdiv_rn(v[k], s);
+}
+
 // Tiles of (rpb rows) x (tx*U column vectors), persistent grid-stride over tiles; no
 // per-element integer division (one 32-bit division per tile).  All 128-bit loads of a
 // tile (U vectors, x2 for gate/up) are issued before the first use.  Like the row
@@ -214,11 +219,11 @@ __global__ void __launch_bounds__(256) flat_quant_kernel(const FlatParams p) {
           }
           const float r = __frcp_rn(s);
           if (leader) *sp = s;
-          if (!(r <= FLT_MAX)) {
+          if (__builtin_expect(!(r <= FLT_MAX), 0)) {
             // s is subnormal or zero (an all-zero / vanishing group): 1/s overflows, take the
-            // IEEE divide (0 / s = 0, matching the reference)
-#pragma unroll
-            for (int k = 0; k < 8; ++k) q[k] = __fdiv_rn(v[k], s);
+            // IEEE divide (0 / s = 0, matching the reference).  Out of line on purpose: inlined,
+            // the compiler predicates it and every vector pays for the eight divides.
+            slow_div8(v, s, q);
           } else if (Q != VXK_Q_INT8 && sat) {
 #pragma unroll
             for (int k = 0; k < 8; ++k) q[k] = div_by<true>(v[k], s, r, kQMax);
