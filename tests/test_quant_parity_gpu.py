@@ -531,6 +531,31 @@ def test_silu_modes_stay_within_the_bar(ops, fast, mag):
     assert ((u8(q4) != r4) & same4.repeat_interleave(16, dim=1)).float().mean().item() <= 2e-4
 
 
+@pytest.mark.parametrize("fast", [0, 1])
+def test_silu_extreme_gates(ops, fast):
+    """Gates far outside the sigmoid's useful range (exp overflow side) next to ordinary ones: scales and codes still match the reference."""
+    from vllm_xpu_kernels_b200 import _loader
+    lib = _loader.cdll()
+    seed()
+    x = torch.randn(64, 2 * 1024, dtype=torch.bfloat16)
+    x[:, 0:1024:7] = -60.0
+    x[:, 1:1024:7] = -90.0
+    x[:, 2:1024:11] = 100.0
+    x[3, :1024] = -80.0          # a whole row of vanishing silu values
+    rq, rs = quant.silu_and_mul_per_block_quant(x, 128, E4)
+    prev = lib.vxk_set_silu_fast(fast)
+    try:
+        q, s = ops.silu_and_mul_per_block_quant(x.to(DEV), 128, E4)
+    finally:
+        lib.vxk_set_silu_fast(prev)
+    live = rs > 1e-12            # groups whose scale is not the tiny-value floor
+    same = (s.cpu() == rs) | ~live
+    assert same.float().mean().item() >= 0.999
+    m = (same & live).repeat_interleave(128, dim=1)
+    assert_codes_close(u8(q)[m], u8(rq)[m], 5e-4, f"a11 extreme fast={fast}")
+    assert torch.isfinite(s).all()
+
+
 # ------------------------------------------------------------------ boundary behaviour
 def test_empty_inputs_and_errors(ops):
     x = torch.empty(0, 128, dtype=torch.bfloat16, device=DEV)

@@ -38,8 +38,7 @@ struct FlatParams {
   float eps;
   // thread -> (row-in-block, column) mapping: tx column threads, rpb rows per block
   int tx, rpb;
-  int ncb;               // column blocks per row = ceil(nvec / (tx * U))
-  unsigned tiles;        // ceil(T / rpb) * ncb
+  int ncb;               // column blocks per row = ceil(nvec / (tx * U)) = gridDim.y
 };
 
 // ---- packed 16-bit helpers (bf16x2 / half2 held in a 32-bit register) ----
@@ -84,14 +83,17 @@ __device__ __forceinline__ void raw_to_f32(const RawV<T>& r, float (&v)[8]) {
   }
 }
 
-// gate/up vectors -> the fp32 values to quantise.
+// gate/up vectors -> the fp32 values to quantise (v) and, for 16-bit T, the same values still
+// packed two per word (yw) -- the sign bits of the packed words patch the fp8 codes after an
+// exact division (see pack_q8_signed).
 //  PRO_SILU_T  : y = T(T(silu(gate)) * up)  -- the product and its rounding are one packed
 //                HMUL2 (a product of two 8/11-bit significands is exact before the rounding)
 //  PRO_SILU_F32: y = (gate * sigmoid(gate)) * up in fp32
-template <typename T, int PRO, bool FAST>
-__device__ __forceinline__ void prologue(const RawV<T>& g, const RawV<T>& up, float (&v)[8]) {
+template <typename T, int PRO, int FAST>
+__device__ __forceinline__ void prologue(const RawV<T>& g, const RawV<T>& up, float (&v)[8], uint32_t (&yw)[4]) {
   if constexpr (PRO == PRO_NONE) {
     raw_to_f32<T>(g, v);
+    if constexpr (sizeof(T) == 2) { yw[0] = g.a.x; yw[1] = g.a.y; yw[2] = g.a.z; yw[3] = g.a.w; }
   } else if constexpr (PRO == PRO_SILU_T && sizeof(T) == 2) {
     const uint32_t gw[4] = {g.a.x, g.a.y, g.a.z, g.a.w};
     const uint32_t uw[4] = {up.a.x, up.a.y, up.a.z, up.a.w};
@@ -100,7 +102,8 @@ __device__ __forceinline__ void prologue(const RawV<T>& g, const RawV<T>& up, fl
       const float2 f = Pair<T>::unpack(gw[i]);
       const typename Pair<T>::V s2 = Pair<T>::pack(silu_f32<FAST>(f.x), silu_f32<FAST>(f.y));
       const typename Pair<T>::V y2 = __hmul2(s2, *reinterpret_cast<const typename Pair<T>::V*>(&uw[i]));
-      const float2 y = Pair<T>::unpack(*reinterpret_cast<const uint32_t*>(&y2));
+      yw[i] = *reinterpret_cast<const uint32_t*>(&y2);
+      const float2 y = Pair<T>::unpack(yw[i]);
       v[2 * i] = y.x;
       v[2 * i + 1] = y.y;
     }
@@ -109,82 +112,124 @@ __device__ __forceinline__ void prologue(const RawV<T>& g, const RawV<T>& up, fl
     raw_to_f32<T>(g, v);
     raw_to_f32<T>(up, u);
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      if constexpr (PRO == PRO_SILU_T) v[j] = round_to<T>(round_to<T>(silu_f32<FAST>(v[j])) * u[j]);
-      else if constexpr (FAST) v[j] = silu_f32<true>(v[j]) * u[j];
-      else v[j] = (v[j] * __fdiv_rn(1.0f, 1.0f + expf(-v[j]))) * u[j];
+    for (int j = 0; j < 8; j += 2) {
+      if constexpr (PRO == PRO_SILU_T) {
+        v[j] = round_to<T>(round_to<T>(silu_f32<FAST>(v[j])) * u[j]);
+        v[j + 1] = round_to<T>(round_to<T>(silu_f32<FAST>(v[j + 1])) * u[j + 1]);
+      } else if constexpr (FAST) {
+        v[j] = silu_f32<1>(v[j]) * u[j];
+        v[j + 1] = silu_f32<1>(v[j + 1]) * u[j + 1];
+      } else {
+        v[j] = (v[j] * __fdiv_rn(1.0f, 1.0f + expf(-v[j]))) * u[j];
+        v[j + 1] = (v[j + 1] * __fdiv_rn(1.0f, 1.0f + expf(-v[j + 1]))) * u[j + 1];
+      }
     }
   }
 }
 
-__device__ __noinline__ void slow_div8(const float (&v)[8], float s, float (&q)[8]) {
+// IEEE x / s for the vanishing-group case (s subnormal or zero, 1/s overflows).  Out of line and
+// scalar on purpose: inlined, ptxas predicates the divide sequence into the hot path; by-reference
+// arrays would force the hot path's values through local memory.
+__device__ __noinline__ float slow_div(float x, float s) { return __fdiv_rn(x, s); }
+
+// eight exact quotients x/s (r = RN(1/s)) -> 8 fp8 codes.  Each quotient is the Markstein pair
+// q0 = RN(x*r), q = RN(q0 + RN(x - q0*s)*r); a zero quotient can come out with the wrong sign,
+// so the sign bits are taken from the packed 16-bit inputs (s > 0 => sign(x/s) = sign(x)):
+// one PRMT gathers the four high bytes, one LOP3 merges them under the 0x80808080 mask.
+template <int Q>
+__device__ __forceinline__ uint2 div_pack_fp8_signed(const float (&v)[8], const uint32_t (&yw)[4], float s, float r) {
+  float q[8];
 #pragma unroll
-  for (int k = 0; k < 8; ++k) q[k] = __fdiv_rn(v[k], s);
+  for (int k = 0; k < 8; ++k) {
+    const float q0 = v[k] * r;
+    const float rem = fmaf(-q0, s, v[k]);
+    q[k] = fmaf(rem, r, q0);
+  }
+  const uint2 c = pack_q8<Q>(q);
+  const uint32_t s_lo = __byte_perm(yw[0], yw[1], 0x7531), s_hi = __byte_perm(yw[2], yw[3], 0x7531);
+  return make_uint2(c.x ^ ((c.x ^ s_lo) & 0x80808080u), c.y ^ ((c.y ^ s_hi) & 0x80808080u));   // one LOP3 each
 }
 
-// Tiles of (rpb rows) x (tx*U column vectors), persistent grid-stride over tiles; no
-// per-element integer division (one 32-bit division per tile).  All 128-bit loads of a
-// tile (U vectors, x2 for gate/up) are issued before the first use.  Like the row
-// kernels these are instruction-issue bound on B200, so the body is kept minimal:
-// packed 16-bit multiply for silu*up, constant-divisor and reciprocal-based exact
-// divisions, unrolled segmented shuffles.
-template <typename T, int Q, int PRO, int FMT, bool FAST, int U>
+// Work decomposition: blockIdx.y picks a fixed block of U*tx column vectors, the CTA grid-strides
+// over row blocks of rpb rows (blockIdx.x).  Every per-thread column quantity (validity, scale
+// offset, leader flag) is loop-invariant and the three row pointers advance by a constant, so the
+// loop body is loads + arithmetic + stores only.  All 128-bit loads of an iteration (U vectors, x2
+// for gate/up) are issued before the first use.  These kernels are instruction-issue / XU-pipe
+// bound on B200 rather than HBM bound unless the body is kept minimal: packed 16-bit multiply for
+// silu*up, constant-divisor and reciprocal-based exact divisions, compile-time segmented shuffles.
+// LL = log2(lanes per group) or -1 (runtime p.lanes_log2).
+template <typename T, int Q, int PRO, int FMT, int FAST, int U, int LL>
 __global__ void __launch_bounds__(256) flat_quant_kernel(const FlatParams p) {
   constexpr float kQMax = QTraits<Q>::kMax;
   constexpr bool kGated = PRO != PRO_NONE;
-  const int ry = threadIdx.x / p.tx;            // once per thread
-  const int cx = threadIdx.x - ry * p.tx;
-  const int lanes_log2 = p.lanes_log2;
-  const int lane_mask = (1 << lanes_log2) - 1;
-  const bool sat = p.scale_in != nullptr;
-  float r_static = 0.0f;
-  if constexpr (FMT == FMT_STATIC) r_static = __frcp_rn(__ldg(p.scale_in));
-  const int64_t in_row = static_cast<int64_t>(p.nvec) * kVec * (kGated ? 2 : 1);
   constexpr int kOutVecBytes = (FMT == FMT_MXFP4) ? 4 : kVec;
+  constexpr bool kSignPatch = FMT == FMT_FP8_DIV && Q != VXK_Q_INT8 && sizeof(T) == 2;
+  const int tx = p.tx;
+  const int ry = threadIdx.x / tx;            // once per thread
+  const int cx = threadIdx.x - ry * tx;
+  const int ll = LL >= 0 ? LL : p.lanes_log2;
+  const int nvec = p.nvec;
+  const int c0 = blockIdx.y * (U * tx) + cx;
+  const bool sat = p.scale_in != nullptr;
+  float r_static = 0.0f, ub = 0.0f;
+  if constexpr (FMT == FMT_STATIC) r_static = __frcp_rn(__ldg(p.scale_in));
+  else if (sat) ub = __ldg(p.scale_in);
+  const int ue8m0 = p.ue8m0;
+  const float eps = p.eps;
 
-  for (unsigned tile = blockIdx.x; tile < p.tiles; tile += gridDim.x) {
-    const unsigned rb = tile / static_cast<unsigned>(p.ncb);
-    const int cb = static_cast<int>(tile - rb * p.ncb);
-    const int64_t t = static_cast<int64_t>(rb) * p.rpb + ry;
-    const int c0 = cb * U * p.tx + cx;
-    const bool row_ok = t < p.T;
-    const T* __restrict__ xrow = static_cast<const T*>(p.in) + t * in_row;
+  const int64_t in_row = static_cast<int64_t>(nvec) * kVec * (kGated ? 2 : 1);
+  int64_t t = static_cast<int64_t>(blockIdx.x) * p.rpb + ry;
+  const int64_t t_step = static_cast<int64_t>(gridDim.x) * p.rpb;
+  const T* __restrict__ gp = static_cast<const T*>(p.in) + t * in_row + static_cast<int64_t>(c0) * kVec;
+  uint8_t* op = static_cast<uint8_t*>(p.out) + (t * nvec + c0) * kOutVecBytes;
+  float* sp = p.scales + t * p.ss0;
+  const int64_t g_step = t_step * in_row, o_step = t_step * nvec * kOutVecBytes, s_step = t_step * p.ss0;
+  const int u_in = tx * kVec, u_out = tx * kOutVecBytes, up_ofs = nvec * kVec;
 
+  bool ok[U], leader[U];
+  int64_t s_ofs[U];
+#pragma unroll
+  for (int u = 0; u < U; ++u) {
+    const int c = c0 + u * tx;
+    ok[u] = c < nvec;
+    leader[u] = ok[u] && ((c & ((1 << ll) - 1)) == 0);
+    s_ofs[u] = static_cast<int64_t>(c >> ll) * p.ss1;
+  }
+
+  for (; t < p.T; t += t_step, gp += g_step, op += o_step, sp += s_step) {   // warp-uniform (tx % 32 == 0)
     RawV<T> g[U], up[kGated ? U : 1];
 #pragma unroll
     for (int u = 0; u < U; ++u) {
-      const int c = c0 + u * p.tx;
-      if (row_ok && c < p.nvec) {
-        g[u] = ldg_raw<T>(xrow + c * kVec);
-        if constexpr (kGated) up[u] = ldg_raw<T>(xrow + (p.nvec + c) * kVec);
+      if (ok[u]) {
+        g[u] = ldg_raw<T>(gp + u * u_in);
+        if constexpr (kGated) up[u] = ldg_raw<T>(gp + u * u_in + up_ofs);
       } else {
         g[u] = RawV<T>{};
         if constexpr (kGated) up[u] = RawV<T>{};
       }
     }
-    uint8_t* orow = static_cast<uint8_t*>(p.out) + t * p.nvec * kOutVecBytes;
-    float* srow = p.scales + t * p.ss0;
 #pragma unroll
     for (int u = 0; u < U; ++u) {
-      const int c = c0 + u * p.tx;
-      const bool valid = row_ok && c < p.nvec;
       float v[8], q[8];
-      prologue<T, PRO, FAST>(g[u], up[kGated ? u : 0], v);
+      uint32_t yw[4] = {0, 0, 0, 0};
+      prologue<T, PRO, FAST>(g[u], up[kGated ? u : 0], v, yw);
+      uint8_t* o = op + u * u_out;
       if constexpr (FMT == FMT_STATIC) {
 #pragma unroll
         for (int k = 0; k < 8; ++k) q[k] = v[k] * r_static;
-        if (valid) stg_stream(orow + c * kVec, pack_q8<Q>(q));
+        if (ok[u]) stg_stream(o, pack_q8<Q>(q));
       } else {
         float gmax = 0.0f;
 #pragma unroll
         for (int k = 0; k < 8; ++k) gmax = fmaxf(gmax, fabsf(v[k]));
-        gmax = seg_max_pow2(gmax, lanes_log2);   // every lane takes part (invalid ones carry 0)
-        const bool leader = valid && ((c & lane_mask) == 0);
-        float* sp = srow + (c >> lanes_log2) * p.ss1;
+        // every lane takes part (invalid ones carry 0)
+        if constexpr (LL >= 0) gmax = seg_max_c<(1 << (LL >= 0 ? LL : 0))>(gmax);
+        else gmax = seg_max(gmax, 1 << ll);
+        float* sq = sp + s_ofs[u];
         if constexpr (FMT == FMT_MXFP4) {
           const int e = rceil_e8m0(div_const<6>(gmax));
           const float d = e8m0_descale(e);
-          if (leader) *sp = e8m0_scale(e);
+          if (leader[u]) *sq = e8m0_scale(e);
 #pragma unroll
           for (int k = 0; k < 8; ++k) q[k] = fminf(fmaxf(v[k] * d, -6.0f), 6.0f);
           // bf16 inputs scaled by a power of two are already bf16 values; everything else
@@ -198,40 +243,46 @@ __global__ void __launch_bounds__(256) flat_quant_kernel(const FlatParams p) {
               q[k + 1] = bf16_hi(w);
             }
           }
-          if (valid) stg_stream(orow + c * 4, pack_e2m1x8(q));
+          if (ok[u]) stg_stream(o, pack_e2m1x8(q));
         } else if constexpr (FMT == FMT_MX8) {
           const int e = rceil_e8m0(div_qmax<Q>(gmax));
           const float d = e8m0_descale(e);
-          if (leader) *sp = e8m0_scale(e);
+          if (leader[u]) *sq = e8m0_scale(e);
 #pragma unroll
           for (int k = 0; k < 8; ++k) q[k] = v[k] * d;
-          if (valid) stg_stream(orow + c * kVec, pack_q8<Q>(q));
+          if (ok[u]) stg_stream(o, pack_q8<Q>(q));
         } else {
           float s;
           if constexpr (PRO == PRO_NONE) {
-            s = fmaxf(div_qmax<Q>(gmax), p.eps);            // a4: s = max(amax / qmax, eps)
+            s = fmaxf(div_qmax<Q>(gmax), eps);            // a4: s = max(amax / qmax, eps)
           } else if constexpr (Q == VXK_Q_INT8) {
             s = div_qmax<Q>(fmaxf(gmax, 1e-10f));
           } else {
             s = div_qmax<Q>(fmaxf(gmax, FLT_MIN));
-            if (sat) s = fminf(s, __ldg(p.scale_in));
-            if (p.ue8m0) s = exp2_ceil_log2(fmaxf(s, 1e-10f));
+            if (sat) s = fminf(s, ub);
+            if (ue8m0) s = exp2_ceil_log2(fmaxf(s, 1e-10f));
           }
           const float r = __frcp_rn(s);
-          if (leader) *sp = s;
+          if (leader[u]) *sq = s;
+          uint2 packed;
           if (__builtin_expect(!(r <= FLT_MAX), 0)) {
             // s is subnormal or zero (an all-zero / vanishing group): 1/s overflows, take the
-            // IEEE divide (0 / s = 0, matching the reference).  Out of line on purpose: inlined,
-            // the compiler predicates it and every vector pays for the eight divides.
-            slow_div8(v, s, q);
+            // IEEE divide (0 / s = 0, matching the reference)
+#pragma unroll
+            for (int k = 0; k < 8; ++k) q[k] = slow_div(v[k], s);
+            packed = pack_q8<Q>(q);
           } else if (Q != VXK_Q_INT8 && sat) {
 #pragma unroll
             for (int k = 0; k < 8; ++k) q[k] = div_by<true>(v[k], s, r, kQMax);
+            packed = pack_q8<Q>(q);
+          } else if constexpr (kSignPatch) {
+            packed = div_pack_fp8_signed<Q>(v, yw, s, r);
           } else {
 #pragma unroll
             for (int k = 0; k < 8; ++k) q[k] = div_by<false>(v[k], s, r);
+            packed = pack_q8<Q>(q);
           }
-          if (valid) stg_stream(orow + c * kVec, pack_q8<Q>(q));
+          if (ok[u]) stg_stream(o, packed);
         }
       }
     }
@@ -239,7 +290,7 @@ __global__ void __launch_bounds__(256) flat_quant_kernel(const FlatParams p) {
 }
 
 // Generic group kernel (any G that divides H, any alignment): one warp per group.
-template <typename T, int Q, int PRO, int FMT, bool FAST>
+template <typename T, int Q, int PRO, int FMT, int FAST>
 __global__ void __launch_bounds__(256) flat_quant_generic(const FlatParams p, int64_t H, int G,
                                                           int64_t num_groups) {
   constexpr float kQMax = QTraits<Q>::kMax;
@@ -254,7 +305,7 @@ __global__ void __launch_bounds__(256) flat_quant_generic(const FlatParams p, in
       const T* row = static_cast<const T*>(p.in) + t * 2 * H;
       const float g = to_f32<T>(row[h]), u = to_f32<T>(row[H + h]);
       if constexpr (PRO == PRO_SILU_T) return round_to<T>(round_to<T>(silu_f32<FAST>(g)) * u);
-      else if constexpr (FAST) return silu_f32<true>(g) * u;
+      else if constexpr (FAST) return silu_f32<1>(g) * u;
       else return (g * __fdiv_rn(1.0f, 1.0f + expf(-g))) * u;
     }
   };
@@ -413,10 +464,43 @@ static int flat_grid(int64_t work_items, int per_block) {
   return static_cast<int>(blocks < 1 ? 1 : (blocks < cap ? blocks : cap));
 }
 
+// resident CTAs per SM of one kernel instantiation (queried once per instantiation)
+template <typename K>
+static int resident_ctas(K kernel, int threads) {
+  int n = 0;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kernel, threads, 0) != cudaSuccess || n < 1) n = 1;
+  return n;
+}
+
+template <typename T, int Q, int PRO, int FMT, int FAST, int U, int LL>
+static void launch_flat_vec(const FlatParams& p, int64_t row_blocks, int ncb, int threads, cudaStream_t st) {
+  auto kernel = flat_quant_kernel<T, Q, PRO, FMT, FAST, U, LL>;
+  static thread_local int occ[9] = {0};       // by threads / 32
+  int& o = occ[threads / 32];
+  if (o == 0) o = resident_ctas(kernel, threads);
+  // one wave of resident CTAs: a CTA that only starts when another retires would run its whole
+  // share of the rows at a fraction of the machine
+  int64_t gx = static_cast<int64_t>(sm_count()) * o / ncb;
+  if (gx < 1) gx = 1;
+  if (gx > row_blocks) gx = row_blocks;
+  kernel<<<dim3(static_cast<unsigned>(gx), static_cast<unsigned>(ncb)), threads, 0, st>>>(p);
+}
+
+template <typename T, int Q, int PRO, int FMT, int FAST, int U>
+static void launch_flat_ll(const FlatParams& p, int64_t row_blocks, int ncb, int threads, cudaStream_t st) {
+  switch (p.lanes_log2) {   // the group sizes of the reference's kernels get unrolled shuffles
+    case 0: return launch_flat_vec<T, Q, PRO, FMT, FAST, U, 0>(p, row_blocks, ncb, threads, st);
+    case 2: return launch_flat_vec<T, Q, PRO, FMT, FAST, U, 2>(p, row_blocks, ncb, threads, st);
+    case 3: return launch_flat_vec<T, Q, PRO, FMT, FAST, U, 3>(p, row_blocks, ncb, threads, st);
+    case 4: return launch_flat_vec<T, Q, PRO, FMT, FAST, U, 4>(p, row_blocks, ncb, threads, st);
+    default: return launch_flat_vec<T, Q, PRO, FMT, FAST, U, -1>(p, row_blocks, ncb, threads, st);
+  }
+}
+
 template <typename T, int Q, int PRO, int FMT>
 static int launch_flat(FlatParams p, int64_t T_, int64_t H, int G, bool vec_ok, cudaStream_t st) {
   if (T_ == 0 || H == 0) return VXK_OK;
-  const bool fast = (PRO != PRO_NONE) && g_silu_fast.load(std::memory_order_relaxed) != 0;
+  const int mode = (PRO != PRO_NONE) ? g_silu_fast.load(std::memory_order_relaxed) : 0;
   p.T = T_;
   if (vec_ok) {
     constexpr int U = (PRO == PRO_NONE) ? 4 : 2;   // 4 x 16 B loads in flight per thread either way
@@ -424,25 +508,33 @@ static int launch_flat(FlatParams p, int64_t T_, int64_t H, int G, bool vec_ok, 
     const int lanes = G / kVec;
     p.lanes_log2 = 0;
     while ((1 << p.lanes_log2) < lanes) ++p.lanes_log2;
-    // columns per block: a multiple of 32 (and so of `lanes`); short rows share a block
-    int per_thread = (p.nvec + U - 1) / U;                   // column threads wanted for one row
-    p.tx = per_thread >= 256 ? 256 : (per_thread + 31) / 32 * 32;
+    // column threads per row: the multiple of 32 (hence of `lanes`) that leaves the fewest idle
+    // lanes in the last column block; short rows share a CTA (rpb rows per block)
+    int best_tx = 256;
+    double best_idle = 2.0;
+    for (int tx = 256; tx >= 32; tx -= 32) {
+      const int64_t cols = (static_cast<int64_t>(p.nvec) + tx * U - 1) / (tx * U) * (tx * U);
+      const double idle = static_cast<double>(cols - p.nvec) / static_cast<double>(cols);
+      if (idle < best_idle - 1e-9) { best_idle = idle; best_tx = tx; }
+    }
+    p.tx = best_tx;
     p.rpb = 256 / p.tx;
     p.ncb = (p.nvec + p.tx * U - 1) / (p.tx * U);
     const int64_t row_blocks = (T_ + p.rpb - 1) / p.rpb;
-    const int64_t tiles = row_blocks * p.ncb;
-    if (tiles > 0xffffffffLL) return fail(VXK_ERR_INVALID, "problem too large (%lld tiles)", (long long)tiles);
-    p.tiles = static_cast<unsigned>(tiles);
+    if (row_blocks > 0x7fffffffLL || p.ncb > 65535)
+      return fail(VXK_ERR_INVALID, "problem too large (%lld row blocks x %d column blocks)", (long long)row_blocks, p.ncb);
     const int threads = p.tx * p.rpb;
-    const int64_t cap = static_cast<int64_t>(sm_count()) * 8;
-    const unsigned grid = static_cast<unsigned>(tiles < cap ? tiles : cap);
-    if (fast) flat_quant_kernel<T, Q, PRO, FMT, (PRO != PRO_NONE), U><<<grid, threads, 0, st>>>(p);
-    else flat_quant_kernel<T, Q, PRO, FMT, false, U><<<grid, threads, 0, st>>>(p);
+    if constexpr (PRO == PRO_NONE) {
+      launch_flat_ll<T, Q, PRO, FMT, 0, U>(p, row_blocks, p.ncb, threads, st);
+    } else {
+      if (mode == 0) launch_flat_ll<T, Q, PRO, FMT, 0, U>(p, row_blocks, p.ncb, threads, st);
+      else launch_flat_ll<T, Q, PRO, FMT, 1, U>(p, row_blocks, p.ncb, threads, st);
+    }
   } else {
     const int64_t ngroups = T_ * (H / G);
     const int grid = flat_grid(ngroups, 8);
-    if (fast) flat_quant_generic<T, Q, PRO, FMT, (PRO != PRO_NONE)><<<grid, 256, 0, st>>>(p, H, G, ngroups);
-    else flat_quant_generic<T, Q, PRO, FMT, false><<<grid, 256, 0, st>>>(p, H, G, ngroups);
+    if (mode != 0) flat_quant_generic<T, Q, PRO, FMT, (PRO != PRO_NONE) ? 1 : 0><<<grid, 256, 0, st>>>(p, H, G, ngroups);
+    else flat_quant_generic<T, Q, PRO, FMT, 0><<<grid, 256, 0, st>>>(p, H, G, ngroups);
   }
   return check_launch("flat_quant");
 }

@@ -313,30 +313,24 @@ __device__ __forceinline__ float block_reduce(float v, float* scratch) {
 }
 
 // ---- silu ----
-// ACCURATE: expf (<= 2 ulp) and an IEEE divide, the same formula torch's CPU
-// kernels evaluate (x / (1 + exp(-x))).  FAST: ex2.approx / rcp.approx.
-template <bool FAST>
-__device__ __forceinline__ float sigmoid_f32(float x) {
-  if constexpr (FAST) {
-    float e, rc;
-    const float t = x * -1.4426950408889634f;
-    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(t));
-    const float d = 1.0f + e;
-    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(rc) : "f"(d));
-    return rc;
-  } else {
-    return __fdiv_rn(1.0f, 1.0f + expf(-x));
-  }
+// MODE 0 (accurate): expf (<= 2 ulp) and an IEEE divide, the same formula torch's CPU
+// kernels evaluate (x / (1 + exp(-x))).  MODE 1: ex2.approx / rcp.approx (about 2^-22
+// relative).  (Sharing one reciprocal between two elements to unload the XU pipe was
+// measured slower on B200: the kernels are issue-bound, not XU-bound.)
+__device__ __forceinline__ float ex2_approx(float t) {
+  float e;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(t));
+  return e;
 }
-template <bool FAST>
+__device__ __forceinline__ float rcp_approx(float d) {
+  float r;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(d));
+  return r;
+}
+template <int MODE>
 __device__ __forceinline__ float silu_f32(float x) {
-  if constexpr (FAST) {
-    float e, rc;
-    const float t = x * -1.4426950408889634f;
-    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(t));
-    const float d = 1.0f + e;
-    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(rc) : "f"(d));
-    return x * rc;
+  if constexpr (MODE != 0) {
+    return x * rcp_approx(1.0f + ex2_approx(x * -1.4426950408889634f));
   } else {
     return __fdiv_rn(x, 1.0f + expf(-x));
   }
