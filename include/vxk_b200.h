@@ -21,7 +21,7 @@
 extern "C" {
 #endif
 
-#define VXK_ABI_VERSION 1
+#define VXK_ABI_VERSION 2
 
 typedef struct CUstream_st* vxk_stream_t; /* == cudaStream_t */
 
@@ -179,11 +179,19 @@ int vxk_set_gemm_force_fallback(int on);
  *   B: W[N, K/2] packed bytes, row stride ldb_bytes (the op receives it as the
  *      transposed view [K/2, N]; only this K-major layout exists for FP4).
  *   sA: [M, K/32] e8m0 bytes at sA[m*sa0 + kb*sa1]; sB: [N, K/32] at sB[n*sb0 + kb*sb1].
+ *   workspace: device scratch of vxk_fp4_gemm_workspace_bytes(...) bytes (may be null).
  */
 int vxk_fp4_gemm(void* D, const void* A, const void* B, const void* a_scale, const void* b_scale,
                  const void* bias, int64_t M, int64_t N, int64_t K, int64_t lda_bytes,
                  int64_t ldb_bytes, int64_t ldd, int64_t sa0, int64_t sa1, int64_t sb0, int64_t sb1,
-                 int out_dtype, int bias_dtype, vxk_stream_t stream);
+                 int out_dtype, int bias_dtype, void* workspace, int64_t workspace_bytes,
+                 vxk_stream_t stream);
+
+/* Scratch the caller must provide to vxk_fp4_gemm (device memory, any alignment; the scale
+ * factors are re-packed there in the tensor core's layout); 0 when none is needed.  Without
+ * it the call still runs, on the single-CTA kernel.
+ * ref: the per-call scratchpad of fp4_gemm_w4a4.h:159-162. */
+int64_t vxk_fp4_gemm_workspace_bytes(int64_t M, int64_t N, int64_t K);
 
 #ifdef __cplusplus
 }

@@ -1,7 +1,7 @@
 // Host side of the scaled GEMMs: eligibility checks, TMA tensor maps, scale-factor
 // canonicalisation, launch of the tcgen05 kernels (gemm_tc.cuh) or of the CUDA-core
 // fallback (gemm_fallback.cu), and the two C-ABI entry points.
-#include "gemm_tc.cuh"
+#include "gemm_tc2.cuh"
 
 #include <mutex>
 
@@ -44,6 +44,23 @@ static int make_map_2d_u8(CUtensorMap* map, const void* base, uint64_t cols_byte
   return VXK_OK;
 }
 
+// packed scale-factor workspace: [chunks][128 words], box = `box_chunks` whole chunks
+static int make_map_sf_chunks(CUtensorMap* map, const void* base, uint64_t chunks, uint32_t box_chunks) {
+  EncodeTiledFn fn = encode_tiled_fn();
+  if (!fn) return fail(VXK_ERR_CUDA, "cuTensorMapEncodeTiled entry point not available");
+  const cuuint64_t dims[2] = {128, chunks};
+  const cuuint64_t strides[1] = {512};
+  const cuuint32_t box[2] = {128, box_chunks};
+  const cuuint32_t estr[2] = {1, 1};
+  const CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_UINT32, 2, const_cast<void*>(base), dims, strides, box, estr,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS)
+    return fail(VXK_ERR_CUDA, "cuTensorMapEncodeTiled failed (%d) for %llu scale-factor chunks", static_cast<int>(r),
+                (unsigned long long)chunks);
+  return VXK_OK;
+}
+
 // ---- scale-factor canonicalisation: any e8m0 block grid -> bytes [rows, pitch] per 32 K-elements ----
 __global__ void canon_sf_kernel(uint8_t* out, int64_t rows, int64_t groups32, int64_t pitch, const uint8_t* src,
                                 int64_t row_div, int64_t row_stride, int64_t k_per_scale32, int64_t k_stride) {
@@ -77,8 +94,145 @@ static int launch_tc(const TcParams& tp, const CUtensorMap& ma, const CUtensorMa
   return check_launch("gemm_tc");
 }
 
+// ---- scale-factor packing for the CTA-pair kernels ----
+// Any e8m0 scale grid -> chunks of 512 B in the layout tcgen05.cp.32x128b.warpx4 consumes:
+//   chunk (kb, blk, w) = [32 lanes][4 words], word (lane, c) = the four scale bytes of row
+//   blk*128 + c*32 + lane for the 32-element K groups kb*G + 4w .. 4w+3   (G groups per K slice)
+// ordered [kb][blk][w] so that the chunks of consecutive 128-row blocks of one K slice are
+// contiguous (one TMA box per operand per stage).  Rows / groups outside the tensor pack as 0.
+__global__ void sf_pack_kernel(uint32_t* out, int64_t rows, int64_t groups32, int num_kb, int nblk, int sf_words,
+                               const uint8_t* src, int64_t row_div, int64_t row_stride, int64_t k_per_scale32,
+                               int64_t k_stride, int word_loads) {
+  const int64_t total = static_cast<int64_t>(num_kb) * nblk * sf_words * 128;
+  const int groups_per_kb = sf_words * 4;
+  for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+    const int c = static_cast<int>(i & 3), lane = static_cast<int>((i >> 2) & 31);
+    const int64_t chunk = i >> 7;
+    const int w = static_cast<int>(chunk % sf_words);
+    const int64_t t = chunk / sf_words;
+    const int blk = static_cast<int>(t % nblk);
+    const int64_t kb = t / nblk;
+    const int64_t row = static_cast<int64_t>(blk) * 128 + c * 32 + lane;
+    const int64_t g0 = kb * groups_per_kb + w * 4;
+    uint32_t v = 0;
+    if (row < rows && g0 < groups32) {
+      const uint8_t* rp = src + (row / row_div) * row_stride;
+      if (word_loads && g0 + 4 <= groups32) {
+        v = *reinterpret_cast<const uint32_t*>(rp + g0);
+      } else {
+#pragma unroll
+        for (int b = 0; b < 4; ++b)
+          if (g0 + b < groups32) v |= static_cast<uint32_t>(rp[((g0 + b) / k_per_scale32) * k_stride]) << (8 * b);
+      }
+    }
+    out[i] = v;
+  }
+}
+
+struct SfPack {
+  int num_kb, sf_words, a_blocks, b_blocks;
+  int64_t a_bytes, b_bytes;
+};
+static SfPack sf_pack_plan(int64_t M, int64_t N, int64_t K_elems, bool fp4) {
+  SfPack s;
+  const int64_t elems_per_kb = fp4 ? 2 * kBlockKBytes : kBlockKBytes;
+  s.num_kb = static_cast<int>((K_elems + elems_per_kb - 1) / elems_per_kb);
+  s.sf_words = fp4 ? 2 : 1;
+  s.a_blocks = static_cast<int>((M + 127) / 128) + 1;     // +1: a tile's second block never leaves the grid
+  s.b_blocks = static_cast<int>((N + 127) / 128) + 2;
+  s.a_bytes = static_cast<int64_t>(s.num_kb) * s.a_blocks * s.sf_words * 512;
+  s.b_bytes = static_cast<int64_t>(s.num_kb) * s.b_blocks * s.sf_words * 512;
+  return s;
+}
+
+static int max_cluster_pairs(const void* kernel, int smem_bytes) {
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(2 * sm_count());
+  cfg.blockDim = dim3(kTc2Threads);
+  cfg.dynamicSmemBytes = smem_bytes;
+  cudaLaunchAttribute attr{};
+  attr.id = cudaLaunchAttributeClusterDimension;
+  attr.val.clusterDim.x = 2; attr.val.clusterDim.y = 1; attr.val.clusterDim.z = 1;
+  cfg.attrs = &attr;
+  cfg.numAttrs = 1;
+  int n = 0;
+  if (cudaOccupancyMaxActiveClusters(&n, kernel, &cfg) != cudaSuccess || n < 1) {
+    cudaGetLastError();
+    n = sm_count() / 2;
+  }
+  return n;
+}
+
+static int env_int(const char* name, int dflt) {
+  const char* e = getenv(name);
+  return e ? atoi(e) : dflt;
+}
+
+static int pair_count_hint() {   // SM pairs a cluster launch can keep resident (all TPCs on B200)
+  return sm_count() / 2;
+}
+
+template <int KIND, int BLOCK_N, int NACC>
+static int launch_tc2(Tc2Params tp, const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& msa,
+                      const CUtensorMap& msb, cudaStream_t st) {
+  using L = Tc2Smem<KIND, BLOCK_N, NACC>;
+  auto kernel = gemm_tc2_kernel<KIND, BLOCK_N, NACC>;
+  static std::once_flag once;
+  static cudaError_t attr_err = cudaSuccess;
+  static int pairs = 0;
+  std::call_once(once, [&] {
+    attr_err = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotalBytes);
+    if (attr_err == cudaSuccess) pairs = max_cluster_pairs(reinterpret_cast<const void*>(kernel), L::kTotalBytes);
+  });
+  if (attr_err != cudaSuccess)
+    return fail(VXK_ERR_CUDA, "cudaFuncSetAttribute(smem=%d): %s", L::kTotalBytes, cudaGetErrorString(attr_err));
+  static const int dbg = env_int("VXK_GEMM_DEBUG", 0);
+  static const int group_m = env_int("VXK_GEMM_GROUP_M", 8);
+  tp.b.debug = dbg;   // bring-up / timing switches: 1 skip tcgen05.cp, 8 skip scale-factor TMA
+  tp.group_m = group_m < 1 ? 1 : group_m;
+  const int tiles = tp.num_m_pairs * tp.num_n_blocks;
+  const int grid = 2 * (tiles < pairs ? tiles : pairs);
+  kernel<<<grid, kTc2Threads, L::kTotalBytes, st>>>(tp, ma, mb, msa, msb);
+  g_gemm_tc_calls.fetch_add(1, std::memory_order_relaxed);
+  return check_launch("gemm_tc2");
+}
+
+// Two W tiles per K loop (NACC = 2) cut the L2 bytes per flop by a quarter but quantise the
+// work into tiles twice as large and expose part of the epilogue: take them when the last
+// wave of super-tiles is not much emptier than the last wave of single tiles.
+static bool prefer_two_acc(int64_t M, int64_t N, int bn) {
+  static const int forced = env_int("VXK_GEMM_NACC", 0);
+  if (forced == 1 || forced == 2) return forced == 2;
+  const int64_t pairs = pair_count_hint();
+  const int64_t mt = (M + 255) / 256;
+  const int64_t t1 = mt * ((N + bn - 1) / bn), t2 = mt * ((N + 2 * bn - 1) / (2 * bn));
+  const double c1 = static_cast<double>((t1 + pairs - 1) / pairs) * bn;
+  const double c2 = static_cast<double>((t2 + pairs - 1) / pairs) * 2 * bn * 0.85;
+  return c2 <= c1;
+}
+
+// Tile-shape choice by a wave count model: per-SM time of one tile ~ rows x cols handled by
+// the SM, weighted by how well the shape feeds the tensor core (shared-memory / L2 bytes per
+// MMA).  1-CTA 128 x bn1 tiles over all SMs against 256 x bn2 pair tiles over SM pairs.
+static bool prefer_pair(int64_t M, int64_t N, int bn1, int bn2) {
+  if (M <= 128) return false;
+  const int64_t sms = sm_count();
+  const int64_t t1 = ((M + 127) / 128) * ((N + bn1 - 1) / bn1);
+  const int64_t t2 = ((M + 255) / 256) * ((N + bn2 - 1) / bn2);
+  const double c1 = static_cast<double>((t1 + sms - 1) / sms) * 128.0 * bn1 * (bn1 >= 256 ? 1.20 : 1.35);
+  const double c2 = static_cast<double>((t2 + sms / 2 - 1) / (sms / 2)) * 128.0 * bn2;
+  return c2 <= c1;
+}
+
 static bool tma_ok(const void* base, int64_t pitch_bytes) {
   return aligned16(base) && pitch_bytes % 16 == 0 && pitch_bytes > 0;
+}
+
+// testing / profiling aid: VXK_GEMM_SINGLE_CTA=1 keeps every GEMM on the single-CTA kernels
+static bool force_single() {
+  static const bool v = [] { const char* e = getenv("VXK_GEMM_SINGLE_CTA"); return e && e[0] == '1'; }();
+  return v;
 }
 
 static int g_force_fallback = -1;
@@ -88,6 +242,50 @@ static bool force_fallback() {
     g_force_fallback = (e && e[0] == '1') ? 1 : 0;
   }
   return g_force_fallback == 1;
+}
+
+// Packs both scale grids into `workspace` and launches the CTA-pair block-scaled kernel.
+// a_* / b_*: addressing of the source grids as in sf_pack_kernel (row_div, row_stride, K groups
+// per scale, K stride).
+template <int KIND>
+static int run_pair_block_scaled(Tc2Params tp, const void* A, int64_t lda_bytes, const void* B, int64_t ldb_bytes,
+                                 int64_t M, int64_t N, int64_t K_elems, const uint8_t* a_scale, int64_t a_row_stride,
+                                 int64_t a_kps, int64_t a_k_stride, const uint8_t* b_scale, int64_t b_row_div,
+                                 int64_t b_row_stride, int64_t b_kps, int64_t b_k_stride, void* workspace,
+                                 cudaStream_t st) {
+  constexpr bool fp4 = KIND == KIND_MXF4;
+  constexpr int BN = 192;
+  const SfPack sp = sf_pack_plan(M, N, K_elems, fp4);
+  uint8_t* ws = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(workspace) + 255) & ~uintptr_t(255));
+  uint32_t* sfa = reinterpret_cast<uint32_t*>(ws);
+  uint32_t* sfb = reinterpret_cast<uint32_t*>(ws + sp.a_bytes);
+  const int64_t groups32 = (K_elems + 31) / 32;
+  const int blocks = 8 * sm_count();
+  const int a_words = a_kps == 1 && a_k_stride == 1 && a_row_stride % 4 == 0 && reinterpret_cast<uintptr_t>(a_scale) % 4 == 0;
+  const int b_words = b_kps == 1 && b_k_stride == 1 && b_row_stride % 4 == 0 && reinterpret_cast<uintptr_t>(b_scale) % 4 == 0;
+  int rc;
+  sf_pack_kernel<<<blocks, 256, 0, st>>>(sfa, M, groups32, sp.num_kb, sp.a_blocks, sp.sf_words, a_scale, 1,
+                                         a_row_stride, a_kps, a_k_stride, a_words);
+  if ((rc = check_launch("sf_pack_a"))) return rc;
+  sf_pack_kernel<<<blocks, 256, 0, st>>>(sfb, N, groups32, sp.num_kb, sp.b_blocks, sp.sf_words, b_scale, b_row_div,
+                                         b_row_stride, b_kps, b_k_stride, b_words);
+  if ((rc = check_launch("sf_pack_b"))) return rc;
+  const bool two = prefer_two_acc(M, N, BN);
+  const int tile_n = two ? 2 * BN : BN;
+  tp.num_m_pairs = static_cast<int>((M + 255) / 256);
+  tp.num_n_blocks = static_cast<int>((N + tile_n - 1) / tile_n);
+  tp.sfa_blocks = sp.a_blocks;
+  tp.sfb_blocks = sp.b_blocks;
+  const uint64_t kbytes = fp4 ? K_elems / 2 : K_elems;
+  CUtensorMap ma, mb, msa, msb;
+  if ((rc = make_map_2d_u8(&ma, A, kbytes, M, lda_bytes, kBlockKBytes, kBlockM, true))) return rc;
+  if ((rc = make_map_2d_u8(&mb, B, kbytes, N, ldb_bytes, kBlockKBytes, BN / 2, true))) return rc;
+  if ((rc = make_map_sf_chunks(&msa, sfa, static_cast<uint64_t>(sp.num_kb) * sp.a_blocks * sp.sf_words, sp.sf_words)))
+    return rc;
+  if ((rc = make_map_sf_chunks(&msb, sfb, static_cast<uint64_t>(sp.num_kb) * sp.b_blocks * sp.sf_words,
+                               (two ? Tc2Smem<KIND, BN, 2>::kSfbBlocks : 2) * sp.sf_words)))
+    return rc;
+  return two ? launch_tc2<KIND, BN, 2>(tp, ma, mb, msa, msb, st) : launch_tc2<KIND, BN, 1>(tp, ma, mb, msa, msb, st);
 }
 
 }  // namespace vxk
@@ -103,7 +301,16 @@ extern "C" int vxk_set_gemm_force_fallback(int on) {
 extern "C" int64_t vxk_fp8_gemm_workspace_bytes(int64_t M, int64_t N, int64_t K, int a_scale_mode, int scale_dtype) {
   if (a_scale_mode != 2 || scale_dtype != VXK_S_E8M0) return 0;
   const int64_t pitch = ((K + 31) / 32 + 15) / 16 * 16;
-  return (M + N) * pitch + 256;
+  const int64_t single = (M + N) * pitch + 256;
+  const SfPack sp = sf_pack_plan(M, N, K, false);
+  const int64_t pair = sp.a_bytes + sp.b_bytes + 512;
+  return single > pair ? single : pair;
+}
+
+extern "C" int64_t vxk_fp4_gemm_workspace_bytes(int64_t M, int64_t N, int64_t K) {
+  if (M <= 128) return 0;   // single-CTA kernel reads the caller's scale tensors directly
+  const SfPack sp = sf_pack_plan(M, N, K, true);
+  return sp.a_bytes + sp.b_bytes + 512;
 }
 
 extern "C" int vxk_fp8_gemm(void* D, const void* A, const void* B, const void* a_scale, const void* b_scale,
@@ -140,6 +347,17 @@ extern "C" int vxk_fp8_gemm(void* D, const void* A, const void* B, const void* a
     tp.b_scale = static_cast<const float*>(b_scale);
     const bool wide = N >= 256 && (M * N) >= 148LL * 128 * 256;   // enough tiles to fill the SMs at 128x256
     const int bn = wide ? 256 : 128;
+    if (!force_single() && prefer_pair(M, N, bn, 256)) {
+      Tc2Params t2{};
+      t2.b = tp;
+      const bool two = prefer_two_acc(M, N, 256);
+      t2.num_m_pairs = (int)((M + 255) / 256);
+      t2.num_n_blocks = (int)((N + (two ? 511 : 255)) / (two ? 512 : 256));
+      if ((rc = make_map_2d_u8(&ma, A, K, M, lda, kBlockKBytes, kBlockM, true))) return rc;
+      if ((rc = make_map_2d_u8(&mb, B, K, N, b_stride_n, kBlockKBytes, 128, true))) return rc;
+      return two ? launch_tc2<KIND_F8, 256, 2>(t2, ma, mb, msa, msb, st)
+                 : launch_tc2<KIND_F8, 256, 1>(t2, ma, mb, msa, msb, st);
+    }
     tp.num_n_blocks = (int)((N + bn - 1) / bn);
     if ((rc = make_map_2d_u8(&ma, A, K, M, lda, kBlockKBytes, kBlockM, true))) return rc;
     if ((rc = make_map_2d_u8(&mb, B, K, N, b_stride_n, kBlockKBytes, bn, true))) return rc;
@@ -147,6 +365,13 @@ extern "C" int vxk_fp8_gemm(void* D, const void* A, const void* B, const void* a
   }
   if (operands_ok && a_scale_mode == 2 && scale_dtype == VXK_S_E8M0 && group_k % 32 == 0 && workspace &&
       workspace_bytes >= vxk_fp8_gemm_workspace_bytes(M, N, K, a_scale_mode, scale_dtype)) {
+    if (!force_single() && prefer_pair(M, N, N >= 192 ? 192 : 128, 192)) {
+      Tc2Params t2{};
+      t2.b = tp;
+      return run_pair_block_scaled<KIND_MXF8>(t2, A, lda, B, b_stride_n, M, N, K, static_cast<const uint8_t*>(a_scale),
+                                              sa0, group_k / 32, sa1, static_cast<const uint8_t*>(b_scale), group_n,
+                                              sb1, group_k / 32, sb0, workspace, st);
+    }
     // native block-scaled MMA: expand the scale grids to one byte per (row, 32 K-elements)
     const int64_t groups32 = (K + 31) / 32, pitch = (groups32 + 15) / 16 * 16;
     uint8_t* ws = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(workspace) + 255) & ~uintptr_t(255));
@@ -175,7 +400,7 @@ extern "C" int vxk_fp8_gemm(void* D, const void* A, const void* B, const void* a
 extern "C" int vxk_fp4_gemm(void* D, const void* A, const void* B, const void* a_scale, const void* b_scale,
                             const void* bias, int64_t M, int64_t N, int64_t K, int64_t lda_bytes, int64_t ldb_bytes,
                             int64_t ldd, int64_t sa0, int64_t sa1, int64_t sb0, int64_t sb1, int out_dtype,
-                            int bias_dtype, vxk_stream_t stream) {
+                            int bias_dtype, void* workspace, int64_t workspace_bytes, vxk_stream_t stream) {
   VXK_REQUIRE(M >= 0 && N >= 0 && K >= 0, "negative shape");
   VXK_REQUIRE(K % 32 == 0, "K must be a multiple of the MX block (32)");
   VXK_REQUIRE(out_dtype == VXK_BF16 || out_dtype == VXK_F16, "output must be bf16 or f16");
@@ -196,6 +421,14 @@ extern "C" int vxk_fp4_gemm(void* D, const void* A, const void* B, const void* a
   tp.num_n_blocks = (int)((N + bn - 1) / bn);
   tp.num_k_blocks = (int)((K / 2 + kBlockKBytes - 1) / kBlockKBytes);
   tp.vec_store_ok = aligned16(D) && (ldd * 2) % 16 == 0;
+  if (!force_single() && prefer_pair(M, N, bn, 192) && workspace &&
+      workspace_bytes >= vxk_fp4_gemm_workspace_bytes(M, N, K)) {
+    Tc2Params t2{};
+    t2.b = tp;
+    return run_pair_block_scaled<KIND_MXF4>(t2, A, lda_bytes, B, ldb_bytes, M, N, K,
+                                            static_cast<const uint8_t*>(a_scale), sa0, 1, sa1,
+                                            static_cast<const uint8_t*>(b_scale), 1, sb0, 1, sb1, workspace, st);
+  }
   CUtensorMap ma, mb, msa, msb;
   int rc;
   if ((rc = make_map_2d_u8(&ma, A, K / 2, M, lda_bytes, kBlockKBytes, kBlockM, true))) return rc;

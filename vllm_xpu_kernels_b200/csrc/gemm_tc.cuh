@@ -45,6 +45,63 @@ struct TcParams {
   int debug;              // bring-up switches (env VXK_GEMM_DEBUG): 1 skip tcgen05.cp, 2 plain MMA, 4 skip re-tiler
 };
 
+// One thread's 32 consecutive accumulator columns of output row m: scales, bias, conversion
+// to bf16 / f16 and the stores (128-bit when the row is 16-byte aligned and the chunk is whole).
+// Every array index is a compile-time constant (no local memory).
+__device__ __forceinline__ void epilogue_store_32(const TcParams& p, const uint32_t (&r)[32], int m, int nbase,
+                                                  float row_scale, bool per_col) {
+  float v[32];
+  const bool whole = nbase + 32 <= p.N;
+#pragma unroll
+  for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]) * row_scale;
+  if (per_col) {
+    if (whole && (reinterpret_cast<uintptr_t>(p.b_scale) & 15) == 0) {   // nbase % 32 == 0: 128-bit broadcast loads
+      const float4* s4 = reinterpret_cast<const float4*>(p.b_scale + nbase);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const float4 s = __ldg(s4 + j);
+        v[4 * j] *= s.x; v[4 * j + 1] *= s.y; v[4 * j + 2] *= s.z; v[4 * j + 3] *= s.w;
+      }
+    } else {
+#pragma unroll
+      for (int j = 0; j < 32; ++j)
+        if (nbase + j < p.N) v[j] *= __ldg(p.b_scale + nbase + j);
+    }
+  }
+  if (p.bias) {
+#pragma unroll
+    for (int j = 0; j < 32; ++j) {
+      const int n = nbase + j;
+      if (n < p.N)
+        v[j] += (p.bias_dtype == VXK_F32)   ? __ldg(static_cast<const float*>(p.bias) + n)
+                : (p.bias_dtype == VXK_F16) ? __half2float(static_cast<const __half*>(p.bias)[n])
+                                            : __bfloat162float(static_cast<const __nv_bfloat16*>(p.bias)[n]);
+    }
+  }
+  uint16_t* drow = static_cast<uint16_t*>(p.D) + static_cast<int64_t>(m) * p.ldd + nbase;
+  const bool bf = p.out_dtype == VXK_BF16;
+  uint32_t w[16];
+#pragma unroll
+  for (int t = 0; t < 16; ++t) {
+    if (bf) {
+      __nv_bfloat162 h = __floats2bfloat162_rn(v[2 * t], v[2 * t + 1]);
+      w[t] = *reinterpret_cast<uint32_t*>(&h);
+    } else {
+      __half2 h = __floats2half2_rn(v[2 * t], v[2 * t + 1]);
+      w[t] = *reinterpret_cast<uint32_t*>(&h);
+    }
+  }
+  if (p.vec_store_ok && whole) {
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+      *reinterpret_cast<uint4*>(drow + 8 * j) = make_uint4(w[4 * j], w[4 * j + 1], w[4 * j + 2], w[4 * j + 3]);
+  } else {
+#pragma unroll
+    for (int j = 0; j < 32; ++j)
+      if (nbase + j < p.N) drow[j] = static_cast<uint16_t>(j & 1 ? w[j >> 1] >> 16 : w[j >> 1] & 0xffffu);
+  }
+}
+
 template <int KIND, int BLOCK_N>
 struct TcSmem {
   static constexpr int kScaled = KIND != KIND_F8;
@@ -265,51 +322,7 @@ gemm_tc_kernel(const TcParams p, const __grid_constant__ CUtensorMap map_a, cons
         tmem_ld_32x32b_x32(taddr, r);
         tmem_ld_wait();
         const int nbase = n0 + c * 32;
-        if (m < p.M && nbase < p.N) {
-          float v[32];
-#pragma unroll
-          for (int j = 0; j < 32; ++j) {
-            float x = __uint_as_float(r[j]) * row_scale;
-            const int n = nbase + j;
-            if (n < p.N) {
-              if (per_col) x *= __ldg(p.b_scale + n);
-              if (p.bias) {
-                x += (p.bias_dtype == VXK_F32)   ? __ldg(static_cast<const float*>(p.bias) + n)
-                     : (p.bias_dtype == VXK_F16) ? __half2float(static_cast<const __half*>(p.bias)[n])
-                                                 : __bfloat162float(static_cast<const __nv_bfloat16*>(p.bias)[n]);
-              }
-            }
-            v[j] = x;
-          }
-          uint16_t* drow = static_cast<uint16_t*>(p.D) + static_cast<int64_t>(m) * p.ldd + nbase;
-          if (p.vec_store_ok && nbase + 32 <= p.N) {
-#pragma unroll
-            for (int j = 0; j < 32; j += 8) {
-              uint32_t w[4];
-#pragma unroll
-              for (int t = 0; t < 4; ++t) {
-                if (p.out_dtype == VXK_BF16) {
-                  __nv_bfloat162 h = __floats2bfloat162_rn(v[j + 2 * t], v[j + 2 * t + 1]);
-                  w[t] = *reinterpret_cast<uint32_t*>(&h);
-                } else {
-                  __half2 h = __floats2half2_rn(v[j + 2 * t], v[j + 2 * t + 1]);
-                  w[t] = *reinterpret_cast<uint32_t*>(&h);
-                }
-              }
-              *reinterpret_cast<uint4*>(drow + j) = make_uint4(w[0], w[1], w[2], w[3]);
-            }
-          } else {
-            for (int j = 0; j < 32 && nbase + j < p.N; ++j) {
-              if (p.out_dtype == VXK_BF16) {
-                __nv_bfloat16 h = __float2bfloat16_rn(v[j]);
-                drow[j] = *reinterpret_cast<uint16_t*>(&h);
-              } else {
-                __half h = __float2half_rn(v[j]);
-                drow[j] = *reinterpret_cast<uint16_t*>(&h);
-              }
-            }
-          }
-        }
+        if (m < p.M && nbase < p.N) epilogue_store_32(p, r, m, nbase, row_scale, per_col);
       }
       tc_fence_before();
       mbar_arrive(&tmem_empty_bar[as]);

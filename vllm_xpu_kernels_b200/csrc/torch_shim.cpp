@@ -573,10 +573,15 @@ Tensor fp4_gemm(const Tensor& A, const Tensor& B, const Tensor& A_scale, const T
     bias = bias_->data_ptr();
     bias_dtype = bias_dtype_of(*bias_);
   }
+  // per-call scratch, like the reference's scratchpad tensor (fp4_gemm_w4a4.h:159-162)
+  const int64_t ws_bytes = vxk_fp4_gemm_workspace_bytes(r.M, N, K);
+  Tensor ws;
+  if (ws_bytes > 0) ws = at::empty({ws_bytes}, A.options().dtype(at::kByte));
   check_rc(vxk_fp4_gemm(result.data_ptr(), A.data_ptr(), B.data_ptr(), A_scale.data_ptr(), B_scale.data_ptr(), bias,
                         r.M, N, K, r.lda, B.stride(1), r.ldd, A_scale.stride(0), A_scale.stride(1),
                         B_scale.stride(0), B_scale.stride(1),
-                        result.scalar_type() == at::kBFloat16 ? VXK_BF16 : VXK_F16, bias_dtype, cur_stream()),
+                        result.scalar_type() == at::kBFloat16 ? VXK_BF16 : VXK_F16, bias_dtype,
+                        ws_bytes > 0 ? ws.data_ptr() : nullptr, ws_bytes, cur_stream()),
            "fp4_gemm");
   return result;
 }
