@@ -1,8 +1,4 @@
 timeout 300 python -m pytest tests/test_gemm_parity_gpu.py -x -q 2>&1 | tail -3
-VXK_GEMM_NACC=1 timeout 300 python -m pytest tests/test_gemm_parity_gpu.py -x -q 2>&1 | tail -2
-VXK_GEMM_NACC=2 timeout 300 python -m pytest tests/test_gemm_parity_gpu.py -x -q 2>&1 | tail -2
-P="timeout 120 python benchmarks/gemm_probe.py 8192 8192 8192 --secs 0.3 --kinds fp8_w8a8,mxfp8_block,mxfp4"
-for n in 1 2; do echo "NACC=$n"; VXK_GEMM_NACC=$n $P; done
-echo "NACC=2 no cp"; VXK_GEMM_NACC=2 VXK_GEMM_DEBUG=1 $P
-echo "auto K=28672"; timeout 120 python benchmarks/gemm_probe.py 8192 8192 28672 --secs 0.3 --kinds fp8_w8a8,mxfp4
-echo "auto N=57344"; timeout 120 python benchmarks/gemm_probe.py 8192 57344 8192 --secs 0.3 --kinds fp8_w8a8,mxfp4
+P="timeout 120 python benchmarks/gemm_probe.py"
+for m in 1 16 128; do $P $m 4096 4096 --secs 0.2 --kinds fp8_cublaslt,fp8_w8a8,mxfp4; $P $m 28672 4096 --secs 0.2 --kinds fp8_cublaslt,fp8_w8a8,mxfp4; $P $m 4096 14336 --secs 0.2 --kinds fp8_cublaslt,fp8_w8a8,mxfp4; done
+for m in 256 512 1024 2048; do $P $m 6144 4096 --secs 0.2 --kinds fp8_cublaslt,fp8_w8a8,mxfp4; done

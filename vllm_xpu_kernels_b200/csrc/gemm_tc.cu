@@ -188,7 +188,7 @@ static int launch_tc2(Tc2Params tp, const CUtensorMap& ma, const CUtensorMap& mb
   if (attr_err != cudaSuccess)
     return fail(VXK_ERR_CUDA, "cudaFuncSetAttribute(smem=%d): %s", L::kTotalBytes, cudaGetErrorString(attr_err));
   static const int dbg = env_int("VXK_GEMM_DEBUG", 0);
-  static const int group_m = env_int("VXK_GEMM_GROUP_M", 8);
+  static const int group_m = env_int("VXK_GEMM_GROUP_M", 16);
   tp.b.debug = dbg;   // bring-up / timing switches: 1 skip tcgen05.cp, 8 skip scale-factor TMA
   tp.group_m = group_m < 1 ? 1 : group_m;
   const int tiles = tp.num_m_pairs * tp.num_n_blocks;
@@ -201,15 +201,41 @@ static int launch_tc2(Tc2Params tp, const CUtensorMap& ma, const CUtensorMap& mb
 // Two W tiles per K loop (NACC = 2) cut the L2 bytes per flop by a quarter but quantise the
 // work into tiles twice as large and expose part of the epilogue: take them when the last
 // wave of super-tiles is not much emptier than the last wave of single tiles.
-static bool prefer_two_acc(int64_t M, int64_t N, int bn) {
+static bool prefer_two_acc(int64_t M, int64_t N, int64_t K_bytes, int bn) {
   static const int forced = env_int("VXK_GEMM_NACC", 0);
   if (forced == 1 || forced == 2) return forced == 2;
   const int64_t pairs = pair_count_hint();
   const int64_t mt = (M + 255) / 256;
   const int64_t t1 = mt * ((N + bn - 1) / bn), t2 = mt * ((N + 2 * bn - 1) / (2 * bn));
   const double c1 = static_cast<double>((t1 + pairs - 1) / pairs) * bn;
-  const double c2 = static_cast<double>((t2 + pairs - 1) / pairs) * 2 * bn * 0.85;
-  return c2 <= c1;
+  const double c2 = static_cast<double>((t2 + pairs - 1) / pairs) * 2 * bn;
+  return c2 <= c1 && K_bytes >= 12288;   // measured: pays off only when the K loop dwarfs the exposed epilogue
+}
+
+// Single-CTA tile width: the widest of {256 (fp8 only), 192 (block-scaled only), 128, 64, 32} that still
+// gives every SM a tile.  Small-M GEMMs are bound by streaming W from HBM: what matters is that
+// all SMs pull on it, not the shape the tensor core sees.
+static int single_cta_bn(int64_t M, int64_t N, int widest) {
+  const int64_t mt = (M + kBlockM - 1) / kBlockM, sms = sm_count();
+  const int cand[5] = {widest, 128, 64, 32, 0};
+  for (int i = 0; cand[i]; ++i) {
+    if (cand[i] > widest) continue;
+    if (N >= cand[i] && mt * ((N + cand[i] - 1) / cand[i]) >= sms) return cand[i];
+  }
+  return 32;
+}
+
+template <int KIND>
+static int launch_tc_bn(int bn, const TcParams& tp, const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& msa,
+                        const CUtensorMap& msb, cudaStream_t st) {
+  switch (bn) {
+    case 256: if constexpr (KIND == KIND_F8) return launch_tc<KIND, 256>(tp, ma, mb, msa, msb, st); else break;
+    case 192: if constexpr (KIND != KIND_F8) return launch_tc<KIND, 192>(tp, ma, mb, msa, msb, st); else break;
+    case 128: return launch_tc<KIND, 128>(tp, ma, mb, msa, msb, st);
+    case 64: return launch_tc<KIND, 64>(tp, ma, mb, msa, msb, st);
+    default: return launch_tc<KIND, 32>(tp, ma, mb, msa, msb, st);
+  }
+  return fail(VXK_ERR_INVALID, "no kernel for tile width %d", bn);
 }
 
 // Tile-shape choice by a wave count model: per-SM time of one tile ~ rows x cols handled by
@@ -270,7 +296,7 @@ static int run_pair_block_scaled(Tc2Params tp, const void* A, int64_t lda_bytes,
   sf_pack_kernel<<<blocks, 256, 0, st>>>(sfb, N, groups32, sp.num_kb, sp.b_blocks, sp.sf_words, b_scale, b_row_div,
                                          b_row_stride, b_kps, b_k_stride, b_words);
   if ((rc = check_launch("sf_pack_b"))) return rc;
-  const bool two = prefer_two_acc(M, N, BN);
+  const bool two = prefer_two_acc(M, N, fp4 ? K_elems / 2 : K_elems, BN);
   const int tile_n = two ? 2 * BN : BN;
   tp.num_m_pairs = static_cast<int>((M + 255) / 256);
   tp.num_n_blocks = static_cast<int>((N + tile_n - 1) / tile_n);
@@ -345,12 +371,11 @@ extern "C" int vxk_fp8_gemm(void* D, const void* A, const void* B, const void* a
   if (operands_ok && a_scale_mode != 2) {
     tp.a_scale = static_cast<const float*>(a_scale);
     tp.b_scale = static_cast<const float*>(b_scale);
-    const bool wide = N >= 256 && (M * N) >= 148LL * 128 * 256;   // enough tiles to fill the SMs at 128x256
-    const int bn = wide ? 256 : 128;
+    const int bn = single_cta_bn(M, N, 256);
     if (!force_single() && prefer_pair(M, N, bn, 256)) {
       Tc2Params t2{};
       t2.b = tp;
-      const bool two = prefer_two_acc(M, N, 256);
+      const bool two = prefer_two_acc(M, N, K, 256);
       t2.num_m_pairs = (int)((M + 255) / 256);
       t2.num_n_blocks = (int)((N + (two ? 511 : 255)) / (two ? 512 : 256));
       if ((rc = make_map_2d_u8(&ma, A, K, M, lda, kBlockKBytes, kBlockM, true))) return rc;
@@ -361,11 +386,12 @@ extern "C" int vxk_fp8_gemm(void* D, const void* A, const void* B, const void* a
     tp.num_n_blocks = (int)((N + bn - 1) / bn);
     if ((rc = make_map_2d_u8(&ma, A, K, M, lda, kBlockKBytes, kBlockM, true))) return rc;
     if ((rc = make_map_2d_u8(&mb, B, K, N, b_stride_n, kBlockKBytes, bn, true))) return rc;
-    return wide ? launch_tc<KIND_F8, 256>(tp, ma, mb, msa, msb, st) : launch_tc<KIND_F8, 128>(tp, ma, mb, msa, msb, st);
+    return launch_tc_bn<KIND_F8>(bn, tp, ma, mb, msa, msb, st);
   }
   if (operands_ok && a_scale_mode == 2 && scale_dtype == VXK_S_E8M0 && group_k % 32 == 0 && workspace &&
       workspace_bytes >= vxk_fp8_gemm_workspace_bytes(M, N, K, a_scale_mode, scale_dtype)) {
-    if (!force_single() && prefer_pair(M, N, N >= 192 ? 192 : 128, 192)) {
+    const int bn = single_cta_bn(M, N, 192);
+    if (!force_single() && prefer_pair(M, N, bn, 192)) {
       Tc2Params t2{};
       t2.b = tp;
       return run_pair_block_scaled<KIND_MXF8>(t2, A, lda, B, b_stride_n, M, N, K, static_cast<const uint8_t*>(a_scale),
@@ -385,14 +411,12 @@ extern "C" int vxk_fp8_gemm(void* D, const void* A, const void* B, const void* a
     canon_sf_kernel<<<blocks, 256, 0, st>>>(sfb, N, groups32, pitch, static_cast<const uint8_t*>(b_scale), group_n, sb1,
                                             group_k / 32, sb0);
     if ((rc = check_launch("canon_sfb"))) return rc;
-    const bool wide = N >= 192 && (M * N) >= 148LL * 128 * 192;
-    const int bn = wide ? 192 : 128;
     tp.num_n_blocks = (int)((N + bn - 1) / bn);
     if ((rc = make_map_2d_u8(&ma, A, K, M, lda, kBlockKBytes, kBlockM, true))) return rc;
     if ((rc = make_map_2d_u8(&mb, B, K, N, b_stride_n, kBlockKBytes, bn, true))) return rc;
     if ((rc = make_map_2d_u8(&msa, sfa, pitch, M, pitch, 16, kBlockM, false))) return rc;
     if ((rc = make_map_2d_u8(&msb, sfb, pitch, N, pitch, 16, bn, false))) return rc;
-    return wide ? launch_tc<KIND_MXF8, 192>(tp, ma, mb, msa, msb, st) : launch_tc<KIND_MXF8, 128>(tp, ma, mb, msa, msb, st);
+    return launch_tc_bn<KIND_MXF8>(bn, tp, ma, mb, msa, msb, st);
   }
   return launch_gemm_fallback(p, /*is_fp4=*/false, st);
 }
@@ -416,8 +440,7 @@ extern "C" int vxk_fp4_gemm(void* D, const void* A, const void* B, const void* a
   tp.D = D; tp.bias = bias; tp.M = (int)M; tp.N = (int)N; tp.K_bytes = (int)(K / 2); tp.ldd = ldd;
   tp.a_scale_mode = 2; tp.b_scale_mode = 2; tp.out_dtype = out_dtype; tp.bias_dtype = bias_dtype;
   tp.num_m_blocks = (int)((M + kBlockM - 1) / kBlockM);
-  const bool wide = N >= 192 && (M * N) >= 148LL * 128 * 192;
-  const int bn = wide ? 192 : 128;
+  const int bn = single_cta_bn(M, N, 192);
   tp.num_n_blocks = (int)((N + bn - 1) / bn);
   tp.num_k_blocks = (int)((K / 2 + kBlockKBytes - 1) / kBlockKBytes);
   tp.vec_store_ok = aligned16(D) && (ldd * 2) % 16 == 0;
@@ -435,5 +458,5 @@ extern "C" int vxk_fp4_gemm(void* D, const void* A, const void* B, const void* a
   if ((rc = make_map_2d_u8(&mb, B, K / 2, N, ldb_bytes, kBlockKBytes, bn, true))) return rc;
   if ((rc = make_map_2d_u8(&msa, a_scale, K / 32, M, sa0, 16, kBlockM, false))) return rc;
   if ((rc = make_map_2d_u8(&msb, b_scale, K / 32, N, sb0, 16, bn, false))) return rc;
-  return wide ? launch_tc<KIND_MXF4, 192>(tp, ma, mb, msa, msb, st) : launch_tc<KIND_MXF4, 128>(tp, ma, mb, msa, msb, st);
+  return launch_tc_bn<KIND_MXF4>(bn, tp, ma, mb, msa, msb, st);
 }

@@ -182,8 +182,8 @@ gemm_tc_kernel(const TcParams p, const __grid_constant__ CUtensorMap map_a, cons
   const int num_tiles = p.num_m_blocks * p.num_n_blocks;
 
   if (warp == 0) {
-    // ===================== TMA producer =====================
-    if (lane == 0) {
+    // ===================== TMA producer (whole warp converged, one elected lane issues) =====================
+    {
       int stage = 0;
       uint32_t phase = 0;
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
@@ -191,20 +191,23 @@ gemm_tc_kernel(const TcParams p, const __grid_constant__ CUtensorMap map_a, cons
         const int n0 = (tile / p.num_m_blocks) * BLOCK_N;
         for (int kb = 0; kb < p.num_k_blocks; ++kb) {
           mbar_wait(&empty_bar[stage], phase ^ 1);
-          mbar_arrive_expect_tx(&full_bar[stage], L::kTxBytes);
-          tma_load_2d(stage_a(stage), &map_a, &full_bar[stage], kb * kBlockKBytes, m0);
-          tma_load_2d(stage_b(stage), &map_b, &full_bar[stage], kb * kBlockKBytes, n0);
-          if constexpr (kScaled) {
-            tma_load_2d(stage_raw_sfa(stage), &map_sfa, &full_bar[stage], (kb * L::kSfGroups) & ~15, m0);
-            tma_load_2d(stage_raw_sfb(stage), &map_sfb, &full_bar[stage], (kb * L::kSfGroups) & ~15, n0);
+          if (elect_one()) {
+            mbar_arrive_expect_tx(&full_bar[stage], L::kTxBytes);
+            tma_load_2d(stage_a(stage), &map_a, &full_bar[stage], kb * kBlockKBytes, m0);
+            tma_load_2d(stage_b(stage), &map_b, &full_bar[stage], kb * kBlockKBytes, n0);
+            if constexpr (kScaled) {
+              tma_load_2d(stage_raw_sfa(stage), &map_sfa, &full_bar[stage], (kb * L::kSfGroups) & ~15, m0);
+              tma_load_2d(stage_raw_sfb(stage), &map_sfb, &full_bar[stage], (kb * L::kSfGroups) & ~15, n0);
+            }
           }
+          __syncwarp();
           if (++stage == S) { stage = 0; phase ^= 1; }
         }
       }
     }
   } else if (warp == 1) {
-    // ===================== MMA issuer =====================
-    if (lane == 0) {
+    // ===================== MMA issuer (whole warp converged, one elected lane issues) =====================
+    {
       const uint32_t idesc = make_idesc_block_scaled(KIND == KIND_MXF4 ? 1 : p.fp8_fmt, kBlockM, BLOCK_N);
       const uint32_t idesc_f8 = make_idesc_f8(p.fp8_fmt, kBlockM, BLOCK_N);
       int stage = 0;
@@ -219,38 +222,41 @@ gemm_tc_kernel(const TcParams p, const __grid_constant__ CUtensorMap map_a, cons
         for (int kb = 0; kb < p.num_k_blocks; ++kb) {
           mbar_wait(kScaled ? &sf_bar[stage] : &full_bar[stage], phase);
           tc_fence_after();
-          const uint64_t da = make_kmajor_sw128_desc(smem_u32(stage_a(stage)));
-          const uint64_t db = make_kmajor_sw128_desc(smem_u32(stage_b(stage)));
-          if (kScaled && !(p.debug & 1)) {
+          if (elect_one()) {
+            const uint64_t da = make_kmajor_sw128_desc(smem_u32(stage_a(stage)));
+            const uint64_t db = make_kmajor_sw128_desc(smem_u32(stage_b(stage)));
+            if (kScaled && !(p.debug & 1)) {
 #pragma unroll
-            for (int w = 0; w < L::kSfWords; ++w) {
-              utccp_32x128b_warpx4(tmem_base + kSfaCol + w * 4, make_sf_desc(smem_u32(stage_sfa_t(stage) + w * 512)));
+              for (int w = 0; w < L::kSfWords; ++w) {
+                utccp_32x128b_warpx4(tmem_base + kSfaCol + w * 4, make_sf_desc(smem_u32(stage_sfa_t(stage) + w * 512)));
 #pragma unroll
-              for (int j = 0; j < NB; ++j)
-                utccp_32x128b_warpx4(tmem_base + kSfbCol + (w * NB + j) * 4,
-                                     make_sf_desc(smem_u32(stage_sfb_t(stage) + (w * NB + j) * 512)));
+                for (int j = 0; j < NB; ++j)
+                  utccp_32x128b_warpx4(tmem_base + kSfbCol + (w * NB + j) * 4,
+                                       make_sf_desc(smem_u32(stage_sfb_t(stage) + (w * NB + j) * 512)));
+              }
             }
-          }
 #pragma unroll
-          for (int k = 0; k < kBlockKBytes / kUmmaKBytes; ++k) {
-            const uint64_t dak = da + static_cast<uint64_t>(k * (kUmmaKBytes >> 4));
-            const uint64_t dbk = db + static_cast<uint64_t>(k * (kUmmaKBytes >> 4));
-            const uint32_t acc = (kb > 0 || k > 0) ? 1u : 0u;
-            if (KIND == KIND_F8 || (p.debug & 2)) {
-              umma_f8f6f4(tmem_d, dak, dbk, idesc_f8, acc);
-            } else if constexpr (KIND == KIND_MXF8) {
-              // one SF byte per row per MMA: byte k of the row's 32-bit word
-              umma_mxf8f6f4(tmem_d, dak, dbk, idesc_with_sf_ids(idesc, k, k), acc, tmem_base + kSfaCol,
-                            tmem_base + kSfbCol);
-            } else {
-              // two SF bytes per row per MMA: bytes {0,1} or {2,3} of word k/2
-              const uint32_t w = k >> 1, id = (k & 1) * 2;
-              umma_mxf4(tmem_d, dak, dbk, idesc_with_sf_ids(idesc, id, id), acc, tmem_base + kSfaCol + w * 4,
-                        tmem_base + kSfbCol + w * NB * 4);
+            for (int k = 0; k < kBlockKBytes / kUmmaKBytes; ++k) {
+              const uint64_t dak = da + static_cast<uint64_t>(k * (kUmmaKBytes >> 4));
+              const uint64_t dbk = db + static_cast<uint64_t>(k * (kUmmaKBytes >> 4));
+              const uint32_t acc = (kb > 0 || k > 0) ? 1u : 0u;
+              if (KIND == KIND_F8 || (p.debug & 2)) {
+                umma_f8f6f4(tmem_d, dak, dbk, idesc_f8, acc);
+              } else if constexpr (KIND == KIND_MXF8) {
+                // one SF byte per row per MMA: byte k of the row's 32-bit word
+                umma_mxf8f6f4(tmem_d, dak, dbk, idesc_with_sf_ids(idesc, k, k), acc, tmem_base + kSfaCol,
+                              tmem_base + kSfbCol);
+              } else {
+                // two SF bytes per row per MMA: bytes {0,1} or {2,3} of word k/2
+                const uint32_t w = k >> 1, id = (k & 1) * 2;
+                umma_mxf4(tmem_d, dak, dbk, idesc_with_sf_ids(idesc, id, id), acc, tmem_base + kSfaCol + w * 4,
+                          tmem_base + kSfbCol + w * NB * 4);
+              }
             }
+            umma_commit(&empty_bar[stage]);                 // frees the ring slot when the MMAs retire
+            if (kb == p.num_k_blocks - 1) umma_commit(&tmem_full_bar[as]);
           }
-          umma_commit(&empty_bar[stage]);                 // frees the ring slot when the MMAs retire
-          if (kb == p.num_k_blocks - 1) umma_commit(&tmem_full_bar[as]);
+          __syncwarp();
           if (++stage == S) { stage = 0; phase ^= 1; }
         }
       }
