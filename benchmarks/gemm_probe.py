@@ -92,6 +92,13 @@ def main():
             sw = torch.rand(N, 1, device=dev) * 0.01 + 0.001
             wt = w.t()
             fn = lambda: torch.ops._xpu_C.fp8_gemm(a, wt, torch.bfloat16, sa, sw, None)  # noqa: E731
+        elif kind == "fp8_block_f32":
+            a = (torch.randn(M, K, device=dev) / 4).to(E4)
+            w = (torch.randn(N, K, device=dev) / 4).to(E4)
+            sa = torch.rand(M, K // 128, device=dev) * 0.01 + 0.001
+            sw = torch.rand(K // 128, (N + 127) // 128, device=dev) * 0.01 + 0.001
+            wt = w.t()
+            fn = lambda: torch.ops._xpu_C.fp8_gemm(a, wt, torch.bfloat16, sa, sw, None)  # noqa: E731
         elif kind == "mxfp8_block":
             a = (torch.randn(M, K, device=dev) / 4).to(E4)
             w = (torch.randn(N, K, device=dev) / 4).to(E4)

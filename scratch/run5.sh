@@ -1,4 +1,5 @@
-timeout 300 python -m pytest tests/test_gemm_parity_gpu.py -x -q 2>&1 | tail -3
-P="timeout 120 python benchmarks/gemm_probe.py"
-for m in 1 16 128; do $P $m 4096 4096 --secs 0.2 --kinds fp8_cublaslt,fp8_w8a8,mxfp4; $P $m 28672 4096 --secs 0.2 --kinds fp8_cublaslt,fp8_w8a8,mxfp4; $P $m 4096 14336 --secs 0.2 --kinds fp8_cublaslt,fp8_w8a8,mxfp4; done
-for m in 256 512 1024 2048; do $P $m 6144 4096 --secs 0.2 --kinds fp8_cublaslt,fp8_w8a8,mxfp4; done
+timeout 300 python -m pytest tests/test_gemm_parity_gpu.py -x -q 2>&1 | tail -2
+P="timeout 60 python benchmarks/gemm_probe.py"
+$P 8192 8192 8192 --secs 0.3 --kinds fp8_block_f32,mxfp8_block,fp8_w8a8,mxfp4
+$P 4096 7168 16384 --secs 0.3 --kinds fp8_block_f32,mxfp8_block
+$P 4096 24576 1536 --secs 0.3 --kinds fp8_block_f32,mxfp8_block

@@ -36,7 +36,8 @@ CU_SOURCES = {
     "gemm_fallback.cu": [],
     "gemm_tc.cu": [],
 }
-HEADERS = ["vxk_common.cuh", "gemm_common.cuh", "gemm_tc.cuh", "quant_row_impl.cuh", os.path.join(ROOT, "include", "vxk_b200.h")]
+# every header under csrc/ feeds every object's digest (a header missing here means stale objects)
+HEADERS = sorted(f for f in os.listdir(CSRC) if f.endswith((".cuh", ".h"))) + [os.path.join(ROOT, "include", "vxk_b200.h")]
 
 
 def _digest(paths, extra=""):

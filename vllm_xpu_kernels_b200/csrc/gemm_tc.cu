@@ -1,7 +1,7 @@
 // Host side of the scaled GEMMs: eligibility checks, TMA tensor maps, scale-factor
 // canonicalisation, launch of the tcgen05 kernels (gemm_tc.cuh) or of the CUDA-core
 // fallback (gemm_fallback.cu), and the two C-ABI entry points.
-#include "gemm_tc2.cuh"
+#include "gemm_tc2_blk.cuh"
 
 #include <mutex>
 
@@ -198,6 +198,30 @@ static int launch_tc2(Tc2Params tp, const CUtensorMap& ma, const CUtensorMap& mb
   return check_launch("gemm_tc2");
 }
 
+template <int BLOCK_N>
+static int launch_tc2_blk(Tc2BlkParams tp, const CUtensorMap& ma, const CUtensorMap& mb, cudaStream_t st) {
+  using L = Tc2Smem<KIND_F8, BLOCK_N, 1>;
+  auto kernel = gemm_tc2_blk_kernel<BLOCK_N>;
+  static std::once_flag once;
+  static cudaError_t attr_err = cudaSuccess;
+  static int pairs = 0;
+  std::call_once(once, [&] {
+    attr_err = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotalBytes);
+    if (attr_err == cudaSuccess) pairs = max_cluster_pairs(reinterpret_cast<const void*>(kernel), L::kTotalBytes);
+  });
+  if (attr_err != cudaSuccess)
+    return fail(VXK_ERR_CUDA, "cudaFuncSetAttribute(smem=%d): %s", L::kTotalBytes, cudaGetErrorString(attr_err));
+  static const int group_m = env_int("VXK_GEMM_GROUP_M", 16);
+  static const int dbg = env_int("VXK_GEMM_DEBUG", 0);
+  tp.b.debug = dbg;
+  tp.group_m = group_m < 1 ? 1 : group_m;
+  const int tiles = tp.num_m_pairs * tp.num_n_blocks;
+  const int grid = 2 * (tiles < pairs ? tiles : pairs);
+  kernel<<<grid, kTc2Threads, L::kTotalBytes, st>>>(tp, ma, mb);
+  g_gemm_tc_calls.fetch_add(1, std::memory_order_relaxed);
+  return check_launch("gemm_tc2_blk");
+}
+
 // Two W tiles per K loop (NACC = 2) cut the L2 bytes per flop by a quarter but quantise the
 // work into tiles twice as large and expose part of the epilogue: take them when the last
 // wave of super-tiles is not much emptier than the last wave of single tiles.
@@ -387,6 +411,23 @@ extern "C" int vxk_fp8_gemm(void* D, const void* A, const void* B, const void* a
     if ((rc = make_map_2d_u8(&ma, A, K, M, lda, kBlockKBytes, kBlockM, true))) return rc;
     if ((rc = make_map_2d_u8(&mb, B, K, N, b_stride_n, kBlockKBytes, bn, true))) return rc;
     return launch_tc_bn<KIND_F8>(bn, tp, ma, mb, msa, msb, st);
+  }
+  if (operands_ok && a_scale_mode == 2 && scale_dtype == VXK_S_F32 && group_k % 128 == 0 && group_n % 32 == 0 &&
+      K % group_k == 0) {
+    // fp32 block scales: two-level accumulation (tensor core per K slice, CUDA cores across slices)
+    constexpr int BN = 192;
+    Tc2BlkParams t2{};
+    t2.b = tp;
+    t2.sa = static_cast<const float*>(a_scale);
+    t2.sb = static_cast<const float*>(b_scale);
+    t2.sa0 = sa0; t2.sa1 = sa1; t2.sb0 = sb0; t2.sb1 = sb1;
+    t2.group_k_blocks = (int)(group_k / 128);
+    t2.group_n = (int)group_n;
+    t2.num_m_pairs = (int)((M + 255) / 256);
+    t2.num_n_blocks = (int)((N + BN - 1) / BN);
+    if ((rc = make_map_2d_u8(&ma, A, K, M, lda, kBlockKBytes, kBlockM, true))) return rc;
+    if ((rc = make_map_2d_u8(&mb, B, K, N, b_stride_n, kBlockKBytes, BN / 2, true))) return rc;
+    return launch_tc2_blk<BN>(t2, ma, mb, st);
   }
   if (operands_ok && a_scale_mode == 2 && scale_dtype == VXK_S_E8M0 && group_k % 32 == 0 && workspace &&
       workspace_bytes >= vxk_fp8_gemm_workspace_bytes(M, N, K, a_scale_mode, scale_dtype)) {

@@ -76,11 +76,14 @@ __device__ __forceinline__ void tma_load_2d_pair(void* smem_dst, const CUtensorM
       "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar) & kPeerBitMask), "r"(c0), "r"(c1)
       : "memory");
 }
-// arrive on the barrier at the same shared-memory offset in CTA `rank` of the cluster
+// arrive on the barrier at the same shared-memory offset in CTA `rank` of the cluster.  Default
+// (CTA-scope) semantics on purpose: the arrival only says "this warp's tcgen05.ld of the buffer has
+// completed" (ordered by tcgen05.wait::ld + tcgen05.fence::before_thread_sync); cluster scope
+// compiles to MEMBAR.ALL.GPU and holds the signal back until the warp's global accesses drain.
 __device__ __forceinline__ void mbar_arrive_cluster(uint64_t* bar, uint32_t rank) {
   asm volatile(
       "{\n\t.reg .b32 ra;\n\tmapa.shared::cluster.u32 ra, %0, %1;\n\t"
-      "mbarrier.arrive.release.cluster.shared::cluster.b64 _, [ra];\n\t}" ::"r"(smem_u32(bar)),
+      "mbarrier.arrive.shared::cluster.b64 _, [ra];\n\t}" ::"r"(smem_u32(bar)),
       "r"(rank)
       : "memory");
 }

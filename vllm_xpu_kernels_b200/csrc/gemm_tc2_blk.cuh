@@ -1,0 +1,211 @@
+// FP8 GEMM with fp32 block scales (DeepSeek-V3 recipe: activations scaled per 1 x group_k,
+// weights per group_k x group_n, any fp32 values -- not powers of two, so the block-scaled MMA
+// kinds do not apply).  CTA-pair tcgen05 kernel with two-level accumulation:
+//
+//   for every K slice of 128:   P   = A[:, slice] * W[:, slice]^T        tensor core -> TMEM
+//                               acc += sA[m, slice] * sW[slice, n] * P    CUDA cores, fp32 registers
+//
+// Same producer / ring / CTA-pair structure as gemm_tc2.cuh (256 x 192 tile per pair, plain
+// kind::f8f6f4 MMAs), but the two TMEM buffers alternate per K SLICE: while the tensor core
+// fills one, the eight promotion warps of each CTA pull the other into registers
+// (tcgen05.ld), hand the buffer back at once, and fold it into their accumulators (96 columns
+// per thread).  The promotion warps take 224 registers (setmaxnreg), the role warps give theirs up.
+// ref: fp8_gemm_w8a8.h:28-41,86-134 (block scale shapes), tests/test_fp8_gemm_onednn.py:270-358.
+#pragma once
+
+#include "gemm_tc2.cuh"
+
+namespace vxk {
+
+struct Tc2BlkParams {
+  TcParams b;
+  const float* sa;        // sA[m * sa0 + kg * sa1]
+  const float* sb;        // sW[kg * sb0 + ng * sb1]
+  int64_t sa0, sa1, sb0, sb1;
+  int group_k_blocks;     // group_k / 128
+  int group_n;
+  int num_m_pairs, num_n_blocks, group_m;
+};
+
+template <int BLOCK_N>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTc2Threads, 1)
+gemm_tc2_blk_kernel(const Tc2BlkParams pp, const __grid_constant__ CUtensorMap map_a,
+                    const __grid_constant__ CUtensorMap map_b) {
+  using L = Tc2Smem<KIND_F8, BLOCK_N, 1>;
+  constexpr int S = L::kStages;
+  const TcParams& p = pp.b;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  constexpr int kOffB = L::kABytes;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + S * L::kStageBytes);
+  uint64_t* full_bar = bars;                 // leader CTA
+  uint64_t* empty_bar = bars + S;            // per CTA
+  uint64_t* p_full_bar = bars + 2 * S;       // per CTA: partial product of one K slice is in TMEM buffer i
+  uint64_t* p_empty_bar = bars + 2 * S + 2;  // leader CTA: buffer i has been pulled into registers by all 16 warps
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(bars + 2 * S + 4);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();
+  const bool leader = rank == 0;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&map_a);
+    tma_prefetch_desc(&map_b);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int i = 0; i < S; ++i) {
+      mbar_init(&full_bar[i], 1);
+      mbar_init(&empty_bar[i], 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&p_full_bar[i], 1);
+      mbar_init(&p_empty_bar[i], 16);
+    }
+    fence_barrier_init();
+  }
+  if (warp == 2) tmem_alloc_pair<kTmemCols>(tmem_ptr_smem);
+  tc_fence_before();
+  cluster_sync_all();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr_smem;
+  constexpr uint32_t kAccCols = BLOCK_N;
+  static_assert(2 * kAccCols <= kTmemCols, "TMEM budget");
+
+  const int num_tiles = pp.num_m_pairs * pp.num_n_blocks;
+  const int pair = blockIdx.x >> 1, num_pairs = gridDim.x >> 1;
+  const int KB = p.num_k_blocks;
+
+  if (warp < 4) {
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 56;");
+    if (warp == 0) {
+      // ===================== TMA producer (both CTAs) =====================
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = pair; tile < num_tiles; tile += num_pairs) {
+        int mt, nt;
+        tile_coords(tile, pp.num_m_pairs, pp.num_n_blocks, pp.group_m, mt, nt);
+        const int m0 = mt * (2 * kBlockM) + static_cast<int>(rank) * kBlockM;
+        const int nb = nt * BLOCK_N + static_cast<int>(rank) * (BLOCK_N / 2);
+        for (int kb = 0; kb < KB; ++kb) {
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          if (elect_one()) {
+            uint8_t* st = smem + stage * L::kStageBytes;
+            if (leader) mbar_arrive_expect_tx(&full_bar[stage], 2 * (L::kABytes + L::kBBytes));
+            tma_load_2d_pair(st, &map_a, &full_bar[stage], kb * kBlockKBytes, m0);
+            tma_load_2d_pair(st + kOffB, &map_b, &full_bar[stage], kb * kBlockKBytes, nb);
+          }
+          __syncwarp();
+          if (++stage == S) { stage = 0; phase ^= 1; }
+        }
+      }
+    } else if (warp == 1 && leader) {
+      // ===================== MMA issuer (leader CTA) =====================
+      const uint32_t idesc = make_idesc_f8(p.fp8_fmt, 2 * kBlockM, BLOCK_N);
+      const uint32_t lo_base = desc_lo(smem);
+      int stage = 0;
+      uint32_t phase = 0;
+      uint32_t g = 0;   // K slices issued so far (all tiles)
+      for (int tile = pair; tile < num_tiles; tile += num_pairs) {
+        for (int kb = 0; kb < KB; ++kb, ++g) {
+          const uint32_t buf = g & 1;
+          mbar_wait(&p_empty_bar[buf], ((g >> 1) & 1) ^ 1);
+          mbar_wait(&full_bar[stage], phase);
+          tc_fence_after();
+          if (elect_one()) {
+            const uint32_t lo_a = lo_base + stage * (L::kStageBytes >> 4);
+            const uint32_t lo_b = lo_a + (kOffB >> 4);
+            const uint32_t tmem_d = tmem_base + buf * kAccCols;
+#pragma unroll
+            for (int k = 0; k < kBlockKBytes / kUmmaKBytes; ++k)
+              umma2_issue<KIND_F8>(tmem_d, lo_a + k * 2, lo_b + k * 2, idesc, k > 0 ? 1u : 0u, 0, 0);
+            umma_commit_pair(&empty_bar[stage]);
+            umma_commit_pair(&p_full_bar[buf]);
+          }
+          __syncwarp();
+          if (++stage == S) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else {
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 224;");
+    // ===================== promotion + epilogue warps (both CTAs) =====================
+    const int e = warp - 4;
+    const int q = e & 3;                    // TMEM lane quarter
+    const int h = e >> 2;                   // column half of the tile
+    constexpr int kCols = BLOCK_N / 2;      // columns per thread
+    constexpr int kChunks = kCols / 32;
+    static_assert(kCols % 32 == 0, "column halves must be whole 32-column chunks");
+    const int row_in_tile = static_cast<int>(rank) * kBlockM + q * 32 + lane;
+    uint32_t g = 0;
+    for (int tile = pair; tile < num_tiles; tile += num_pairs) {
+      int mt, nt;
+      tile_coords(tile, pp.num_m_pairs, pp.num_n_blocks, pp.group_m, mt, nt);
+      const int m = mt * (2 * kBlockM) + row_in_tile;
+      const int n_first = nt * BLOCK_N + h * kCols;
+      const bool row_ok = m < p.M;
+      const float* sa_row = pp.sa + static_cast<int64_t>(row_ok ? m : 0) * pp.sa0;
+      // scale column groups of this thread's chunks (a 32-column chunk never straddles a group: group_n % 32 == 0)
+      int ng[kChunks];
+#pragma unroll
+      for (int c = 0; c < kChunks; ++c) {
+        const int n = n_first + c * 32;
+        ng[c] = (n < p.N ? n : 0) / pp.group_n;
+      }
+      float acc[kCols];
+#pragma unroll
+      for (int j = 0; j < kCols; ++j) acc[j] = 0.0f;
+      // scale products of the NEXT slice are fetched right after this slice's buffer has been handed
+      // back, a whole slice ahead of their use: no global load is in flight at the hand-over
+      auto load_scales = [&](int kb, float (&s)[kChunks]) {
+        const int kg = pp.group_k_blocks == 1 ? kb : kb / pp.group_k_blocks;
+        const float sa = row_ok ? __ldg(sa_row + static_cast<int64_t>(kg) * pp.sa1) : 0.0f;
+#pragma unroll
+        for (int c = 0; c < kChunks; ++c) s[c] = sa * __ldg(pp.sb + kg * pp.sb0 + ng[c] * pp.sb1);
+      };
+      float s_next[kChunks];
+      load_scales(0, s_next);
+      for (int kb = 0; kb < KB; ++kb, ++g) {
+        const uint32_t buf = g & 1;
+        float s[kChunks];
+#pragma unroll
+        for (int c = 0; c < kChunks; ++c) s[c] = s_next[c];
+        mbar_wait(&p_full_bar[buf], (g >> 1) & 1);
+        tc_fence_after();
+        uint32_t r[kChunks][32];
+#pragma unroll
+        for (int c = 0; c < kChunks; ++c)
+          tmem_ld_32x32b_x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + buf * kAccCols + h * kCols + c * 32, r[c]);
+        tmem_ld_wait();
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive_cluster(&p_empty_bar[buf], 0);   // buffer is in registers: hand it back first
+        if (kb + 1 < KB) load_scales(kb + 1, s_next);
+#pragma unroll
+        for (int c = 0; c < kChunks; ++c)
+#pragma unroll
+          for (int j = 0; j < 32; ++j) acc[c * 32 + j] = fmaf(__uint_as_float(r[c][j]), s[c], acc[c * 32 + j]);
+      }
+      if (row_ok) {
+#pragma unroll
+        for (int c = 0; c < kChunks; ++c) {
+          const int nbase = n_first + c * 32;
+          if (nbase < p.N) {
+            uint32_t bits[32];
+#pragma unroll
+            for (int j = 0; j < 32; ++j) bits[j] = __float_as_uint(acc[c * 32 + j]);
+            epilogue_store_32(p, bits, m, nbase, 1.0f, false);
+          }
+        }
+      }
+    }
+  }
+
+  tc_fence_before();
+  cluster_sync_all();
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc_pair<kTmemCols>(tmem_base);
+  }
+}
+
+}  // namespace vxk
