@@ -100,7 +100,10 @@ __device__ __forceinline__ void prologue(const RawV<T>& g, const RawV<T>& up, fl
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
       const float2 f = Pair<T>::unpack(gw[i]);
-      const typename Pair<T>::V s2 = Pair<T>::pack(silu_f32<FAST>(f.x), silu_f32<FAST>(f.y));
+      float s0, s1;
+      if constexpr (FAST) silu2_approx(f.x, f.y, s0, s1);
+      else { s0 = silu_f32<0>(f.x); s1 = silu_f32<0>(f.y); }
+      const typename Pair<T>::V s2 = Pair<T>::pack(s0, s1);
       const typename Pair<T>::V y2 = __hmul2(s2, *reinterpret_cast<const typename Pair<T>::V*>(&uw[i]));
       yw[i] = *reinterpret_cast<const uint32_t*>(&y2);
       const float2 y = Pair<T>::unpack(yw[i]);
@@ -117,8 +120,8 @@ __device__ __forceinline__ void prologue(const RawV<T>& g, const RawV<T>& up, fl
         v[j] = round_to<T>(round_to<T>(silu_f32<FAST>(v[j])) * u[j]);
         v[j + 1] = round_to<T>(round_to<T>(silu_f32<FAST>(v[j + 1])) * u[j + 1]);
       } else if constexpr (FAST) {
-        v[j] = silu_f32<1>(v[j]) * u[j];
-        v[j + 1] = silu_f32<1>(v[j + 1]) * u[j + 1];
+        silu2_approx(v[j], v[j + 1], v[j], v[j + 1]);
+        mul2(v[j], v[j + 1], u[j], u[j + 1]);
       } else {
         v[j] = (v[j] * __fdiv_rn(1.0f, 1.0f + expf(-v[j]))) * u[j];
         v[j + 1] = (v[j + 1] * __fdiv_rn(1.0f, 1.0f + expf(-v[j + 1]))) * u[j + 1];
@@ -139,11 +142,15 @@ __device__ __noinline__ float slow_div(float x, float s) { return __fdiv_rn(x, s
 template <int Q>
 __device__ __forceinline__ uint2 div_pack_fp8_signed(const float (&v)[8], const uint32_t (&yw)[4], float s, float r) {
   float q[8];
+  const float ns = -s;
 #pragma unroll
-  for (int k = 0; k < 8; ++k) {
-    const float q0 = v[k] * r;
-    const float rem = fmaf(-q0, s, v[k]);
-    q[k] = fmaf(rem, r, q0);
+  for (int k = 0; k < 8; k += 2) {
+    q[k] = v[k];
+    q[k + 1] = v[k + 1];
+    mul2(q[k], q[k + 1], r, r);
+    float r0, r1;
+    fma2_to(r0, r1, q[k], q[k + 1], ns, ns, v[k], v[k + 1]);
+    fma2(q[k], q[k + 1], r0, r1, r, r);
   }
   const uint2 c = pack_q8<Q>(q);
   const uint32_t s_lo = __byte_perm(yw[0], yw[1], 0x7531), s_hi = __byte_perm(yw[2], yw[3], 0x7531);
@@ -216,7 +223,11 @@ __global__ void __launch_bounds__(256) flat_quant_kernel(const FlatParams p) {
       uint8_t* o = op + u * u_out;
       if constexpr (FMT == FMT_STATIC) {
 #pragma unroll
-        for (int k = 0; k < 8; ++k) q[k] = v[k] * r_static;
+        for (int k = 0; k < 8; k += 2) {
+          q[k] = v[k];
+          q[k + 1] = v[k + 1];
+          mul2(q[k], q[k + 1], r_static, r_static);
+        }
         if (ok[u]) stg_stream(o, pack_q8<Q>(q));
       } else {
         float gmax = 0.0f;
@@ -230,8 +241,13 @@ __global__ void __launch_bounds__(256) flat_quant_kernel(const FlatParams p) {
           const int e = rceil_e8m0(div_const<6>(gmax));
           const float d = e8m0_descale(e);
           if (leader[u]) *sq = e8m0_scale(e);
+          // (the reference's clamp to +-6 is what the saturating conversion does anyway)
 #pragma unroll
-          for (int k = 0; k < 8; ++k) q[k] = fminf(fmaxf(v[k] * d, -6.0f), 6.0f);
+          for (int k = 0; k < 8; k += 2) {
+            q[k] = v[k];
+            q[k + 1] = v[k + 1];
+            mul2(q[k], q[k + 1], d, d);
+          }
           // bf16 inputs scaled by a power of two are already bf16 values; everything else
           // takes the reference's intermediate rounding to bf16 (mx_utils.py:346)
           if constexpr (!(PRO == PRO_NONE && std::is_same<T, __nv_bfloat16>::value)) {
@@ -249,7 +265,11 @@ __global__ void __launch_bounds__(256) flat_quant_kernel(const FlatParams p) {
           const float d = e8m0_descale(e);
           if (leader[u]) *sq = e8m0_scale(e);
 #pragma unroll
-          for (int k = 0; k < 8; ++k) q[k] = v[k] * d;
+          for (int k = 0; k < 8; k += 2) {
+            q[k] = v[k];
+            q[k + 1] = v[k + 1];
+            mul2(q[k], q[k + 1], d, d);
+          }
           if (ok[u]) stg_stream(o, pack_q8<Q>(q));
         } else {
           float s;

@@ -112,80 +112,137 @@ __device__ __forceinline__ double block_sum_f64(double v, double* scratch) {
   return r;
 }
 
+// CTA-wide reduction with ONE barrier: per-warp partials go to one of two scratch rows (the
+// caller alternates `slot`), every thread then reads all partials back (broadcast loads) and
+// combines them in the same order.  Two slots make the single barrier safe: a warp can only
+// overwrite slot k after the barrier of the reduction in between.
+template <bool IS_MAX>
+__device__ __forceinline__ float block_reduce1(float v, float (*scratch)[32], int slot) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = (blockDim.x + 31) >> 5;
+  v = IS_MAX ? warp_max(v) : warp_sum(v);
+  if (nwarp == 1) return v;
+  if (lane == 0) scratch[slot][warp] = v;
+  __syncthreads();
+  // entries past nwarp hold 0 (the identity of both reductions here: sums and maxima of magnitudes)
+  const float4* s4 = reinterpret_cast<const float4*>(scratch[slot]);
+  auto comb = [](float a, float b) { return IS_MAX ? fmaxf(a, b) : a + b; };
+  const float4 a = s4[0];
+  float r = comb(comb(a.x, a.y), comb(a.z, a.w));
+  if (nwarp > 4) {
+    const float4 b = s4[1];
+    r = comb(r, comb(comb(b.x, b.y), comb(b.z, b.w)));
+    if (nwarp > 8) {
+      const float4 c = s4[2], d = s4[3];
+      r = comb(r, comb(comb(comb(c.x, c.y), comb(c.z, c.w)), comb(comb(d.x, d.y), comb(d.z, d.w))));
+    }
+  }
+  return r;
+}
+
 // Persistent CTAs (grid = min(T, resident CTAs)), each loops over rows.  A thread owns
-// VPT vectors of a row (tid + i * blockDim); all of its 128-bit loads are issued before
-// the first use and the row then lives in registers as fp32, so every element is
-// converted, normalised and scaled exactly once.  These kernels are instruction-issue
-// bound on B200 (HBM delivers one bf16 element per ~14 issue slots), hence no value is
-// ever recomputed.  SAT: clamp the quotient before the conversion (only needed when a
-// scale upper bound can push |x / s| past the format maximum).
-template <typename T, int Q, int MODE, bool RMS, bool HAS_RES, int VPT>
+// VPT vectors of a row (tid + i * blockDim); the row lives in registers as fp32, so every
+// element is converted, normalised and scaled exactly once, and the NEXT row's 128-bit loads are
+// issued (into the packed registers the current row has just vacated) before the current row's
+// arithmetic, so HBM always has a row per CTA in flight.  These kernels are instruction-issue
+// bound on B200 (HBM delivers one bf16 element per ~14 issue slots): element-wise multiplies and
+// the sum of squares are packed fp32x2 operations, the rms weight is staged once per CTA as fp32
+// in shared memory (two planes of float4: conflict-free 128-bit reads, no per-row unpacking), and
+// each row reduction costs a single barrier.  FULL: nvec == VPT * blockDim (no tail predicates).
+// SAT: clamp the quotient before the conversion (only needed when a scale upper bound can push
+// |x / s| past the format maximum).
+template <typename T, int Q, int MODE, bool RMS, bool HAS_RES, int VPT, bool FULL>
 __global__ void __launch_bounds__(512) row_quant_kernel(const RowParams p, const int64_t T_rows) {
-  __shared__ float scratch[33];
+  __shared__ __align__(16) float scratch[2][32];
+  extern __shared__ float4 wsm[];     // RMS: [2][nvec] float4 (elements 0-3 / 4-7 of every vector)
   const int tid = threadIdx.x, nthr = blockDim.x;
   constexpr float kQMax = QTraits<Q>::kMax;
-  const T* __restrict__ w = static_cast<const T*>(p.weight);
   const bool sat = p.scale_in != nullptr;
+  const int nvec = p.nvec;
+  int slot = 0;
+  if (tid < 64) scratch[tid >> 5][tid & 31] = 0.0f;
+  if (!RMS) __syncthreads();
 
-  for (int64_t row = blockIdx.x; row < T_rows; row += gridDim.x) {
-    const T* __restrict__ xin = static_cast<const T*>(p.in) + row * p.in_row_stride;
+  if constexpr (RMS) {
+    const T* __restrict__ w = static_cast<const T*>(p.weight);
+    for (int idx = tid; idx < nvec; idx += nthr) {
+      float wv[8];
+      load8<T, false>(w + idx * kVec, wv);
+      wsm[idx] = make_float4(wv[0], wv[1], wv[2], wv[3]);
+      wsm[nvec + idx] = make_float4(wv[4], wv[5], wv[6], wv[7]);
+    }
+    __syncthreads();
+  }
+
+  bool ok[VPT];
+#pragma unroll
+  for (int i = 0; i < VPT; ++i) ok[i] = FULL || (tid + i * nthr < nvec);
+
+  // per-thread element offsets of its vectors and row pointers that advance by a constant:
+  // no per-row 64-bit address arithmetic in the loop
+  int voff[VPT];
+#pragma unroll
+  for (int i = 0; i < VPT; ++i) voff[i] = (tid + i * nthr) * kVec;
+  const int64_t in_step = static_cast<int64_t>(gridDim.x) * p.in_row_stride;
+  const int64_t out_step = static_cast<int64_t>(gridDim.x) * (MODE == MODE_MXFP4 ? p.H / 2 : p.H);
+  const T* __restrict__ xnext = static_cast<const T*>(p.in) + static_cast<int64_t>(blockIdx.x) * p.in_row_stride;
+  uint8_t* orow = static_cast<uint8_t*>(p.out) + static_cast<int64_t>(blockIdx.x) * (MODE == MODE_MXFP4 ? p.H / 2 : p.H);
+
+  Raw8<T> raw[VPT];
+#pragma unroll
+  for (int i = 0; i < VPT; ++i)
+    raw[i] = (static_cast<int64_t>(blockIdx.x) < T_rows && ok[i]) ? load_raw<T, true>(xnext + voff[i]) : Raw8<T>{};
+
+  for (int64_t row = blockIdx.x; row < T_rows; row += gridDim.x, orow += out_step) {
     float v[VPT][8];
-    {
-      Raw8<T> raw[VPT];
+    if constexpr (RMS && HAS_RES) {
+      T* res = static_cast<T*>(p.residual) + row * p.H;
+      Raw8<T> rr[VPT];
+#pragma unroll
+      for (int i = 0; i < VPT; ++i) rr[i] = ok[i] ? load_raw<T, false>(res + voff[i]) : Raw8<T>{};
 #pragma unroll
       for (int i = 0; i < VPT; ++i) {
-        const int idx = tid + i * nthr;
-        raw[i] = (idx < p.nvec) ? load_raw<T, true>(xin + idx * kVec) : Raw8<T>{};
+        float b[8];
+        unpack_raw<T>(raw[i], v[i]);
+        unpack_raw<T>(rr[i], b);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) v[i][j] = v[i][j] + b[j];
+        const Raw8<T> z = pack_raw<T>(v[i]);  // z = T(x + res): new residual and norm input
+        if (ok[i]) store_raw<T>(res + voff[i], z);
+        unpack_raw<T>(z, v[i]);
       }
-      if constexpr (RMS && HAS_RES) {
-        T* res = static_cast<T*>(p.residual) + row * p.H;
-        Raw8<T> rr[VPT];
+    } else {
 #pragma unroll
-        for (int i = 0; i < VPT; ++i) {
-          const int idx = tid + i * nthr;
-          rr[i] = (idx < p.nvec) ? load_raw<T, false>(res + idx * kVec) : Raw8<T>{};
-        }
+      for (int i = 0; i < VPT; ++i) unpack_raw<T>(raw[i], v[i]);
+    }
+    xnext += in_step;   // prefetch the next row of this CTA into the packed registers just vacated
+    if (row + gridDim.x < T_rows) {
 #pragma unroll
-        for (int i = 0; i < VPT; ++i) {
-          const int idx = tid + i * nthr;
-          float b[8];
-          unpack_raw<T>(raw[i], v[i]);
-          unpack_raw<T>(rr[i], b);
-#pragma unroll
-          for (int j = 0; j < 8; ++j) v[i][j] = v[i][j] + b[j];
-          const Raw8<T> z = pack_raw<T>(v[i]);  // z = T(x + res): new residual and norm input
-          if (idx < p.nvec) store_raw<T>(res + idx * kVec, z);
-          unpack_raw<T>(z, v[i]);
-        }
-      } else {
-#pragma unroll
-        for (int i = 0; i < VPT; ++i) unpack_raw<T>(raw[i], v[i]);
-      }
+      for (int i = 0; i < VPT; ++i)
+        if (ok[i]) raw[i] = load_raw<T, true>(xnext + voff[i]);
     }
 
     if constexpr (RMS) {
-      float ss = 0.0f;
+      float s0 = 0.0f, s1 = 0.0f;
 #pragma unroll
-      for (int i = 0; i < VPT; ++i) {
-        float part = 0.0f;
+      for (int i = 0; i < VPT; ++i)
 #pragma unroll
-        for (int j = 0; j < 8; ++j) part = fmaf(v[i][j], v[i][j], part);
-        ss += part;
-      }
-      ss = block_reduce<false>(ss, scratch);
+        for (int j = 0; j < 8; j += 2) fma2(s0, s1, v[i][j], v[i][j + 1], v[i][j], v[i][j + 1]);
+      const float ss = block_reduce1<false>(s0 + s1, scratch, slot);
+      slot ^= 1;
       const float var = __fdiv_rn(ss, static_cast<float>(p.H));
       const float inv_rms = __fdiv_rn(1.0f, __fsqrt_rn(var + p.eps));
 #pragma unroll
       for (int i = 0; i < VPT; ++i) {
-        const int idx = tid + i * nthr;
-        float wv[8];
-        if (idx < p.nvec) load8<T, false>(w + idx * kVec, wv);
-        else {
-#pragma unroll
-          for (int j = 0; j < 8; ++j) wv[j] = 0.0f;
-        }
-#pragma unroll
-        for (int j = 0; j < 8; ++j) v[i][j] = (v[i][j] * inv_rms) * wv[j];
+        const int idx = FULL ? tid + i * nthr : min(tid + i * nthr, nvec - 1);
+        const float4 wa = wsm[idx], wb = wsm[nvec + idx];
+        mul2(v[i][0], v[i][1], inv_rms, inv_rms);
+        mul2(v[i][2], v[i][3], inv_rms, inv_rms);
+        mul2(v[i][4], v[i][5], inv_rms, inv_rms);
+        mul2(v[i][6], v[i][7], inv_rms, inv_rms);
+        mul2(v[i][0], v[i][1], wa.x, wa.y);
+        mul2(v[i][2], v[i][3], wa.z, wa.w);
+        mul2(v[i][4], v[i][5], wb.x, wb.y);
+        mul2(v[i][6], v[i][7], wb.z, wb.w);
       }
     }
 
@@ -195,7 +252,8 @@ __global__ void __launch_bounds__(512) row_quant_kernel(const RowParams p, const
       for (int i = 0; i < VPT; ++i)
 #pragma unroll
         for (int j = 0; j < 8; ++j) amax = fmaxf(amax, fabsf(v[i][j]));
-      amax = block_reduce<true>(amax, scratch);
+      amax = block_reduce1<true>(amax, scratch, slot);
+      slot ^= 1;
       float s;
       if constexpr (Q == VXK_Q_INT8) {
         s = amax > 0.0f ? div_qmax<Q>(amax) : 1.0f;
@@ -205,46 +263,36 @@ __global__ void __launch_bounds__(512) row_quant_kernel(const RowParams p, const
       }
       const float r = __frcp_rn(s);
       if (tid == 0) p.scales[row] = s;
-      uint8_t* o = static_cast<uint8_t*>(p.out) + row * p.H;
 #pragma unroll
       for (int i = 0; i < VPT; ++i) {
-        const int idx = tid + i * nthr;
-        float q[8];
-        if constexpr (Q == VXK_Q_INT8) {
+        if constexpr (Q == VXK_Q_INT8 || MODE == MODE_TOKEN_DIV) {
+          if (Q != VXK_Q_INT8 && sat) {
 #pragma unroll
-          for (int j = 0; j < 8; ++j) q[j] = div_by<false>(v[i][j], s, r);
-        } else if constexpr (MODE == MODE_TOKEN_DIV) {
-          if (sat) {
-#pragma unroll
-            for (int j = 0; j < 8; ++j) q[j] = div_by<true>(v[i][j], s, r, kQMax);
+            for (int j = 0; j < 8; j += 2) div_by2<true>(v[i][j], v[i][j + 1], s, r, kQMax);
           } else {
 #pragma unroll
-            for (int j = 0; j < 8; ++j) q[j] = div_by<false>(v[i][j], s, r);
+            for (int j = 0; j < 8; j += 2) div_by2<false>(v[i][j], v[i][j + 1], s, r);
           }
         } else {
 #pragma unroll
-          for (int j = 0; j < 8; ++j) q[j] = v[i][j] * r;
+          for (int j = 0; j < 8; j += 2) mul2(v[i][j], v[i][j + 1], r, r);
         }
-        if (idx < p.nvec) stg_stream(o + idx * kVec, pack_q8<Q>(q));
+        if (ok[i]) stg_stream(orow + voff[i], pack_q8<Q>(v[i]));
       }
     } else if constexpr (MODE == MODE_STATIC) {
       const float r = __frcp_rn(__ldg(p.scale_in));
-      uint8_t* o = static_cast<uint8_t*>(p.out) + row * p.H;
 #pragma unroll
       for (int i = 0; i < VPT; ++i) {
-        const int idx = tid + i * nthr;
-        float q[8];
 #pragma unroll
-        for (int j = 0; j < 8; ++j) q[j] = v[i][j] * r;
-        if (idx < p.nvec) stg_stream(o + idx * kVec, pack_q8<Q>(q));
+        for (int j = 0; j < 8; j += 2) mul2(v[i][j], v[i][j + 1], r, r);
+        if (ok[i]) stg_stream(orow + voff[i], pack_q8<Q>(v[i]));
       }
     } else {  // MODE_GROUP / MODE_MXFP4: 1 x G groups, G/8 consecutive lanes per group
       const int lanes_log2 = p.lanes_log2;
 #pragma unroll
       for (int i = 0; i < VPT; ++i) {
         const int idx = tid + i * nthr;
-        const bool valid = idx < p.nvec;
-        float q[8];
+        const bool valid = ok[i];
         float gmax = 0.0f;
 #pragma unroll
         for (int j = 0; j < 8; ++j) gmax = fmaxf(gmax, fabsf(v[i][j]));
@@ -255,17 +303,18 @@ __global__ void __launch_bounds__(512) row_quant_kernel(const RowParams p, const
           const int e = rceil_e8m0(div_const<6>(gmax));
           const float d = e8m0_descale(e);
           if (leader) p.scales[row * p.ss0 + g * p.ss1] = e8m0_scale(e);
+          float q[8];
 #pragma unroll
-          for (int j = 0; j < 8; ++j) q[j] = fminf(fmaxf(v[i][j] * d, -6.0f), 6.0f);
-#pragma unroll
-          for (int j = 0; j < 8; j += 2) {  // the reference's intermediate rounding to bf16
-            const __nv_bfloat162 b2 = __floats2bfloat162_rn(q[j], q[j + 1]);
+          for (int j = 0; j < 8; j += 2) {
+            mul2(v[i][j], v[i][j + 1], d, d);
+            // the reference's intermediate rounding to bf16; its clamp to +-6 before that is what
+            // the saturating conversion below does anyway (RNE to bf16 is monotonic)
+            const __nv_bfloat162 b2 = __floats2bfloat162_rn(v[i][j], v[i][j + 1]);
             const uint32_t wd = *reinterpret_cast<const uint32_t*>(&b2);
             q[j] = bf16_lo(wd);
             q[j + 1] = bf16_hi(wd);
           }
-          uint8_t* o = static_cast<uint8_t*>(p.out) + row * (p.H / 2);
-          if (valid) stg_stream(o + idx * 4, pack_e2m1x8(q));
+          if (valid) stg_stream(orow + (voff[i] >> 1), pack_e2m1x8(q));
         } else {
           float s;
           if constexpr (Q == VXK_Q_INT8) {
@@ -277,12 +326,11 @@ __global__ void __launch_bounds__(512) row_quant_kernel(const RowParams p, const
           const float r = __frcp_rn(s);
           if (leader) p.scales[row * p.ss0 + g * p.ss1] = s;
 #pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            if constexpr (Q == VXK_Q_INT8) q[j] = div_by<false>(v[i][j], s, r);
-            else q[j] = v[i][j] * r;
+          for (int j = 0; j < 8; j += 2) {
+            if constexpr (Q == VXK_Q_INT8) div_by2<false>(v[i][j], v[i][j + 1], s, r);
+            else mul2(v[i][j], v[i][j + 1], r, r);
           }
-          uint8_t* o = static_cast<uint8_t*>(p.out) + row * p.H;
-          if (valid) stg_stream(o + idx * kVec, pack_q8<Q>(q));
+          if (valid) stg_stream(orow + voff[i], pack_q8<Q>(v[i]));
         }
       }
     }
@@ -402,19 +450,43 @@ inline int resident_ctas(K kernel, int threads) {
   return n * sm_count();
 }
 
-template <typename T, int Q, int MODE, bool RMS, bool HAS_RES, int VPT>
-inline void launch_row_vpt2(const RowParams& p, int64_t T_rows, int threads, cudaStream_t st) {
-  auto kernel = row_quant_kernel<T, Q, MODE, RMS, HAS_RES, VPT>;
-  const int64_t cap = resident_ctas(kernel, threads);
+template <typename T, int Q, int MODE, bool RMS, bool HAS_RES, int VPT, bool FULL>
+inline int launch_row_vpt3(const RowParams& p, int64_t T_rows, int threads, cudaStream_t st) {
+  auto kernel = row_quant_kernel<T, Q, MODE, RMS, HAS_RES, VPT, FULL>;
+  const size_t smem = RMS ? static_cast<size_t>(p.nvec) * 32 : 0;
+  if (smem > 48 * 1024) {
+    static thread_local size_t configured = 0;     // per instantiation
+    if (smem > configured) {
+      if (cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)) != cudaSuccess) {
+        cudaGetLastError();
+        return 1;                                   // row too long for the staged weight: caller falls back
+      }
+      configured = smem;
+    }
+  }
+  static thread_local int c_threads = 0, c_per_sm = 0;   // per instantiation; smem follows from nvec = f(threads) mostly
+  static thread_local size_t c_smem = 0;
+  int per_sm = c_per_sm;
+  if (c_threads != threads || c_smem != smem || per_sm < 1) {
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, threads, smem) != cudaSuccess || per_sm < 1) per_sm = 1;
+    c_threads = threads; c_smem = smem; c_per_sm = per_sm;
+  }
+  const int64_t cap = static_cast<int64_t>(per_sm) * sm_count();
   const unsigned grid = static_cast<unsigned>(T_rows < cap ? T_rows : cap);
-  kernel<<<grid, threads, 0, st>>>(p, T_rows);
+  kernel<<<grid, threads, smem, st>>>(p, T_rows);
+  return 0;
+}
+template <typename T, int Q, int MODE, bool RMS, bool HAS_RES, int VPT>
+inline int launch_row_vpt2(const RowParams& p, int64_t T_rows, int threads, cudaStream_t st) {
+  if (p.nvec == VPT * threads) return launch_row_vpt3<T, Q, MODE, RMS, HAS_RES, VPT, true>(p, T_rows, threads, st);
+  return launch_row_vpt3<T, Q, MODE, RMS, HAS_RES, VPT, false>(p, T_rows, threads, st);
 }
 template <typename T, int Q, int MODE, bool RMS, int VPT>
-inline void launch_row_vpt(const RowParams& p, int64_t T_rows, int threads, cudaStream_t st) {
+inline int launch_row_vpt(const RowParams& p, int64_t T_rows, int threads, cudaStream_t st) {
   if constexpr (RMS) {
     if (p.residual != nullptr) return launch_row_vpt2<T, Q, MODE, RMS, true, VPT>(p, T_rows, threads, st);
   }
-  launch_row_vpt2<T, Q, MODE, RMS, false, VPT>(p, T_rows, threads, st);
+  return launch_row_vpt2<T, Q, MODE, RMS, false, VPT>(p, T_rows, threads, st);
 }
 
 template <typename T, int Q, int MODE, bool RMS>
@@ -434,14 +506,16 @@ int launch_row(const RowParams& p_in, int64_t T_rows, bool vec_ok, cudaStream_t 
   while ((nvec + vpt - 1) / vpt > 256 && vpt < kMaxVpt) vpt *= 2;  // long rows: up to 8 x 512 threads
   if (vpt > kMaxVpt) vpt = kMaxVpt;
   const int threads = ((nvec + vpt - 1) / vpt + 31) / 32 * 32;
+  int not_launched = 1;
   if (vec_ok && threads <= 512) {
     switch (vpt) {
-      case 1: launch_row_vpt<T, Q, MODE, RMS, 1>(p, T_rows, threads, st); break;
-      case 2: launch_row_vpt<T, Q, MODE, RMS, 2>(p, T_rows, threads, st); break;
-      case 4: launch_row_vpt<T, Q, MODE, RMS, 4>(p, T_rows, threads, st); break;
-      default: launch_row_vpt<T, Q, MODE, RMS, 8>(p, T_rows, threads, st); break;
+      case 1: not_launched = launch_row_vpt<T, Q, MODE, RMS, 1>(p, T_rows, threads, st); break;
+      case 2: not_launched = launch_row_vpt<T, Q, MODE, RMS, 2>(p, T_rows, threads, st); break;
+      case 4: not_launched = launch_row_vpt<T, Q, MODE, RMS, 4>(p, T_rows, threads, st); break;
+      default: not_launched = launch_row_vpt<T, Q, MODE, RMS, 8>(p, T_rows, threads, st); break;
     }
-  } else {
+  }
+  if (not_launched) {
     if (T_rows > 0x7fffffffLL) return fail(VXK_ERR_INVALID, "too many rows (%lld)", (long long)T_rows);
     row_quant_generic<T, Q, MODE, RMS><<<static_cast<unsigned>(T_rows), 256, 0, st>>>(p);
   }

@@ -206,6 +206,37 @@ __device__ __forceinline__ uint32_t pack_e2m1x8(const float (&v)[8]) {
          (cvt_e2m1x2(v[7], v[6]) << 24);
 }
 
+// ---- packed fp32 pairs (Blackwell FMUL2 / FFMA2: two IEEE RN operations per issue slot) ----
+// The quantisation kernels are issue-bound, not FLOP-bound: halving the instruction count of
+// the element-wise multiplies is worth more than any scheduling tweak.  Results are bit-identical
+// to the scalar mul.rn / fma.rn.
+__device__ __forceinline__ void mul2(float& x, float& y, float a, float b) {
+  asm("{\n\t.reg .b64 rx, ra;\n\tmov.b64 rx, {%0, %1};\n\tmov.b64 ra, {%2, %3};\n\t"
+      "mul.rn.f32x2 rx, rx, ra;\n\tmov.b64 {%0, %1}, rx;\n\t}"
+      : "+f"(x), "+f"(y)
+      : "f"(a), "f"(b));
+}
+// (c0, c1) = (a0, a1) * (b0, b1) + (c0, c1)
+__device__ __forceinline__ void fma2(float& c0, float& c1, float a0, float a1, float b0, float b1) {
+  asm("{\n\t.reg .b64 rc, ra, rb;\n\tmov.b64 rc, {%0, %1};\n\tmov.b64 ra, {%2, %3};\n\tmov.b64 rb, {%4, %5};\n\t"
+      "fma.rn.f32x2 rc, ra, rb, rc;\n\tmov.b64 {%0, %1}, rc;\n\t}"
+      : "+f"(c0), "+f"(c1)
+      : "f"(a0), "f"(a1), "f"(b0), "f"(b1));
+}
+__device__ __forceinline__ void add2(float& x, float& y, float a, float b) {
+  asm("{\n\t.reg .b64 rx, ra;\n\tmov.b64 rx, {%0, %1};\n\tmov.b64 ra, {%2, %3};\n\t"
+      "add.rn.f32x2 rx, rx, ra;\n\tmov.b64 {%0, %1}, rx;\n\t}"
+      : "+f"(x), "+f"(y)
+      : "f"(a), "f"(b));
+}
+// (d0, d1) = (a0, a1) * (b0, b1) + (c0, c1)
+__device__ __forceinline__ void fma2_to(float& d0, float& d1, float a0, float a1, float b0, float b1, float c0, float c1) {
+  asm("{\n\t.reg .b64 rd, ra, rb, rc;\n\tmov.b64 ra, {%2, %3};\n\tmov.b64 rb, {%4, %5};\n\tmov.b64 rc, {%6, %7};\n\t"
+      "fma.rn.f32x2 rd, ra, rb, rc;\n\tmov.b64 {%0, %1}, rd;\n\t}"
+      : "=f"(d0), "=f"(d1)
+      : "f"(a0), "f"(a1), "f"(b0), "f"(b1), "f"(c0), "f"(c1));
+}
+
 // ---- exact division by a row/group constant ----
 // r must be RN(1/s), s > 0.  q0 = RN(x*r) is within 2 ulp of x/s; one FMA residual +
 // one FMA correction lands on RN(x/s) (Markstein) -- 3 ops instead of the ~10 of
@@ -220,6 +251,25 @@ __device__ __forceinline__ float div_by(float x, float s, float r, float sat_max
   float q1 = fabsf(fmaf(rem, r, q0));
   if constexpr (SAT) q1 = fminf(q1, sat_max);
   return copysignf(q1, x);
+}
+
+// the same Markstein division on a pair of values (3 packed ops + 2 sign patches)
+template <bool SAT>
+__device__ __forceinline__ void div_by2(float& x0, float& x1, float s, float r, float sat_max = 0.0f) {
+  float q0 = x0, q1 = x1;
+  mul2(q0, q1, r, r);
+  float r0, r1;
+  const float ns = -s;                       // x - q0*s as fma(q0, -s, x): the negation is loop-invariant
+  fma2_to(r0, r1, q0, q1, ns, ns, x0, x1);
+  fma2(q0, q1, r0, r1, r, r);
+  q0 = fabsf(q0);
+  q1 = fabsf(q1);
+  if constexpr (SAT) {
+    q0 = fminf(q0, sat_max);
+    q1 = fminf(q1, sat_max);
+  }
+  x0 = copysignf(q0, x0);
+  x1 = copysignf(q1, x1);
 }
 
 // x / C for a compile-time constant C > 0, correctly rounded (same Markstein step with
@@ -326,6 +376,16 @@ __device__ __forceinline__ float rcp_approx(float d) {
   float r;
   asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(d));
   return r;
+}
+// silu of two values, approximate mode: the multiplies and the 1 + e add are packed
+__device__ __forceinline__ void silu2_approx(float x0, float x1, float& s0, float& s1) {
+  float t0 = x0, t1 = x1;
+  mul2(t0, t1, -1.4426950408889634f, -1.4426950408889634f);
+  float e0 = ex2_approx(t0), e1 = ex2_approx(t1);
+  add2(e0, e1, 1.0f, 1.0f);
+  s0 = rcp_approx(e0);
+  s1 = rcp_approx(e1);
+  mul2(s0, s1, x0, x1);
 }
 template <int MODE>
 __device__ __forceinline__ float silu_f32(float x) {
