@@ -198,10 +198,10 @@ static int launch_tc2(Tc2Params tp, const CUtensorMap& ma, const CUtensorMap& mb
   return check_launch("gemm_tc2");
 }
 
-template <int BLOCK_N>
+template <int BLOCK_N, bool PIPE>
 static int launch_tc2_blk(Tc2BlkParams tp, const CUtensorMap& ma, const CUtensorMap& mb, cudaStream_t st) {
   using L = Tc2Smem<KIND_F8, BLOCK_N, 1>;
-  auto kernel = gemm_tc2_blk_kernel<BLOCK_N>;
+  auto kernel = gemm_tc2_blk_kernel<BLOCK_N, PIPE>;
   static std::once_flag once;
   static cudaError_t attr_err = cudaSuccess;
   static int pairs = 0;
@@ -427,7 +427,8 @@ extern "C" int vxk_fp8_gemm(void* D, const void* A, const void* B, const void* a
     t2.num_n_blocks = (int)((N + BN - 1) / BN);
     if ((rc = make_map_2d_u8(&ma, A, K, M, lda, kBlockKBytes, kBlockM, true))) return rc;
     if ((rc = make_map_2d_u8(&mb, B, K, N, b_stride_n, kBlockKBytes, BN / 2, true))) return rc;
-    return launch_tc2_blk<BN>(t2, ma, mb, st);
+    static const int blk_pipe = env_int("VXK_BLK_PIPE", 1);
+    return blk_pipe ? launch_tc2_blk<BN, true>(t2, ma, mb, st) : launch_tc2_blk<BN, false>(t2, ma, mb, st);
   }
   if (operands_ok && a_scale_mode == 2 && scale_dtype == VXK_S_E8M0 && group_k % 32 == 0 && workspace &&
       workspace_bytes >= vxk_fp8_gemm_workspace_bytes(M, N, K, a_scale_mode, scale_dtype)) {

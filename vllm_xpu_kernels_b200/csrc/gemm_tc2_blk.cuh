@@ -8,8 +8,15 @@
 // Same producer / ring / CTA-pair structure as gemm_tc2.cuh (256 x 192 tile per pair, plain
 // kind::f8f6f4 MMAs), but the two TMEM buffers alternate per K SLICE: while the tensor core
 // fills one, the eight promotion warps of each CTA pull the other into registers
-// (tcgen05.ld), hand the buffer back at once, and fold it into their accumulators (96 columns
-// per thread).  The promotion warps take 224 registers (setmaxnreg), the role warps give theirs up.
+// (tcgen05.ld, 32-column chunks through two rotating register buffers so that the FMAs of one
+// chunk overlap the load of the next), hand the buffer back as soon as its last chunk has landed,
+// and fold it into their accumulators (96 columns per thread, packed fp32x2 FMAs).  The promotion
+// warps take 224 registers (setmaxnreg), the role warps give theirs up.
+// What bounds it (clock64 stamps per slice, round 1d): not TMEM bandwidth (tcgen05.ld 32x32b.x32
+// drains >= 340 B/clk/SM with 8 warps, scratch/tmem_bw.cu) and not the FMAs, but the LATENCY of the
+// hand-over loop  MMA retires -> commit -> promotion warps -> tcgen05.ld -> 16 arrivals (two CTAs)
+// -> MMA warp -> issue: ~1500 clk per buffer round trip against 384 clk of tensor work per slice.
+// A 4 x 128-column variant (more units in flight, more hand-overs) measured slower.
 // ref: fp8_gemm_w8a8.h:28-41,86-134 (block scale shapes), tests/test_fp8_gemm_onednn.py:270-358.
 #pragma once
 
@@ -27,7 +34,7 @@ struct Tc2BlkParams {
   int num_m_pairs, num_n_blocks, group_m;
 };
 
-template <int BLOCK_N>
+template <int BLOCK_N, bool PIPE>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTc2Threads, 1)
 gemm_tc2_blk_kernel(const Tc2BlkParams pp, const __grid_constant__ CUtensorMap map_a,
                     const __grid_constant__ CUtensorMap map_b) {
@@ -154,36 +161,104 @@ gemm_tc2_blk_kernel(const Tc2BlkParams pp, const __grid_constant__ CUtensorMap m
       float acc[kCols];
 #pragma unroll
       for (int j = 0; j < kCols; ++j) acc[j] = 0.0f;
-      // scale products of the NEXT slice are fetched right after this slice's buffer has been handed
-      // back, a whole slice ahead of their use: no global load is in flight at the hand-over
-      auto load_scales = [&](int kb, float (&s)[kChunks]) {
+      // Scales are fetched one slice ahead and kept RAW: the warp issues in order, so forming the
+      // product sA * sW right after the loads would stall every slice on an L2 round trip (~600 clk,
+      // measured with clock64 stamps); the product is formed when the slice is consumed.
+      struct RawScales { float a; float b[kChunks]; };
+      auto load_scales = [&](int kb, RawScales& s) {
         const int kg = pp.group_k_blocks == 1 ? kb : kb / pp.group_k_blocks;
-        const float sa = row_ok ? __ldg(sa_row + static_cast<int64_t>(kg) * pp.sa1) : 0.0f;
+        s.a = row_ok ? __ldg(sa_row + static_cast<int64_t>(kg) * pp.sa1) : 0.0f;
 #pragma unroll
-        for (int c = 0; c < kChunks; ++c) s[c] = sa * __ldg(pp.sb + kg * pp.sb0 + ng[c] * pp.sb1);
+        for (int c = 0; c < kChunks; ++c) s.b[c] = __ldg(pp.sb + kg * pp.sb0 + ng[c] * pp.sb1);
       };
-      float s_next[kChunks];
+      RawScales s_next;
       load_scales(0, s_next);
-      for (int kb = 0; kb < KB; ++kb, ++g) {
-        const uint32_t buf = g & 1;
-        float s[kChunks];
+      const uint32_t t_lane = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + h * kCols;
+      if constexpr (!PIPE) {
+        // all chunks of a slice at once: shortest hand-back latency, no overlap of ld and FMAs inside the warp
+        for (int kb = 0; kb < KB; ++kb, ++g) {
+          const uint32_t buf = g & 1;
+          float s[kChunks];
+          asm volatile("" : "+f"(s_next.a));
 #pragma unroll
-        for (int c = 0; c < kChunks; ++c) s[c] = s_next[c];
-        mbar_wait(&p_full_bar[buf], (g >> 1) & 1);
+          for (int c = 0; c < kChunks; ++c) s[c] = s_next.a * s_next.b[c];
+          mbar_wait(&p_full_bar[buf], (g >> 1) & 1);
+          tc_fence_after();
+          uint32_t r[kChunks][32];
+#pragma unroll
+          for (int c = 0; c < kChunks; ++c) tmem_ld_32x32b_x32(t_lane + buf * kAccCols + c * 32, r[c]);
+          tmem_ld_wait();
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive_cluster(&p_empty_bar[buf], 0);   // buffer is in registers: hand it back first
+          if (kb + 1 < KB) load_scales(kb + 1, s_next);
+#pragma unroll
+          for (int c = 0; c < kChunks; ++c)
+#pragma unroll
+            for (int j = 0; j < 32; j += 2)
+              fma2(acc[c * 32 + j], acc[c * 32 + j + 1], __uint_as_float(r[c][j]), __uint_as_float(r[c][j + 1]), s[c], s[c]);
+        }
+      } else {
+        // Software pipeline over (K slice, 32-column chunk) units: while the FMAs of one chunk run, the
+        // tcgen05.ld of the next chunk -- of the next slice after the last one -- is already in flight
+        // (two rotating 32-register buffers; tcgen05.wait::ld has no finer granularity than "all").
+        // A slice's TMEM buffer goes back to the MMA warp as soon as its last chunk has landed.
+        uint32_t r[2][32];
+        mbar_wait(&p_full_bar[g & 1], (g >> 1) & 1);
         tc_fence_after();
-        uint32_t r[kChunks][32];
+        tmem_ld_32x32b_x32(t_lane + (g & 1) * kAccCols, r[0]);
+        auto slice = [&](auto kp_tag, int kb) {
+          constexpr int KP = decltype(kp_tag)::value;      // parity of the slice index within the tile
+          const uint32_t buf = g & 1;
+          float s[kChunks];
+          asm volatile("" : "+f"(s_next.a));
 #pragma unroll
-        for (int c = 0; c < kChunks; ++c)
-          tmem_ld_32x32b_x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + buf * kAccCols + h * kCols + c * 32, r[c]);
-        tmem_ld_wait();
-        tc_fence_before();
-        __syncwarp();
-        if (lane == 0) mbar_arrive_cluster(&p_empty_bar[buf], 0);   // buffer is in registers: hand it back first
-        if (kb + 1 < KB) load_scales(kb + 1, s_next);
+          for (int c = 0; c < kChunks; ++c) s[c] = s_next.a * s_next.b[c];
+          const bool more = kb + 1 < KB;
 #pragma unroll
-        for (int c = 0; c < kChunks; ++c)
+          for (int c = 0; c < kChunks; ++c) {
+            constexpr int kOdd = kChunks & 1;              // chunks per slice odd: buffer roles flip every slice
+            const int cur = (KP * kOdd + c) & 1;
+            tmem_ld_wait();
 #pragma unroll
-          for (int j = 0; j < 32; ++j) acc[c * 32 + j] = fmaf(__uint_as_float(r[c][j]), s[c], acc[c * 32 + j]);
+            for (int j = 0; j < 32; ++j) asm volatile("" : "+r"(r[cur][j]));   // values are defined from here on
+            bool issued = false;
+            if (c + 1 < kChunks) {
+              tmem_ld_32x32b_x32(t_lane + buf * kAccCols + (c + 1) * 32, r[cur ^ 1]);
+              issued = true;
+            } else {
+              tc_fence_before();
+              __syncwarp();
+              if (lane == 0) mbar_arrive_cluster(&p_empty_bar[buf], 0);   // whole slice is in registers: hand it back
+              if (more) {
+                load_scales(kb + 1, s_next);
+                const uint32_t gn = g + 1;
+                if (__all_sync(0xffffffffu, mbar_try_wait(&p_full_bar[gn & 1], (gn >> 1) & 1))) {
+                  tc_fence_after();
+                  tmem_ld_32x32b_x32(t_lane + (gn & 1) * kAccCols, r[cur ^ 1]);
+                  issued = true;
+                }
+              }
+            }
+#pragma unroll
+            for (int j = 0; j < 32; j += 2)
+              fma2(acc[c * 32 + j], acc[c * 32 + j + 1], __uint_as_float(r[cur][j]), __uint_as_float(r[cur][j + 1]),
+                   s[c], s[c]);
+            if (c + 1 == kChunks && more && !issued) {     // next slice was not ready: wait for it now
+              const uint32_t gn = g + 1;
+              mbar_wait(&p_full_bar[gn & 1], (gn >> 1) & 1);
+              tc_fence_after();
+              tmem_ld_32x32b_x32(t_lane + (gn & 1) * kAccCols, r[cur ^ 1]);
+            }
+          }
+          ++g;
+        };
+        int kb = 0;
+        for (; kb + 1 < KB; kb += 2) {
+          slice(std::integral_constant<int, 0>{}, kb);
+          slice(std::integral_constant<int, 1>{}, kb + 1);
+        }
+        if (kb < KB) slice(std::integral_constant<int, 0>{}, kb);
       }
       if (row_ok) {
 #pragma unroll
