@@ -18,7 +18,8 @@ struct RowParams {
   int64_t H, in_row_stride, ss0, ss1;
   int nvec;             // H / 8
   int group;            // group size (MODE_GROUP / MODE_MXFP4)
-  int lanes_log2;       // log2(group / 8) on the vector path
+  int lanes_log2;       // log2(lanes that share a group) on the vector path
+  int gv_log2;          // log2(vectors per group) = log2(group / 8)
   int ue8m0;
   float eps;
 };
@@ -150,10 +151,17 @@ __device__ __forceinline__ float block_reduce1(float v, float (*scratch)[32], in
 // each row reduction costs a single barrier.  FULL: nvec == VPT * blockDim (no tail predicates).
 // SAT: clamp the quotient before the conversion (only needed when a scale upper bound can push
 // |x / s| past the format maximum).
-template <typename T, int Q, int MODE, bool RMS, bool HAS_RES, int VPT, bool FULL>
+// VG (group modes): a thread's vectors come in runs of VG vectors of the SAME 1 x G group, so the
+// group maximum needs log2(G / 8 / VG) shuffle steps and the scale arithmetic (exact division by
+// the format maximum, reciprocal, E8M0 rounding) is done once per VG vectors instead of once per
+// vector -- these kernels are issue-bound, and that per-vector scalar work was what kept the
+// per-group variants at half the per-token variant's rate.  Vector index of (thread, i):
+//   (i / VG) * (threads * VG) + (tid / lpg) * gv + (i % VG) * lpg + tid % lpg,   lpg = gv / VG
+// (lpg adjacent lanes read lpg * 16 contiguous bytes: whole 32-byte sectors for lpg >= 2).
+template <typename T, int Q, int MODE, bool RMS, bool HAS_RES, int VPT, bool FULL, int VG = 1>
 __global__ void __launch_bounds__(512) row_quant_kernel(const RowParams p, const int64_t T_rows) {
   __shared__ __align__(16) float scratch[2][32];
-  extern __shared__ float4 wsm[];     // RMS: [2][nvec] float4 (elements 0-3 / 4-7 of every vector)
+  extern __shared__ float4 wsm[];     // RMS: [2][VPT][threads] float4 (elements 0-3 / 4-7 of every vector)
   const int tid = threadIdx.x, nthr = blockDim.x;
   constexpr float kQMax = QTraits<Q>::kMax;
   const bool sat = p.scale_in != nullptr;
@@ -162,26 +170,45 @@ __global__ void __launch_bounds__(512) row_quant_kernel(const RowParams p, const
   if (tid < 64) scratch[tid >> 5][tid & 31] = 0.0f;
   if (!RMS) __syncthreads();
 
+  constexpr bool kGrouped = MODE == MODE_GROUP || MODE == MODE_MXFP4;
+  static_assert(VG == 1 || kGrouped, "VG only applies to the per-group modes");
+  static_assert(VPT % VG == 0, "whole runs per thread");
+  // vector index of (thread, i), see above; VG == 1 without groups degenerates to tid + i * nthr
+  int vidx[VPT];
+#pragma unroll
+  for (int i = 0; i < VPT; ++i) {
+    if constexpr (kGrouped) {
+      const int lpg_log2 = p.lanes_log2;
+      vidx[i] = (i / VG) * (nthr * VG) + ((tid >> lpg_log2) << p.gv_log2) + ((i % VG) << lpg_log2) +
+                (tid & ((1 << lpg_log2) - 1));
+    } else {
+      vidx[i] = tid + i * nthr;
+    }
+  }
+  bool ok[VPT];
+#pragma unroll
+  for (int i = 0; i < VPT; ++i) ok[i] = FULL || (vidx[i] < nvec);
+
+  // rms weight, staged once per CTA as fp32 in THREAD order: slot i * nthr + tid holds the weight
+  // vector this thread multiplies its i-th vector with (two planes: elements 0-3 / 4-7), so the
+  // per-row reads are conflict-free 128-bit loads whatever the vector-to-thread mapping is
   if constexpr (RMS) {
     const T* __restrict__ w = static_cast<const T*>(p.weight);
-    for (int idx = tid; idx < nvec; idx += nthr) {
-      float wv[8];
-      load8<T, false>(w + idx * kVec, wv);
-      wsm[idx] = make_float4(wv[0], wv[1], wv[2], wv[3]);
-      wsm[nvec + idx] = make_float4(wv[4], wv[5], wv[6], wv[7]);
+#pragma unroll
+    for (int i = 0; i < VPT; ++i) {
+      float wv[8] = {0.0f, 0.0f, 0.0f, 0.0f, 0.0f, 0.0f, 0.0f, 0.0f};
+      if (ok[i]) load8<T, false>(w + vidx[i] * kVec, wv);
+      wsm[i * nthr + tid] = make_float4(wv[0], wv[1], wv[2], wv[3]);
+      wsm[(VPT + i) * nthr + tid] = make_float4(wv[4], wv[5], wv[6], wv[7]);
     }
     __syncthreads();
   }
-
-  bool ok[VPT];
-#pragma unroll
-  for (int i = 0; i < VPT; ++i) ok[i] = FULL || (tid + i * nthr < nvec);
 
   // per-thread element offsets of its vectors and row pointers that advance by a constant:
   // no per-row 64-bit address arithmetic in the loop
   int voff[VPT];
 #pragma unroll
-  for (int i = 0; i < VPT; ++i) voff[i] = (tid + i * nthr) * kVec;
+  for (int i = 0; i < VPT; ++i) voff[i] = vidx[i] * kVec;
   const int64_t in_step = static_cast<int64_t>(gridDim.x) * p.in_row_stride;
   const int64_t out_step = static_cast<int64_t>(gridDim.x) * (MODE == MODE_MXFP4 ? p.H / 2 : p.H);
   const T* __restrict__ xnext = static_cast<const T*>(p.in) + static_cast<int64_t>(blockIdx.x) * p.in_row_stride;
@@ -233,8 +260,7 @@ __global__ void __launch_bounds__(512) row_quant_kernel(const RowParams p, const
       const float inv_rms = __fdiv_rn(1.0f, __fsqrt_rn(var + p.eps));
 #pragma unroll
       for (int i = 0; i < VPT; ++i) {
-        const int idx = FULL ? tid + i * nthr : min(tid + i * nthr, nvec - 1);
-        const float4 wa = wsm[idx], wb = wsm[nvec + idx];
+        const float4 wa = wsm[i * nthr + tid], wb = wsm[(VPT + i) * nthr + tid];
         mul2(v[i][0], v[i][1], inv_rms, inv_rms);
         mul2(v[i][2], v[i][3], inv_rms, inv_rms);
         mul2(v[i][4], v[i][5], inv_rms, inv_rms);
@@ -287,34 +313,54 @@ __global__ void __launch_bounds__(512) row_quant_kernel(const RowParams p, const
         for (int j = 0; j < 8; j += 2) mul2(v[i][j], v[i][j + 1], r, r);
         if (ok[i]) stg_stream(orow + voff[i], pack_q8<Q>(v[i]));
       }
-    } else {  // MODE_GROUP / MODE_MXFP4: 1 x G groups, G/8 consecutive lanes per group
+    } else {  // MODE_GROUP / MODE_MXFP4: 1 x G groups; VG vectors per thread and 2^lanes_log2 lanes per group
       const int lanes_log2 = p.lanes_log2;
+      const bool lead_lane = (tid & ((1 << lanes_log2) - 1)) == 0;
 #pragma unroll
-      for (int i = 0; i < VPT; ++i) {
-        const int idx = tid + i * nthr;
-        const bool valid = ok[i];
+      for (int gi = 0; gi < VPT / VG; ++gi) {
+        const int i0 = gi * VG;
+        const bool valid = ok[i0];              // H % G == 0: a group is valid or invalid as a whole
         float gmax = 0.0f;
 #pragma unroll
-        for (int j = 0; j < 8; ++j) gmax = fmaxf(gmax, fabsf(v[i][j]));
+        for (int i = i0; i < i0 + VG; ++i)
+#pragma unroll
+          for (int j = 0; j < 8; ++j) gmax = fmaxf(gmax, fabsf(v[i][j]));
         gmax = seg_max_pow2(gmax, lanes_log2);  // all lanes participate (invalid ones carry 0)
-        const int g = idx >> lanes_log2;
-        const bool leader = valid && ((idx & ((1 << lanes_log2) - 1)) == 0);
+        const int g = vidx[i0] >> p.gv_log2;
+        const bool leader = valid && lead_lane;
         if constexpr (MODE == MODE_MXFP4) {
           const int e = rceil_e8m0(div_const<6>(gmax));
           const float d = e8m0_descale(e);
           if (leader) p.scales[row * p.ss0 + g * p.ss1] = e8m0_scale(e);
-          float q[8];
+          uint32_t code[VG];
 #pragma unroll
-          for (int j = 0; j < 8; j += 2) {
-            mul2(v[i][j], v[i][j + 1], d, d);
-            // the reference's intermediate rounding to bf16; its clamp to +-6 before that is what
-            // the saturating conversion below does anyway (RNE to bf16 is monotonic)
-            const __nv_bfloat162 b2 = __floats2bfloat162_rn(v[i][j], v[i][j + 1]);
-            const uint32_t wd = *reinterpret_cast<const uint32_t*>(&b2);
-            q[j] = bf16_lo(wd);
-            q[j + 1] = bf16_hi(wd);
+          for (int i = i0; i < i0 + VG; ++i) {
+            float q[8];
+#pragma unroll
+            for (int j = 0; j < 8; j += 2) {
+              mul2(v[i][j], v[i][j + 1], d, d);
+              // the reference's intermediate rounding to bf16; its clamp to +-6 before that is what
+              // the saturating conversion below does anyway (RNE to bf16 is monotonic)
+              const __nv_bfloat162 b2 = __floats2bfloat162_rn(v[i][j], v[i][j + 1]);
+              const uint32_t wd = *reinterpret_cast<const uint32_t*>(&b2);
+              q[j] = bf16_lo(wd);
+              q[j + 1] = bf16_hi(wd);
+            }
+            code[i - i0] = pack_e2m1x8(q);
           }
-          if (valid) stg_stream(orow + (voff[i] >> 1), pack_e2m1x8(q));
+          if constexpr (VG == 2) {
+            // G = 32: a lane pair holds vectors {0, 2} / {1, 3} of the group (interleaved so that the
+            // 128-bit loads fill whole sectors); swap one code word so that each lane stores 8
+            // contiguous bytes (vectors {0, 1} / {2, 3}) instead of two half-filled sectors
+            const bool odd = tid & 1;
+            const uint32_t got = __shfl_xor_sync(0xffffffffu, odd ? code[0] : code[1], 1);
+            const uint2 o2 = odd ? make_uint2(got, code[1]) : make_uint2(code[0], got);
+            if (valid) stg_stream(orow + ((voff[i0] - (odd ? kVec : 0)) >> 1) + (odd ? 8 : 0), o2);
+          } else {
+#pragma unroll
+            for (int i = i0; i < i0 + VG; ++i)
+              if (valid) stg_stream(orow + (voff[i] >> 1), code[i - i0]);
+          }
         } else {
           float s;
           if constexpr (Q == VXK_Q_INT8) {
@@ -326,11 +372,14 @@ __global__ void __launch_bounds__(512) row_quant_kernel(const RowParams p, const
           const float r = __frcp_rn(s);
           if (leader) p.scales[row * p.ss0 + g * p.ss1] = s;
 #pragma unroll
-          for (int j = 0; j < 8; j += 2) {
-            if constexpr (Q == VXK_Q_INT8) div_by2<false>(v[i][j], v[i][j + 1], s, r);
-            else mul2(v[i][j], v[i][j + 1], r, r);
+          for (int i = i0; i < i0 + VG; ++i) {
+#pragma unroll
+            for (int j = 0; j < 8; j += 2) {
+              if constexpr (Q == VXK_Q_INT8) div_by2<false>(v[i][j], v[i][j + 1], s, r);
+              else mul2(v[i][j], v[i][j + 1], r, r);
+            }
+            if (valid) stg_stream(orow + voff[i], pack_q8<Q>(v[i]));
           }
-          if (valid) stg_stream(orow + voff[i], pack_q8<Q>(v[i]));
         }
       }
     }
@@ -450,10 +499,10 @@ inline int resident_ctas(K kernel, int threads) {
   return n * sm_count();
 }
 
-template <typename T, int Q, int MODE, bool RMS, bool HAS_RES, int VPT, bool FULL>
+template <typename T, int Q, int MODE, bool RMS, bool HAS_RES, int VPT, bool FULL, int VG>
 inline int launch_row_vpt3(const RowParams& p, int64_t T_rows, int threads, cudaStream_t st) {
-  auto kernel = row_quant_kernel<T, Q, MODE, RMS, HAS_RES, VPT, FULL>;
-  const size_t smem = RMS ? static_cast<size_t>(p.nvec) * 32 : 0;
+  auto kernel = row_quant_kernel<T, Q, MODE, RMS, HAS_RES, VPT, FULL, VG>;
+  const size_t smem = RMS ? static_cast<size_t>(VPT) * threads * 32 : 0;
   if (smem > 48 * 1024) {
     static thread_local size_t configured = 0;     // per instantiation
     if (smem > configured) {
@@ -476,24 +525,35 @@ inline int launch_row_vpt3(const RowParams& p, int64_t T_rows, int threads, cuda
   kernel<<<grid, threads, smem, st>>>(p, T_rows);
   return 0;
 }
-template <typename T, int Q, int MODE, bool RMS, bool HAS_RES, int VPT>
+template <typename T, int Q, int MODE, bool RMS, bool HAS_RES, int VPT, int VG>
 inline int launch_row_vpt2(const RowParams& p, int64_t T_rows, int threads, cudaStream_t st) {
-  if (p.nvec == VPT * threads) return launch_row_vpt3<T, Q, MODE, RMS, HAS_RES, VPT, true>(p, T_rows, threads, st);
-  return launch_row_vpt3<T, Q, MODE, RMS, HAS_RES, VPT, false>(p, T_rows, threads, st);
+  if (p.nvec == VPT * threads) return launch_row_vpt3<T, Q, MODE, RMS, HAS_RES, VPT, true, VG>(p, T_rows, threads, st);
+  return launch_row_vpt3<T, Q, MODE, RMS, HAS_RES, VPT, false, VG>(p, T_rows, threads, st);
 }
-template <typename T, int Q, int MODE, bool RMS, int VPT>
-inline int launch_row_vpt(const RowParams& p, int64_t T_rows, int threads, cudaStream_t st) {
+template <typename T, int Q, int MODE, bool RMS, int VPT, int VG>
+inline int launch_row_vg(const RowParams& p, int64_t T_rows, int threads, cudaStream_t st) {
   if constexpr (RMS) {
-    if (p.residual != nullptr) return launch_row_vpt2<T, Q, MODE, RMS, true, VPT>(p, T_rows, threads, st);
+    if (p.residual != nullptr) return launch_row_vpt2<T, Q, MODE, RMS, true, VPT, VG>(p, T_rows, threads, st);
   }
-  return launch_row_vpt2<T, Q, MODE, RMS, false, VPT>(p, T_rows, threads, st);
+  return launch_row_vpt2<T, Q, MODE, RMS, false, VPT, VG>(p, T_rows, threads, st);
+}
+// vg = vectors of one group per thread: 1 outside the group modes, else min(VPT, 4, (G / 8) / 2)
+template <typename T, int Q, int MODE, bool RMS, int VPT>
+inline int launch_row_vpt(const RowParams& p, int64_t T_rows, int threads, int vg, cudaStream_t st) {
+  if constexpr ((MODE == MODE_GROUP || MODE == MODE_MXFP4) && VPT >= 2) {
+    if (vg == 2) return launch_row_vg<T, Q, MODE, RMS, VPT, 2>(p, T_rows, threads, st);
+    if constexpr (VPT >= 4) {
+      if (vg == 4) return launch_row_vg<T, Q, MODE, RMS, VPT, 4>(p, T_rows, threads, st);
+    }
+  }
+  return launch_row_vg<T, Q, MODE, RMS, VPT, 1>(p, T_rows, threads, st);
 }
 
 template <typename T, int Q, int MODE, bool RMS>
 int launch_row(const RowParams& p_in, int64_t T_rows, bool vec_ok, cudaStream_t st) {
   RowParams p = p_in;
-  p.lanes_log2 = 0;
-  while (p.group > 0 && (kVec << p.lanes_log2) < p.group) ++p.lanes_log2;
+  p.gv_log2 = 0;
+  while (p.group > 0 && (kVec << p.gv_log2) < p.group) ++p.gv_log2;
   if (T_rows == 0 || p.H == 0) return VXK_OK;
   const int nvec = p.nvec;
   // per-thread vectors: enough to keep one warp busy, 4 by default (two register
@@ -506,13 +566,26 @@ int launch_row(const RowParams& p_in, int64_t T_rows, bool vec_ok, cudaStream_t 
   while ((nvec + vpt - 1) / vpt > 256 && vpt < kMaxVpt) vpt *= 2;  // long rows: up to 8 x 512 threads
   if (vpt > kMaxVpt) vpt = kMaxVpt;
   const int threads = ((nvec + vpt - 1) / vpt + 31) / 32 * 32;
+  // group modes: runs of vg vectors of one group per thread, 2^lanes_log2 adjacent lanes per group
+  int vg = 1;
+  if (MODE == MODE_GROUP || MODE == MODE_MXFP4) {
+    static const int env_vg = [] { const char* e = getenv("VXK_ROW_VG"); return e ? atoi(e) : 0; }();
+    const int gv = 1 << p.gv_log2;
+    while (vg * 2 <= vpt && vg * 2 <= 4 && vg * 2 <= gv / 2) vg *= 2;
+    if (env_vg == 1 || (env_vg == 2 && vg >= 2)) vg = env_vg;
+    int l = 0;
+    while ((vg << l) < gv) ++l;
+    p.lanes_log2 = l;
+  } else {
+    p.lanes_log2 = 0;
+  }
   int not_launched = 1;
   if (vec_ok && threads <= 512) {
     switch (vpt) {
-      case 1: not_launched = launch_row_vpt<T, Q, MODE, RMS, 1>(p, T_rows, threads, st); break;
-      case 2: not_launched = launch_row_vpt<T, Q, MODE, RMS, 2>(p, T_rows, threads, st); break;
-      case 4: not_launched = launch_row_vpt<T, Q, MODE, RMS, 4>(p, T_rows, threads, st); break;
-      default: not_launched = launch_row_vpt<T, Q, MODE, RMS, 8>(p, T_rows, threads, st); break;
+      case 1: not_launched = launch_row_vpt<T, Q, MODE, RMS, 1>(p, T_rows, threads, vg, st); break;
+      case 2: not_launched = launch_row_vpt<T, Q, MODE, RMS, 2>(p, T_rows, threads, vg, st); break;
+      case 4: not_launched = launch_row_vpt<T, Q, MODE, RMS, 4>(p, T_rows, threads, vg, st); break;
+      default: not_launched = launch_row_vpt<T, Q, MODE, RMS, 8>(p, T_rows, threads, vg, st); break;
     }
   }
   if (not_launched) {
