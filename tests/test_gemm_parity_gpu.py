@@ -222,6 +222,40 @@ LLAMA70B = [(8192, 10240), (8192, 8192), (8192, 57344), (28672, 8192)]      # (K
 DEEPSEEK = [(7168, 1536), (1536, 24576), (512, 32768), (16384, 7168), (7168, 36864), (18432, 7168)]  # config 5
 
 
+@pytest.mark.parametrize("fp8", [E4, E5])
+@pytest.mark.parametrize("per_channel", [True, False])
+@pytest.mark.parametrize("bias", [False, True])
+@pytest.mark.parametrize("nk", [(384, 512), (1000, 1040), (4096, 4096), (136, 7168), (6144, 640)])
+@pytest.mark.parametrize("m", [3, 33, 64, 65, 128, 129, 200, 256])
+def test_fp8_gemm_skinny(ops, lib, fp8, per_channel, bias, nk, m):
+    """Small-M kernel (gemm_skinny.cuh: operands swapped, K split over a cluster, DSMEM reduction): token
+    tiles 32 / 64 / 128 / 256, N and K tails, odd numbers of K slices per cluster rank, every scale mode.
+    Same checker as tests/test_fp8_gemm_onednn.py:174-214 (dequantised matmul), atol = rtol = 1e-2."""
+    torch.manual_seed(m * 7 + nk[0])
+    n, k = nk
+    out_dtype = torch.bfloat16 if (m + n) % 2 else torch.float16
+    x = torch.randn(m, k, dtype=torch.float32) / 10.0
+    w = torch.randn(n, k, dtype=torch.float32) / 10.0
+    if per_channel:
+        xq, xs = oq.dynamic_per_token_scaled_fp8_quant(x, fp8)
+        wq, ws = oq.dynamic_per_token_scaled_fp8_quant(w, fp8)
+    else:
+        xs = x.abs().max().reshape(1) / torch.finfo(fp8).max
+        ws = w.abs().max().reshape(1) / torch.finfo(fp8).max
+        xq = (x / xs).clamp(-torch.finfo(fp8).max, torch.finfo(fp8).max).to(fp8)
+        wq = (w / ws).clamp(-torch.finfo(fp8).max, torch.finfo(fp8).max).to(fp8)
+    b = torch.randn(n, dtype=out_dtype) if bias else None
+    tc0, fb0 = gemm_stats(lib)
+    out = ops.fp8_gemm(xq.to(DEV), wq.to(DEV).t(), out_dtype, xs.to(DEV), ws.to(DEV),
+                       b.to(DEV) if bias else torch.Tensor())
+    assert gemm_stats(lib) == (tc0 + 1, fb0)
+    close(out, og.fp8_gemm_ref(xq, wq.t(), out_dtype, xs, ws, b))
+    # deterministic: the cluster reduction sums in rank order
+    out2 = ops.fp8_gemm(xq.to(DEV), wq.to(DEV).t(), out_dtype, xs.to(DEV), ws.to(DEV),
+                        b.to(DEV) if bias else torch.Tensor())
+    assert torch.equal(out, out2)
+
+
 def _gpu_ref(a_deq, w_deq, out_dtype):
     """fp32 matmul of dequantised operands on the GPU (TF32 off) as the full-size checker."""
     prev = torch.backends.cuda.matmul.allow_tf32

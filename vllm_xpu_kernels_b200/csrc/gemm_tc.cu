@@ -2,6 +2,7 @@
 // canonicalisation, launch of the tcgen05 kernels (gemm_tc.cuh) or of the CUDA-core
 // fallback (gemm_fallback.cu), and the two C-ABI entry points.
 #include "gemm_tc2_blk.cuh"
+#include "gemm_skinny.cuh"
 
 #include <mutex>
 
@@ -338,6 +339,78 @@ static int run_pair_block_scaled(Tc2Params tp, const void* A, int64_t lda_bytes,
   return two ? launch_tc2<KIND, BN, 2>(tp, ma, mb, msa, msb, st) : launch_tc2<KIND, BN, 1>(tp, ma, mb, msa, msb, st);
 }
 
+// Small-M FP8 GEMM (M <= 128): operands swapped, K split over a cluster.  See gemm_skinny.cuh.
+template <int MT>
+static int launch_skinny(SkinnyParams sp, const CUtensorMap& mw, const CUtensorMap& ma, int n_tiles, cudaStream_t st) {
+  using L = SkinnySmem<MT>;
+  auto kernel = gemm_skinny_kernel<MT>;
+  static std::once_flag once;
+  static cudaError_t attr_err = cudaSuccess;
+  std::call_once(once, [&] {
+    attr_err = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotalBytes);
+  });
+  if (attr_err != cudaSuccess)
+    return fail(VXK_ERR_CUDA, "cudaFuncSetAttribute(smem=%d): %s", L::kTotalBytes, cudaGetErrorString(attr_err));
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(n_tiles, sp.splits, 1);
+  cfg.blockDim = dim3(kSkinnyThreads);
+  cfg.dynamicSmemBytes = L::kTotalBytes;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[2];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 1;
+  attr[0].val.clusterDim.y = sp.splits;
+  attr[0].val.clusterDim.z = 1;
+  // programmatic dependent launch: prologue + weight prefetch overlap the previous kernel's tail
+  static const int pdl = env_int("VXK_SKINNY_PDL", 1);
+  attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[1].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl ? 2 : 1;
+  const cudaError_t e = cudaLaunchKernelEx(&cfg, kernel, sp, mw, ma);
+  if (e != cudaSuccess) return fail(VXK_ERR_CUDA, "gemm_skinny launch: %s", cudaGetErrorString(e));
+  g_gemm_tc_calls.fetch_add(1, std::memory_order_relaxed);
+  return check_launch("gemm_skinny");
+}
+
+static int run_skinny_f8(const TcParams& tp, const void* A, const void* W, int64_t M, int64_t N, int64_t K,
+                         int64_t lda, int64_t ldw, cudaStream_t st) {
+  SkinnyParams sp{};
+  sp.D = tp.D; sp.a_scale = tp.a_scale; sp.b_scale = tp.b_scale; sp.bias = tp.bias;
+  sp.M = (int)M; sp.N = (int)N; sp.ldd = tp.ldd;
+  sp.a_scale_mode = tp.a_scale_mode; sp.b_scale_mode = tp.b_scale_mode; sp.out_dtype = tp.out_dtype;
+  sp.bias_dtype = tp.bias_dtype; sp.fp8_fmt = tp.fp8_fmt;
+  sp.num_k_blocks = tp.num_k_blocks;
+  const int n_tiles = (int)((N + 127) / 128);
+  // K split: enough CTAs for one wave, every rank at least two ring stages, portable cluster size
+  static const int env_splits = env_int("VXK_SKINNY_SPLITS", 0);
+  const int mt = M <= 32 ? 32 : (M <= 64 ? 64 : (M <= 128 ? 128 : 256));
+  const int ks = mt <= 128 ? 2 : 1;
+  static const int env_pow2 = env_int("VXK_SKINNY_POW2", 1);
+  int splits = sm_count() / n_tiles;
+  if (splits > 8) splits = 8;
+  if (env_splits > 0) splits = env_splits > 8 ? 8 : env_splits;
+  const int max_by_k = sp.num_k_blocks / (2 * ks);
+  if (splits > max_by_k) splits = max_by_k;
+  if (splits < 1) splits = 1;
+  if (env_pow2) while (splits & (splits - 1)) --splits;   // cluster sizes 1 / 2 / 4 / 8
+  int per = (sp.num_k_blocks + splits - 1) / splits;
+  per = (per + ks - 1) / ks * ks;
+  splits = (sp.num_k_blocks + per - 1) / per;          // no empty rank
+  sp.kb_per_split = per;
+  sp.splits = splits;
+  CUtensorMap mw, ma;
+  int rc;
+  if ((rc = make_map_2d_u8(&mw, W, K, N, ldw, kBlockKBytes, 128, true))) return rc;
+  if ((rc = make_map_2d_u8(&ma, A, K, M, lda, kBlockKBytes, mt, true))) return rc;
+  switch (mt) {
+    case 32: return launch_skinny<32>(sp, mw, ma, n_tiles, st);
+    case 64: return launch_skinny<64>(sp, mw, ma, n_tiles, st);
+    case 128: return launch_skinny<128>(sp, mw, ma, n_tiles, st);
+    default: return launch_skinny<256>(sp, mw, ma, n_tiles, st);
+  }
+}
+
 }  // namespace vxk
 
 using namespace vxk;
@@ -395,6 +468,10 @@ extern "C" int vxk_fp8_gemm(void* D, const void* A, const void* B, const void* a
   if (operands_ok && a_scale_mode != 2) {
     tp.a_scale = static_cast<const float*>(a_scale);
     tp.b_scale = static_cast<const float*>(b_scale);
+    static const int skinny_max_m = env_int("VXK_SKINNY_MAX_M", 256);
+    // 129..256 tokens: only while the 128-row weight tiles fit one wave (else the general kernels win)
+    if (M <= skinny_max_m && M <= 256 && K >= 512 && (M <= 128 || (N + 127) / 128 <= sm_count()))
+      return run_skinny_f8(tp, A, B, M, N, K, lda, b_stride_n, st);
     const int bn = single_cta_bn(M, N, 256);
     if (!force_single() && prefer_pair(M, N, bn, 256)) {
       Tc2Params t2{};
