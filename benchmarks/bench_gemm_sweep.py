@@ -4,6 +4,8 @@
   llama8b_fp8    per-token x per-channel FP8 W8A8, Llama-3-8B (K, N)         config 3
   llama70b_mxfp4 MXFP4 (E2M1 + E8M0 per 32), Llama-3-70B (K, N)              config 4
   dsv3_blockfp8  1x128 / 128x128 fp32 block-scaled FP8, DeepSeek-V3 (K, N)   config 5
+  llama8b_w8a16  bf16 activations x per-channel FP8 weights (fp8_gemm_w8a16), Llama-3-8B (K, N);
+                 tensor peak = bf16 dense, weight stream 1 B / element         SURVEY 8(f) #1
 
 For every (shape, M) the roofline time is max(2MNK / tensor peak, algorithmic bytes / HBM peak)
 (small M is bound by streaming the weight from HBM) and the line reports
@@ -30,6 +32,7 @@ DEV = "cuda"
 SETS = {
     "llama8b_fp8": [(4096, 6144), (4096, 4096), (4096, 28672), (14336, 4096)],
     "llama70b_mxfp4": [(8192, 10240), (8192, 8192), (8192, 57344), (28672, 8192)],
+    "llama8b_w8a16": [(4096, 6144), (4096, 4096), (4096, 28672), (14336, 4096)],
     "dsv3_blockfp8": [(7168, 1536), (1536, 24576), (512, 32768), (16384, 7168), (7168, 36864), (18432, 7168)],
 }
 
@@ -45,6 +48,13 @@ def make_case(kind, M, K, N, copies):
             sw = torch.rand(N, 1, device=DEV) * 0.01 + 0.001
             fns.append(lambda w=w, sw=sw: torch.ops._xpu_C.fp8_gemm(a, w.t(), torch.bfloat16, sa, sw, None))
         nbytes = M * K + K * N + 2 * M * N + 4 * (M + N)
+    elif kind == "llama8b_w8a16":
+        a = torch.randn(M, K, device=DEV, dtype=torch.bfloat16) / 4
+        for _ in range(copies):
+            w = (torch.randn(N, K, device=DEV) / 4).to(E4)
+            sw = torch.rand(N, device=DEV) * 0.01 + 0.001
+            fns.append(lambda w=w, sw=sw: torch.ops._xpu_C.fp8_gemm_w8a16(a, w.t(), sw, None))
+        nbytes = 2 * M * K + K * N + 2 * M * N + 4 * N
     elif kind == "llama70b_mxfp4":
         a = torch.randint(0, 256, (M, K // 2), dtype=torch.uint8, device=DEV).view(torch.float4_e2m1fn_x2)
         sa = torch.randint(118, 130, (M, K // 32), dtype=torch.uint8, device=DEV).view(E8)
@@ -112,14 +122,14 @@ def time_graph(fns, iters):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--graph", action="store_true", help="time CUDA-graph replays instead of eager launches")
-    ap.add_argument("--sets", default=",".join(SETS))
+    ap.add_argument("--sets", default="llama8b_fp8,llama70b_mxfp4,dsv3_blockfp8")
     ap.add_argument("--Ms", default="1,16,64,256,1024,4096,8192")
     ap.add_argument("--json", default=None)
     args = ap.parse_args()
     pk = peaks()
     out = []
     for kind in args.sets.split(","):
-        peak_tf = (4.0 if kind == "llama70b_mxfp4" else 2.0) * pk["bf16"]
+        peak_tf = (4.0 if kind == "llama70b_mxfp4" else 1.0 if kind == "llama8b_w8a16" else 2.0) * pk["bf16"]
         for (K, N) in SETS[kind]:
             wbytes = K * N // (2 if kind == "llama70b_mxfp4" else 1)
             for M in [int(m) for m in args.Ms.split(",")]:

@@ -21,7 +21,7 @@
 extern "C" {
 #endif
 
-#define VXK_ABI_VERSION 2
+#define VXK_ABI_VERSION 3
 
 typedef struct CUstream_st* vxk_stream_t; /* == cudaStream_t */
 
@@ -192,6 +192,26 @@ int vxk_fp4_gemm(void* D, const void* A, const void* B, const void* a_scale, con
  * it the call still runs, on the single-CTA kernel.
  * ref: the per-call scratchpad of fp4_gemm_w4a4.h:159-162. */
 int64_t vxk_fp4_gemm_workspace_bytes(int64_t M, int64_t N, int64_t K);
+
+/* ------------------------------------------------------- (f) next #1 ---
+ * ref: fp8_gemm_w8a16  csrc/xpu/onednn/onednn_matmul.cpp:81-99 -> dnnl_matmul_w8a16_fp8
+ *      csrc/xpu/onednn/fp8_gemm_w8a16.h:13-145, schema csrc/xpu/torch_bindings.cpp:19-21
+ *
+ *   D[M,N] = A[M,K] (bf16 / f16, act_dtype; D has the same type) x dequant(B), + bias.
+ *   A: row stride lda (elements).  B(k, n) at B[k*b_stride_k + n*b_stride_n], FP8 bytes
+ *      (b_stride_k == 1 is the "nt" layout W[N,K] the tensor-core kernel takes; anything
+ *      else runs on the CUDA-core kernel).
+ *   b_scale (fp32): b_scale_mode 0 = one scalar, 1 = per output channel [N],
+ *      2 = block: sB[k/group_k, n/group_n] at b_scale[kb*sb0 + nb*sb1]
+ *      (fp8_gemm_w8a16.h:29-35: 2-D scale with size(0) > 1).
+ *   bias: nullable, [N], bias_dtype VXK_F32/F16/BF16.
+ *   force_fallback: testing aid, non-zero routes the call to the CUDA-core kernel.
+ */
+int vxk_fp8_gemm_w8a16(void* D, const void* A, const void* B, const float* b_scale, const void* bias,
+                       int64_t M, int64_t N, int64_t K, int64_t lda, int64_t b_stride_k,
+                       int64_t b_stride_n, int64_t ldd, int b_scale_mode, int64_t group_k,
+                       int64_t group_n, int64_t sb0, int64_t sb1, int act_dtype, int fp8_dtype,
+                       int bias_dtype, int force_fallback, vxk_stream_t stream);
 
 #ifdef __cplusplus
 }

@@ -112,3 +112,47 @@ def fp4_gemm_ref(A: torch.Tensor, B: torch.Tensor, A_scale: torch.Tensor,
     if bias is not None and bias.numel() > 0:
         d = d + bias.to(torch.float64)
     return d.to(out_dtype)
+
+
+# --------------------------------------------------------------------------
+# (f)#1  fp8_gemm_w8a16   onednn_matmul.cpp:81-99, fp8_gemm_w8a16.h:13-145
+# --------------------------------------------------------------------------
+def fp8_gemm_w8a16_ref(A: torch.Tensor, B: torch.Tensor,
+                       B_scale: Optional[torch.Tensor] = None,
+                       bias: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """A [M,K] bf16/f16, B [K,N] fp8 (any strides).  Weight scale by shape
+    (fp8_gemm_w8a16.h:29-35,103-128): 2-D with size(0) > 1 = block
+    [K/gs, N/gs]; numel 1 = per tensor; else per output channel ([N] or [1,N]).
+    Exact statement: float64 dequantise, float64 accumulate, one rounding to
+    A.dtype."""
+    M, K = A.shape
+    N = B.shape[1]
+    a = A.to(torch.float32).to(torch.float64)
+    b = B.to(torch.float32).to(torch.float64)
+    if B_scale is not None and B_scale.numel() > 0:
+        if B_scale.dim() == 2 and B_scale.shape[0] > 1:
+            b = b * _expand(B_scale, K, N)
+        else:
+            sb = B_scale.to(torch.float32).to(torch.float64).reshape(-1)
+            b = b * (sb.reshape(1, -1) if sb.numel() > 1 else sb)
+    d = a @ b
+    if bias is not None and bias.numel() > 0:
+        d = d + bias.to(torch.float64)
+    return d.to(A.dtype)
+
+
+def fp8_block_dequant_2d(q: torch.Tensor, s: torch.Tensor, bm: int, bn: int,
+                         dtype: torch.dtype) -> torch.Tensor:
+    """tests/ops/fp8_quant_op.py:81-106: weight [N,K] fp8 with scales
+    [N/bm, K/bn]: fp32 multiply, one rounding to `dtype`."""
+    gm, gn = s.shape
+    M, N = q.shape
+    return (q.to(F32).reshape(gm, bm, gn, bn) * s.to(F32).reshape(gm, 1, gn, 1)).reshape(M, N).to(dtype)
+
+
+def fp8_gemm_w8a16_literal(A: torch.Tensor, W_fp8: torch.Tensor, scale_nk: torch.Tensor) -> torch.Tensor:
+    """tests/test_fp8_gemm_onednn.py:105-111,246-248,393-396: the weight
+    W_fp8 [N,K] is dequantised INTO the activation dtype (scale broadcastable
+    to [N,K], also cast to that dtype), then torch.matmul in that dtype."""
+    w = W_fp8.to(A.dtype) * scale_nk.to(A.dtype)
+    return torch.matmul(A, w.t())

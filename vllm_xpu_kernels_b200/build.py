@@ -35,6 +35,7 @@ CU_SOURCES = {
     "quant_flat.cu": ["-fmad=false"],
     "gemm_fallback.cu": [],
     "gemm_tc.cu": [],
+    "gemm_w8a16.cu": [],
 }
 # every header under csrc/ feeds every object's digest (a header missing here means stale objects)
 HEADERS = sorted(f for f in os.listdir(CSRC) if f.endswith((".cuh", ".h"))) + [os.path.join(ROOT, "include", "vxk_b200.h")]

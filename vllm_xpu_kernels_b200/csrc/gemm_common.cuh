@@ -32,6 +32,9 @@ struct GemmParams {
 
 int launch_gemm_fallback(const GemmParams& p, bool is_fp4, cudaStream_t st);
 extern std::atomic<uint64_t> g_gemm_tc_calls, g_gemm_fallback_calls;
+// 2-D row-major byte tensor [rows, cols_bytes] with row pitch `pitch_bytes`, box [box_rows, box_cols] (gemm_tc.cu)
+int make_map_2d_u8(CUtensorMap* map, const void* base, uint64_t cols_bytes, uint64_t rows, uint64_t pitch_bytes,
+                   uint32_t box_cols, uint32_t box_rows, bool swizzle128);
 
 // ----------------------------------------------------------------------------
 // device-side PTX wrappers

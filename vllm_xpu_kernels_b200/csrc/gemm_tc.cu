@@ -26,7 +26,7 @@ static EncodeTiledFn encode_tiled_fn() {
 }
 
 // 2-D row-major byte tensor [rows, cols_bytes] with row pitch `pitch_bytes`, box [box_rows, box_cols]
-static int make_map_2d_u8(CUtensorMap* map, const void* base, uint64_t cols_bytes, uint64_t rows,
+int make_map_2d_u8(CUtensorMap* map, const void* base, uint64_t cols_bytes, uint64_t rows,
                           uint64_t pitch_bytes, uint32_t box_cols, uint32_t box_rows, bool swizzle128) {
   EncodeTiledFn fn = encode_tiled_fn();
   if (!fn) return fail(VXK_ERR_CUDA, "cuTensorMapEncodeTiled entry point not available");

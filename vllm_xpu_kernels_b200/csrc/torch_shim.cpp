@@ -586,6 +586,65 @@ Tensor fp4_gemm(const Tensor& A, const Tensor& B, const Tensor& A_scale, const T
   return result;
 }
 
+// ref: onednn_matmul.cpp:81-99, fp8_gemm_w8a16.h:13-145
+Tensor fp8_gemm_w8a16(const Tensor& A, const Tensor& B, const std::optional<Tensor>& B_scale_,
+                      const std::optional<Tensor>& bias_) {
+  const c10::cuda::CUDAGuard guard(A.device());
+  TORCH_CHECK(A.scalar_type() == at::kHalf || A.scalar_type() == at::kBFloat16,
+              "Unsupported data type for fp8 matmul: ", A.scalar_type());      // fp8_gemm_w8a16.h:51-53
+  Tensor result = check_and_create_output_tensor(A, B, A.scalar_type());
+  const auto b_st = B.scalar_type();
+  TORCH_CHECK(b_st == at::kFloat8_e5m2 || b_st == at::kFloat8_e4m3fn,
+              "weight must be f8_e5m2 or f8_e4m3fn for fp8 matmul");
+  check_cuda(B, "B");
+  const ARows r = flatten_rows(A, result);
+  const int64_t K = A.size(-1), N = B.size(1);
+  TORCH_CHECK(B.size(0) == K, "A and B have mismatched K: ", K, " vs ", B.size(0));
+  if (r.M == 0 || N == 0) return result;
+
+  // missing scale defaults to 1.0 (onednn_matmul.cpp:94-96); any float dtype is taken, the kernels read fp32
+  Tensor B_scale = B_scale_.has_value() && B_scale_->defined() && B_scale_->numel() > 0
+                       ? *B_scale_ : at::ones({1}, A.options().dtype(at::kFloat));
+  check_cuda(B_scale, "B_scale");
+  if (B_scale.scalar_type() != at::kFloat) {
+    TORCH_CHECK(B_scale.scalar_type() == at::kHalf || B_scale.scalar_type() == at::kBFloat16,
+                "weight scale must be float32, float16 or bfloat16");
+    B_scale = B_scale.to(at::kFloat);
+  }
+  int b_mode;
+  int64_t gk = 0, gn = 0, sb0 = 0, sb1 = 0;
+  const bool is_block = B_scale.dim() == 2 && B_scale.size(0) > 1;   // fp8_gemm_w8a16.h:29-35
+  if (is_block) {
+    TORCH_CHECK(K % B_scale.size(0) == 0 && N % B_scale.size(1) == 0, "K and N must be divisible by the scale grid");
+    gk = K / B_scale.size(0);
+    gn = N / B_scale.size(1);
+    sb0 = B_scale.stride(0); sb1 = B_scale.stride(1);
+    b_mode = 2;
+  } else if (B_scale.numel() == 1) {
+    b_mode = 0;
+  } else {
+    TORCH_CHECK(B_scale.numel() == N, "per-channel weight scale must have N elements ([N] or [1, N]), got ",
+                B_scale.sizes());
+    B_scale = B_scale.contiguous();
+    b_mode = 1;
+  }
+  const void* bias = nullptr;
+  int bias_dtype = VXK_F32;
+  if (bias_.has_value() && bias_->defined() && bias_->numel() > 0) {
+    TORCH_CHECK(bias_->numel() == N && bias_->is_contiguous(), "only a contiguous [N] bias is supported, got ",
+                bias_->sizes());
+    check_cuda(*bias_, "bias");
+    bias = bias_->data_ptr();
+    bias_dtype = bias_dtype_of(*bias_);
+  }
+  check_rc(vxk_fp8_gemm_w8a16(result.data_ptr(), A.data_ptr(), B.data_ptr(), B_scale.data_ptr<float>(), bias, r.M, N,
+                              K, r.lda, B.stride(0), B.stride(1), r.ldd, b_mode, gk, gn, sb0, sb1,
+                              A.scalar_type() == at::kBFloat16 ? VXK_BF16 : VXK_F16,
+                              b_st == at::kFloat8_e4m3fn ? VXK_Q_E4M3 : VXK_Q_E5M2, bias_dtype, 0, cur_stream()),
+           "fp8_gemm_w8a16");
+  return result;
+}
+
 }  // namespace
 
 // Schemas verbatim from /root/reference/csrc/torch_bindings.cpp (line numbers in SURVEY.md 8b).
@@ -638,6 +697,7 @@ TORCH_LIBRARY_IMPL(_C, CUDA, ops) {
 TORCH_LIBRARY_FRAGMENT(_xpu_C, xpu_ops) {
   xpu_ops.def("fp8_gemm(Tensor A, Tensor B, ScalarType? out_dtype, Tensor? A_scale_, Tensor? B_scale_, "
               "Tensor? bias_) -> Tensor");
+  xpu_ops.def("fp8_gemm_w8a16(Tensor A, Tensor B, Tensor? B_scale_, Tensor? bias_) -> Tensor");
   xpu_ops.def("fp4_gemm(Tensor A, Tensor B, Tensor A_scale, Tensor B_scale, ScalarType? out_dtype, "
               "Tensor? bias_) -> Tensor");
 }
@@ -645,4 +705,5 @@ TORCH_LIBRARY_FRAGMENT(_xpu_C, xpu_ops) {
 TORCH_LIBRARY_IMPL(_xpu_C, CUDA, xpu_ops) {
   xpu_ops.impl("fp8_gemm", &fp8_gemm);
   xpu_ops.impl("fp4_gemm", &fp4_gemm);
+  xpu_ops.impl("fp8_gemm_w8a16", &fp8_gemm_w8a16);
 }

@@ -36,6 +36,11 @@ def fp8_gemm(input, weight, out_dtype, scale_act, scale_wei, bias=None):
     return torch.ops._xpu_C.fp8_gemm(input, weight, out_dtype, scale_act, scale_wei, bias)
 
 
+def fp8_gemm_w8a16(input, weight, scale_wei, bias=None):
+    """tests/register_ops.py:412-415 (its 4th argument, named scale_act there, is the bias slot of the schema)."""
+    return torch.ops._xpu_C.fp8_gemm_w8a16(input, weight, scale_wei, bias)
+
+
 def fp4_gemm(input, weight, scale_act, scale_wei, out_dtype, bias=None):
     return torch.ops._xpu_C.fp4_gemm(input, weight, scale_act, scale_wei, out_dtype, bias)
 
