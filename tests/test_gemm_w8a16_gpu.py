@@ -185,3 +185,36 @@ def test_w8a16_errors(ops):
         ops.fp8_gemm_w8a16(x.half()[:, :32], w, None, None)                    # K mismatch
     out = ops.fp8_gemm_w8a16(x.half()[:0], w, None, None)
     assert out.shape == (0, 32)
+
+
+@pytest.mark.parametrize("fp8", [E4, E5])
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+@pytest.mark.parametrize("mode", ["tensor", "channel", "block"])
+@pytest.mark.parametrize("mnk", [(1, 4096, 4096), (17, 1000, 1536), (33, 384, 8192), (65, 136, 640),
+                                 (128, 256, 2048), (7, 28672, 512)])
+def test_w8a16_small_m_kernel(ops, lib, fp8, dtype, mode, mnk):
+    """The swapped-operand, cluster split-K kernel (M <= 128, K % 128 == 0): every K split count from 1
+    to 8, partial 128-row weight tiles, bias, all three scale modes."""
+    torch.manual_seed(7)
+    m, n, k = mnk
+    if mode == "block" and (n % 128 or k % 128):
+        pytest.skip("shape not divisible by the 128 x 128 block")
+    x = torch.randn(m, k, dtype=dtype) / 10.0
+    w = torch.randn(n, k, dtype=torch.float32) / 10.0
+    b = torch.randn(n, dtype=dtype) / 4
+    if mode == "tensor":
+        s = torch.tensor(0.02)
+        wq = oq.static_scaled_fp8_quant(w, s, fp8)
+        s_op = s_ref = s
+    elif mode == "channel":
+        wq, ws = oq.dynamic_per_token_scaled_fp8_quant(w, fp8)
+        s_op, s_ref = ws.flatten(), ws.flatten()
+    else:
+        wq, ws = og.fp8_block_quant_2d(w, 128, 128)
+        wq = wq if fp8 == E4 else wq.float().to(fp8)
+        s_op = s_ref = ws.t().contiguous()
+    tc0, fb0 = gemm_stats(lib)
+    out = ops.fp8_gemm_w8a16(x.to(DEV), wq.to(DEV).t(), s_op.to(DEV), b.to(DEV))
+    tc1, fb1 = gemm_stats(lib)
+    assert (tc1 - tc0, fb1 - fb0) == (1, 0)
+    close(out, og.fp8_gemm_w8a16_ref(x, wq.t(), s_ref, b))

@@ -1,7 +1,7 @@
 // Host side of fp8_gemm_w8a16 (16-bit activations x FP8 weights): eligibility checks, TMA
 // tensor maps, tile-width choice, launch of gemm_w8a16_kernel (gemm_w8a16.cuh) or of the
 // CUDA-core kernel below for layouts TMA cannot express (N-major W, unaligned rows).
-#include "gemm_w8a16.cuh"
+#include "gemm_w8a16_skinny.cuh"
 
 #include <mutex>
 
@@ -120,6 +120,78 @@ static bool w16_force_fallback() {
   return v;
 }
 
+// ---- small-M path (M <= 128): operands swapped, K split over a cluster.  See gemm_w8a16_skinny.cuh ----
+template <int MT, bool BF16, bool E5M2>
+static int launch_w16_skinny(const W16SkinnyParams& sp, const CUtensorMap& mw, const CUtensorMap& ma, int n_tiles,
+                             cudaStream_t st) {
+  using L = W16SkinnySmem<MT>;
+  auto kernel = gemm_w8a16_skinny_kernel<MT, BF16, E5M2>;
+  static std::once_flag once;
+  static cudaError_t attr_err = cudaSuccess;
+  std::call_once(once, [&] {
+    attr_err = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotalBytes);
+  });
+  if (attr_err != cudaSuccess)
+    return fail(VXK_ERR_CUDA, "cudaFuncSetAttribute(smem=%d): %s", L::kTotalBytes, cudaGetErrorString(attr_err));
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(n_tiles, sp.splits, 1);
+  cfg.blockDim = dim3(kW16SkThreads);
+  cfg.dynamicSmemBytes = L::kTotalBytes;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[2];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 1;
+  attr[0].val.clusterDim.y = sp.splits;
+  attr[0].val.clusterDim.z = 1;
+  static const int pdl = [] { const char* e = getenv("VXK_SKINNY_PDL"); return e ? atoi(e) : 1; }();
+  attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[1].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl ? 2 : 1;
+  const cudaError_t e = cudaLaunchKernelEx(&cfg, kernel, sp, mw, ma);
+  if (e != cudaSuccess) return fail(VXK_ERR_CUDA, "gemm_w8a16_skinny launch: %s", cudaGetErrorString(e));
+  g_gemm_tc_calls.fetch_add(1, std::memory_order_relaxed);
+  return check_launch("gemm_w8a16_skinny");
+}
+
+template <int MT>
+static int launch_w16_skinny_types(const W16SkinnyParams& sp, const CUtensorMap& mw, const CUtensorMap& ma, int n_tiles,
+                                   bool bf16, bool e5m2, cudaStream_t st) {
+  if (bf16) return e5m2 ? launch_w16_skinny<MT, true, true>(sp, mw, ma, n_tiles, st)
+                        : launch_w16_skinny<MT, true, false>(sp, mw, ma, n_tiles, st);
+  return e5m2 ? launch_w16_skinny<MT, false, true>(sp, mw, ma, n_tiles, st)
+              : launch_w16_skinny<MT, false, false>(sp, mw, ma, n_tiles, st);
+}
+
+static int run_w16_skinny(W16SkinnyParams sp, const void* A, const void* W, int64_t M, int64_t N, int64_t K,
+                          int64_t lda, int64_t ldw, bool bf16, bool e5m2, cudaStream_t st) {
+  const int n_tiles = (int)((N + 127) / 128);
+  sp.num_k_blocks = (int)(K / kW16SkBlockK);
+  // K split: enough CTAs for one wave, every rank at least two raw stages, cluster sizes 1 / 2 / 4 / 8
+  static const int env_splits = [] { const char* e = getenv("VXK_W16_SPLITS"); return e ? atoi(e) : 0; }();
+  int splits = sm_count() / n_tiles;
+  if (splits > 8) splits = 8;
+  if (env_splits > 0) splits = env_splits > 8 ? 8 : env_splits;
+  if (splits > sp.num_k_blocks / 2) splits = sp.num_k_blocks / 2;
+  if (splits < 1) splits = 1;
+  while (splits & (splits - 1)) --splits;
+  const int per = (sp.num_k_blocks + splits - 1) / splits;
+  splits = (sp.num_k_blocks + per - 1) / per;            // no empty rank
+  sp.kb_per_split = per;
+  sp.splits = splits;
+  const int mt = M <= 32 ? 32 : (M <= 64 ? 64 : 128);
+  CUtensorMap mw, ma;
+  int rc;
+  if ((rc = make_map_2d_u8(&mw, W, K, N, ldw, kW16SkBlockK, 128, true))) return rc;
+  if ((rc = make_map_2d_u8(&ma, A, static_cast<uint64_t>(K) * 2, M, static_cast<uint64_t>(lda) * 2, 128, mt, true)))
+    return rc;
+  switch (mt) {
+    case 32: return launch_w16_skinny_types<32>(sp, mw, ma, n_tiles, bf16, e5m2, st);
+    case 64: return launch_w16_skinny_types<64>(sp, mw, ma, n_tiles, bf16, e5m2, st);
+    default: return launch_w16_skinny_types<128>(sp, mw, ma, n_tiles, bf16, e5m2, st);
+  }
+}
+
 }  // namespace vxk
 
 using namespace vxk;
@@ -150,6 +222,17 @@ extern "C" int vxk_fp8_gemm_w8a16(void* D, const void* A, const void* B, const f
     gemm_w8a16_fallback_kernel<<<grid, 1024, 0, st>>>(fp);
     g_gemm_fallback_calls.fetch_add(1, std::memory_order_relaxed);
     return check_launch("gemm_w8a16_fallback");
+  }
+
+  static const int skinny_max_m = [] { const char* e = getenv("VXK_W16_SKINNY_MAX_M"); return e ? atoi(e) : 128; }();
+  if (M <= skinny_max_m && M <= 128 && K % kW16SkBlockK == 0 && K >= 512 &&
+      (b_scale_mode != 2 || group_k % kW16SkBlockK == 0)) {
+    W16SkinnyParams sp{};
+    sp.D = D; sp.b_scale = b_scale; sp.bias = bias; sp.M = (int)M; sp.N = (int)N; sp.ldd = ldd;
+    sp.b_scale_mode = b_scale_mode; sp.out_dtype = act_dtype; sp.bias_dtype = bias_dtype;
+    sp.sb0 = sb0; sp.sb1 = sb1;
+    sp.group_k = b_scale_mode == 2 ? (int)group_k : 1; sp.group_n = b_scale_mode == 2 ? (int)group_n : 1;
+    return run_w16_skinny(sp, A, B, M, N, K, lda, b_stride_n, act_dtype == VXK_BF16, fp8_dtype == VXK_Q_E5M2, st);
   }
 
   W16Params wp{};

@@ -61,19 +61,41 @@ __device__ __forceinline__ uint32_t fp8x2_to_f16x2(uint32_t pair) {
   else asm("cvt.rn.f16x2.e4m3x2 %0, %1;" : "=r"(out) : "h"(in));
   return out;
 }
-// two FP8 codes -> packed bf16x2 (exact) without going through fp32: put sign / exponent / mantissa
-// bits where bf16 keeps them (exponent still carrying the FP8 bias), then one packed multiply by
-// 2^(127 - bias) fixes the bias and normalises FP8 subnormals in the same step.
+// four FP8 codes (one 32-bit word) -> two packed bf16x2 words (exact) without going through fp32:
+// sign / exponent / mantissa bits are put where bf16 keeps them (the exponent still carrying the FP8
+// bias), then one packed multiply by 2^(127 - bias) fixes the bias and normalises FP8 subnormals in
+// the same step.  The 4-bit (e4m3) / 3-bit (e5m2) shift is done on all four codes at once, split into
+// the byte that becomes the high half-byte (sign + upper magnitude bits) and the byte that becomes the
+// low one; two byte permutes interleave them: 7 ALU-pipe instructions + 2 multiplies per 4 codes (the
+// widening is bound by the half-rate ALU pipe, ncu profiles/r01e_w8a16_*.csv).
 template <bool E5M2>
-__device__ __forceinline__ uint32_t fp8x2_to_bf16x2(uint32_t word, uint32_t sel) {
-  const uint32_t spread = __byte_perm(word, 0u, sel);              // code << 8 in each half
+__device__ __forceinline__ void fp8x4_to_bf16x4(uint32_t word, uint32_t& lo, uint32_t& hi) {
   constexpr int sh = E5M2 ? 3 : 4;
-  constexpr uint32_t mag = E5M2 ? 0x0fe00fe0u : 0x07f007f0u;
-  const uint32_t t = ((spread >> sh) & mag) | (spread & 0x80008000u);
-  constexpr uint32_t fix = E5M2 ? 0x77807780u : 0x7b807b80u;       // bf16 2^112 / 2^120, packed
-  uint32_t out;
-  asm("mul.rn.bf16x2 %0, %1, %2;" : "=r"(out) : "r"(t), "r"(fix));
-  return out;
+  constexpr uint32_t hmask = E5M2 ? 0x0f0f0f0fu : 0x07070707u;
+  constexpr uint32_t lmask = E5M2 ? 0xe0e0e0e0u : 0xf0f0f0f0u;
+  const uint32_t x = ((word >> sh) & hmask) | (word & 0x80808080u);   // high bytes: s000 0eee (e4m3)
+  const uint32_t y = (word << (8 - sh)) & lmask;                      // low bytes:  emmm 0000
+  const uint32_t t0 = __byte_perm(y, x, 0x5140u);                     // codes 0, 1
+  const uint32_t t1 = __byte_perm(y, x, 0x7362u);                     // codes 2, 3
+  constexpr uint32_t fix = E5M2 ? 0x77807780u : 0x7b807b80u;          // bf16 2^112 / 2^120, packed
+  asm("mul.rn.bf16x2 %0, %1, %2;" : "=r"(lo) : "r"(t0), "r"(fix));
+  asm("mul.rn.bf16x2 %0, %1, %2;" : "=r"(hi) : "r"(t1), "r"(fix));
+}
+
+// shared-space accesses with 32-bit addresses (a generic pointer costs 64-bit address arithmetic and the
+// generic load / store path in the converters' inner loop)
+__device__ __forceinline__ uint4 lds128(uint32_t addr) {
+  uint4 v;
+  asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ void sts128(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+  asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
+}
+// wait of a warp that has nothing to do for a long time (epilogue warps during the main loop): poll with
+// back-off so that the polling does not take issue slots from the converter warps on the same scheduler
+__device__ __forceinline__ void mbar_wait_backoff(uint64_t* bar, uint32_t phase) {
+  while (!mbar_try_wait(bar, phase)) __nanosleep(256);
 }
 
 // 16 FP8 codes -> 16 activation-type values (8 packed words), optional fp32 scale folded in.
@@ -97,8 +119,7 @@ __device__ __forceinline__ void widen16(const uint4& raw, float s, uint32_t (&w)
         }
       }
     } else if constexpr (BF16) {
-      w[2 * i] = fp8x2_to_bf16x2<E5M2>(in[i], 0x1404u);
-      w[2 * i + 1] = fp8x2_to_bf16x2<E5M2>(in[i], 0x3424u);
+      fp8x4_to_bf16x4<E5M2>(in[i], w[2 * i], w[2 * i + 1]);
     } else {
       w[2 * i] = fp8x2_to_f16x2<E5M2>(in[i]);
       w[2 * i + 1] = fp8x2_to_f16x2<E5M2>(in[i] >> 16);
@@ -223,8 +244,14 @@ gemm_w8a16_kernel(const W16Params wp, const __grid_constant__ CUtensorMap map_a,
       const int n0 = (tile / p.num_m_blocks) * BLOCK_N;
       for (int kb = 0; kb < p.num_k_blocks; ++kb) {
         mbar_wait(&full_bar[stage], phase);
-        const uint8_t* raw = stage_raw(stage);
-        uint8_t* dst = stage_w(stage);
+        const uint32_t raw = smem_u32(stage_raw(stage));
+        const uint32_t dst = smem_u32(stage_w(stage));
+        uint4 v[kIter];
+#pragma unroll
+        for (int i = 0; i < kIter; ++i) {
+          const int c = i * 256 + ct;
+          if (kChunks % 256 == 0 || c < kChunks) v[i] = lds128(raw + c * 16);
+        }
 #pragma unroll
         for (int i = 0; i < kIter; ++i) {
           const int c = i * 256 + ct;
@@ -237,13 +264,12 @@ gemm_w8a16_kernel(const W16Params wp, const __grid_constant__ CUtensorMap map_a,
               s = __ldg(wp.blk_scale + static_cast<int64_t>((kb * kW16BlockK) / wp.group_k) * wp.sb0 +
                         static_cast<int64_t>(nn / wp.group_n) * wp.sb1);
             }
-            const uint4 v = *reinterpret_cast<const uint4*>(raw + c * 16);
             uint32_t w[8];
-            widen16<BF16, E5M2, SCALED>(v, s, w);
-            uint8_t* rowp = dst + row * 128;
+            widen16<BF16, E5M2, SCALED>(v[i], s, w);
+            const uint32_t rowp = dst + row * 128;
             const int sw = row & 7;
-            *reinterpret_cast<uint4*>(rowp + (((2 * j) ^ sw) << 4)) = make_uint4(w[0], w[1], w[2], w[3]);
-            *reinterpret_cast<uint4*>(rowp + (((2 * j + 1) ^ sw) << 4)) = make_uint4(w[4], w[5], w[6], w[7]);
+            sts128(rowp + (((2 * j) ^ sw) << 4), w[0], w[1], w[2], w[3]);
+            sts128(rowp + (((2 * j + 1) ^ sw) << 4), w[4], w[5], w[6], w[7]);
           }
         }
         fence_proxy_async_smem();          // generic-proxy writes -> visible to tcgen05.mma (async proxy)
@@ -263,7 +289,7 @@ gemm_w8a16_kernel(const W16Params wp, const __grid_constant__ CUtensorMap map_a,
       const int m0 = (tile % p.num_m_blocks) * kBlockM;
       const int n0 = (tile / p.num_m_blocks) * BLOCK_N;
       const int m = m0 + row_in_tile;
-      mbar_wait(&tmem_full_bar[as], aphase);
+      mbar_wait_backoff(&tmem_full_bar[as], aphase);
       tc_fence_after();
       const float row_scale = (!SCALED && p.b_scale_mode == 0) ? __ldg(p.b_scale) : 1.0f;
       const bool per_col = !SCALED && p.b_scale_mode == 1;
