@@ -48,7 +48,7 @@ def bench_gemms(dev, rank, world, pk, steps=10, m_tokens=8192):
     for (K, N) in LLAMA70B_KN:
         n0, n1 = shard.column_shard(N, rank, world)
         nloc = n1 - n0
-        for kind in ("fp8_w8a8", "mxfp4"):
+        for kind in ("fp8_w8a8", "mxfp4", "fp8_w8a16"):
             if nloc == 0:
                 ms = 0.0
             elif kind == "fp8_w8a8":
@@ -58,6 +58,14 @@ def bench_gemms(dev, rank, world, pk, steps=10, m_tokens=8192):
                 sw = torch.rand(nloc, 1, device=dev) * 0.01 + 0.001
                 wt = w.t()
                 fn = lambda: torch.ops._xpu_C.fp8_gemm(a, wt, torch.bfloat16, sa, sw, None)  # noqa: E731
+                ms = _time(fn, steps)
+            elif kind == "fp8_w8a16":      # bf16 activations x per-channel FP8 weights
+                a = torch.randn(M, K, device=dev, dtype=torch.bfloat16) / 4
+                w = (torch.randn(nloc, K, device=dev) / 4).to(E4)
+                sa = None
+                sw = torch.rand(nloc, device=dev) * 0.01 + 0.001
+                wt = w.t()
+                fn = lambda: torch.ops._xpu_C.fp8_gemm_w8a16(a, wt, sw, None)  # noqa: E731
                 ms = _time(fn, steps)
             else:
                 a = torch.randint(0, 256, (M, K // 2), dtype=torch.uint8, device=dev).view(torch.float4_e2m1fn_x2)
@@ -72,7 +80,7 @@ def bench_gemms(dev, rank, world, pk, steps=10, m_tokens=8192):
                 dist.all_reduce(t, op=dist.ReduceOp.MAX)
             ms_max = float(t.item())
             tflops = 2.0 * M * N * K / (ms_max * 1e-3) / 1e12
-            peak = peak_fp8 if kind == "fp8_w8a8" else peak_fp4
+            peak = peak_fp8 if kind == "fp8_w8a8" else pk["bf16"] if kind == "fp8_w8a16" else peak_fp4
             rows.append({"kind": kind, "M": M, "N": N, "K": K, "n_per_gpu": nloc if world > 1 else N,
                          "ms": ms_max, "tflops": tflops, "peak_tflops": peak * world,
                          "frac_of_dense_peak": tflops / (peak * world)})
@@ -100,7 +108,7 @@ def bench_gemms(dev, rank, world, pk, steps=10, m_tokens=8192):
         gather = {"shape": [M, N, K], "kind": "fp8_w8a8", "ms_gemm_plus_allgather": float(t.item()),
                   "tflops_reassembled": 2.0 * M * N * K / (float(t.item()) * 1e-3) / 1e12}
     tc, fb = stats()
-    best = max(rows, key=lambda r: r["frac_of_dense_peak"]) if rows else None
+    best = max((r for r in rows if r["kind"] != "fp8_w8a16"), key=lambda r: r["frac_of_dense_peak"]) if rows else None
     return {"shapes": "Llama-3-70B (K,N) x M=%d, N sharded over %d GPU(s)" % (M, world), "rows": rows,
             "best": best, "reassembled": gather, "tensor_core_calls": tc, "fallback_calls": fb,
-            "peak_source": pk["src"] + " bf16 cuBLAS x2 (fp8) / x4 (fp4)"}
+            "peak_source": pk["src"] + " bf16 cuBLAS x2 (fp8) / x4 (fp4) / x1 (fp8_w8a16: bf16 MMA)"}

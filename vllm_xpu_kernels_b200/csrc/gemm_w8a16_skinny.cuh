@@ -59,7 +59,7 @@ struct W16SkinnySmem {
   static_assert(kStages * kRawStage + kConvSlots * kConvSlot >= MT * 128 * 4, "the partial tile is parked in the rings");
 };
 
-template <int MT, bool BF16, bool E5M2>
+template <int MT, bool BF16, bool E5M2, bool SCALED>
 __global__ void __launch_bounds__(kW16SkThreads, 1)
 gemm_w8a16_skinny_kernel(const W16SkinnyParams p, const __grid_constant__ CUtensorMap map_w,
                          const __grid_constant__ CUtensorMap map_a) {
@@ -172,7 +172,7 @@ gemm_w8a16_skinny_kernel(const W16SkinnyParams p, const __grid_constant__ CUtens
   } else if (warp >= 8) {
     // ===================== converters =====================
     const int ct = threadIdx.x - 256;          // 0..255; 2 x 512 chunks of 16 FP8 bytes per stage
-    const bool scaled = p.b_scale_mode == 2;
+    constexpr bool scaled = SCALED;
     int stage = 0, cs = 0;
     uint32_t phase = 0, cphase = 0;
     for (int it = 0; it < nk; ++it) {
@@ -187,7 +187,7 @@ gemm_w8a16_skinny_kernel(const W16SkinnyParams p, const __grid_constant__ CUtens
 #pragma unroll
         for (int i = 0; i < 2; ++i) v[h][i] = lds128(raw + (r0 + 64 * i) * 128 + (((h * 4 + jq) ^ sw) << 4));
       float sc[2] = {1.0f, 1.0f};
-      if (scaled) {
+      if constexpr (scaled) {
 #pragma unroll
         for (int i = 0; i < 2; ++i) {
           const int n = min(n0 + r0 + 64 * i, p.N - 1);
@@ -201,8 +201,7 @@ gemm_w8a16_skinny_kernel(const W16SkinnyParams p, const __grid_constant__ CUtens
 #pragma unroll
         for (int i = 0; i < 2; ++i) {
           uint32_t w[8];
-          if (scaled) widen16<BF16, E5M2, true>(v[h][i], sc[i], w);
-          else widen16<BF16, E5M2, false>(v[h][i], 1.0f, w);
+          widen16<BF16, E5M2, SCALED>(v[h][i], sc[i], w);
           const uint32_t rowp = dst + (r0 + 64 * i) * 128;
           sts128(rowp + (((2 * jq) ^ sw) << 4), w[0], w[1], w[2], w[3]);
           sts128(rowp + (((2 * jq + 1) ^ sw) << 4), w[4], w[5], w[6], w[7]);
