@@ -11,13 +11,14 @@
 //              this is what HBM has to deliver, and all of it is payload -- 16 KB of weight bytes per
 //              stage, 64 KB in flight per SM at MT = 32 (the general kernel has 2 KB per stage at M = 1
 //              because its stage is dominated by a 128-row activation box of padding)
-//   CONV ring  6 slots of one K-major SWIZZLE_128B operand tile (128 rows x 64 elements of bf16 / f16) --
-//              half a raw stage each, so that the converter -> MMA -> converter hand-over latency is
-//              spread over six units in flight
-//   warps 8-15 converters: raw stage -> conv slot (exact widening, widen16 of gemm_w8a16.cuh; 128x128
-//              block scales folded in), proxy fence, arrive
-//   warp 1     tcgen05.mma.kind::f16 128 x MT x 16, four per conv slot; commits free the conv slot and,
-//              after the second half, the raw stage (activation boxes)
+//   CONV ring  3 slots of two K-major SWIZZLE_128B operand tiles (128 rows x 64 elements of bf16 / f16 each)
+//   warps 8-23 converters (16 warps): raw stage -> conv slot (exact widening, widen16 of gemm_w8a16.cuh;
+//              128x128 block scales folded in); a thread widens 32 codes of one weight row per stage in
+//              registers BEFORE it waits for the slot, then stores, ONE generic->async proxy fence and
+//              one arrive per warp per stage (the fence, not the arithmetic, is what a converter warp
+//              waits on: six half-stage slots with a fence each measured slower than two full ones)
+//   warp 1     tcgen05.mma.kind::f16 128 x MT x 16, eight per stage; its commits free the conv slot and
+//              the raw stage (activation boxes)
 #pragma once
 
 #include "gemm_skinny.cuh"
@@ -25,7 +26,8 @@
 
 namespace vxk {
 
-constexpr int kW16SkThreads = 512;
+constexpr int kW16SkThreads = 768;
+constexpr int kW16SkConvWarps = 16;   // warps 8-23
 constexpr int kW16SkWarps = kW16SkThreads / 32;
 constexpr int kW16SkBlockK = 128;   // K elements per raw stage
 
@@ -48,8 +50,8 @@ struct W16SkinnySmem {
   static constexpr int kRawW = 128 * kW16SkBlockK;          // 16 KB
   static constexpr int kABox = MT * 128;                    // one 64-element activation slice
   static constexpr int kRawStage = kRawW + 2 * kABox;
-  static constexpr int kConvSlot = 128 * 128;               // one operand tile (128 rows x 64 elements), 16 KB
-  static constexpr int kConvSlots = 6;
+  static constexpr int kConvSlot = 2 * 128 * 128;           // two operand tiles (128 rows x 64 elements each), 32 KB
+  static constexpr int kConvSlots = 3;
   static constexpr int kStagesRaw = (196 * 1024 - kConvSlots * kConvSlot) / kRawStage;
   static constexpr int kStages = kStagesRaw > 8 ? 8 : kStagesRaw;
   static constexpr int kBarrierBytes = (2 * kStages + 2 * kConvSlots + 1) * 8 + 16;
@@ -94,7 +96,7 @@ gemm_w8a16_skinny_kernel(const W16SkinnyParams p, const __grid_constant__ CUtens
       mbar_init(&empty_bar[i], 1);
     }
     for (int i = 0; i < C; ++i) {
-      mbar_init(&conv_full[i], kW16ConvWarps);
+      mbar_init(&conv_full[i], kW16SkConvWarps);
       mbar_init(&conv_empty[i], 1);
     }
     mbar_init(acc_bar, 1);
@@ -147,70 +149,61 @@ gemm_w8a16_skinny_kernel(const W16SkinnyParams p, const __grid_constant__ CUtens
     uint32_t phase = 0, cphase = 0;
     for (int it = 0; it < nk; ++it) {
       mbar_wait(&full_bar[stage], phase);      // activation boxes
+      mbar_wait(&conv_full[cs], cphase);       // widened weight tiles
+      tc_fence_after();
+      if (elect_one()) {
+        const uint32_t w_addr = smem_u32(conv_base + cs * L::kConvSlot);
+        const uint32_t a_addr = smem_u32(smem + stage * L::kRawStage + L::kRawW);
 #pragma unroll
-      for (int h = 0; h < 2; ++h) {
-        mbar_wait(&conv_full[cs], cphase);     // widened weight tile of this 64-element half
-        tc_fence_after();
-        if (elect_one()) {
-          const uint64_t dw = make_kmajor_sw128_desc(smem_u32(conv_base + cs * L::kConvSlot));
-          const uint64_t da = make_kmajor_sw128_desc(smem_u32(smem + stage * L::kRawStage + L::kRawW + h * L::kABox));
+        for (int h = 0; h < 2; ++h) {
+          const uint64_t dw = make_kmajor_sw128_desc(w_addr + h * 128 * 128);
+          const uint64_t da = make_kmajor_sw128_desc(a_addr + h * L::kABox);
 #pragma unroll
           for (int k = 0; k < 4; ++k)
             umma_f16(tmem_base, dw + static_cast<uint64_t>(2 * k), da + static_cast<uint64_t>(2 * k), idesc,
                      (it > 0 || h > 0 || k > 0) ? 1u : 0u);
-          umma_commit(&conv_empty[cs]);
-          if (h == 1) {
-            umma_commit(&empty_bar[stage]);
-            if (it == nk - 1) umma_commit(acc_bar);
-          }
         }
-        __syncwarp();
-        if (++cs == C) { cs = 0; cphase ^= 1; }
+        umma_commit(&conv_empty[cs]);
+        umma_commit(&empty_bar[stage]);
+        if (it == nk - 1) umma_commit(acc_bar);
       }
+      __syncwarp();
+      if (++cs == C) { cs = 0; cphase ^= 1; }
       if (++stage == S) { stage = 0; phase ^= 1; }
     }
   } else if (warp >= 8) {
     // ===================== converters =====================
-    const int ct = threadIdx.x - 256;          // 0..255; 2 x 512 chunks of 16 FP8 bytes per stage
+    const int ct = threadIdx.x - 256;          // 0..511: weight row ct / 4, 16-byte chunks jq and 4 + jq of its 128 bytes
     constexpr bool scaled = SCALED;
+    const int row = ct >> 2, jq = ct & 3, sw = row & 7;
     int stage = 0, cs = 0;
     uint32_t phase = 0, cphase = 0;
     for (int it = 0; it < nk; ++it) {
       mbar_wait(&full_bar[stage], phase);
-      const uint32_t raw = smem_u32(smem + stage * L::kRawStage);   // [128 rows][128 B], SWIZZLE_128B as TMA wrote it
-      const int64_t kgrp = scaled ? static_cast<int64_t>(((kb0 + it) * kW16SkBlockK) / p.group_k) * p.sb0 : 0;
-      // this thread's 4 chunks of the stage: rows r0, r0 + 64 (r0 = ct / 4), 16 K elements at h * 64 + 16 jq
-      const int r0 = ct >> 2, jq = ct & 3, sw = r0 & 7;             // (r0 + 64) & 7 == r0 & 7
-      uint4 v[2][2];
+      const uint32_t raw = smem_u32(smem + stage * L::kRawStage) + row * 128;   // SWIZZLE_128B as TMA wrote it
+      uint4 v[2];
 #pragma unroll
-      for (int h = 0; h < 2; ++h)
-#pragma unroll
-        for (int i = 0; i < 2; ++i) v[h][i] = lds128(raw + (r0 + 64 * i) * 128 + (((h * 4 + jq) ^ sw) << 4));
-      float sc[2] = {1.0f, 1.0f};
+      for (int h = 0; h < 2; ++h) v[h] = lds128(raw + (((h * 4 + jq) ^ sw) << 4));
+      float sc = 1.0f;
       if constexpr (scaled) {
-#pragma unroll
-        for (int i = 0; i < 2; ++i) {
-          const int n = min(n0 + r0 + 64 * i, p.N - 1);
-          sc[i] = __ldg(p.b_scale + kgrp + static_cast<int64_t>(n / p.group_n) * p.sb1);
-        }
+        const int n = min(n0 + row, p.N - 1);
+        sc = __ldg(p.b_scale + static_cast<int64_t>(((kb0 + it) * kW16SkBlockK) / p.group_k) * p.sb0 +
+                   static_cast<int64_t>(n / p.group_n) * p.sb1);
       }
+      uint32_t w[2][8];
+#pragma unroll
+      for (int h = 0; h < 2; ++h) widen16<BF16, E5M2, SCALED>(v[h], sc, w[h]);
+      mbar_wait(&conv_empty[cs], cphase ^ 1);
+      const uint32_t dst = smem_u32(conv_base + cs * L::kConvSlot) + row * 128;
 #pragma unroll
       for (int h = 0; h < 2; ++h) {
-        mbar_wait(&conv_empty[cs], cphase ^ 1);
-        const uint32_t dst = smem_u32(conv_base + cs * L::kConvSlot);
-#pragma unroll
-        for (int i = 0; i < 2; ++i) {
-          uint32_t w[8];
-          widen16<BF16, E5M2, SCALED>(v[h][i], sc[i], w);
-          const uint32_t rowp = dst + (r0 + 64 * i) * 128;
-          sts128(rowp + (((2 * jq) ^ sw) << 4), w[0], w[1], w[2], w[3]);
-          sts128(rowp + (((2 * jq + 1) ^ sw) << 4), w[4], w[5], w[6], w[7]);
-        }
-        fence_proxy_async_smem();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&conv_full[cs]);
-        if (++cs == C) { cs = 0; cphase ^= 1; }
+        sts128(dst + h * (128 * 128) + (((2 * jq) ^ sw) << 4), w[h][0], w[h][1], w[h][2], w[h][3]);
+        sts128(dst + h * (128 * 128) + (((2 * jq + 1) ^ sw) << 4), w[h][4], w[h][5], w[h][6], w[h][7]);
       }
+      fence_proxy_async_smem();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&conv_full[cs]);
+      if (++cs == C) { cs = 0; cphase ^= 1; }
       if (++stage == S) { stage = 0; phase ^= 1; }
     }
   }
