@@ -106,7 +106,29 @@ def bench_gemms(dev, rank, world, pk, steps=10, m_tokens=8192):
         t = torch.tensor([ms], dtype=torch.float64, device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         gather = {"shape": [M, N, K], "kind": "fp8_w8a8", "ms_gemm_plus_allgather": float(t.item()),
-                  "tflops_reassembled": 2.0 * M * N * K / (float(t.item()) * 1e-3) / 1e12}
+                  "tflops_reassembled": 2.0 * M * N * K / (float(t.item()) * 1e-3) / 1e12,
+                  "how": "fp8_gemm, then NCCL all-gather of the [M, N/p] slabs"}
+        # the same product through ONE kernel: the GEMM epilogue stores each tile into every rank's
+        # [M, N] output over NVLink peer mappings (vxk_fp8_gemm_allgather), then one barrier
+        try:
+            ref_full = fn()
+            so = shard.SymmetricOutput(M, N, torch.bfloat16, dev)
+            fused = lambda: shard.fp8_gemm_allgather(a, wt, sa, sw, so, n0)  # noqa: E731
+            got = fused()
+            torch.cuda.synchronize()
+            same = bool(torch.equal(got, ref_full))
+            ms_f = _time(fused, max(2, steps // 2))
+            tf = torch.tensor([ms_f], dtype=torch.float64, device=dev)
+            dist.all_reduce(tf, op=dist.ReduceOp.MAX)
+            ok = torch.tensor([1.0 if same else 0.0], device=dev)
+            dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+            gather["fused"] = {"ms_gemm_with_fused_allgather": float(tf.item()),
+                               "tflops_reassembled": 2.0 * M * N * K / (float(tf.item()) * 1e-3) / 1e12,
+                               "bit_identical_to_nccl_path_on_all_ranks": bool(ok.item() == 1.0),
+                               "how": "vxk_fp8_gemm_allgather: epilogue peer stores over NVLink + one barrier"}
+            del ref_full, got, so
+        except Exception as exc:  # symmetric memory unavailable on this box / build
+            gather["fused"] = {"error": f"{type(exc).__name__}: {exc}"[:300]}
     tc, fb = stats()
     best = max((r for r in rows if r["kind"] != "fp8_w8a16"), key=lambda r: r["frac_of_dense_peak"]) if rows else None
     return {"shapes": "Llama-3-70B (K,N) x M=%d, N sharded over %d GPU(s)" % (M, world), "rows": rows,

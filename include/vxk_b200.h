@@ -161,6 +161,23 @@ int vxk_fp8_gemm(void* D, const void* A, const void* B, const void* a_scale, con
                  int64_t sb0, int64_t sb1, int scale_dtype, int fp8_dtype, int out_dtype,
                  int bias_dtype, void* workspace, int64_t workspace_bytes, vxk_stream_t stream);
 
+/* Column-parallel FP8 GEMM fused with the all-gather of its output (the only
+ * collective of the path).  Rank r owns W[n0:n0+N, :]; instead of writing a private [M, N]
+ * slab that an NCCL all-gather reassembles afterwards, the epilogue stores every finished tile
+ * into columns [col_offset, col_offset + N) of ALL ranks' [M, out_ld] outputs through NVLink
+ * peer mappings (peer_out[i] = base pointer of rank i's output as mapped into this process,
+ * e.g. torch symmetric memory; peer_out[self_rank] is this rank's own buffer: the tile is stored there
+ * first and then pushed to the others as whole 512-byte row segments).  The caller
+ * synchronises the ranks afterwards (one barrier) before reading.  Per-tensor / per-token /
+ * per-channel scales only.  No reference counterpart: the reference has no parallelism, the
+ * all-gather is the caller's (vLLM's) in tensor-parallel column-linear layers. */
+int vxk_fp8_gemm_allgather(void* const* peer_out, int n_peers, int self_rank, int64_t col_offset, int64_t out_ld,
+                           const void* A, const void* B, const void* a_scale, const void* b_scale,
+                           const void* bias, int64_t M, int64_t N, int64_t K, int64_t lda,
+                           int64_t b_stride_k, int64_t b_stride_n, int a_scale_mode,
+                           int b_scale_mode, int fp8_dtype, int out_dtype, int bias_dtype,
+                           vxk_stream_t stream);
+
 /* Scratch the caller must provide to vxk_fp8_gemm (device memory, any alignment); 0 when
  * none is needed.  ref: the per-call scratchpad of fp8_gemm_w8a8.h:176-179. */
 int64_t vxk_fp8_gemm_workspace_bytes(int64_t M, int64_t N, int64_t K, int a_scale_mode, int scale_dtype);

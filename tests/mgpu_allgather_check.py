@@ -1,0 +1,54 @@
+"""Run under torchrun with >= 2 GPUs (tests/test_multigpu_gpu.py launches it): the fused column-parallel
+FP8 GEMM + all-gather (vxk_fp8_gemm_allgather, epilogue peer stores over NVLink) against the unfused path
+(fp8_gemm on the local shard + NCCL all-gather) and against the single-GPU product, on every rank."""
+import os
+import sys
+
+import torch
+import torch.distributed as dist
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+
+
+def main():
+    rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+    torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", rank)))
+    dev = torch.device("cuda", torch.cuda.current_device())
+    dist.init_process_group("nccl", device_id=dev)
+    import vllm_xpu_kernels_b200._xpu_C  # noqa: F401
+    from vllm_xpu_kernels_b200 import shard
+    E4 = torch.float8_e4m3fn
+    for (M, N, K, per_token, with_bias) in [(300, 1024, 512, True, False), (1000, 4096 + 256, 2048, True, True),
+                                            (512, 2048, 1024, False, False), (130, 384, 4096, True, True)]:
+        torch.manual_seed(5)     # same operands on every rank
+        a = (torch.randn(M, K, device=dev) / 4).to(E4)
+        w = (torch.randn(N, K, device=dev) / 4).to(E4)
+        sa = (torch.rand(M, 1, device=dev) * 0.01 + 0.001) if per_token else torch.full((1,), 0.01, device=dev)
+        sw = torch.rand(N, 1, device=dev) * 0.01 + 0.001
+        bias = (torch.randn(N, device=dev, dtype=torch.bfloat16) / 8) if with_bias else None
+        n0, n1 = shard.column_shard(N, rank, world)
+        wl, swl = w[n0:n1], sw[n0:n1].contiguous()
+        bl = bias[n0:n1].contiguous() if with_bias else None
+        full = torch.ops._xpu_C.fp8_gemm(a, w.t(), torch.bfloat16, sa, sw, bias)          # single-GPU product
+        so = shard.SymmetricOutput(M, N, torch.bfloat16, dev)
+        so.buf.fill_(float("nan"))
+        so.barrier()
+        got = shard.fp8_gemm_allgather(a, wl.t(), sa, swl, so, n0, bl)
+        torch.cuda.synchronize()
+        assert not torch.isnan(got.float()).any(), (rank, "unwritten columns", M, N, K)
+        # tile shapes differ between the sharded and the unsharded call (accumulation order inside the tensor
+        # core does not): the results agree to output rounding
+        torch.testing.assert_close(got.float(), full.float(), atol=1e-2, rtol=1e-2)
+        local = torch.ops._xpu_C.fp8_gemm(a, wl.t(), torch.bfloat16, sa, swl, bl)
+        unfused = shard.all_gather_columns(local, N)
+        assert torch.equal(got, unfused), (rank, "fused != fp8_gemm + NCCL all-gather", M, N, K)
+        so.barrier()
+        del so
+    dist.barrier()
+    if rank == 0:
+        print("mgpu allgather ok", world)
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

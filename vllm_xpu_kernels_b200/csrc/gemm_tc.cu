@@ -286,6 +286,10 @@ static bool force_single() {
   return v;
 }
 
+// fused all-gather destination of the NEXT vxk_fp8_gemm call of this thread (set by vxk_fp8_gemm_allgather)
+struct PeerCfg { int n; void* ptr[8]; };
+static thread_local PeerCfg g_peer_cfg{0, {}};
+
 static int g_force_fallback = -1;
 static bool force_fallback() {
   if (g_force_fallback < 0) {
@@ -462,6 +466,17 @@ extern "C" int vxk_fp8_gemm(void* D, const void* A, const void* B, const void* a
   tp.num_m_blocks = (int)((M + kBlockM - 1) / kBlockM);
   tp.num_k_blocks = (int)((K + kBlockKBytes - 1) / kBlockKBytes);
   tp.vec_store_ok = aligned16(D) && (ldd * 2) % 16 == 0;
+  const PeerCfg peers = g_peer_cfg;
+  g_peer_cfg.n = 0;
+  if (peers.n > 0) {
+    VXK_REQUIRE(operands_ok && a_scale_mode != 2,
+                "fused all-gather: only the per-tensor / per-token / per-channel tensor-core path supports it");
+    tp.n_peers = peers.n;
+    for (int i = 0; i < peers.n; ++i) {
+      tp.peer_D[i] = peers.ptr[i];
+      tp.vec_store_ok = tp.vec_store_ok && aligned16(peers.ptr[i]);
+    }
+  }
   CUtensorMap ma, mb, msa{}, msb{};
   int rc;
 
@@ -470,7 +485,7 @@ extern "C" int vxk_fp8_gemm(void* D, const void* A, const void* B, const void* a
     tp.b_scale = static_cast<const float*>(b_scale);
     static const int skinny_max_m = env_int("VXK_SKINNY_MAX_M", 256);
     // 129..256 tokens: only while the 128-row weight tiles fit one wave (else the general kernels win)
-    if (M <= skinny_max_m && M <= 256 && K >= 512 && (M <= 128 || (N + 127) / 128 <= sm_count()))
+    if (peers.n == 0 && M <= skinny_max_m && M <= 256 && K >= 512 && (M <= 128 || (N + 127) / 128 <= sm_count()))
       return run_skinny_f8(tp, A, B, M, N, K, lda, b_stride_n, st);
     const int bn = single_cta_bn(M, N, 256);
     if (!force_single() && prefer_pair(M, N, bn, 256)) {
@@ -538,6 +553,29 @@ extern "C" int vxk_fp8_gemm(void* D, const void* A, const void* B, const void* a
     return launch_tc_bn<KIND_MXF8>(bn, tp, ma, mb, msa, msb, st);
   }
   return launch_gemm_fallback(p, /*is_fp4=*/false, st);
+}
+
+extern "C" int vxk_fp8_gemm_allgather(void* const* peer_out, int n_peers, int self_rank, int64_t col_offset, int64_t out_ld,
+                                      const void* A, const void* B, const void* a_scale, const void* b_scale,
+                                      const void* bias, int64_t M, int64_t N, int64_t K, int64_t lda,
+                                      int64_t b_stride_k, int64_t b_stride_n, int a_scale_mode, int b_scale_mode,
+                                      int fp8_dtype, int out_dtype, int bias_dtype, vxk_stream_t stream) {
+  VXK_REQUIRE(peer_out && n_peers >= 1 && n_peers <= 8, "1..8 peer outputs");
+  VXK_REQUIRE(a_scale_mode != 2 && b_scale_mode != 2, "fused all-gather: block scales are not supported");
+  VXK_REQUIRE(col_offset >= 0 && col_offset + N <= out_ld, "this rank's columns must lie inside a row of the output");
+  VXK_REQUIRE(self_rank >= 0 && self_rank < n_peers, "self_rank must index peer_out");
+  int others = 0;
+  for (int i = 0; i < n_peers; ++i) {
+    VXK_REQUIRE(peer_out[i], "null peer output");
+    if (i != self_rank) g_peer_cfg.ptr[others++] = static_cast<uint16_t*>(peer_out[i]) + col_offset;
+  }
+  g_peer_cfg.n = others;
+  void* own = static_cast<uint16_t*>(peer_out[self_rank]) + col_offset;
+  const int rc = vxk_fp8_gemm(own, A, B, a_scale, b_scale, bias, M, N, K, lda, b_stride_k, b_stride_n,
+                              out_ld, a_scale_mode, b_scale_mode, 0, 0, 0, 0, 0, 0, VXK_S_F32, fp8_dtype, out_dtype,
+                              bias_dtype, nullptr, 0, stream);
+  g_peer_cfg.n = 0;
+  return rc;
 }
 
 extern "C" int vxk_fp4_gemm(void* D, const void* A, const void* B, const void* a_scale, const void* b_scale,

@@ -42,6 +42,8 @@ struct TcParams {
   int fp8_fmt;            // 0 = E4M3, 1 = E5M2 (fp8 kinds)
   int num_m_blocks, num_n_blocks, num_k_blocks;
   int vec_store_ok;       // D rows 16-byte aligned -> 128-bit stores
+  int n_peers;            // > 0: fused all-gather -- the tile also goes to peer_D[0..n_peers), the OTHER ranks'
+  void* peer_D[8];        //      peer-mapped [M, N_total] outputs (offset to this rank's columns, row stride ldd like D)
   int debug;              // bring-up switches (env VXK_GEMM_DEBUG): 1 skip tcgen05.cp, 2 plain MMA, 4 skip re-tiler
 };
 
@@ -49,7 +51,7 @@ struct TcParams {
 // to bf16 / f16 and the stores (128-bit when the row is 16-byte aligned and the chunk is whole).
 // Every array index is a compile-time constant (no local memory).
 __device__ __forceinline__ void epilogue_store_32(const TcParams& p, const uint32_t (&r)[32], int m, int nbase,
-                                                  float row_scale, bool per_col) {
+                                                  float row_scale, bool per_col, bool direct_peers = true) {
   float v[32];
   const bool whole = nbase + 32 <= p.N;
 #pragma unroll
@@ -78,7 +80,6 @@ __device__ __forceinline__ void epilogue_store_32(const TcParams& p, const uint3
                                             : __bfloat162float(static_cast<const __nv_bfloat16*>(p.bias)[n]);
     }
   }
-  uint16_t* drow = static_cast<uint16_t*>(p.D) + static_cast<int64_t>(m) * p.ldd + nbase;
   const bool bf = p.out_dtype == VXK_BF16;
   uint32_t w[16];
 #pragma unroll
@@ -91,6 +92,27 @@ __device__ __forceinline__ void epilogue_store_32(const TcParams& p, const uint3
       w[t] = *reinterpret_cast<uint32_t*>(&h);
     }
   }
+  const int64_t off = static_cast<int64_t>(m) * p.ldd + nbase;
+  if (p.n_peers > 0 && direct_peers) {
+    // fused all-gather, simple form: the 32-column piece is stored straight into every other rank's output
+    // through its NVLink peer mapping.  One thread = one row, so a warp's store touches 32 rows: correct for
+    // any shape / alignment but NVLink-inefficient; the CTA-pair kernel copies whole tile rows instead
+    // (gemm_tc2.cuh) and only falls back to this for unaligned outputs.
+#pragma unroll 1
+    for (int pe = 0; pe < p.n_peers; ++pe) {
+      uint16_t* drow = static_cast<uint16_t*>(p.peer_D[pe]) + off;
+      if (p.vec_store_ok && whole) {
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+          *reinterpret_cast<uint4*>(drow + 8 * j) = make_uint4(w[4 * j], w[4 * j + 1], w[4 * j + 2], w[4 * j + 3]);
+      } else {
+#pragma unroll
+        for (int j = 0; j < 32; ++j)
+          if (nbase + j < p.N) drow[j] = static_cast<uint16_t>(j & 1 ? w[j >> 1] >> 16 : w[j >> 1] & 0xffffu);
+      }
+    }
+  }
+  uint16_t* drow = static_cast<uint16_t*>(p.D) + off;
   if (p.vec_store_ok && whole) {
 #pragma unroll
     for (int j = 0; j < 4; ++j)

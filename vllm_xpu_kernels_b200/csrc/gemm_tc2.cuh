@@ -64,6 +64,12 @@ __device__ __forceinline__ uint32_t cluster_ctarank() {
   asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
   return r;
 }
+// plain (coherent, L1-allocating) 128-bit global load the compiler may not turn into a read-only-path load
+__device__ __forceinline__ uint4 ld_global_v4(const void* ptr) {
+  uint4 v;
+  asm volatile("ld.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(ptr) : "memory");
+  return v;
+}
 __device__ __forceinline__ void cluster_sync_all() {
   asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
 }
@@ -364,6 +370,7 @@ gemm_tc2_kernel(const Tc2Params pp, const __grid_constant__ CUtensorMap map_a, c
     const int h = e >> 2;                   // NACC == 2: accumulator; NACC == 1: column half
     const int row_in_tile = static_cast<int>(rank) * kBlockM + q * 32 + lane;
     constexpr int kChunks = NACC == 2 ? BLOCK_N / 32 : BLOCK_N / 64;
+    const bool row_copy = p.n_peers > 0 && p.vec_store_ok && kTileN % 256 == 0;   // else: direct peer stores
     int iter = 0;
     for (int tile = pair; tile < num_tiles; tile += num_pairs, ++iter) {
       int mt, nt;
@@ -389,11 +396,51 @@ gemm_tc2_kernel(const Tc2Params pp, const __grid_constant__ CUtensorMap map_a, c
         tmem_ld_32x32b_x32(taddr, r);
         tmem_ld_wait();
         const int nbase = n0 + col0 + c * 32;
-        if (m < p.M && nbase < p.N) epilogue_store_32(p, r, m, nbase, row_scale, per_col);
+        if (m < p.M && nbase < p.N) epilogue_store_32(p, r, m, nbase, row_scale, per_col, !row_copy);
       }
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive_cluster(&tmem_empty_bar[NACC == 2 ? h : as], 0);
+      if (row_copy) {
+        // Fused all-gather: this CTA's 128 x kTileN part of the tile now sits in the local output
+        // (still in L2).  The eight epilogue warps push it to the other ranks as WHOLE ROW SEGMENTS -- a warp
+        // reads 512 contiguous bytes of one row (16 B per lane) and stores them to every peer mapping, so the
+        // NVLink writes are full 512-byte runs instead of the 16-byte pieces a row-per-thread store gives.
+        // The accumulator was handed back above: the transfer overlaps the next tile's main loop.
+        asm volatile("bar.sync 1, 256;" ::: "memory");     // all epilogue warps' local stores of this tile are visible
+        const int mrow0 = mt * (2 * kBlockM) + static_cast<int>(rank) * kBlockM;
+#pragma unroll 1
+        for (int seg = 0; seg < kTileN / 256; ++seg) {
+          const int nc = n0 + seg * 256 + lane * 8;
+          if (nc >= p.N) continue;
+          const bool whole8 = nc + 8 <= p.N;
+#pragma unroll 1
+          for (int rr = e; rr < kBlockM; rr += 16) {
+            const int ma = mrow0 + rr, mb = ma + 8;
+            const uint16_t* la = static_cast<const uint16_t*>(p.D) + static_cast<int64_t>(ma) * p.ldd + nc;
+            const uint16_t* lb = static_cast<const uint16_t*>(p.D) + static_cast<int64_t>(mb) * p.ldd + nc;
+            uint4 va = make_uint4(0, 0, 0, 0), vb = va;
+            if (whole8) {
+              if (ma < p.M) va = ld_global_v4(la);
+              if (mb < p.M) vb = ld_global_v4(lb);
+#pragma unroll 1
+              for (int pe = 0; pe < p.n_peers; ++pe) {
+                uint16_t* pa = static_cast<uint16_t*>(p.peer_D[pe]) + static_cast<int64_t>(ma) * p.ldd + nc;
+                uint16_t* pb = static_cast<uint16_t*>(p.peer_D[pe]) + static_cast<int64_t>(mb) * p.ldd + nc;
+                if (ma < p.M) *reinterpret_cast<uint4*>(pa) = va;
+                if (mb < p.M) *reinterpret_cast<uint4*>(pb) = vb;
+              }
+            } else {
+              for (int j = 0; nc + j < p.N; ++j)
+                for (int pe = 0; pe < p.n_peers; ++pe) {
+                  uint16_t* pd = static_cast<uint16_t*>(p.peer_D[pe]);
+                  if (ma < p.M) pd[static_cast<int64_t>(ma) * p.ldd + nc + j] = *(volatile const uint16_t*)(la + j);
+                  if (mb < p.M) pd[static_cast<int64_t>(mb) * p.ldd + nc + j] = *(volatile const uint16_t*)(lb + j);
+                }
+            }
+          }
+        }
+      }
     }
   }
 

@@ -63,3 +63,63 @@ def all_gather_columns(local: torch.Tensor, n_total: int, align: int = 128, grou
     out = [torch.empty_like(pad) for _ in range(world)]
     dist.all_gather(out, pad, group=group)
     return torch.cat([o[:, :b - a] for o, (a, b) in zip(out, widths)], dim=1)
+
+
+# ---------------------------------------------------------------------------------------------
+# Fused column-parallel FP8 GEMM + all-gather over NVLink peer memory (C ABI vxk_fp8_gemm_allgather)
+# ---------------------------------------------------------------------------------------------
+class SymmetricOutput:
+    """An [M, N_total] output allocated in torch symmetric memory on every rank and mapped into every
+    peer: `ptrs[r]` is rank r's buffer as seen from this process.  Create once, reuse across calls."""
+
+    def __init__(self, m: int, n_total: int, dtype: torch.dtype, device, group=None):
+        import torch.distributed._symmetric_memory as symm
+        self.buf = symm.empty((m, n_total), dtype=dtype, device=device)
+        self.hdl = symm.rendezvous(self.buf, group=group if group is not None else dist.group.WORLD)
+        self.ptrs = [int(p) for p in self.hdl.buffer_ptrs]
+        self.world = len(self.ptrs)
+        self.rank = int(self.hdl.rank)
+
+    def barrier(self):
+        """Device-side barrier of all ranks on the current stream: after it every rank's columns have landed."""
+        self.hdl.barrier()
+
+
+def fp8_gemm_allgather(a: torch.Tensor, wt_local: torch.Tensor, a_scale: torch.Tensor, w_scale_local: torch.Tensor,
+                       out: SymmetricOutput, col_offset: int, bias_local: Optional[torch.Tensor] = None,
+                       sync: bool = True) -> torch.Tensor:
+    """D[:, col_offset : col_offset + N_local] = fp8_gemm(a, wt_local) written by the GEMM epilogue into EVERY
+    rank's `out.buf` (NVLink peer stores), then one barrier: on return (stream order) `out.buf` holds the full
+    [M, N_total] product on all ranks -- GEMM and all-gather in one kernel, no NCCL call.
+    a [M, K] e4m3/e5m2; wt_local [K, N_local] K-major view of this rank's W[n0:n1, :]; scales fp32
+    (per tensor, per token [M] / [M,1], per channel [N_local] / [N_local,1])."""
+    import ctypes
+
+    from . import _loader
+    lib = _loader.cdll()
+    assert a.dim() == 2 and wt_local.dim() == 2 and a.stride(1) == 1 and a.shape[1] == wt_local.shape[0]
+    M, K = a.shape
+    n_local = wt_local.shape[1]
+    dt = {torch.bfloat16: 2, torch.float16: 1}[out.buf.dtype]
+    f8 = {torch.float8_e4m3fn: 0, torch.float8_e5m2: 1}[a.dtype]
+    a_scale = a_scale.contiguous()
+    w_scale_local = w_scale_local.contiguous()
+    bias_dt = 0
+    if bias_local is not None:
+        bias_dt = {torch.float32: 0, torch.float16: 1, torch.bfloat16: 2}[bias_local.dtype]
+    ptrs = (ctypes.c_void_p * out.world)(*out.ptrs)
+    i64 = ctypes.c_int64
+    rc = lib.vxk_fp8_gemm_allgather(
+        ptrs, ctypes.c_int(out.world), ctypes.c_int(out.rank), i64(col_offset), i64(out.buf.stride(0)),
+        ctypes.c_void_p(a.data_ptr()), ctypes.c_void_p(wt_local.data_ptr()),
+        ctypes.c_void_p(a_scale.data_ptr()), ctypes.c_void_p(w_scale_local.data_ptr()),
+        ctypes.c_void_p(bias_local.data_ptr() if bias_local is not None else 0),
+        i64(M), i64(n_local), i64(K), i64(a.stride(0)), i64(wt_local.stride(0)), i64(wt_local.stride(1)),
+        ctypes.c_int(0 if a_scale.numel() == 1 else 1), ctypes.c_int(0 if w_scale_local.numel() == 1 else 1),
+        ctypes.c_int(f8), ctypes.c_int(dt), ctypes.c_int(bias_dt),
+        ctypes.c_void_p(torch.cuda.current_stream().cuda_stream))
+    if rc != 0:
+        raise RuntimeError("vxk_fp8_gemm_allgather: " + lib.vxk_last_error().decode())
+    if sync:
+        out.barrier()
+    return out.buf
