@@ -113,7 +113,7 @@ def bench_gemms(dev, rank, world, pk, steps=10, m_tokens=8192):
         try:
             ref_full = fn()
             so = shard.SymmetricOutput(M, N, torch.bfloat16, dev)
-            fused = lambda: shard.fp8_gemm_allgather(a, wt, sa, sw, so, n0)  # noqa: E731
+            fused = lambda: shard.fp8_gemm_allgather(a, wt, sa, sw, so, n0, multicast=False)  # noqa: E731
             got = fused()
             torch.cuda.synchronize()
             same = bool(torch.equal(got, ref_full))
@@ -126,6 +126,23 @@ def bench_gemms(dev, rank, world, pk, steps=10, m_tokens=8192):
                                "tflops_reassembled": 2.0 * M * N * K / (float(tf.item()) * 1e-3) / 1e12,
                                "bit_identical_to_nccl_path_on_all_ranks": bool(ok.item() == 1.0),
                                "how": "vxk_fp8_gemm_allgather: epilogue peer stores over NVLink + one barrier"}
+            if so.mc_ptr:
+                so.buf.zero_()
+                so.barrier()
+                fmc = lambda: shard.fp8_gemm_allgather(a, wt, sa, sw, so, n0, multicast=True)  # noqa: E731
+                got = fmc()
+                torch.cuda.synchronize()
+                same = torch.tensor([1.0 if torch.equal(got, ref_full) else 0.0], device=dev)
+                dist.all_reduce(same, op=dist.ReduceOp.MIN)
+                ms_m = _time(fmc, max(2, steps // 2))
+                tm = torch.tensor([ms_m], dtype=torch.float64, device=dev)
+                dist.all_reduce(tm, op=dist.ReduceOp.MAX)
+                gather["fused_multicast"] = {"ms_gemm_with_fused_allgather": float(tm.item()),
+                                             "tflops_reassembled": 2.0 * M * N * K / (float(tm.item()) * 1e-3) / 1e12,
+                                             "bit_identical_to_nccl_path_on_all_ranks": bool(same.item() == 1.0),
+                                             "how": "same kernel, one multimem.st per row segment through the NVSwitch (NVLS)"}
+            else:
+                gather["fused_multicast"] = {"unavailable": "symmetric-memory handle has no multicast mapping"}
             del ref_full, got, so
         except Exception as exc:  # symmetric memory unavailable on this box / build
             gather["fused"] = {"error": f"{type(exc).__name__}: {exc}"[:300]}

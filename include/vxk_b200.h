@@ -167,11 +167,14 @@ int vxk_fp8_gemm(void* D, const void* A, const void* B, const void* a_scale, con
  * into columns [col_offset, col_offset + N) of ALL ranks' [M, out_ld] outputs through NVLink
  * peer mappings (peer_out[i] = base pointer of rank i's output as mapped into this process,
  * e.g. torch symmetric memory; peer_out[self_rank] is this rank's own buffer: the tile is stored there
- * first and then pushed to the others as whole 512-byte row segments).  The caller
+ * first and then pushed to the others as whole 512-byte row segments; multicast_out, when
+ * non-null, is an NVLS multicast mapping of the same buffers -- one multimem.st per segment
+ * then reaches every rank through the NVSwitch, needs M > 256 and N % 256 == 0).  The caller
  * synchronises the ranks afterwards (one barrier) before reading.  Per-tensor / per-token /
  * per-channel scales only.  No reference counterpart: the reference has no parallelism, the
  * all-gather is the caller's (vLLM's) in tensor-parallel column-linear layers. */
-int vxk_fp8_gemm_allgather(void* const* peer_out, int n_peers, int self_rank, int64_t col_offset, int64_t out_ld,
+int vxk_fp8_gemm_allgather(void* const* peer_out, int n_peers, int self_rank, void* multicast_out,
+                           int64_t col_offset, int64_t out_ld,
                            const void* A, const void* B, const void* a_scale, const void* b_scale,
                            const void* bias, int64_t M, int64_t N, int64_t K, int64_t lda,
                            int64_t b_stride_k, int64_t b_stride_n, int a_scale_mode,

@@ -19,7 +19,8 @@ def main():
     from vllm_xpu_kernels_b200 import shard
     E4 = torch.float8_e4m3fn
     for (M, N, K, per_token, with_bias) in [(300, 1024, 512, True, False), (1000, 4096 + 256, 2048, True, True),
-                                            (512, 2048, 1024, False, False), (130, 384, 4096, True, True)]:
+                                            (512, 2048, 1024, False, False), (130, 384, 4096, True, True),
+                                            (700, 4096, 1024, True, True)]:
         torch.manual_seed(5)     # same operands on every rank
         a = (torch.randn(M, K, device=dev) / 4).to(E4)
         w = (torch.randn(N, K, device=dev) / 4).to(E4)
@@ -43,6 +44,13 @@ def main():
         unfused = shard.all_gather_columns(local, N)
         assert torch.equal(got, unfused), (rank, "fused != fp8_gemm + NCCL all-gather", M, N, K)
         so.barrier()
+        if so.mc_ptr and M > 256 and (n1 - n0) % 256 == 0 and n0 % 8 == 0:      # NVLS multicast variant
+            so.buf.fill_(float("nan"))
+            so.barrier()
+            got = shard.fp8_gemm_allgather(a, wl.t(), sa, swl, so, n0, bl, multicast=True)
+            torch.cuda.synchronize()
+            assert torch.equal(got, unfused), (rank, "multicast fused != fp8_gemm + NCCL all-gather", M, N, K)
+            so.barrier()
         del so
     dist.barrier()
     if rank == 0:

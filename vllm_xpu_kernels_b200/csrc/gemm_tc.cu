@@ -287,8 +287,8 @@ static bool force_single() {
 }
 
 // fused all-gather destination of the NEXT vxk_fp8_gemm call of this thread (set by vxk_fp8_gemm_allgather)
-struct PeerCfg { int n; void* ptr[8]; };
-static thread_local PeerCfg g_peer_cfg{0, {}};
+struct PeerCfg { int n; void* ptr[8]; int multicast; };
+static thread_local PeerCfg g_peer_cfg{0, {}, 0};
 
 static int g_force_fallback = -1;
 static bool force_fallback() {
@@ -472,6 +472,11 @@ extern "C" int vxk_fp8_gemm(void* D, const void* A, const void* B, const void* a
     VXK_REQUIRE(operands_ok && a_scale_mode != 2,
                 "fused all-gather: only the per-tensor / per-token / per-channel tensor-core path supports it");
     tp.n_peers = peers.n;
+    tp.peer_multicast = peers.multicast;
+    // a multicast mapping only takes the whole-row-segment stores of the CTA-pair kernel
+    if (peers.multicast)
+      VXK_REQUIRE(M > 256 && N % 256 == 0 && tp.vec_store_ok && !force_single(),
+                  "multicast all-gather needs M > 256, N %% 256 == 0 and 16-byte aligned output rows");
     for (int i = 0; i < peers.n; ++i) {
       tp.peer_D[i] = peers.ptr[i];
       tp.vec_store_ok = tp.vec_store_ok && aligned16(peers.ptr[i]);
@@ -488,7 +493,7 @@ extern "C" int vxk_fp8_gemm(void* D, const void* A, const void* B, const void* a
     if (peers.n == 0 && M <= skinny_max_m && M <= 256 && K >= 512 && (M <= 128 || (N + 127) / 128 <= sm_count()))
       return run_skinny_f8(tp, A, B, M, N, K, lda, b_stride_n, st);
     const int bn = single_cta_bn(M, N, 256);
-    if (!force_single() && prefer_pair(M, N, bn, 256)) {
+    if (!force_single() && (prefer_pair(M, N, bn, 256) || peers.multicast)) {
       Tc2Params t2{};
       t2.b = tp;
       const bool two = prefer_two_acc(M, N, K, 256);
@@ -555,7 +560,8 @@ extern "C" int vxk_fp8_gemm(void* D, const void* A, const void* B, const void* a
   return launch_gemm_fallback(p, /*is_fp4=*/false, st);
 }
 
-extern "C" int vxk_fp8_gemm_allgather(void* const* peer_out, int n_peers, int self_rank, int64_t col_offset, int64_t out_ld,
+extern "C" int vxk_fp8_gemm_allgather(void* const* peer_out, int n_peers, int self_rank, void* multicast_out,
+                                      int64_t col_offset, int64_t out_ld,
                                       const void* A, const void* B, const void* a_scale, const void* b_scale,
                                       const void* bias, int64_t M, int64_t N, int64_t K, int64_t lda,
                                       int64_t b_stride_k, int64_t b_stride_n, int a_scale_mode, int b_scale_mode,
@@ -570,6 +576,12 @@ extern "C" int vxk_fp8_gemm_allgather(void* const* peer_out, int n_peers, int se
     if (i != self_rank) g_peer_cfg.ptr[others++] = static_cast<uint16_t*>(peer_out[i]) + col_offset;
   }
   g_peer_cfg.n = others;
+  g_peer_cfg.multicast = 0;
+  if (multicast_out && others > 0) {     // one NVLS store instead of (ranks - 1) unicast stores
+    g_peer_cfg.ptr[0] = static_cast<uint16_t*>(multicast_out) + col_offset;
+    g_peer_cfg.n = 1;
+    g_peer_cfg.multicast = 1;
+  }
   void* own = static_cast<uint16_t*>(peer_out[self_rank]) + col_offset;
   const int rc = vxk_fp8_gemm(own, A, B, a_scale, b_scale, bias, M, N, K, lda, b_stride_k, b_stride_n,
                               out_ld, a_scale_mode, b_scale_mode, 0, 0, 0, 0, 0, 0, VXK_S_F32, fp8_dtype, out_dtype,

@@ -44,6 +44,7 @@ struct TcParams {
   int vec_store_ok;       // D rows 16-byte aligned -> 128-bit stores
   int n_peers;            // > 0: fused all-gather -- the tile also goes to peer_D[0..n_peers), the OTHER ranks'
   void* peer_D[8];        //      peer-mapped [M, N_total] outputs (offset to this rank's columns, row stride ldd like D)
+  int peer_multicast;     // 1: peer_D[0] is an NVLS multicast mapping of all ranks' outputs (one multimem.st reaches all)
   int debug;              // bring-up switches (env VXK_GEMM_DEBUG): 1 skip tcgen05.cp, 2 plain MMA, 4 skip re-tiler
 };
 

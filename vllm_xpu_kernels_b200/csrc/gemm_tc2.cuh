@@ -70,6 +70,12 @@ __device__ __forceinline__ uint4 ld_global_v4(const void* ptr) {
   asm volatile("ld.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(ptr) : "memory");
   return v;
 }
+// 128-bit store through an NVLS multicast mapping: the NVSwitch replicates it into every rank's buffer
+__device__ __forceinline__ void multimem_st_v4(void* mc_ptr, const uint4& v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(mc_ptr), "r"(v.x), "r"(v.y),
+               "r"(v.z), "r"(v.w)
+               : "memory");
+}
 __device__ __forceinline__ void cluster_sync_all() {
   asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
 }
@@ -371,6 +377,7 @@ gemm_tc2_kernel(const Tc2Params pp, const __grid_constant__ CUtensorMap map_a, c
     const int row_in_tile = static_cast<int>(rank) * kBlockM + q * 32 + lane;
     constexpr int kChunks = NACC == 2 ? BLOCK_N / 32 : BLOCK_N / 64;
     const bool row_copy = p.n_peers > 0 && p.vec_store_ok && kTileN % 256 == 0;   // else: direct peer stores
+    const bool mcast = p.peer_multicast != 0;
     int iter = 0;
     for (int tile = pair; tile < num_tiles; tile += num_pairs, ++iter) {
       int mt, nt;
@@ -427,8 +434,13 @@ gemm_tc2_kernel(const Tc2Params pp, const __grid_constant__ CUtensorMap map_a, c
               for (int pe = 0; pe < p.n_peers; ++pe) {
                 uint16_t* pa = static_cast<uint16_t*>(p.peer_D[pe]) + static_cast<int64_t>(ma) * p.ldd + nc;
                 uint16_t* pb = static_cast<uint16_t*>(p.peer_D[pe]) + static_cast<int64_t>(mb) * p.ldd + nc;
-                if (ma < p.M) *reinterpret_cast<uint4*>(pa) = va;
-                if (mb < p.M) *reinterpret_cast<uint4*>(pb) = vb;
+                if (mcast) {      // one store, replicated by the switch: egress = the slab once, not (ranks - 1) times
+                  if (ma < p.M) multimem_st_v4(pa, va);
+                  if (mb < p.M) multimem_st_v4(pb, vb);
+                } else {
+                  if (ma < p.M) *reinterpret_cast<uint4*>(pa) = va;
+                  if (mb < p.M) *reinterpret_cast<uint4*>(pb) = vb;
+                }
               }
             } else {
               for (int j = 0; nc + j < p.N; ++j)

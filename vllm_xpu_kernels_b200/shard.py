@@ -79,6 +79,10 @@ class SymmetricOutput:
         self.ptrs = [int(p) for p in self.hdl.buffer_ptrs]
         self.world = len(self.ptrs)
         self.rank = int(self.hdl.rank)
+        try:      # NVLS multicast mapping of the same buffers (0 / missing when the fabric has no multicast)
+            self.mc_ptr = int(self.hdl.multicast_ptr or 0)
+        except Exception:
+            self.mc_ptr = 0
 
     def barrier(self):
         """Device-side barrier of all ranks on the current stream: after it every rank's columns have landed."""
@@ -87,7 +91,7 @@ class SymmetricOutput:
 
 def fp8_gemm_allgather(a: torch.Tensor, wt_local: torch.Tensor, a_scale: torch.Tensor, w_scale_local: torch.Tensor,
                        out: SymmetricOutput, col_offset: int, bias_local: Optional[torch.Tensor] = None,
-                       sync: bool = True) -> torch.Tensor:
+                       sync: bool = True, multicast: bool = False) -> torch.Tensor:
     """D[:, col_offset : col_offset + N_local] = fp8_gemm(a, wt_local) written by the GEMM epilogue into EVERY
     rank's `out.buf` (NVLink peer stores), then one barrier: on return (stream order) `out.buf` holds the full
     [M, N_total] product on all ranks -- GEMM and all-gather in one kernel, no NCCL call.
@@ -108,9 +112,16 @@ def fp8_gemm_allgather(a: torch.Tensor, wt_local: torch.Tensor, a_scale: torch.T
     if bias_local is not None:
         bias_dt = {torch.float32: 0, torch.float16: 1, torch.bfloat16: 2}[bias_local.dtype]
     ptrs = (ctypes.c_void_p * out.world)(*out.ptrs)
+    # multicast=True sends each row segment once through the NVSwitch (multimem.st) instead of once per peer.
+    # An all-gather is bound by every rank's NVLink INGRESS (it must receive (p-1)/p of the output either way),
+    # so this measured no faster than unicast at 2 and 8 GPUs (profiles/r01e_bench_n8.json) and is off by default.
+    mc = out.mc_ptr if multicast else 0
+    if multicast and not mc:
+        raise RuntimeError("no multicast mapping on this symmetric-memory handle")
     i64 = ctypes.c_int64
     rc = lib.vxk_fp8_gemm_allgather(
-        ptrs, ctypes.c_int(out.world), ctypes.c_int(out.rank), i64(col_offset), i64(out.buf.stride(0)),
+        ptrs, ctypes.c_int(out.world), ctypes.c_int(out.rank), ctypes.c_void_p(mc), i64(col_offset),
+        i64(out.buf.stride(0)),
         ctypes.c_void_p(a.data_ptr()), ctypes.c_void_p(wt_local.data_ptr()),
         ctypes.c_void_p(a_scale.data_ptr()), ctypes.c_void_p(w_scale_local.data_ptr()),
         ctypes.c_void_p(bias_local.data_ptr() if bias_local is not None else 0),
