@@ -146,6 +146,37 @@ def bench_gemms(dev, rank, world, pk, steps=10, m_tokens=8192):
             del ref_full, got, so
         except Exception as exc:  # symmetric memory unavailable on this box / build
             gather["fused"] = {"error": f"{type(exc).__name__}: {exc}"[:300]}
+        # the same for the MXFP4 GEMM (BASELINE config 4)
+        try:
+            del a, w, sa, sw, wt
+            torch.cuda.empty_cache()
+            a4 = torch.randint(0, 256, (M, K // 2), dtype=torch.uint8, device=dev).view(torch.float4_e2m1fn_x2)
+            w4 = torch.randint(0, 256, (n1 - n0, K // 2), dtype=torch.uint8, device=dev).view(torch.float4_e2m1fn_x2)
+            sa4 = torch.randint(118, 130, (M, K // 32), dtype=torch.uint8, device=dev).view(E8)
+            sw4 = torch.randint(118, 130, (n1 - n0, K // 32), dtype=torch.uint8, device=dev).view(E8)
+            wt4 = w4.t()
+
+            def fn4():
+                return shard.all_gather_columns(torch.ops._xpu_C.fp4_gemm(a4, wt4, sa4, sw4, torch.bfloat16, None), N)
+
+            ref4 = fn4()
+            ms_u = _time(fn4, max(2, steps // 2))
+            so4 = shard.SymmetricOutput(M, N, torch.bfloat16, dev)
+            fused4 = lambda: shard.fp4_gemm_allgather(a4, wt4, sa4, sw4, so4, n0)  # noqa: E731
+            got4 = fused4()
+            torch.cuda.synchronize()
+            same4 = torch.tensor([1.0 if torch.equal(got4, ref4) else 0.0], device=dev)
+            ms_f4 = _time(fused4, max(2, steps // 2))
+            tt = torch.tensor([ms_u, ms_f4], dtype=torch.float64, device=dev)
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+            dist.all_reduce(same4, op=dist.ReduceOp.MIN)
+            gather["mxfp4"] = {"ms_gemm_plus_allgather": float(tt[0].item()),
+                               "ms_gemm_with_fused_allgather": float(tt[1].item()),
+                               "tflops_reassembled_fused": 2.0 * M * N * K / (float(tt[1].item()) * 1e-3) / 1e12,
+                               "bit_identical_to_nccl_path_on_all_ranks": bool(same4.item() == 1.0)}
+            del ref4, got4, so4
+        except Exception as exc:
+            gather["mxfp4"] = {"error": f"{type(exc).__name__}: {exc}"[:300]}
     tc, fb = stats()
     best = max((r for r in rows if r["kind"] != "fp8_w8a16"), key=lambda r: r["frac_of_dense_peak"]) if rows else None
     return {"shapes": "Llama-3-70B (K,N) x M=%d, N sharded over %d GPU(s)" % (M, world), "rows": rows,

@@ -207,6 +207,15 @@ int vxk_fp4_gemm(void* D, const void* A, const void* B, const void* a_scale, con
                  int out_dtype, int bias_dtype, void* workspace, int64_t workspace_bytes,
                  vxk_stream_t stream);
 
+/* MXFP4 counterpart of vxk_fp8_gemm_allgather (BASELINE config 4: Llama-3-70B MXFP4 GEMM, column-parallel):
+ * same contract, operands as vxk_fp4_gemm; needs M > 128 and the vxk_fp4_gemm_workspace_bytes scratch. */
+int vxk_fp4_gemm_allgather(void* const* peer_out, int n_peers, int self_rank, int64_t col_offset,
+                           int64_t out_ld, const void* A, const void* B, const void* a_scale,
+                           const void* b_scale, const void* bias, int64_t M, int64_t N, int64_t K,
+                           int64_t lda_bytes, int64_t ldb_bytes, int64_t sa0, int64_t sa1, int64_t sb0,
+                           int64_t sb1, int out_dtype, int bias_dtype, void* workspace,
+                           int64_t workspace_bytes, vxk_stream_t stream);
+
 /* Scratch the caller must provide to vxk_fp4_gemm (device memory, any alignment; the scale
  * factors are re-packed there in the tensor core's layout); 0 when none is needed.  Without
  * it the call still runs, on the single-CTA kernel.

@@ -52,6 +52,28 @@ def main():
             assert torch.equal(got, unfused), (rank, "multicast fused != fp8_gemm + NCCL all-gather", M, N, K)
             so.barrier()
         del so
+    # ---- MXFP4 (BASELINE config 4): packed E2M1 operands, E8M0 scales per 32
+    E8 = torch.float8_e8m0fnu
+    FP4 = torch.float4_e2m1fn_x2
+    for (M, N, K) in [(300, 1024, 512), (1000, 3072, 2048), (257, 384, 4096)]:
+        torch.manual_seed(9)
+        a = torch.randint(0, 256, (M, K // 2), dtype=torch.uint8, device=dev).view(FP4)
+        w = torch.randint(0, 256, (N, K // 2), dtype=torch.uint8, device=dev).view(FP4)
+        sa = torch.randint(118, 130, (M, K // 32), dtype=torch.uint8, device=dev).view(E8)
+        sw = torch.randint(118, 130, (N, K // 32), dtype=torch.uint8, device=dev).view(E8)
+        n0, n1 = shard.column_shard(N, rank, world)
+        wl = w.view(torch.uint8)[n0:n1].view(FP4)
+        swl = sw.view(torch.uint8)[n0:n1].contiguous().view(E8)
+        so = shard.SymmetricOutput(M, N, torch.bfloat16, dev)
+        so.buf.fill_(float("nan"))
+        so.barrier()
+        got = shard.fp4_gemm_allgather(a, wl.t(), sa, swl, so, n0)
+        torch.cuda.synchronize()
+        local = torch.ops._xpu_C.fp4_gemm(a, wl.t(), sa, swl, torch.bfloat16, None)
+        unfused = shard.all_gather_columns(local, N)
+        assert torch.equal(got, unfused), (rank, "mxfp4 fused != fp4_gemm + NCCL all-gather", M, N, K)
+        so.barrier()
+        del so
     dist.barrier()
     if rank == 0:
         print("mgpu allgather ok", world)

@@ -604,16 +604,25 @@ extern "C" int vxk_fp4_gemm(void* D, const void* A, const void* B, const void* a
   cudaStream_t st = stream;
   const bool ok = !force_fallback() && tma_ok(A, lda_bytes) && tma_ok(B, ldb_bytes) && sa1 == 1 && sb1 == 1 &&
                   tma_ok(a_scale, sa0) && tma_ok(b_scale, sb0) && K >= 64 && M < (1LL << 31) && N < (1LL << 31);
+  const PeerCfg peers = g_peer_cfg;
+  g_peer_cfg.n = 0;
+  if (peers.n > 0)
+    VXK_REQUIRE(ok && M > 128 && !force_single() && !peers.multicast && workspace &&
+                    workspace_bytes >= vxk_fp4_gemm_workspace_bytes(M, N, K),
+                "fused all-gather: needs the CTA-pair MXFP4 path (M > 128, TMA-expressible operands, workspace)");
   if (!ok) return launch_gemm_fallback(p, /*is_fp4=*/true, st);
   TcParams tp{};
   tp.D = D; tp.bias = bias; tp.M = (int)M; tp.N = (int)N; tp.K_bytes = (int)(K / 2); tp.ldd = ldd;
+  tp.n_peers = peers.n;
+  for (int i = 0; i < peers.n; ++i) tp.peer_D[i] = peers.ptr[i];
   tp.a_scale_mode = 2; tp.b_scale_mode = 2; tp.out_dtype = out_dtype; tp.bias_dtype = bias_dtype;
   tp.num_m_blocks = (int)((M + kBlockM - 1) / kBlockM);
   const int bn = single_cta_bn(M, N, 192);
   tp.num_n_blocks = (int)((N + bn - 1) / bn);
   tp.num_k_blocks = (int)((K / 2 + kBlockKBytes - 1) / kBlockKBytes);
   tp.vec_store_ok = aligned16(D) && (ldd * 2) % 16 == 0;
-  if (!force_single() && prefer_pair(M, N, bn, 192) && workspace &&
+  for (int i = 0; i < peers.n; ++i) tp.vec_store_ok = tp.vec_store_ok && aligned16(peers.ptr[i]);
+  if (!force_single() && (prefer_pair(M, N, bn, 192) || peers.n > 0) && workspace &&
       workspace_bytes >= vxk_fp4_gemm_workspace_bytes(M, N, K)) {
     Tc2Params t2{};
     t2.b = tp;
@@ -628,4 +637,27 @@ extern "C" int vxk_fp4_gemm(void* D, const void* A, const void* B, const void* a
   if ((rc = make_map_2d_u8(&msa, a_scale, K / 32, M, sa0, 16, kBlockM, false))) return rc;
   if ((rc = make_map_2d_u8(&msb, b_scale, K / 32, N, sb0, 16, bn, false))) return rc;
   return launch_tc_bn<KIND_MXF4>(bn, tp, ma, mb, msa, msb, st);
+}
+
+extern "C" int vxk_fp4_gemm_allgather(void* const* peer_out, int n_peers, int self_rank, int64_t col_offset,
+                                      int64_t out_ld, const void* A, const void* B, const void* a_scale,
+                                      const void* b_scale, const void* bias, int64_t M, int64_t N, int64_t K,
+                                      int64_t lda_bytes, int64_t ldb_bytes, int64_t sa0, int64_t sa1, int64_t sb0,
+                                      int64_t sb1, int out_dtype, int bias_dtype, void* workspace,
+                                      int64_t workspace_bytes, vxk_stream_t stream) {
+  VXK_REQUIRE(peer_out && n_peers >= 1 && n_peers <= 8, "1..8 peer outputs");
+  VXK_REQUIRE(self_rank >= 0 && self_rank < n_peers, "self_rank must index peer_out");
+  VXK_REQUIRE(col_offset >= 0 && col_offset + N <= out_ld, "this rank's columns must lie inside a row of the output");
+  int others = 0;
+  for (int i = 0; i < n_peers; ++i) {
+    VXK_REQUIRE(peer_out[i], "null peer output");
+    if (i != self_rank) g_peer_cfg.ptr[others++] = static_cast<uint16_t*>(peer_out[i]) + col_offset;
+  }
+  g_peer_cfg.n = others;
+  g_peer_cfg.multicast = 0;
+  void* own = static_cast<uint16_t*>(peer_out[self_rank]) + col_offset;
+  const int rc = vxk_fp4_gemm(own, A, B, a_scale, b_scale, bias, M, N, K, lda_bytes, ldb_bytes, out_ld, sa0, sa1, sb0,
+                              sb1, out_dtype, bias_dtype, workspace, workspace_bytes, stream);
+  g_peer_cfg.n = 0;
+  return rc;
 }

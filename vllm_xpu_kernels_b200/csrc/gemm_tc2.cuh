@@ -376,7 +376,7 @@ gemm_tc2_kernel(const Tc2Params pp, const __grid_constant__ CUtensorMap map_a, c
     const int h = e >> 2;                   // NACC == 2: accumulator; NACC == 1: column half
     const int row_in_tile = static_cast<int>(rank) * kBlockM + q * 32 + lane;
     constexpr int kChunks = NACC == 2 ? BLOCK_N / 32 : BLOCK_N / 64;
-    const bool row_copy = p.n_peers > 0 && p.vec_store_ok && kTileN % 256 == 0;   // else: direct peer stores
+    const bool row_copy = p.n_peers > 0 && p.vec_store_ok;   // else (unaligned output rows): direct peer stores
     const bool mcast = p.peer_multicast != 0;
     int iter = 0;
     for (int tile = pair; tile < num_tiles; tile += num_pairs, ++iter) {
@@ -411,15 +411,16 @@ gemm_tc2_kernel(const Tc2Params pp, const __grid_constant__ CUtensorMap map_a, c
       if (row_copy) {
         // Fused all-gather: this CTA's 128 x kTileN part of the tile now sits in the local output
         // (still in L2).  The eight epilogue warps push it to the other ranks as WHOLE ROW SEGMENTS -- a warp
-        // reads 512 contiguous bytes of one row (16 B per lane) and stores them to every peer mapping, so the
-        // NVLink writes are full 512-byte runs instead of the 16-byte pieces a row-per-thread store gives.
+        // reads up to 512 contiguous bytes of one row (16 B per lane) and stores them to every peer mapping, so the
+        // NVLink writes are full 384 / 512-byte runs instead of the 16-byte pieces a row-per-thread store gives.
         // The accumulator was handed back above: the transfer overlaps the next tile's main loop.
         asm volatile("bar.sync 1, 256;" ::: "memory");     // all epilogue warps' local stores of this tile are visible
         const int mrow0 = mt * (2 * kBlockM) + static_cast<int>(rank) * kBlockM;
 #pragma unroll 1
-        for (int seg = 0; seg < kTileN / 256; ++seg) {
-          const int nc = n0 + seg * 256 + lane * 8;
-          if (nc >= p.N) continue;
+        for (int seg = 0; seg < (kTileN + 255) / 256; ++seg) {
+          const int cw = seg * 256 + lane * 8;            // column inside the tile (192-wide tiles: 24 lanes)
+          const int nc = n0 + cw;
+          if (cw >= kTileN || nc >= p.N) continue;
           const bool whole8 = nc + 8 <= p.N;
 #pragma unroll 1
           for (int rr = e; rr < kBlockM; rr += 16) {

@@ -134,3 +134,41 @@ def fp8_gemm_allgather(a: torch.Tensor, wt_local: torch.Tensor, a_scale: torch.T
     if sync:
         out.barrier()
     return out.buf
+
+
+def fp4_gemm_allgather(a: torch.Tensor, wt_local: torch.Tensor, a_scale: torch.Tensor, w_scale_local: torch.Tensor,
+                       out: SymmetricOutput, col_offset: int, bias_local: Optional[torch.Tensor] = None,
+                       sync: bool = True) -> torch.Tensor:
+    """MXFP4 counterpart of fp8_gemm_allgather (C ABI vxk_fp4_gemm_allgather): a [M, K/2] float4_e2m1fn_x2,
+    wt_local [K/2, N_local] = transposed view of this rank's packed W[n0:n1, :], a_scale [M, K/32] and
+    w_scale_local [N_local, K/32] float8_e8m0fnu.  Needs M > 128 (CTA-pair kernel)."""
+    import ctypes
+
+    from . import _loader
+    lib = _loader.cdll()
+    assert a.dim() == 2 and wt_local.dim() == 2 and a.stride(1) == 1 and wt_local.stride(0) == 1
+    M, K = a.shape[0], 2 * a.shape[1]
+    n_local = wt_local.shape[1]
+    dt = {torch.bfloat16: 2, torch.float16: 1}[out.buf.dtype]
+    bias_dt = 0
+    if bias_local is not None:
+        bias_dt = {torch.float32: 0, torch.float16: 1, torch.bfloat16: 2}[bias_local.dtype]
+    i64 = ctypes.c_int64
+    lib.vxk_fp4_gemm_workspace_bytes.restype = ctypes.c_int64
+    ws_bytes = int(lib.vxk_fp4_gemm_workspace_bytes(i64(M), i64(n_local), i64(K)))
+    ws = torch.empty(max(ws_bytes, 16), dtype=torch.uint8, device=a.device)
+    ptrs = (ctypes.c_void_p * out.world)(*out.ptrs)
+    rc = lib.vxk_fp4_gemm_allgather(
+        ptrs, ctypes.c_int(out.world), ctypes.c_int(out.rank), i64(col_offset), i64(out.buf.stride(0)),
+        ctypes.c_void_p(a.data_ptr()), ctypes.c_void_p(wt_local.data_ptr()),
+        ctypes.c_void_p(a_scale.data_ptr()), ctypes.c_void_p(w_scale_local.data_ptr()),
+        ctypes.c_void_p(bias_local.data_ptr() if bias_local is not None else 0),
+        i64(M), i64(n_local), i64(K), i64(a.stride(0)), i64(wt_local.stride(1)),
+        i64(a_scale.stride(0)), i64(a_scale.stride(1)), i64(w_scale_local.stride(0)), i64(w_scale_local.stride(1)),
+        ctypes.c_int(dt), ctypes.c_int(bias_dt), ctypes.c_void_p(ws.data_ptr()), i64(ws_bytes),
+        ctypes.c_void_p(torch.cuda.current_stream().cuda_stream))
+    if rc != 0:
+        raise RuntimeError("vxk_fp4_gemm_allgather: " + lib.vxk_last_error().decode())
+    if sync:
+        out.barrier()
+    return out.buf
