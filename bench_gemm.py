@@ -177,6 +177,38 @@ def bench_gemms(dev, rank, world, pk, steps=10, m_tokens=8192):
             del ref4, got4, so4
         except Exception as exc:
             gather["mxfp4"] = {"error": f"{type(exc).__name__}: {exc}"[:300]}
+        # and for the DeepSeek-V3 block-scaled FP8 GEMM (BASELINE config 5: 1x128 / 128x128 fp32 scales)
+        try:
+            torch.cuda.empty_cache()
+            Kd, Nd = 7168, 36864
+            d0, d1 = shard.column_shard(Nd, rank, world)
+            ab = (torch.randn(M, Kd, device=dev) / 4).to(E4)
+            wb = (torch.randn(d1 - d0, Kd, device=dev) / 4).to(E4)
+            sab = torch.rand(M, Kd // 128, device=dev) + 0.5
+            swb = torch.rand(Kd // 128, (d1 - d0) // 128, device=dev) + 0.5
+            wtb = wb.t()
+
+            def fnb():
+                return shard.all_gather_columns(torch.ops._xpu_C.fp8_gemm(ab, wtb, torch.bfloat16, sab, swb, None), Nd)
+
+            refb = fnb()
+            ms_u = _time(fnb, max(2, steps // 2))
+            sob = shard.SymmetricOutput(M, Nd, torch.bfloat16, dev)
+            fusedb = lambda: shard.fp8_gemm_allgather(ab, wtb, sab, swb, sob, d0)  # noqa: E731
+            gotb = fusedb()
+            torch.cuda.synchronize()
+            sameb = torch.tensor([1.0 if torch.equal(gotb, refb) else 0.0], device=dev)
+            ms_fb = _time(fusedb, max(2, steps // 2))
+            tt = torch.tensor([ms_u, ms_fb], dtype=torch.float64, device=dev)
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+            dist.all_reduce(sameb, op=dist.ReduceOp.MIN)
+            gather["block_fp8_dsv3"] = {"shape": [M, Nd, Kd], "ms_gemm_plus_allgather": float(tt[0].item()),
+                                        "ms_gemm_with_fused_allgather": float(tt[1].item()),
+                                        "tflops_reassembled_fused": 2.0 * M * Nd * Kd / (float(tt[1].item()) * 1e-3) / 1e12,
+                                        "bit_identical_to_nccl_path_on_all_ranks": bool(sameb.item() == 1.0)}
+            del refb, gotb, sob
+        except Exception as exc:
+            gather["block_fp8_dsv3"] = {"error": f"{type(exc).__name__}: {exc}"[:300]}
     tc, fb = stats()
     best = max((r for r in rows if r["kind"] != "fp8_w8a16"), key=lambda r: r["frac_of_dense_peak"]) if rows else None
     return {"shapes": "Llama-3-70B (K,N) x M=%d, N sharded over %d GPU(s)" % (M, world), "rows": rows,

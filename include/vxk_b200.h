@@ -170,16 +170,17 @@ int vxk_fp8_gemm(void* D, const void* A, const void* B, const void* a_scale, con
  * first and then pushed to the others as whole 512-byte row segments; multicast_out, when
  * non-null, is an NVLS multicast mapping of the same buffers -- one multimem.st per segment
  * then reaches every rank through the NVSwitch, needs M > 256 and N % 256 == 0).  The caller
- * synchronises the ranks afterwards (one barrier) before reading.  Per-tensor / per-token /
- * per-channel scales only.  No reference counterpart: the reference has no parallelism, the
+ * synchronises the ranks afterwards (one barrier) before reading.  Scale arguments as vxk_fp8_gemm
+ * (block scales -- DeepSeek-V3 1x128 / 128x128, BASELINE config 5 -- need M > 128).  No reference counterpart: the reference has no parallelism, the
  * all-gather is the caller's (vLLM's) in tensor-parallel column-linear layers. */
 int vxk_fp8_gemm_allgather(void* const* peer_out, int n_peers, int self_rank, void* multicast_out,
-                           int64_t col_offset, int64_t out_ld,
-                           const void* A, const void* B, const void* a_scale, const void* b_scale,
-                           const void* bias, int64_t M, int64_t N, int64_t K, int64_t lda,
-                           int64_t b_stride_k, int64_t b_stride_n, int a_scale_mode,
-                           int b_scale_mode, int fp8_dtype, int out_dtype, int bias_dtype,
-                           vxk_stream_t stream);
+                           int64_t col_offset, int64_t out_ld, const void* A, const void* B,
+                           const void* a_scale, const void* b_scale, const void* bias, int64_t M,
+                           int64_t N, int64_t K, int64_t lda, int64_t b_stride_k, int64_t b_stride_n,
+                           int a_scale_mode, int b_scale_mode, int64_t group_k, int64_t group_n,
+                           int64_t sa0, int64_t sa1, int64_t sb0, int64_t sb1, int scale_dtype,
+                           int fp8_dtype, int out_dtype, int bias_dtype, void* workspace,
+                           int64_t workspace_bytes, vxk_stream_t stream);
 
 /* Scratch the caller must provide to vxk_fp8_gemm (device memory, any alignment); 0 when
  * none is needed.  ref: the per-call scratchpad of fp8_gemm_w8a8.h:176-179. */

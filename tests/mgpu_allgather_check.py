@@ -52,6 +52,31 @@ def main():
             assert torch.equal(got, unfused), (rank, "multicast fused != fp8_gemm + NCCL all-gather", M, N, K)
             so.barrier()
         del so
+    # ---- DeepSeek-V3 block scales (BASELINE config 5): A 1x128 fp32 / UE8M0, W 128x128
+    for (M, N, K, ue8m0) in [(300, 1024, 512, False), (1000, 3072, 2048, False), (700, 1536, 1024, True)]:
+        torch.manual_seed(11)
+        a = (torch.randn(M, K, device=dev) / 4).to(E4)
+        w = (torch.randn(N, K, device=dev) / 4).to(E4)
+        if ue8m0:
+            sa = torch.randint(120, 128, (M, K // 128), dtype=torch.uint8, device=dev).view(torch.float8_e8m0fnu)
+            sw = torch.randint(120, 128, (K // 128, N // 128), dtype=torch.uint8, device=dev).view(torch.float8_e8m0fnu)
+        else:
+            sa = torch.rand(M, K // 128, device=dev) + 0.5
+            sw = torch.rand(K // 128, N // 128, device=dev) + 0.5
+        n0, n1 = shard.column_shard(N, rank, world)
+        wl = w[n0:n1]
+        swl = sw.view(torch.uint8)[:, n0 // 128:n1 // 128].contiguous().view(sw.dtype) if ue8m0 \
+            else sw[:, n0 // 128:n1 // 128].contiguous()
+        so = shard.SymmetricOutput(M, N, torch.bfloat16, dev)
+        so.buf.fill_(float("nan"))
+        so.barrier()
+        got = shard.fp8_gemm_allgather(a, wl.t(), sa, swl, so, n0)
+        torch.cuda.synchronize()
+        local = torch.ops._xpu_C.fp8_gemm(a, wl.t(), torch.bfloat16, sa, swl, None)
+        unfused = shard.all_gather_columns(local, N)
+        assert torch.equal(got, unfused), (rank, "block-scaled fused != fp8_gemm + NCCL all-gather", M, N, K, ue8m0)
+        so.barrier()
+        del so
     # ---- MXFP4 (BASELINE config 4): packed E2M1 operands, E8M0 scales per 32
     E8 = torch.float8_e8m0fnu
     FP4 = torch.float4_e2m1fn_x2

@@ -469,8 +469,13 @@ extern "C" int vxk_fp8_gemm(void* D, const void* A, const void* B, const void* a
   const PeerCfg peers = g_peer_cfg;
   g_peer_cfg.n = 0;
   if (peers.n > 0) {
-    VXK_REQUIRE(operands_ok && a_scale_mode != 2,
-                "fused all-gather: only the per-tensor / per-token / per-channel tensor-core path supports it");
+    VXK_REQUIRE(operands_ok && !peers.multicast || (operands_ok && a_scale_mode != 2),
+                "fused all-gather needs TMA-expressible operands (multicast: no block scales)");
+    VXK_REQUIRE(a_scale_mode != 2 || (M > 128 && ((scale_dtype == VXK_S_F32 && group_k % 128 == 0 && group_n % 32 == 0 &&
+                                                  K % group_k == 0) ||
+                                                 (scale_dtype == VXK_S_E8M0 && group_k % 32 == 0 && workspace &&
+                                                  workspace_bytes >= vxk_fp8_gemm_workspace_bytes(M, N, K, 2, scale_dtype)))),
+                "fused all-gather with block scales needs M > 128 and a tensor-core-eligible scale grid");
     tp.n_peers = peers.n;
     tp.peer_multicast = peers.multicast;
     // a multicast mapping only takes the whole-row-segment stores of the CTA-pair kernel
@@ -530,7 +535,7 @@ extern "C" int vxk_fp8_gemm(void* D, const void* A, const void* B, const void* a
   if (operands_ok && a_scale_mode == 2 && scale_dtype == VXK_S_E8M0 && group_k % 32 == 0 && workspace &&
       workspace_bytes >= vxk_fp8_gemm_workspace_bytes(M, N, K, a_scale_mode, scale_dtype)) {
     const int bn = single_cta_bn(M, N, 192);
-    if (!force_single() && prefer_pair(M, N, bn, 192)) {
+    if (!force_single() && (prefer_pair(M, N, bn, 192) || peers.n > 0)) {
       Tc2Params t2{};
       t2.b = tp;
       return run_pair_block_scaled<KIND_MXF8>(t2, A, lda, B, b_stride_n, M, N, K, static_cast<const uint8_t*>(a_scale),
@@ -561,13 +566,13 @@ extern "C" int vxk_fp8_gemm(void* D, const void* A, const void* B, const void* a
 }
 
 extern "C" int vxk_fp8_gemm_allgather(void* const* peer_out, int n_peers, int self_rank, void* multicast_out,
-                                      int64_t col_offset, int64_t out_ld,
-                                      const void* A, const void* B, const void* a_scale, const void* b_scale,
-                                      const void* bias, int64_t M, int64_t N, int64_t K, int64_t lda,
-                                      int64_t b_stride_k, int64_t b_stride_n, int a_scale_mode, int b_scale_mode,
-                                      int fp8_dtype, int out_dtype, int bias_dtype, vxk_stream_t stream) {
+                                      int64_t col_offset, int64_t out_ld, const void* A, const void* B,
+                                      const void* a_scale, const void* b_scale, const void* bias, int64_t M, int64_t N,
+                                      int64_t K, int64_t lda, int64_t b_stride_k, int64_t b_stride_n, int a_scale_mode,
+                                      int b_scale_mode, int64_t group_k, int64_t group_n, int64_t sa0, int64_t sa1,
+                                      int64_t sb0, int64_t sb1, int scale_dtype, int fp8_dtype, int out_dtype,
+                                      int bias_dtype, void* workspace, int64_t workspace_bytes, vxk_stream_t stream) {
   VXK_REQUIRE(peer_out && n_peers >= 1 && n_peers <= 8, "1..8 peer outputs");
-  VXK_REQUIRE(a_scale_mode != 2 && b_scale_mode != 2, "fused all-gather: block scales are not supported");
   VXK_REQUIRE(col_offset >= 0 && col_offset + N <= out_ld, "this rank's columns must lie inside a row of the output");
   VXK_REQUIRE(self_rank >= 0 && self_rank < n_peers, "self_rank must index peer_out");
   int others = 0;
@@ -583,9 +588,9 @@ extern "C" int vxk_fp8_gemm_allgather(void* const* peer_out, int n_peers, int se
     g_peer_cfg.multicast = 1;
   }
   void* own = static_cast<uint16_t*>(peer_out[self_rank]) + col_offset;
-  const int rc = vxk_fp8_gemm(own, A, B, a_scale, b_scale, bias, M, N, K, lda, b_stride_k, b_stride_n,
-                              out_ld, a_scale_mode, b_scale_mode, 0, 0, 0, 0, 0, 0, VXK_S_F32, fp8_dtype, out_dtype,
-                              bias_dtype, nullptr, 0, stream);
+  const int rc = vxk_fp8_gemm(own, A, B, a_scale, b_scale, bias, M, N, K, lda, b_stride_k, b_stride_n, out_ld,
+                              a_scale_mode, b_scale_mode, group_k, group_n, sa0, sa1, sb0, sb1, scale_dtype, fp8_dtype,
+                              out_dtype, bias_dtype, workspace, workspace_bytes, stream);
   g_peer_cfg.n = 0;
   return rc;
 }

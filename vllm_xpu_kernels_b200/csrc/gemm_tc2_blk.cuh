@@ -143,6 +143,8 @@ gemm_tc2_blk_kernel(const Tc2BlkParams pp, const __grid_constant__ CUtensorMap m
     constexpr int kChunks = kCols / 32;
     static_assert(kCols % 32 == 0, "column halves must be whole 32-column chunks");
     const int row_in_tile = static_cast<int>(rank) * kBlockM + q * 32 + lane;
+    // fused all-gather: needs 16-byte aligned output rows and N % 8 == 0 (else direct peer stores)
+    const bool row_copy = p.n_peers > 0 && p.vec_store_ok && p.N % 8 == 0;
     uint32_t g = 0;
     for (int tile = pair; tile < num_tiles; tile += num_pairs) {
       int mt, nt;
@@ -268,7 +270,30 @@ gemm_tc2_blk_kernel(const Tc2BlkParams pp, const __grid_constant__ CUtensorMap m
             uint32_t bits[32];
 #pragma unroll
             for (int j = 0; j < 32; ++j) bits[j] = __float_as_uint(acc[c * 32 + j]);
-            epilogue_store_32(p, bits, m, nbase, 1.0f, false);
+            epilogue_store_32(p, bits, m, nbase, 1.0f, false, !row_copy);
+          }
+        }
+      }
+      if (row_copy) {
+        // fused all-gather (see gemm_tc2.cuh): push this CTA's 128 x BLOCK_N part of the finished tile to the
+        // other ranks as whole 384-byte row segments re-read from the local output (L2)
+        asm volatile("bar.sync 1, 256;" ::: "memory");
+        const int mrow0 = mt * (2 * kBlockM) + static_cast<int>(rank) * kBlockM;
+        const int cw = lane * 8;
+        const int nc = nt * BLOCK_N + cw;
+        if (cw < BLOCK_N && nc + 8 <= p.N) {
+#pragma unroll 1
+          for (int rr = e; rr < kBlockM; rr += 16) {
+            const int ma = mrow0 + rr, mb = ma + 8;
+            uint4 va = make_uint4(0, 0, 0, 0), vb = va;
+            if (ma < p.M) va = ld_global_v4(static_cast<const uint16_t*>(p.D) + static_cast<int64_t>(ma) * p.ldd + nc);
+            if (mb < p.M) vb = ld_global_v4(static_cast<const uint16_t*>(p.D) + static_cast<int64_t>(mb) * p.ldd + nc);
+#pragma unroll 1
+            for (int pe = 0; pe < p.n_peers; ++pe) {
+              uint16_t* pd = static_cast<uint16_t*>(p.peer_D[pe]) + nc;
+              if (ma < p.M) *reinterpret_cast<uint4*>(pd + static_cast<int64_t>(ma) * p.ldd) = va;
+              if (mb < p.M) *reinterpret_cast<uint4*>(pd + static_cast<int64_t>(mb) * p.ldd) = vb;
+            }
           }
         }
       }

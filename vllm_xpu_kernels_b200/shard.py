@@ -96,7 +96,8 @@ def fp8_gemm_allgather(a: torch.Tensor, wt_local: torch.Tensor, a_scale: torch.T
     rank's `out.buf` (NVLink peer stores), then one barrier: on return (stream order) `out.buf` holds the full
     [M, N_total] product on all ranks -- GEMM and all-gather in one kernel, no NCCL call.
     a [M, K] e4m3/e5m2; wt_local [K, N_local] K-major view of this rank's W[n0:n1, :]; scales fp32
-    (per tensor, per token [M] / [M,1], per channel [N_local] / [N_local,1])."""
+    (per tensor, per token [M] / [M,1], per channel [N_local] / [N_local,1]), or block scales a_scale [M, K/gk] with
+    w_scale_local [K/gk, N_local/gn] in fp32 or float8_e8m0fnu (DeepSeek-V3 recipe; needs M > 128)."""
     import ctypes
 
     from . import _loader
@@ -106,8 +107,26 @@ def fp8_gemm_allgather(a: torch.Tensor, wt_local: torch.Tensor, a_scale: torch.T
     n_local = wt_local.shape[1]
     dt = {torch.bfloat16: 2, torch.float16: 1}[out.buf.dtype]
     f8 = {torch.float8_e4m3fn: 0, torch.float8_e5m2: 1}[a.dtype]
-    a_scale = a_scale.contiguous()
-    w_scale_local = w_scale_local.contiguous()
+    block = a_scale.dim() == 2 and a_scale.shape[1] > 1          # [M, K/gk] with w_scale_local [K/gk, N_local/gn]
+    i64 = ctypes.c_int64
+    gk = gn = sa0 = sa1 = sb0 = sb1 = 0
+    scale_dt = 0
+    ws, ws_bytes = None, 0
+    if block:
+        assert w_scale_local.dim() == 2 and w_scale_local.shape[0] == a_scale.shape[1]
+        gk, gn = K // w_scale_local.shape[0], n_local // w_scale_local.shape[1]
+        sa0, sa1, sb0, sb1 = a_scale.stride(0), a_scale.stride(1), w_scale_local.stride(0), w_scale_local.stride(1)
+        a_mode = b_mode = 2
+        if a_scale.dtype == torch.float8_e8m0fnu:
+            scale_dt = 1
+            lib.vxk_fp8_gemm_workspace_bytes.restype = ctypes.c_int64
+            ws_bytes = int(lib.vxk_fp8_gemm_workspace_bytes(i64(M), i64(n_local), i64(K), ctypes.c_int(2), ctypes.c_int(1)))
+            ws = torch.empty(max(ws_bytes, 16), dtype=torch.uint8, device=a.device)
+    else:
+        a_scale = a_scale.contiguous()
+        w_scale_local = w_scale_local.contiguous()
+        a_mode = 0 if a_scale.numel() == 1 else 1
+        b_mode = 0 if w_scale_local.numel() == 1 else 1
     bias_dt = 0
     if bias_local is not None:
         bias_dt = {torch.float32: 0, torch.float16: 1, torch.bfloat16: 2}[bias_local.dtype]
@@ -118,7 +137,6 @@ def fp8_gemm_allgather(a: torch.Tensor, wt_local: torch.Tensor, a_scale: torch.T
     mc = out.mc_ptr if multicast else 0
     if multicast and not mc:
         raise RuntimeError("no multicast mapping on this symmetric-memory handle")
-    i64 = ctypes.c_int64
     rc = lib.vxk_fp8_gemm_allgather(
         ptrs, ctypes.c_int(out.world), ctypes.c_int(out.rank), ctypes.c_void_p(mc), i64(col_offset),
         i64(out.buf.stride(0)),
@@ -126,8 +144,9 @@ def fp8_gemm_allgather(a: torch.Tensor, wt_local: torch.Tensor, a_scale: torch.T
         ctypes.c_void_p(a_scale.data_ptr()), ctypes.c_void_p(w_scale_local.data_ptr()),
         ctypes.c_void_p(bias_local.data_ptr() if bias_local is not None else 0),
         i64(M), i64(n_local), i64(K), i64(a.stride(0)), i64(wt_local.stride(0)), i64(wt_local.stride(1)),
-        ctypes.c_int(0 if a_scale.numel() == 1 else 1), ctypes.c_int(0 if w_scale_local.numel() == 1 else 1),
-        ctypes.c_int(f8), ctypes.c_int(dt), ctypes.c_int(bias_dt),
+        ctypes.c_int(a_mode), ctypes.c_int(b_mode), i64(gk), i64(gn), i64(sa0), i64(sa1), i64(sb0), i64(sb1),
+        ctypes.c_int(scale_dt), ctypes.c_int(f8), ctypes.c_int(dt), ctypes.c_int(bias_dt),
+        ctypes.c_void_p(ws.data_ptr() if ws is not None else 0), i64(ws_bytes),
         ctypes.c_void_p(torch.cuda.current_stream().cuda_stream))
     if rc != 0:
         raise RuntimeError("vxk_fp8_gemm_allgather: " + lib.vxk_last_error().decode())
