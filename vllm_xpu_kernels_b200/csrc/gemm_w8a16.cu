@@ -184,6 +184,11 @@ static int run_w16_skinny(W16SkinnyParams sp, const void* A, const void* W, int6
   splits = (sp.num_k_blocks + per - 1) / per;            // no empty rank
   sp.kb_per_split = per;
   sp.splits = splits;
+  // L2 prefetch depth (raw stages ahead of the ring).  Measured 0 / 6 / 12 / 24: every depth > 0 is slower
+  // (39.6 / 40.4 / 42.0 / 44.4 us at N = 28672) -- the kernel is not bound by HBM latency but by the SM-side
+  // widening, and the extra requests only add contention.  Kept as a switch, off by default.
+  static const int env_pf = [] { const char* e = getenv("VXK_W16_PREFETCH"); return e ? atoi(e) : 0; }();
+  sp.prefetch = env_pf;
   const int mt = M <= 32 ? 32 : (M <= 64 ? 64 : 128);
   CUtensorMap mw, ma;
   int rc;

@@ -11,7 +11,7 @@
 //              this is what HBM has to deliver, and all of it is payload -- 16 KB of weight bytes per
 //              stage, 64 KB in flight per SM at MT = 32 (the general kernel has 2 KB per stage at M = 1
 //              because its stage is dominated by a 128-row activation box of padding)
-//   CONV ring  3 slots of two K-major SWIZZLE_128B operand tiles (128 rows x 64 elements of bf16 / f16 each)
+//   CONV ring  2 slots of two K-major SWIZZLE_128B operand tiles (128 rows x 64 elements of bf16 / f16 each)
 //   warps 8-23 converters (16 warps): raw stage -> conv slot (exact widening, widen16 of gemm_w8a16.cuh;
 //              128x128 block scales folded in); a thread widens 32 codes of one weight row per stage in
 //              registers BEFORE it waits for the slot, then stores, ONE generic->async proxy fence and
@@ -43,7 +43,15 @@ struct W16SkinnyParams {
   int num_k_blocks;       // 128-element K blocks in total
   int kb_per_split;
   int splits;
+  int prefetch;           // raw stages requested into L2 ahead of the ring (cp.async.bulk.prefetch.tensor)
 };
+
+// TMA prefetch of one box into L2: no shared memory, no barrier -- it only starts the HBM read early
+__device__ __forceinline__ void tma_prefetch_2d(const CUtensorMap* m, int c0, int c1) {
+  asm volatile("cp.async.bulk.prefetch.tensor.2d.L2.global.tile [%0, {%1, %2}];" ::"l"(reinterpret_cast<uint64_t>(m)),
+               "r"(c0), "r"(c1)
+               : "memory");
+}
 
 template <int MT>
 struct W16SkinnySmem {
@@ -51,7 +59,7 @@ struct W16SkinnySmem {
   static constexpr int kABox = MT * 128;                    // one 64-element activation slice
   static constexpr int kRawStage = kRawW + 2 * kABox;
   static constexpr int kConvSlot = 2 * 128 * 128;           // two operand tiles (128 rows x 64 elements each), 32 KB
-  static constexpr int kConvSlots = 3;
+  static constexpr int kConvSlots = 2;
   static constexpr int kStagesRaw = (196 * 1024 - kConvSlots * kConvSlot) / kRawStage;
   static constexpr int kStages = kStagesRaw > 8 ? 8 : kStagesRaw;
   static constexpr int kBarrierBytes = (2 * kStages + 2 * kConvSlots + 1) * 8 + 16;
@@ -122,8 +130,12 @@ gemm_w8a16_skinny_kernel(const W16SkinnyParams p, const __grid_constant__ CUtens
       tma_load_2d(st, &map_a, &full_bar[stg], (kb0 + it) * 256, 0);                 // byte coordinates
       tma_load_2d(st + L::kABox, &map_a, &full_bar[stg], (kb0 + it) * 256 + 128, 0);
     };
+    // Optional (p.prefetch > 0, off by default -- measured slower at every depth): request the weight stream
+    // into L2 `prefetch` stages ahead of the ring, so that the ring's own loads hit L2.
+    const int pf = p.prefetch;
     if (elect_one()) {
       for (int it = 0; it < pre; ++it) load_w(it, it);      // the weight does not depend on the previous kernel
+      for (int it = pre; it < min(nk, pre + pf); ++it) tma_prefetch_2d(&map_w, (kb0 + it) * kW16SkBlockK, n0);
     }
     __syncwarp();
     asm volatile("griddepcontrol.wait;" ::: "memory");
@@ -138,6 +150,7 @@ gemm_w8a16_skinny_kernel(const W16SkinnyParams p, const __grid_constant__ CUtens
       if (elect_one()) {
         load_w(it, stage);
         load_a(it, stage);
+        if (it + pf < nk) tma_prefetch_2d(&map_w, (kb0 + it + pf) * kW16SkBlockK, n0);
       }
       __syncwarp();
       if (++stage == S) { stage = 0; phase ^= 1; }
