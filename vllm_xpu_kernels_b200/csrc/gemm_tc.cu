@@ -191,8 +191,8 @@ static int launch_tc2(Tc2Params tp, const CUtensorMap& ma, const CUtensorMap& mb
   static const int dbg = env_int("VXK_GEMM_DEBUG", 0);
   // Row tiles per rasterisation group.  Measured at M = 8192 (profiles/r01e_groupm_sweep.txt): 16 is the best
   // overall; MXFP4 with a shallow K (<= 4096 operand bytes per row) gains 2-6 % from 32 (57344 columns:
-  // 5.11 -> 5.41 PF/s) because its K loop is too short to hide a W panel's first touch, while 32 costs
-  // 17-27 % on deep K and on FP8 with few column tiles.
+  // 5.11 -> 5.41 PF/s; cause not profiled yet), while 32 costs 17-27 % on deep K and on FP8 with few
+  // column tiles.
   static const int env_group_m = env_int("VXK_GEMM_GROUP_M", 0);
   const int group_m = env_group_m > 0 ? env_group_m : (KIND == KIND_MXF4 && tp.b.K_bytes <= 4096 ? 32 : 16);
   tp.b.debug = dbg;   // bring-up / timing switches: 1 skip tcgen05.cp, 8 skip scale-factor TMA
