@@ -21,7 +21,7 @@
 extern "C" {
 #endif
 
-#define VXK_ABI_VERSION 3
+#define VXK_ABI_VERSION 4
 
 typedef struct CUstream_st* vxk_stream_t; /* == cudaStream_t */
 
@@ -46,6 +46,11 @@ uint64_t vxk_launch_count(void);
 /* silu evaluation in the fused silu_and_mul_* kernels: 0 (default) = expf + IEEE divide,
  * 1 = ex2.approx / rcp.approx.  Returns the previous setting.  Process-wide. */
 int vxk_set_silu_fast(int on);
+/* Testing aid: out_t[i] = T(silu(in[i])) exactly as the fused silu_and_mul_* kernels evaluate it
+ * (mode 0 / 1 as vxk_set_silu_fast; mode 2 = approximate form with caller constants c, beta);
+ * out_f32[i] = the fp32 value before the rounding to T.  Either output may be null.  in_dtype F16/BF16. */
+int vxk_debug_silu(void* out_t, float* out_f32, const void* in, int64_t n, int in_dtype, int mode,
+                   float c, float beta, vxk_stream_t stream);
 
 /* ---------------------------------------------------------------- a1 ----
  * ref: dynamic_per_token_scaled_fp8_quant  csrc/quantization/fp8/fp8_quant.cpp:842-881

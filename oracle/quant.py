@@ -144,17 +144,35 @@ def per_token_group_quant_mxfp4(x: torch.Tensor, group_size: int = 32,
 # --------------------------------------------------------------------------
 # rms-norm prologue                   tests/test_fused_norm_quant.py:37-53
 # --------------------------------------------------------------------------
+# The one step of the rms-norm refs whose fp32 result depends on the HOST: torch's fp32
+# x.pow(2).mean() is a vectorised cascade sum whose grouping follows the CPU's vector width, so its
+# last bits differ between machines (and from any GPU reduction tree).  EXACT_VARIANCE = True
+# evaluates the same formula with the mean carried out in fp64 and rounded once to fp32 -- the
+# correctly rounded value every summation order approximates; the CUDA kernels are held to THAT
+# bit for bit, and tests/test_quant_parity_gpu.py measures how far torch's own fp32 order strays
+# from it (a few ulp of the variance at most).
+EXACT_VARIANCE = False
+
+
 def rms_norm_f32(x: torch.Tensor, weight: torch.Tensor, eps: float,
-                 residual: Optional[torch.Tensor] = None):
+                 residual: Optional[torch.Tensor] = None,
+                 exact_variance: Optional[bool] = None):
     """z = x_dtype(float(x) + float(res)) (written back as the new residual);
     var = mean(z^2); normed = z * rsqrt(var + eps) * float(w), all fp32 and no
-    intermediate rounding.  Returns (normed fp32, new residual or None)."""
+    intermediate rounding (tests/test_fused_norm_quant.py:37-53).
+    exact_variance (default: module flag EXACT_VARIANCE): mean in fp64, rounded once.
+    Returns (normed fp32, new residual or None)."""
+    if exact_variance is None:
+        exact_variance = EXACT_VARIANCE
     xf = x.float()
     if residual is not None:
         z = (xf + residual.float()).to(x.dtype)
         residual = z.clone()
         xf = z.float()
-    var = xf.pow(2).mean(dim=-1, keepdim=True)
+    if exact_variance:
+        var = xf.double().pow(2).mean(dim=-1, keepdim=True).float()
+    else:
+        var = xf.pow(2).mean(dim=-1, keepdim=True)
     inv_rms = torch.rsqrt(var + eps)
     return xf * inv_rms * weight.float(), residual
 
@@ -207,9 +225,9 @@ def exp2_ceil_log2(s: torch.Tensor) -> torch.Tensor:
 # a6  rms_norm + dynamic per-token     tests/test_fused_norm_quant.py:179-248
 # --------------------------------------------------------------------------
 def rms_norm_dynamic_per_token_quant(x, weight, eps, qdtype=E4M3, scale_ub=None,
-                                     residual=None):
+                                     residual=None, exact_variance=None):
     """Returns (q [T,H], scales [T], new residual or None)."""
-    normed, res = rms_norm_f32(x, weight, eps, residual)
+    normed, res = rms_norm_f32(x, weight, eps, residual, exact_variance)
     q, s = _per_token_quant_f32(normed, qdtype, scale_ub)
     return q, s, res
 
@@ -218,9 +236,9 @@ def rms_norm_dynamic_per_token_quant(x, weight, eps, qdtype=E4M3, scale_ub=None,
 # a7  rms_norm + per-block             tests/test_fused_norm_quant.py:251-317,565-636
 # --------------------------------------------------------------------------
 def rms_norm_per_block_quant(x, weight, eps, group_size, qdtype=E4M3,
-                             residual=None, scale_ue8m0=False):
+                             residual=None, scale_ue8m0=False, exact_variance=None):
     """Returns (q [T,H], scales [T,H/G], new residual or None)."""
-    normed, res = rms_norm_f32(x, weight, eps, residual)
+    normed, res = rms_norm_f32(x, weight, eps, residual, exact_variance)
     q, s = _per_group_quant_f32(normed, group_size, qdtype, scale_ue8m0)
     return q, s, res
 
@@ -228,10 +246,11 @@ def rms_norm_per_block_quant(x, weight, eps, group_size, qdtype=E4M3,
 # --------------------------------------------------------------------------
 # a8  rms_norm + MXFP4                 tests/test_fused_norm_quant.py:666-737
 # --------------------------------------------------------------------------
-def rms_norm_mxfp4_quant(x, weight, eps, residual=None, exact_exponent=True):
+def rms_norm_mxfp4_quant(x, weight, eps, residual=None, exact_exponent=True,
+                         exact_variance=None):
     """to_mxfp(normed.float(), 32, "mxfp4").  Returns (packed u8 [T,H/2],
     scales fp32 [T,H/32] = 2^(e-127), new residual or None)."""
-    normed, res = rms_norm_f32(x, weight, eps, residual)
+    normed, res = rms_norm_f32(x, weight, eps, residual, exact_variance)
     e, q = mx_quantize(normed.float().contiguous(), "mxfp4",
                        exact_exponent=exact_exponent)
     return q.view(torch.uint8), e8m0_to_f32(e), res
@@ -240,10 +259,10 @@ def rms_norm_mxfp4_quant(x, weight, eps, residual=None, exact_exponent=True):
 # --------------------------------------------------------------------------
 # a9  rms_norm (+add) + static FP8     tests/test_fused_norm_quant.py:448-456
 # --------------------------------------------------------------------------
-def rms_norm_static_fp8_quant(x, weight, scale, eps, residual=None):
+def rms_norm_static_fp8_quant(x, weight, scale, eps, residual=None, exact_variance=None):
     """fp32 normed (no rounding to the activation dtype) * (1/scale) -> e4m3.
     Returns (q, new residual or None)."""
-    normed, res = rms_norm_f32(x, weight, eps, residual)
+    normed, res = rms_norm_f32(x, weight, eps, residual, exact_variance)
     inv = 1.0 / scale.float()
     q = (normed.float() * inv).clamp(-448.0, 448.0).to(E4M3)
     return q, res
@@ -306,3 +325,50 @@ def silu_and_mul_mxfp4_quant(x: torch.Tensor, exact_exponent: bool = True):
     y = (g * torch.sigmoid(g) * u).contiguous()
     e, q = mx_quantize(y, "mxfp4", exact_exponent=exact_exponent)
     return q.view(torch.uint8), e8m0_to_f32(e)
+
+
+# --------------------------------------------------------------------------
+# "codes given the scale": the second half of every quantiser above, on its own.
+# Used by the parity tests where a kernel scale legitimately differs from the
+# oracle's by one step (a 1-ulp difference upstream): the codes must then be
+# exactly what the reference formula gives FOR THAT SCALE.
+# --------------------------------------------------------------------------
+def fp8_codes_given_scale(v: torch.Tensor, s: torch.Tensor, qdtype, group: int = 0,
+                          divide: bool = False) -> torch.Tensor:
+    """v [T,H] fp32 values, s [T] / [T,1] (group == 0) or [T,H/group] fp32 scales.
+    divide=False: sat(v * (1/s)) (a6, a7, a9, a10 -- the refs multiply by the reciprocal);
+    divide=True:  sat(v / s) (a1, a4, a11 -- the refs divide).  int8: round-half-even of v / s."""
+    T, H = v.shape
+    v = v.float()
+    se = s.reshape(T, -1).float()
+    se = se.expand(T, H) if se.shape[1] == 1 else se.repeat_interleave(group, dim=1)
+    if qdtype == torch.int8:
+        return (v / se).round().clamp(-128, 127).to(torch.int8)
+    m = FP8_MAX[qdtype]
+    q = (v / se) if divide else (v * (1.0 / se))
+    return q.clamp(-m, m).to(qdtype)
+
+
+def mxfp4_codes_given_exponent(v: torch.Tensor, e: torch.Tensor) -> torch.Tensor:
+    """to_mxfp's data path (mx_utils.py:327-353) for given E8M0 bytes e [T,H/32] (uint8):
+    clamp(v * 2^(127-e), +-6) -> bf16 -> E2M1 RNE -> packed bytes [T,H/2]."""
+    from .formats import e2m1_encode, pack_nibbles, E8M0_BIAS
+    T, H = v.shape
+    eb = e.view(torch.uint8).reshape(T, H // 32, 1)
+    inv = torch.where(eb == 0, torch.tensor(1.0), torch.exp2(E8M0_BIAS - eb.to(F32)))
+    q = torch.clamp(v.float().reshape(T, H // 32, 32) * inv, min=-6.0, max=6.0)
+    codes = e2m1_encode(q.to(torch.bfloat16).to(F32))
+    return pack_nibbles(codes.reshape(T, H))
+
+
+def silu_mul_T(x: torch.Tensor) -> torch.Tensor:
+    """y = silu(gate) * up evaluated in x.dtype (a10 / a11 prologue)."""
+    H = x.shape[-1] // 2
+    return (F.silu(x[..., :H]) * x[..., H:]).contiguous()
+
+
+def silu_mul_f32(x: torch.Tensor) -> torch.Tensor:
+    """y = gate_f32 * sigmoid(gate_f32) * up_f32 (a12 prologue)."""
+    H = x.shape[-1] // 2
+    g = x[..., :H].float()
+    return (g * torch.sigmoid(g) * x[..., H:].float()).contiguous()

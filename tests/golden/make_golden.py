@@ -238,6 +238,43 @@ def main():
                              a_hp=a_hp, w_hp=w_hp,
                              out=torch.matmul(a_hp, w_hp.t()))
 
+    # ---- (f)#1 fp8_gemm_w8a16: the three expected outputs of the reference's tests
+    # (test_fp8_gemm_onednn.py:88-126 per-tensor, :224-267 per-channel, :367-410 128x128 block),
+    # built from the reference's own helpers and the literal formulas of those tests
+    cases = []
+    for dtype in (torch.bfloat16, torch.float16):
+        m, n, k = 8, 256, 512
+        torch.manual_seed(1234)
+        a = torch.randn(m, k, dtype=dtype) / 10.0
+        w = torch.randn(n, k, dtype=dtype) / 10.0
+        # per tensor: weight * (1/scale) -> fp8 (static quant, :100-104), dequantised in `dtype`
+        s_t = torch.tensor(4.0)
+        wq_t = (w.float() * (1.0 / s_t)).clamp(-448, 448).to(E4)
+        out_t = torch.matmul(a, (wq_t.to(dtype) * s_t.to(dtype)).t())
+        cases.append(dict(kind="tensor", a=a, wq=u8(wq_t), scale=s_t.reshape(1), out=out_t))
+        # per channel: dynamic per-token quant of W[N,K] (:237-239), scale [N,1]
+        wq_c, s_c = t_fp8.ref_dynamic_per_token_quant(w, E4)
+        out_c = torch.matmul(a, (wq_c.to(dtype) * s_c.to(dtype)).t())
+        cases.append(dict(kind="channel", a=a, wq=u8(wq_c), scale=s_c, out=out_c))
+        # block: fp8_block_quant_2d / fp8_block_dequant_2d of tests/ops/fp8_quant_op.py (:384-393)
+        wq_b, s_b = fp8_quant_op.fp8_block_quant_2d(w, 128, 128, fp8_dtype=E4)
+        w_deq = fp8_quant_op.fp8_block_dequant_2d(wq_b, s_b, 128, 128, dtype)
+        out_b = torch.matmul(a, w_deq.t())
+        cases.append(dict(kind="block", a=a, wq=u8(wq_b), scale=s_b, out=out_b))
+    g["f1_fp8_gemm_w8a16"] = cases
+
+    # ---- silu on EVERY 16-bit input, through the reference's own ref function
+    # (test_fused_quant_activation.py:28-40: ref_silu_and_mul_quant = F.silu(gate) * up in x.dtype;
+    # with up = 1 and scale = 1 the e4m3 cast is the only other step, so the table is taken from
+    # F.silu directly -- the same call the ref makes).  The CUDA kernels' silu -> T rounding is held
+    # to this table input by input (tests/test_silu_exhaustive_gpu.py).
+    import torch.nn.functional as F
+    tab = {}
+    for dtype in (torch.bfloat16, torch.float16):
+        allv = torch.arange(0, 65536, dtype=torch.int32).to(torch.int16).view(dtype)
+        tab[str(dtype)] = F.silu(allv).view(torch.int16).clone()
+    g["silu_all_16bit"] = tab
+
     for name, obj in g.items():
         torch.save(obj, os.path.join(OUT, name + ".pt"))
         print(f"{name}: {os.path.getsize(os.path.join(OUT, name + '.pt'))/1024:.1f} KiB")

@@ -352,3 +352,148 @@ def test_gemm_linearity_full_size(ops):
     rows = torch.tensor([0, 1, 4095, 8191], device=DEV)
     ref = _gpu_ref(xq[rows].float() * xs[rows], wq.float() * ws, torch.bfloat16)
     torch.testing.assert_close(out1[rows].float(), ref.float(), atol=1e-2 * float(ref.float().abs().max()), rtol=1e-2)
+
+
+# ------------------------------------------------------------------ round-2 additions
+def _mx4_deq(q, s):
+    lut = torch.tensor(list(formats.E2M1_VALUES) + [-v for v in formats.E2M1_VALUES], device=q.device)
+    b = q.view(torch.uint8)
+    vals = torch.stack((lut[(b & 0xF).long()], lut[(b >> 4).long()]), dim=-1).reshape(b.shape[0], -1)
+    return vals * s.float().repeat_interleave(32, dim=1)
+
+
+@pytest.mark.parametrize("k", [11008, 2880, 96, 544])
+@pytest.mark.parametrize("m", [1, 64, 300])
+def test_mxfp4_gemm_unaligned_scale_pitch(ops, lib, k, m):
+    """K/32 not a multiple of 16 bytes (Llama-2 MLP K = 11008, K = 2880): the scale rows are not
+    TMA-expressible as they stand, the call must still run on the tensor cores."""
+    torch.manual_seed(5)
+    n = 384
+    x = torch.randn(m, k, dtype=torch.bfloat16, device=DEV)
+    w = torch.randn(n, k, dtype=torch.bfloat16, device=DEV) * 0.05
+    xq, xs = ops.per_token_group_quant_mxfp4(x)
+    wq, ws = ops.per_token_group_quant_mxfp4(w)
+    tc0, fb0 = gemm_stats(lib)
+    out = ops.fp4_gemm(xq, wq.t(), xs, ws, torch.bfloat16)
+    tc1, fb1 = gemm_stats(lib)
+    assert (tc1, fb1) == (tc0 + 1, fb0), "must not fall back to the CUDA-core kernel"
+    ref = _gpu_ref(_mx4_deq(xq, xs), _mx4_deq(wq, ws), torch.bfloat16)
+    torch.testing.assert_close(out.float(), ref.float(), atol=1e-2 * float(ref.float().abs().max()), rtol=1e-2)
+
+
+def _rows_sample(m):
+    return torch.tensor(sorted({0, 1, 127, 128, 255, 256, m // 2 - 1, m // 2, m - 2, m - 1}), device=DEV)
+
+
+@pytest.mark.parametrize("kn", LLAMA70B)
+def test_llama70b_mxfp4_full_m(ops, lib, kn):
+    """Config 4 at M = 8192 on a row sample against an fp32 matmul of the dequantised operands
+    (the rows cover both CTAs of a pair, tile edges and the last tile)."""
+    k, n = kn
+    m = 8192
+    torch.manual_seed(6)
+    x = torch.randn(m, k, dtype=torch.bfloat16, device=DEV)
+    w = torch.randn(n, k, dtype=torch.bfloat16, device=DEV) * 0.05
+    xq, xs = ops.per_token_group_quant_mxfp4(x)
+    wq, ws = ops.per_token_group_quant_mxfp4(w)
+    del x, w
+    out = ops.fp4_gemm(xq, wq.t(), xs, ws, torch.bfloat16)
+    rows = _rows_sample(m)
+    ref = _gpu_ref(_mx4_deq(xq[rows], xs[rows]), _mx4_deq(wq, ws), torch.bfloat16)
+    torch.testing.assert_close(out[rows].float(), ref.float(), atol=1e-2 * float(ref.float().abs().max()), rtol=1e-2)
+    # linearity: doubling every weight scale (an exponent-byte increment) doubles the output exactly
+    ws2 = (ws.view(torch.uint8) + 1).view(E8)
+    out2 = ops.fp4_gemm(xq, wq.t(), xs, ws2, torch.bfloat16)
+    assert torch.equal(out2, out * 2.0)
+
+
+@pytest.mark.parametrize("kn", DEEPSEEK + [(7168, 576)])
+@pytest.mark.parametrize("ue8m0", [True, False])
+def test_deepseek_block_fp8_full_m(ops, kn, ue8m0):
+    """Config 5 at M = 8192 on a row sample; (7168, 576) is the N % 128 != 0 edge the reference's integer
+    n / sB.size(1) cannot express with 128-wide blocks (fp8_gemm_w8a8.h:40) -- run with gn = 64."""
+    k, n = kn
+    gn = 128 if n % 128 == 0 else 64
+    m = 8192
+    torch.manual_seed(7)
+    x = torch.randn(m, k, dtype=torch.bfloat16, device=DEV) / 10.0
+    w = torch.randn(n, k, dtype=torch.bfloat16, device=DEV) / 10.0
+    xq, xs = ops.per_token_group_quant_fp8(x, 128, dtype=E4, use_ue8m0=ue8m0)
+    wb = w.float().reshape(n // gn, gn, k // 128, 128)
+    s = wb.abs().amax(dim=(1, 3)).clamp(min=1e-6) / 448.0
+    if ue8m0:
+        s = torch.exp2(torch.ceil(torch.log2(s)))
+    wq = (wb / s[:, None, :, None]).clamp(-448, 448).to(E4).reshape(n, k)
+    ws = s.to(E8) if ue8m0 else s
+    del x, w, wb
+    out = ops.fp8_gemm(xq, wq.t(), torch.bfloat16, xs, ws.t().contiguous(), None)
+    rows = _rows_sample(m)
+    a_deq = xq[rows].float() * xs[rows].float().repeat_interleave(128, dim=1)
+    w_deq = wq.float() * ws.float().repeat_interleave(gn, dim=0).repeat_interleave(128, dim=1)
+    ref = _gpu_ref(a_deq, w_deq, torch.bfloat16)
+    torch.testing.assert_close(out[rows].float(), ref.float(), atol=1e-2 * float(ref.float().abs().max()), rtol=1e-2)
+
+
+@pytest.mark.parametrize("kind", ["fp8", "mxfp4", "block_fp8"])
+def test_gemm_m_sweep(ops, kind):
+    """M = 1, 2, 4, ... 4096 on one shape per kind: every kernel-selection boundary is crossed."""
+    torch.manual_seed(8)
+    k, n = 4096, 6144
+    w = torch.randn(n, k, dtype=torch.bfloat16, device=DEV) / 10.0
+    xall = torch.randn(4096, k, dtype=torch.bfloat16, device=DEV) / 10.0
+    if kind == "fp8":
+        wq, ws = ops.scaled_fp8_quant(w, use_per_token_if_dynamic=True, fp8_dtype=E4)
+        w_deq = wq.float() * ws
+    elif kind == "mxfp4":
+        wq, ws = ops.per_token_group_quant_mxfp4(w)
+        w_deq = _mx4_deq(wq, ws)
+    else:
+        wb = w.float().reshape(n // 128, 128, k // 128, 128)
+        s = wb.abs().amax(dim=(1, 3)).clamp(min=1e-6) / 448.0
+        wq = (wb / s[:, None, :, None]).clamp(-448, 448).to(E4).reshape(n, k)
+        ws = s
+        w_deq = wq.float() * s.repeat_interleave(128, dim=0).repeat_interleave(128, dim=1)
+    for e in range(13):
+        m = 1 << e
+        x = xall[:m]
+        if kind == "fp8":
+            xq, xs = ops.scaled_fp8_quant(x, use_per_token_if_dynamic=True, fp8_dtype=E4)
+            out = ops.fp8_gemm(xq, wq.t(), torch.bfloat16, xs, ws, None)
+            a_deq = xq.float() * xs
+        elif kind == "mxfp4":
+            xq, xs = ops.per_token_group_quant_mxfp4(x)
+            out = ops.fp4_gemm(xq, wq.t(), xs, ws, torch.bfloat16)
+            a_deq = _mx4_deq(xq, xs)
+        else:
+            xq, xs = ops.per_token_group_quant_fp8(x, 128, dtype=E4, use_ue8m0=False)
+            out = ops.fp8_gemm(xq, wq.t(), torch.bfloat16, xs, ws.t().contiguous(), None)
+            a_deq = xq.float() * xs.repeat_interleave(128, dim=1)
+        ref = _gpu_ref(a_deq, w_deq, torch.bfloat16)
+        torch.testing.assert_close(out.float(), ref.float(), atol=1e-2 * float(ref.float().abs().max()), rtol=1e-2,
+                                   msg=lambda s, m=m: f"{kind} M={m}: {s}")
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two CUDA devices in one process")
+def test_ops_on_second_device_after_first(ops):
+    """One process, cuda:0 then cuda:1: per-device kernel attributes (dynamic shared memory above 48 KB)
+    must be set on both."""
+    for dev in ("cuda:0", "cuda:1"):
+        torch.manual_seed(9)
+        x = torch.randn(300, 4096, dtype=torch.bfloat16, device=dev) / 10.0
+        w = torch.randn(512, 4096, dtype=torch.bfloat16, device=dev) / 10.0
+        xq, xs = ops.scaled_fp8_quant(x, use_per_token_if_dynamic=True, fp8_dtype=E4)
+        wq, ws = ops.scaled_fp8_quant(w, use_per_token_if_dynamic=True, fp8_dtype=E4)
+        out = ops.fp8_gemm(xq, wq.t(), torch.bfloat16, xs, ws, None)
+        ref = _gpu_ref(xq.float() * xs, wq.float() * ws, torch.bfloat16)
+        torch.testing.assert_close(out.float(), ref.float(), atol=1e-2, rtol=1e-2)
+        x4, s4 = ops.per_token_group_quant_mxfp4(x)
+        w4, t4 = ops.per_token_group_quant_mxfp4(w)
+        out4 = ops.fp4_gemm(x4, w4.t(), s4, t4, torch.bfloat16)
+        ref4 = _gpu_ref(_mx4_deq(x4, s4), _mx4_deq(w4, t4), torch.bfloat16)
+        torch.testing.assert_close(out4.float(), ref4.float(), atol=1e-2 * float(ref4.float().abs().max()), rtol=1e-2)
+        # rms weight staged in > 48 KB of dynamic shared memory (H = 14336)
+        xr = torch.randn(64, 14336, dtype=torch.bfloat16, device=dev) / 14336
+        wr = torch.empty(14336, dtype=torch.bfloat16, device=dev).normal_(1.0, 0.1)
+        q, s = ops.rms_norm_dynamic_per_token_quant(xr, wr, 1e-6, E4)
+        rq, rs, _ = oq.rms_norm_dynamic_per_token_quant(xr.cpu(), wr.cpu(), 1e-6, E4, exact_variance=True)
+        assert torch.equal(s.cpu(), rs)

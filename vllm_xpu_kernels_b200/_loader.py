@@ -9,6 +9,8 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "_lib", "libvxk_b200.so")
 SHIM_PATH = os.path.join(_HERE, "_lib", "_vxk_torch_ops.so")
 
+ABI_VERSION = 4   # == VXK_ABI_VERSION of include/vxk_b200.h
+
 _lock = threading.Lock()
 _cdll = None
 _ops_loaded = False
@@ -31,6 +33,10 @@ def cdll() -> ctypes.CDLL:
             lib.vxk_last_error.restype = ctypes.c_char_p
             lib.vxk_launch_count.restype = ctypes.c_uint64
             lib.vxk_abi_version.restype = ctypes.c_int
+            if lib.vxk_abi_version() != ABI_VERSION:
+                raise ExtensionMissing(
+                    f"{LIB_PATH} exports C ABI version {lib.vxk_abi_version()}, this package needs {ABI_VERSION}: "
+                    "stale build (run `python -m vllm_xpu_kernels_b200.build --force`).")
             _cdll = lib
     return _cdll
 

@@ -4,7 +4,6 @@
 #include "gemm_tc2_blk.cuh"
 #include "gemm_skinny.cuh"
 
-#include <mutex>
 
 namespace vxk {
 
@@ -78,11 +77,10 @@ static int launch_tc(const TcParams& tp, const CUtensorMap& ma, const CUtensorMa
                      const CUtensorMap& msb, cudaStream_t st) {
   using L = TcSmem<KIND, BLOCK_N>;
   auto kernel = gemm_tc_kernel<KIND, BLOCK_N>;
-  static std::once_flag once;
-  static cudaError_t attr_err = cudaSuccess;
-  std::call_once(once, [&] {
-    attr_err = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotalBytes);
-  });
+  static PerDeviceOnce once;
+  const cudaError_t attr_err = once.get([&](PerDeviceOnce::Entry& x) {
+    x.err = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotalBytes);
+  }).err;
   if (attr_err != cudaSuccess)
     return fail(VXK_ERR_CUDA, "cudaFuncSetAttribute(smem=%d): %s", L::kTotalBytes, cudaGetErrorString(attr_err));
   static const int dbg = [] { const char* e = getenv("VXK_GEMM_DEBUG"); return e ? atoi(e) : 0; }();
@@ -179,13 +177,13 @@ static int launch_tc2(Tc2Params tp, const CUtensorMap& ma, const CUtensorMap& mb
                       const CUtensorMap& msb, cudaStream_t st) {
   using L = Tc2Smem<KIND, BLOCK_N, NACC>;
   auto kernel = gemm_tc2_kernel<KIND, BLOCK_N, NACC>;
-  static std::once_flag once;
-  static cudaError_t attr_err = cudaSuccess;
-  static int pairs = 0;
-  std::call_once(once, [&] {
-    attr_err = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotalBytes);
-    if (attr_err == cudaSuccess) pairs = max_cluster_pairs(reinterpret_cast<const void*>(kernel), L::kTotalBytes);
+  static PerDeviceOnce once;
+  const PerDeviceOnce::Entry cfg_once = once.get([&](PerDeviceOnce::Entry& x) {
+    x.err = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotalBytes);
+    if (x.err == cudaSuccess) x.aux = max_cluster_pairs(reinterpret_cast<const void*>(kernel), L::kTotalBytes);
   });
+  const cudaError_t attr_err = cfg_once.err;
+  const int pairs = cfg_once.aux;
   if (attr_err != cudaSuccess)
     return fail(VXK_ERR_CUDA, "cudaFuncSetAttribute(smem=%d): %s", L::kTotalBytes, cudaGetErrorString(attr_err));
   static const int dbg = env_int("VXK_GEMM_DEBUG", 0);
@@ -208,13 +206,13 @@ template <int BLOCK_N, bool PIPE>
 static int launch_tc2_blk(Tc2BlkParams tp, const CUtensorMap& ma, const CUtensorMap& mb, cudaStream_t st) {
   using L = Tc2Smem<KIND_F8, BLOCK_N, 1>;
   auto kernel = gemm_tc2_blk_kernel<BLOCK_N, PIPE>;
-  static std::once_flag once;
-  static cudaError_t attr_err = cudaSuccess;
-  static int pairs = 0;
-  std::call_once(once, [&] {
-    attr_err = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotalBytes);
-    if (attr_err == cudaSuccess) pairs = max_cluster_pairs(reinterpret_cast<const void*>(kernel), L::kTotalBytes);
+  static PerDeviceOnce once;
+  const PerDeviceOnce::Entry cfg_once = once.get([&](PerDeviceOnce::Entry& x) {
+    x.err = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotalBytes);
+    if (x.err == cudaSuccess) x.aux = max_cluster_pairs(reinterpret_cast<const void*>(kernel), L::kTotalBytes);
   });
+  const cudaError_t attr_err = cfg_once.err;
+  const int pairs = cfg_once.aux;
   if (attr_err != cudaSuccess)
     return fail(VXK_ERR_CUDA, "cudaFuncSetAttribute(smem=%d): %s", L::kTotalBytes, cudaGetErrorString(attr_err));
   static const int group_m = env_int("VXK_GEMM_GROUP_M", 16);
@@ -353,11 +351,10 @@ template <int MT>
 static int launch_skinny(SkinnyParams sp, const CUtensorMap& mw, const CUtensorMap& ma, int n_tiles, cudaStream_t st) {
   using L = SkinnySmem<MT>;
   auto kernel = gemm_skinny_kernel<MT>;
-  static std::once_flag once;
-  static cudaError_t attr_err = cudaSuccess;
-  std::call_once(once, [&] {
-    attr_err = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotalBytes);
-  });
+  static PerDeviceOnce once;
+  const cudaError_t attr_err = once.get([&](PerDeviceOnce::Entry& x) {
+    x.err = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotalBytes);
+  }).err;
   if (attr_err != cudaSuccess)
     return fail(VXK_ERR_CUDA, "cudaFuncSetAttribute(smem=%d): %s", L::kTotalBytes, cudaGetErrorString(attr_err));
   cudaLaunchConfig_t cfg{};
@@ -439,10 +436,22 @@ extern "C" int64_t vxk_fp8_gemm_workspace_bytes(int64_t M, int64_t N, int64_t K,
   return single > pair ? single : pair;
 }
 
+// single-CTA kernel, scale rows that TMA cannot fetch directly (K/32 not a multiple of 16 bytes, e.g.
+// K = 11008 or 2880): both grids are copied once to a 16-byte pitch
+static int64_t fp4_canon_pitch(int64_t K) { return ((K + 31) / 32 + 15) / 16 * 16; }
+static int64_t fp4_canon_bytes(int64_t M, int64_t N, int64_t K) { return (M + N) * fp4_canon_pitch(K) + 512; }
+
 extern "C" int64_t vxk_fp4_gemm_workspace_bytes(int64_t M, int64_t N, int64_t K) {
-  if (M <= 128) return 0;   // single-CTA kernel reads the caller's scale tensors directly
-  const SfPack sp = sf_pack_plan(M, N, K, true);
-  return sp.a_bytes + sp.b_bytes + 512;
+  int64_t need = 0;
+  if (M > 128) {             // CTA-pair kernel: scale factors re-packed in tcgen05.cp order
+    const SfPack sp = sf_pack_plan(M, N, K, true);
+    need = sp.a_bytes + sp.b_bytes + 512;
+  }
+  if ((K / 32) % 16 != 0) {  // (contiguous scale rows assumed; anything else is checked at call time)
+    const int64_t c = fp4_canon_bytes(M, N, K);
+    need = c > need ? c : need;
+  }
+  return need;               // 0: the single-CTA kernel reads the caller's scale tensors directly
 }
 
 extern "C" int vxk_fp8_gemm(void* D, const void* A, const void* B, const void* a_scale, const void* b_scale,
@@ -612,8 +621,10 @@ extern "C" int vxk_fp4_gemm(void* D, const void* A, const void* B, const void* a
   GemmParams p{D, A, B, a_scale, b_scale, bias, M, N, K, lda_bytes, 1, ldb_bytes, ldd, 2, 2, 32, 1, sa0, sa1, sb0, sb1,
                VXK_S_E8M0, VXK_Q_E4M3, out_dtype, bias_dtype};
   cudaStream_t st = stream;
-  const bool ok = !force_fallback() && tma_ok(A, lda_bytes) && tma_ok(B, ldb_bytes) && sa1 == 1 && sb1 == 1 &&
-                  tma_ok(a_scale, sa0) && tma_ok(b_scale, sb0) && K >= 64 && M < (1LL << 31) && N < (1LL << 31);
+  // the operands must be TMA-expressible; the scale grids only when the single-CTA kernel fetches them directly
+  const bool ok = !force_fallback() && tma_ok(A, lda_bytes) && tma_ok(B, ldb_bytes) && K >= 64 && M < (1LL << 31) &&
+                  N < (1LL << 31);
+  const bool scales_direct = sa1 == 1 && sb1 == 1 && tma_ok(a_scale, sa0) && tma_ok(b_scale, sb0);
   const PeerCfg peers = g_peer_cfg;
   g_peer_cfg.n = 0;
   if (peers.n > 0)
@@ -642,10 +653,26 @@ extern "C" int vxk_fp4_gemm(void* D, const void* A, const void* B, const void* a
   }
   CUtensorMap ma, mb, msa, msb;
   int rc;
+  const void* sfa = a_scale;
+  const void* sfb = b_scale;
+  int64_t pa = sa0, pb = sb0;
+  if (!scales_direct) {
+    if (!workspace || workspace_bytes < fp4_canon_bytes(M, N, K)) return launch_gemm_fallback(p, /*is_fp4=*/true, st);
+    const int64_t groups32 = K / 32, pitch = fp4_canon_pitch(K);
+    uint8_t* ws = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(workspace) + 255) & ~uintptr_t(255));
+    uint8_t* wa = ws;
+    uint8_t* wb = ws + M * pitch;
+    const int blocks = 4 * sm_count();
+    canon_sf_kernel<<<blocks, 256, 0, st>>>(wa, M, groups32, pitch, static_cast<const uint8_t*>(a_scale), 1, sa0, 1, sa1);
+    if ((rc = check_launch("canon_sfa"))) return rc;
+    canon_sf_kernel<<<blocks, 256, 0, st>>>(wb, N, groups32, pitch, static_cast<const uint8_t*>(b_scale), 1, sb0, 1, sb1);
+    if ((rc = check_launch("canon_sfb"))) return rc;
+    sfa = wa; sfb = wb; pa = pb = pitch;
+  }
   if ((rc = make_map_2d_u8(&ma, A, K / 2, M, lda_bytes, kBlockKBytes, kBlockM, true))) return rc;
   if ((rc = make_map_2d_u8(&mb, B, K / 2, N, ldb_bytes, kBlockKBytes, bn, true))) return rc;
-  if ((rc = make_map_2d_u8(&msa, a_scale, K / 32, M, sa0, 16, kBlockM, false))) return rc;
-  if ((rc = make_map_2d_u8(&msb, b_scale, K / 32, N, sb0, 16, bn, false))) return rc;
+  if ((rc = make_map_2d_u8(&msa, sfa, scales_direct ? K / 32 : pa, M, pa, 16, kBlockM, false))) return rc;
+  if ((rc = make_map_2d_u8(&msb, sfb, scales_direct ? K / 32 : pb, N, pb, 16, bn, false))) return rc;
   return launch_tc_bn<KIND_MXF4>(bn, tp, ma, mb, msa, msb, st);
 }
 

@@ -78,11 +78,10 @@ template <int BLOCK_N, bool BF16, bool E5M2, bool SCALED>
 static int launch_w16(const W16Params& wp, const CUtensorMap& ma, const CUtensorMap& mw, cudaStream_t st) {
   using L = W16Smem<BLOCK_N>;
   auto kernel = gemm_w8a16_kernel<BLOCK_N, BF16, E5M2, SCALED>;
-  static std::once_flag once;
-  static cudaError_t attr_err = cudaSuccess;
-  std::call_once(once, [&] {
-    attr_err = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotalBytes);
-  });
+  static PerDeviceOnce once;
+  const cudaError_t attr_err = once.get([&](PerDeviceOnce::Entry& x) {
+    x.err = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotalBytes);
+  }).err;
   if (attr_err != cudaSuccess)
     return fail(VXK_ERR_CUDA, "cudaFuncSetAttribute(smem=%d): %s", L::kTotalBytes, cudaGetErrorString(attr_err));
   const int tiles = wp.b.num_m_blocks * wp.b.num_n_blocks;
@@ -126,11 +125,10 @@ static int launch_w16_skinny(const W16SkinnyParams& sp, const CUtensorMap& mw, c
                              cudaStream_t st) {
   using L = W16SkinnySmem<MT>;
   auto kernel = gemm_w8a16_skinny_kernel<MT, BF16, E5M2, SCALED>;
-  static std::once_flag once;
-  static cudaError_t attr_err = cudaSuccess;
-  std::call_once(once, [&] {
-    attr_err = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotalBytes);
-  });
+  static PerDeviceOnce once;
+  const cudaError_t attr_err = once.get([&](PerDeviceOnce::Entry& x) {
+    x.err = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotalBytes);
+  }).err;
   if (attr_err != cudaSuccess)
     return fail(VXK_ERR_CUDA, "cudaFuncSetAttribute(smem=%d): %s", L::kTotalBytes, cudaGetErrorString(attr_err));
   cudaLaunchConfig_t cfg{};

@@ -750,3 +750,35 @@ extern "C" int vxk_dynamic_scaled_fp8_quant(void* out, const void* in, float* sc
     return launch_static<T, VXK_Q_E5M2>(p, v, stream);
   });
 }
+
+// ---- testing aid: the silu evaluation of the fused kernels, element by element --------------
+// out_t[i] = T(silu(in[i])) as a10 / a11 compute it (mode 0 / 1 as vxk_set_silu_fast), out_f32[i] =
+// the fp32 value before the rounding to T (what a12 multiplies by `up`).  mode 2: the approximate
+// form with caller-supplied constants, silu = (x * rcp(1 + ex2(x * c))) * beta -- used once to search
+// for constants whose rounding to bf16 agrees with torch on every input (tests/test_silu_exhaustive_gpu.py).
+namespace vxk {
+template <typename T>
+__global__ void silu_probe_kernel(const T* __restrict__ in, T* out_t, float* out_f32, int64_t n, int mode, float c,
+                                  float beta) {
+  for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < n;
+       i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+    const float x = to_f32<T>(in[i]);
+    float s;
+    if (mode == 0) s = silu_f32<0>(x);
+    else if (mode == 1) s = silu_f32<1>(x);
+    else s = (x * rcp_approx(1.0f + ex2_approx(x * c))) * beta;
+    if (out_t) out_t[i] = from_f32<T>(s);
+    if (out_f32) out_f32[i] = s;
+  }
+}
+}  // namespace vxk
+
+extern "C" int vxk_debug_silu(void* out_t, float* out_f32, const void* in, int64_t n, int in_dtype, int mode,
+                              float c, float beta, vxk_stream_t stream) {
+  VXK_REQUIRE(n >= 0 && mode >= 0 && mode <= 2, "bad arguments");
+  if (n == 0) return VXK_OK;
+  const int grid = flat_grid(n, 256);
+  VXK_DISPATCH_T16(in_dtype,
+    silu_probe_kernel<T><<<grid, 256, 0, stream>>>(static_cast<const T*>(in), static_cast<T*>(out_t), out_f32, n, mode, c, beta);
+    return check_launch("silu_probe"));
+}

@@ -22,6 +22,8 @@ struct RowParams {
   int gv_log2;          // log2(vectors per group) = log2(group / 8)
   int ue8m0;
   float eps;
+  int exact_var;        // rms: variance from an fp64 sum of squares (correctly rounded mean), see row_variance()
+  double inv_H;         // 1.0 / H
 };
 
 // Raw (still packed) copy of 8 input elements: 4 registers for bf16/f16, 8 for f32.
@@ -140,6 +142,42 @@ __device__ __forceinline__ float block_reduce1(float v, float (*scratch)[32], in
   return r;
 }
 
+// One-barrier CTA-wide fp64 sum (same two-slot protocol as block_reduce1).  The terms are squares of
+// 8- / 11- / 24-bit significands, so an fp64 sum of <= 64k of them is exact to far below an fp32 ulp and the
+// combination order does not matter.
+__device__ __forceinline__ double block_sum1_f64(double v, double (*scratch)[32], int slot) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = (blockDim.x + 31) >> 5;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  if (nwarp == 1) return v;
+  if (lane == 0) scratch[slot][warp] = v;
+  __syncthreads();
+  const double2* s2 = reinterpret_cast<const double2*>(scratch[slot]);   // entries past nwarp hold 0
+  double2 a = s2[0], b = s2[1];
+  double r = (a.x + a.y) + (b.x + b.y);
+  if (nwarp > 4) {
+    a = s2[2]; b = s2[3];
+    r += (a.x + a.y) + (b.x + b.y);
+    if (nwarp > 8) {
+#pragma unroll
+      for (int k = 4; k < 8; ++k) { a = s2[k]; r += a.x + a.y; }
+    }
+  }
+  return r;
+}
+
+// mean of squares, rounded once to fp32: float(sum / H) with the fp64 quotient taken as sum * (1/H)
+// unless that product sits within 2 fp64 ulp of an fp32 rounding boundary (then the true quotient
+// decides).  This is the value torch gives for x.double().pow(2).mean().float() -- the reference's
+// formula (tests/test_fused_norm_quant.py:41-47) with the reduction carried out exactly instead of in
+// whatever order the host's fp32 cascade sum happens to use.
+__device__ __forceinline__ float mean_sq_f32(double sum, double inv_H, double H) {
+  const double q = sum * inv_H;
+  const uint32_t low = static_cast<uint32_t>(__double_as_longlong(q)) & 0x1fffffffu;
+  if (__builtin_expect(low - 0x0ffffffeu <= 4u, 0)) return static_cast<float>(sum / H);
+  return static_cast<float>(q);
+}
+
 // Persistent CTAs (grid = min(T, resident CTAs)), each loops over rows.  A thread owns
 // VPT vectors of a row (tid + i * blockDim); the row lives in registers as fp32, so every
 // element is converted, normalised and scaled exactly once, and the NEXT row's 128-bit loads are
@@ -161,13 +199,17 @@ __device__ __forceinline__ float block_reduce1(float v, float (*scratch)[32], in
 template <typename T, int Q, int MODE, bool RMS, bool HAS_RES, int VPT, bool FULL, int VG = 1>
 __global__ void __launch_bounds__(512) row_quant_kernel(const RowParams p, const int64_t T_rows) {
   __shared__ __align__(16) float scratch[2][32];
+  __shared__ __align__(16) double scratch64[2][32];
   extern __shared__ float4 wsm[];     // RMS: [2][VPT][threads] float4 (elements 0-3 / 4-7 of every vector)
   const int tid = threadIdx.x, nthr = blockDim.x;
   constexpr float kQMax = QTraits<Q>::kMax;
   const bool sat = p.scale_in != nullptr;
   const int nvec = p.nvec;
   int slot = 0;
-  if (tid < 64) scratch[tid >> 5][tid & 31] = 0.0f;
+  if (tid < 64) {
+    scratch[tid >> 5][tid & 31] = 0.0f;
+    if constexpr (RMS) scratch64[tid >> 5][tid & 31] = 0.0;
+  }
   if (!RMS) __syncthreads();
 
   constexpr bool kGrouped = MODE == MODE_GROUP || MODE == MODE_MXFP4;
@@ -249,14 +291,28 @@ __global__ void __launch_bounds__(512) row_quant_kernel(const RowParams p, const
     }
 
     if constexpr (RMS) {
-      float s0 = 0.0f, s1 = 0.0f;
+      float var;
+      if (p.exact_var) {
+        // fp64 sum of the (exact) squares: two accumulators, 1 conversion + 1 DFMA per element
+        double d0 = 0.0, d1 = 0.0;
 #pragma unroll
-      for (int i = 0; i < VPT; ++i)
+        for (int i = 0; i < VPT; ++i)
 #pragma unroll
-        for (int j = 0; j < 8; j += 2) fma2(s0, s1, v[i][j], v[i][j + 1], v[i][j], v[i][j + 1]);
-      const float ss = block_reduce1<false>(s0 + s1, scratch, slot);
+          for (int j = 0; j < 8; j += 2) {
+            const double a = static_cast<double>(v[i][j]), b = static_cast<double>(v[i][j + 1]);
+            d0 = fma(a, a, d0);
+            d1 = fma(b, b, d1);
+          }
+        var = mean_sq_f32(block_sum1_f64(d0 + d1, scratch64, slot), p.inv_H, static_cast<double>(p.H));
+      } else {
+        float s0 = 0.0f, s1 = 0.0f;
+#pragma unroll
+        for (int i = 0; i < VPT; ++i)
+#pragma unroll
+          for (int j = 0; j < 8; j += 2) fma2(s0, s1, v[i][j], v[i][j + 1], v[i][j], v[i][j + 1]);
+        var = __fdiv_rn(block_reduce1<false>(s0 + s1, scratch, slot), static_cast<float>(p.H));
+      }
       slot ^= 1;
-      const float var = __fdiv_rn(ss, static_cast<float>(p.H));
       const float inv_rms = __fdiv_rn(1.0f, __fsqrt_rn(var + p.eps));
 #pragma unroll
       for (int i = 0; i < VPT; ++i) {
@@ -405,16 +461,20 @@ __global__ void __launch_bounds__(256) row_quant_generic(const RowParams p) {
   float inv_rms = 1.0f;
   if constexpr (RMS) {
     float ss = 0.0f;
+    double dd = 0.0;
     for (int h = tid; h < H; h += nthr) {
       float x = to_f32<T>(xin[h]);
       if (res) {
         x = round_to<T>(x + to_f32<T>(res[h]));
         res[h] = from_f32<T>(x);
       }
-      ss = fmaf(x, x, ss);
+      if (p.exact_var) dd = fma(static_cast<double>(x), static_cast<double>(x), dd);
+      else ss = fmaf(x, x, ss);
     }
-    ss = block_reduce<false>(ss, scratch);
-    inv_rms = __fdiv_rn(1.0f, __fsqrt_rn(__fdiv_rn(ss, static_cast<float>(H)) + p.eps));
+    float var;
+    if (p.exact_var) var = mean_sq_f32(block_sum_f64(dd, scratch64), p.inv_H, static_cast<double>(H));
+    else var = __fdiv_rn(block_reduce<false>(ss, scratch), static_cast<float>(H));
+    inv_rms = __fdiv_rn(1.0f, __fsqrt_rn(var + p.eps));
   }
   // value to quantise at column h (after the prologue)
   auto value = [&](int h) -> float {
@@ -504,14 +564,17 @@ inline int launch_row_vpt3(const RowParams& p, int64_t T_rows, int threads, cuda
   auto kernel = row_quant_kernel<T, Q, MODE, RMS, HAS_RES, VPT, FULL, VG>;
   const size_t smem = RMS ? static_cast<size_t>(VPT) * threads * 32 : 0;
   if (smem > 48 * 1024) {
-    static thread_local size_t configured = 0;     // per instantiation
-    if (smem > configured) {
-      if (cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)) != cudaSuccess) {
-        cudaGetLastError();
-        return 1;                                   // row too long for the staged weight: caller falls back
-      }
-      configured = smem;
-    }
+    // per instantiation and per device: raise the limit once to the most this kernel can ever ask for
+    static PerDeviceOnce once;
+    const PerDeviceOnce::Entry c = once.get([&](PerDeviceOnce::Entry& x) {
+      int dev = 0, optin = 0;
+      cudaGetDevice(&dev);
+      cudaDeviceGetAttribute(&optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
+      x.smem = static_cast<size_t>(optin > 2048 ? optin - 2048 : 0);   // static scratch lives in the same budget
+      x.err = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(x.smem));
+      if (x.err != cudaSuccess) cudaGetLastError();
+    });
+    if (c.err != cudaSuccess || smem > c.smem) return 1;   // row too long for the staged weight: caller falls back
   }
   static thread_local int c_threads = 0, c_per_sm = 0;   // per instantiation; smem follows from nvec = f(threads) mostly
   static thread_local size_t c_smem = 0;
@@ -552,6 +615,9 @@ inline int launch_row_vpt(const RowParams& p, int64_t T_rows, int threads, int v
 template <typename T, int Q, int MODE, bool RMS>
 int launch_row(const RowParams& p_in, int64_t T_rows, bool vec_ok, cudaStream_t st) {
   RowParams p = p_in;
+  static const int env_exact = [] { const char* e = getenv("VXK_RMS_EXACT_VAR"); return e ? atoi(e) : 1; }();
+  p.exact_var = env_exact;
+  p.inv_H = p.H > 0 ? 1.0 / static_cast<double>(p.H) : 0.0;
   p.gv_log2 = 0;
   while (p.group > 0 && (kVec << p.gv_log2) < p.group) ++p.gv_log2;
   if (T_rows == 0 || p.H == 0) return VXK_OK;

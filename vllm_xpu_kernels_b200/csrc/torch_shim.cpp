@@ -52,6 +52,23 @@ inline void check_cuda(const Tensor& t, const char* name) {
   TORCH_CHECK(t.is_cuda(), name, " must be a CUDA tensor");
 }
 
+// every tensor argument of an op must live on the device of its first input: a host or
+// foreign-device pointer would otherwise reach the kernel and fault the context
+inline void same_device(const Tensor&) {}
+template <typename... Rest>
+inline void same_device(const Tensor& ref, const std::optional<Tensor>& t, const Rest&... rest);
+template <typename... Rest>
+inline void same_device(const Tensor& ref, const Tensor& t, const Rest&... rest) {
+  TORCH_CHECK(!t.defined() || (t.is_cuda() && t.device() == ref.device()),
+              "all tensor arguments must be on the same CUDA device (got ", t.device(), " and ", ref.device(), ")");
+  same_device(ref, rest...);
+}
+template <typename... Rest>
+inline void same_device(const Tensor& ref, const std::optional<Tensor>& t, const Rest&... rest) {
+  if (t.has_value()) same_device(ref, *t);
+  same_device(ref, rest...);
+}
+
 inline const float* opt_f32(const std::optional<Tensor>& t, const char* name) {
   if (!t.has_value() || !t->defined()) return nullptr;
   TORCH_CHECK(t->scalar_type() == at::kFloat, name, " must be float32");
@@ -68,6 +85,7 @@ void dynamic_per_token_scaled_fp8_quant(Tensor& out, const Tensor& input, Tensor
   TORCH_CHECK(out.is_contiguous());
   TORCH_CHECK(scales.scalar_type() == at::kFloat, "scales must be float32");
   check_cuda(input, "input");
+  same_device(input, out, scales, scale_ub);
   const int64_t H = input.size(-1);
   const int64_t T = H ? input.numel() / H : 0;
   TORCH_CHECK(scales.numel() >= T && scales.is_contiguous(), "scales must hold one fp32 per token");
@@ -86,6 +104,7 @@ void static_scaled_fp8_quant(Tensor& out, const Tensor& input, const Tensor& sca
   TORCH_CHECK(out.stride(-1) == 1, "last dimension of output must be contiguous");
   TORCH_CHECK(scale.scalar_type() == at::kFloat, "scale must be float32");
   check_cuda(input, "input");
+  same_device(input, out, scale);
   const int64_t hidden_size = input.size(-1);
   const int64_t num_tokens = hidden_size ? input.numel() / hidden_size : 0;
   int64_t group_m, group_n, ss_i, ss_j;
@@ -146,6 +165,7 @@ void dynamic_scaled_fp8_quant(Tensor& out, const Tensor& input, Tensor& scale) {
   TORCH_CHECK(input.stride(-1) == 1, "last dimension of input must be contiguous");
   TORCH_CHECK(out.stride(-1) == 1, "last dimension of output must be contiguous");
   check_cuda(input, "input");
+  same_device(input, out, scale);
   const int64_t H = input.size(-1);
   const int64_t T = H ? input.numel() / H : 0;
   const int64_t in_rs = input.dim() >= 2 ? input.stride(-2) : H;
@@ -169,6 +189,7 @@ void per_token_group_fp8_quant(const Tensor& input, Tensor& output_q, Tensor& ou
   TORCH_CHECK(output_s.dim() == 2);
   TORCH_CHECK(output_s.scalar_type() == at::kFloat, "output_s must be float32");
   check_cuda(input, "input");
+  same_device(input, output_q, output_s);
   const int64_t T = output_s.size(0);
   if (T == 0 || input.numel() == 0) return;
   const int64_t H = input.numel() / T;
@@ -199,6 +220,7 @@ void per_token_group_quant_mxfp4(const Tensor& input, Tensor& output_q, Tensor& 
     return;
   }
   check_cuda(input, "input");
+  same_device(input, output_q, output_s);
   const int64_t T = output_s.size(0);
   const int64_t H = input.numel() / T;
   TORCH_CHECK(H % group_size == 0 && output_s.size(1) == H / group_size,
@@ -232,6 +254,7 @@ void rms_norm_dynamic_per_token_quant(Tensor& out, const Tensor& input, const Te
     TORCH_CHECK(out.dtype() == at::kFloat8_e4m3fn, "scale_ub is only supported for FP8 output");
   check_residual(residual, input);
   check_cuda(input, "input");
+  same_device(input, out, weight, scales, scale_ub, residual);
   const int64_t H = input.size(-1);
   const int64_t T = H ? input.numel() / H : 0;
   TORCH_CHECK(weight.numel() == H && weight.is_contiguous(), "weight must be a contiguous [hidden] tensor");
@@ -261,6 +284,7 @@ void rms_norm_per_block_quant(Tensor& out, const Tensor& input, const Tensor& we
     TORCH_CHECK(out.dtype() == at::kFloat8_e4m3fn,
                 "scale_ue8m0 (MX FP8) is only supported for float8_e4m3fn output");
   check_cuda(input, "input");
+  same_device(input, out, weight, scales, residual);
   const int64_t H = input.size(-1);
   const int64_t T = H ? input.numel() / H : 0;
   const int64_t G = H / group_size;
@@ -295,6 +319,7 @@ void rms_norm_mxfp4_quant(Tensor& out, const Tensor& input, const Tensor& weight
   TORCH_CHECK(scales.dim() == 2, "scales must be 2-D");
   check_residual(residual, input);
   check_cuda(input, "input");
+  same_device(input, out, weight, scales, residual);
   const int64_t H = input.size(-1);
   const int64_t T = H ? input.numel() / H : 0;
   TORCH_CHECK(scales.size(0) == T && scales.size(1) == H / group_size, "scales must be [num_tokens, hidden/32]");
@@ -314,6 +339,7 @@ void rms_norm_static_impl(Tensor& out, const Tensor& input, Tensor* residual, co
   TORCH_CHECK(input.stride(-1) == 1, "input must be contiguous in the last dimension");
   TORCH_CHECK(scale.scalar_type() == at::kFloat && scale.numel() == 1, "scale must be one float32");
   check_cuda(input, "input");
+  same_device(input, out, weight, scale); if (residual) same_device(input, *residual);
   const int64_t H = input.size(-1);
   const int64_t T = H ? input.numel() / H : 0;
   TORCH_CHECK(input.dim() <= 2 || input.is_contiguous(), "only 2-D inputs may be row-strided");
@@ -353,6 +379,7 @@ void silu_and_mul_quant(Tensor& out, const Tensor& input, const Tensor& scale) {
   const int64_t T = input.size(-1) ? input.numel() / input.size(-1) : 0;
   if (T == 0) return;
   check_cuda(input, "input");
+  same_device(input, out, scale);
   const c10::cuda::CUDAGuard guard(input.device());
   check_rc(vxk_silu_and_mul_quant(out.data_ptr(), input.data_ptr(), scale.data_ptr<float>(), T, d,
                                   in_dtype_of(input, "silu_and_mul_quant"),
@@ -390,6 +417,7 @@ void silu_and_mul_per_block_quant(Tensor& out, const Tensor& input, Tensor& scal
   TORCH_CHECK(scales.size(0) == T && scales.size(1) == G, "scales must have logical shape [num_tokens, num_groups]");
   if (T == 0) return;
   check_cuda(input, "input");
+  same_device(input, out, scales, scale_ub);
   const int64_t ss0 = is_scale_transposed ? 1 : G;
   const int64_t ss1 = is_scale_transposed ? T : 1;
   const c10::cuda::CUDAGuard guard(input.device());
@@ -421,6 +449,7 @@ void silu_and_mul_mxfp4_quant(Tensor& out, const Tensor& input, Tensor& scales, 
   TORCH_CHECK(scales.size(0) == T && scales.size(1) == G, "scales must have logical shape [num_tokens, num_groups]");
   if (T == 0) return;
   check_cuda(input, "input");
+  same_device(input, out, scales);
   const c10::cuda::CUDAGuard guard(input.device());
   check_rc(vxk_silu_and_mul_mxfp4_quant(out.data_ptr(), input.data_ptr(), scales.data_ptr<float>(), T, H,
                                         group_size, eps, scales.stride(0), scales.stride(1),
@@ -491,8 +520,8 @@ Tensor fp8_gemm(const Tensor& A, const Tensor& B, std::optional<c10::ScalarType>
                        ? *A_scale_ : at::ones({1}, A.options().dtype(at::kFloat));
   Tensor B_scale = B_scale_.has_value() && B_scale_->defined() && B_scale_->numel() > 0
                        ? *B_scale_ : at::ones({1}, A.options().dtype(at::kFloat));
-  check_cuda(A_scale, "A_scale");
-  check_cuda(B_scale, "B_scale");
+  check_cuda(A, "A");
+  same_device(A, B, A_scale, B_scale, bias_);
 
   const bool is_block = A_scale.dim() == 2 && A_scale.size(1) > 1;  // fp8_gemm_w8a8.h:28
   int a_mode, b_mode, scale_dtype = VXK_S_F32;
@@ -557,6 +586,8 @@ Tensor fp4_gemm(const Tensor& A, const Tensor& B, const Tensor& A_scale, const T
   TORCH_CHECK(B_scale.scalar_type() == at::kFloat8_e8m0fnu, "Mismatched scale data types in mxfp4 matmul: ",
               A_scale.scalar_type(), " vs ", B_scale.scalar_type());
   TORCH_CHECK(B.stride(0) == 1, "FP4 weights must be K-major: pass W[N, K/2].transpose(0, 1)");
+  check_cuda(A, "A");
+  same_device(A, B, A_scale, B_scale, bias_);
   const ARows r = flatten_rows(A, result);
   const int64_t K = 2 * A.size(-1), N = B.size(1);
   TORCH_CHECK(B.size(0) * 2 == K, "A and B have mismatched K");
@@ -596,7 +627,8 @@ Tensor fp8_gemm_w8a16(const Tensor& A, const Tensor& B, const std::optional<Tens
   const auto b_st = B.scalar_type();
   TORCH_CHECK(b_st == at::kFloat8_e5m2 || b_st == at::kFloat8_e4m3fn,
               "weight must be f8_e5m2 or f8_e4m3fn for fp8 matmul");
-  check_cuda(B, "B");
+  check_cuda(A, "A");
+  same_device(A, B, B_scale_, bias_);
   const ARows r = flatten_rows(A, result);
   const int64_t K = A.size(-1), N = B.size(1);
   TORCH_CHECK(B.size(0) == K, "A and B have mismatched K: ", K, " vs ", B.size(0));

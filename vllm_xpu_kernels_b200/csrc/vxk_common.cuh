@@ -14,6 +14,7 @@
 #include <atomic>
 #include <cstdarg>
 #include <cstdio>
+#include <mutex>
 
 #include "../../include/vxk_b200.h"
 
@@ -45,6 +46,24 @@ inline int check_launch(const char* what) {
 }
 
 int sm_count();  // cached cudaDevAttrMultiProcessorCount of the current device
+
+// One-time per-DEVICE configuration of a kernel (cudaFuncSetAttribute is per device: a process that
+// calls an op on cuda:0 and then on cuda:1 must configure both).  One static instance per kernel
+// instantiation; `init(entry)` runs once for each device ordinal that reaches it.
+struct PerDeviceOnce {
+  struct Entry { bool done = false; cudaError_t err = cudaSuccess; int aux = 0; size_t smem = 0; };
+  std::mutex mu;
+  Entry e[64];
+  template <typename F>
+  Entry get(F&& init) {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) dev = 0;
+    std::lock_guard<std::mutex> g(mu);
+    Entry& x = e[dev & 63];
+    if (!x.done) { init(x); x.done = true; }
+    return x;
+  }
+};
 
 inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
 
