@@ -2,21 +2,29 @@
 """Benchmark of the quantized-linear hot path (BASELINE.json metric:
 "FP8/MXFP4 GEMM TFLOPS (Llama-3 shapes) + quant-kernel HBM GB/s vs peak").
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--no-gemm]
     torchrun --nproc-per-node N bench.py --gpus N ...        (N > 1)
 
-One JSON line on stdout (rank 0).  A "step" is one pass of the hot path over one
-batch of synthetic Llama-3-8B activations (BASELINE.json configs[1]):
-    rms_norm_dynamic_per_token_quant   T x 4096  bf16 -> e4m3 + [T] scales
+One JSON line on stdout (rank 0).  A "step" is one pass of the hot path over one batch of synthetic
+Llama-3-8B activations (BASELINE.json configs[1]):
+    rms_norm_dynamic_per_token_quant   T x 4096    bf16 -> e4m3 + [T] scales
     silu_and_mul_per_block_quant       T x 2*14336 bf16 -> e4m3 + [T,112] scales (G = 128)
-with T = 8192 tokens per GPU (weak scaling: every rank quantises its own T rows,
-no collective -- token rows are independent).  `value` is the algorithmic GB/s of
-that step (BASELINE.md section 3 bytes / CUDA-event time, inputs resident in HBM;
-per-step working set 692 MB > 126 MB L2, so every step streams from HBM).
-`e2e` is the same step through torch.ops with pinned HOST buffers (H2D of the
-activations and D2H of codes + scales inside the timed region).
-`gemm` reports the FP8 / MXFP4 scaled GEMMs on Llama-3-70B shapes (N-sharded over
-the ranks when N > 1) as TFLOP/s, each with its own tensor roofline.
+with T = 8192 tokens per GPU (weak scaling: every rank quantises its own T rows, no collective -- token rows
+are independent).
+
+  value        algorithmic GB/s of that step (BASELINE.md section 3 bytes / CUDA-event time, inputs resident in
+               HBM; per-step working set 692 MB > 126 MB L2, so every step streams from HBM)
+  roofline     the dominant kernel of the step (silu_and_mul + 1x128 FP8) against the measured HBM copy peak,
+               `also`: the other kernel of the step and BASELINE config 1 (4096 x 4096 per-token FP8),
+               `gemm`: the GEMM half of the metric -- FP8 / MXFP4 / fp8_w8a16 at the Llama-3-70B shapes,
+               DeepSeek-V3 block-scaled FP8 (config 5) and a Llama-3-8B W8A8 M sweep (config 3), each row with
+               its own tensor / HBM roofline fraction (bench_gemm.py)
+  cpu_baseline the reference's torch CPU path (oracle/) on a bounded sample, host cores stated; `gemm`: the
+               GEMM test formula (dequantise -> fp32 matmul) at M = 512
+  e2e          the same step through torch.ops with pinned HOST buffers, double-buffered over three streams
+               (H2D of step i+1 | kernels | D2H of step i-1); `gemm`: fp8_gemm with host activations / result
+`--impl reference` times the oracle (the reference's own CPU implementation of the step: its torch reference
+functions, restated -- the SYCL kernels cannot be built here) on `config.reference_sample_rows` rows per step.
 """
 from __future__ import annotations
 
@@ -36,10 +44,25 @@ HIDDEN = 4096
 INTER = 14336
 GROUP = 128
 EPS = 1e-6
+REF_SAMPLE_ROWS = 512
+METRIC = "quant-kernel HBM GB/s (Llama-3-8B fused rms_norm+FP8 / silu_mul+block-FP8 step); GEMM TFLOPS in roofline.gemm"
 
 # algorithmic bytes per output element (bf16 in)
 BYTES_RMS = lambda T: T * HIDDEN * 3 + T * 4                          # noqa: E731
 BYTES_SILU = lambda T: T * INTER * 5 + T * (INTER // GROUP) * 4       # noqa: E731
+BYTES_A1 = lambda T, H: T * H * 3 + T * 4                             # noqa: E731
+
+
+def workload_config(world: int) -> dict:
+    """The `config` object -- identical in both arms."""
+    return {"workload": "llama3-8b fused quant step: rms_norm_dynamic_per_token_quant(Tx4096) + "
+                        "silu_and_mul_per_block_quant(Tx2x14336, G=128)",
+            "tokens_per_gpu": T_TOKENS, "hidden": HIDDEN, "intermediate": INTER, "group": GROUP,
+            "l2": "per-step working set 692 MB > 126 MB L2 (inputs larger than L2)",
+            "parallelism": f"token rows sharded over {world} GPU(s), no collective",
+            "reference_sample_rows": REF_SAMPLE_ROWS,
+            "clock_warmup": "after the W warm-up steps the device is kept busy for ~150 ms of untimed steps "
+                            "so the timed region does not start on idle clocks"}
 
 
 def peaks():
@@ -48,7 +71,7 @@ def peaks():
         d = json.load(open(p))
         return dict(hbm=d["hbm_gbs"], bf16=d["bf16_tflops"], bf16_sustained=d.get("bf16_tflops_sustained"),
                     src="measured")
-    return dict(hbm=6650.0, bf16=1590.0, bf16_sustained=1400.0, src="fallback")
+    return dict(hbm=6650.0, bf16=1590.0, bf16_sustained=1400.0, src="fallback (B200_PROFILING.md)")
 
 
 class ClockSampler(threading.Thread):
@@ -88,8 +111,8 @@ class ClockSampler(threading.Thread):
 # --------------------------------------------------------------------------- reference arm
 def cpu_reference_step(T: int, threads: int):
     """The reference's torch CPU implementation of the same step (oracle/, a restatement of
-    /root/reference/tests/test_fused_norm_quant.py:37-80 and
-    tests/test_fused_silu_mul_block_quant.py:49-79) on T rows.  Returns (seconds, bytes)."""
+    /root/reference/tests/test_fused_norm_quant.py:37-80 and tests/test_fused_silu_mul_block_quant.py:49-79)
+    on T rows.  Returns (closure, algorithmic bytes)."""
     import torch
     from oracle import quant as oq
     torch.set_num_threads(threads)
@@ -106,31 +129,49 @@ def cpu_reference_step(T: int, threads: int):
     return step, BYTES_RMS(T) + BYTES_SILU(T)
 
 
+def cpu_quant_baseline(threads: int, rows: int, reps: int):
+    step, nbytes = cpu_reference_step(rows, threads)
+    step()
+    t0 = time.perf_counter()
+    for _ in range(reps):
+        step()
+    dt = (time.perf_counter() - t0) / reps
+    return {"value": nbytes / dt / 1e9, "unit": "GB/s", "cores": threads, "kind": "port",
+            "sample": f"{rows} of {T_TOKENS} token rows of the same step (oracle/: the reference's torch CPU ops), "
+                      f"{reps} timed passes"}
+
+
 def run_reference(args):
     import torch
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     threads = os.cpu_count() or 1
-    T = 512   # bounded sample of the 8192-row workload
+    T = REF_SAMPLE_ROWS   # bounded sample of the 8192-row workload, every step
     step, nbytes = cpu_reference_step(T, threads)
-    for _ in range(max(1, min(args.warmup, 2))):
+    for _ in range(max(1, args.warmup)):
         step()
-    steps = max(1, min(args.steps, 10))
+    steps = max(1, args.steps)
     t0 = time.perf_counter()
     for _ in range(steps):
         step()
     dt = (time.perf_counter() - t0) / steps
     gbs = nbytes / dt / 1e9
-    sample = f"{T} of {T_TOKENS} token rows of the same step, torch {torch.__version__} CPU ops"
+    sample = (f"{T} of {T_TOKENS} token rows of the same step per timed step, torch {torch.__version__} CPU ops "
+              f"on {threads} threads")
+    cpu = {"value": gbs, "unit": "GB/s", "cores": threads, "kind": "port", "sample": sample}
+    if not args.no_gemm:
+        try:
+            from bench_gemm import cpu_gemm_baseline
+            cpu["gemm"] = cpu_gemm_baseline(threads)
+        except Exception as exc:
+            cpu["gemm"] = {"error": f"{type(exc).__name__}: {exc}"[:200]}
     line = {
-        "impl": "reference", "metric": "quant-kernel HBM GB/s (Llama-3-8B fused rms_norm+FP8 / silu_mul+block-FP8 step)",
-        "value": gbs, "unit": "GB/s", "n_gpus": args.gpus, "steps": steps, "warmup": args.warmup,
-        "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": "bf16->e4m3", "data": "synthetic",
-        "config": {"workload": "llama3-8b fused quant step: rms_norm_dynamic_per_token_quant(Tx4096) + "
-                               "silu_and_mul_per_block_quant(Tx2x14336, G=128)", "tokens_per_gpu": T_TOKENS},
-        "cpu_baseline": {"value": gbs, "unit": "GB/s", "cores": threads, "kind": "port", "sample": sample},
+        "impl": "reference", "metric": METRIC, "value": gbs, "unit": "GB/s", "n_gpus": args.gpus, "steps": steps,
+        "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "bf16->e4m3", "data": "synthetic",
+        "config": workload_config(args.gpus),
+        "cpu_baseline": cpu,
         "e2e": {"value": gbs, "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
     print(json.dumps(line), flush=True)
@@ -150,7 +191,7 @@ def run_ours(args):
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=dev)
 
-    from vllm_xpu_kernels_b200 import _loader, ops  # raises if the CUDA extension is missing
+    from vllm_xpu_kernels_b200 import _loader, ops  # noqa: F401  raises if the CUDA extension is missing
     E4 = torch.float8_e4m3fn
     pk = peaks()
     T = T_TOKENS
@@ -173,25 +214,28 @@ def run_ours(args):
             dist.barrier()
         torch.cuda.synchronize()
 
-    # W untimed warm-up steps (at least 3), extended until the device has been busy for ~150 ms so
-    # that the timed region does not start on idle clocks (10 steps of this workload are only 2 ms)
+    def max_over_ranks(v: float) -> float:
+        t = torch.tensor([v], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    # W untimed warm-up steps, then ~150 ms of further untimed steps (see config.clock_warmup)
     for _ in range(max(args.warmup, 3)):
         step()
     torch.cuda.synchronize()
     t_w = time.perf_counter()
-    extra_warm = 0
     while time.perf_counter() - t_w < 0.15:
         for _ in range(20):
             step()
         torch.cuda.synchronize()
-        extra_warm += 20
     barrier()
 
     sampler = ClockSampler(local_rank) if rank == 0 else None
     if sampler:
         sampler.start()
 
-    # ---- timed region: K steps, CUDA events on the launching (current) stream ----
+    # ---- timed region: exactly K steps, CUDA events on the launching (current) stream ----
     K = args.steps
     ev = [[torch.cuda.Event(enable_timing=True) for _ in range(3)] for _ in range(K)]
     n_launch0 = _loader.launch_count()
@@ -208,64 +252,109 @@ def run_ours(args):
     t_end.record()
     barrier()
     launches = _loader.launch_count() - n_launch0
-    total_ms = t_start.elapsed_time(t_end)
     rms_ms = sum(e[0].elapsed_time(e[1]) for e in ev) / K
     silu_ms = sum(e[1].elapsed_time(e[2]) for e in ev) / K
-
-    tmax = torch.tensor([total_ms], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
-    total_ms_max = float(tmax.item())
-    ms_per_step = total_ms_max / K
+    ms_per_step = max_over_ranks(t_start.elapsed_time(t_end)) / K
     step_bytes = BYTES_RMS(T) + BYTES_SILU(T)
     value = world * step_bytes / (ms_per_step * 1e-3) / 1e9
 
-    # ---- e2e: host buffers, H2D + ops + D2H inside the timed region ----
-    hx = torch.empty(T, HIDDEN, dtype=torch.bfloat16).pin_memory()
-    hgu = torch.empty(T, 2 * INTER, dtype=torch.bfloat16).pin_memory()
-    hx.copy_(x.cpu())
-    hgu.copy_(gu.cpu())
-    hq1 = torch.empty(T, HIDDEN, dtype=torch.uint8).pin_memory()
-    hs1 = torch.empty(T, dtype=torch.float32).pin_memory()
-    hq2 = torch.empty(T, INTER, dtype=torch.uint8).pin_memory()
-    hs2 = torch.empty(T, INTER // GROUP, dtype=torch.float32).pin_memory()
-    dx = torch.empty_like(x)
-    dgu = torch.empty_like(gu)
+    # ---- BASELINE config 1: dynamic per-token FP8 quant of a 4096 x 4096 bf16 activation ----
+    # (50 MB per launch: rotate over 8 buffer sets so that every launch streams from HBM)
+    a1_sets = []
+    for _ in range(8):
+        xa = torch.rand(4096, 4096, dtype=torch.bfloat16, device=dev) + 1e-6
+        a1_sets.append((xa, torch.empty(4096, 4096, dtype=E4, device=dev), torch.empty(4096, 1, device=dev)))
+    for (xa, qa, sa) in a1_sets:
+        torch.ops._C.dynamic_per_token_scaled_fp8_quant(qa, xa, sa, None)
+    torch.cuda.synchronize()
+    c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    n_a1 = 104
+    c0.record()
+    for i in range(n_a1):
+        xa, qa, sa = a1_sets[i % 8]
+        torch.ops._C.dynamic_per_token_scaled_fp8_quant(qa, xa, sa, None)
+    c1.record()
+    torch.cuda.synchronize()
+    a1_ms = c0.elapsed_time(c1) / n_a1
+    del a1_sets
 
-    def e2e_step():
-        dx.copy_(hx, non_blocking=True)
-        dgu.copy_(hgu, non_blocking=True)
-        torch.ops._C.rms_norm_dynamic_per_token_quant(q1, dx, w, s1, EPS, None, None)
-        torch.ops._C.silu_and_mul_per_block_quant(q2, dgu, s2, GROUP, None, False, False)
-        hq1.copy_(q1.view(torch.uint8), non_blocking=True)
-        hs1.copy_(s1, non_blocking=True)
-        hq2.copy_(q2.view(torch.uint8), non_blocking=True)
-        hs2.copy_(s2, non_blocking=True)
+    # ---- e2e: pinned host buffers, H2D | kernels | D2H on three streams, two buffer sets ----
+    NB = 2
+    hx = [torch.empty(T, HIDDEN, dtype=torch.bfloat16).pin_memory() for _ in range(NB)]
+    hgu = [torch.empty(T, 2 * INTER, dtype=torch.bfloat16).pin_memory() for _ in range(NB)]
+    for b in range(NB):
+        hx[b].copy_(x.cpu())
+        hgu[b].copy_(gu.cpu())
+    hq1 = [torch.empty(T, HIDDEN, dtype=torch.uint8).pin_memory() for _ in range(NB)]
+    hs1 = [torch.empty(T, dtype=torch.float32).pin_memory() for _ in range(NB)]
+    hq2 = [torch.empty(T, INTER, dtype=torch.uint8).pin_memory() for _ in range(NB)]
+    hs2 = [torch.empty(T, INTER // GROUP, dtype=torch.float32).pin_memory() for _ in range(NB)]
+    dx = [torch.empty_like(x) for _ in range(NB)]
+    dgu = [torch.empty_like(gu) for _ in range(NB)]
+    dq1 = [torch.empty_like(q1) for _ in range(NB)]
+    ds1 = [torch.empty_like(s1) for _ in range(NB)]
+    dq2 = [torch.empty_like(q2) for _ in range(NB)]
+    ds2 = [torch.empty_like(s2) for _ in range(NB)]
+    st_in, st_k, st_out = torch.cuda.Stream(), torch.cuda.Stream(), torch.cuda.Stream()
+    ev_in = [torch.cuda.Event() for _ in range(NB)]      # inputs of set b are on the device
+    ev_k = [torch.cuda.Event() for _ in range(NB)]       # kernels of set b are done (inputs free, outputs ready)
+    ev_out = [torch.cuda.Event() for _ in range(NB)]     # outputs of set b are on the host (device outputs free)
 
-    e2e_steps = max(1, min(K, 5))
-    e2e_step()
+    def e2e_run(n):
+        for i in range(n):
+            b = i % NB
+            with torch.cuda.stream(st_in):
+                st_in.wait_event(ev_k[b])                 # the kernels that last read this input set
+                dx[b].copy_(hx[b], non_blocking=True)
+                dgu[b].copy_(hgu[b], non_blocking=True)
+                ev_in[b].record(st_in)
+            with torch.cuda.stream(st_k):
+                st_k.wait_event(ev_in[b])
+                st_k.wait_event(ev_out[b])                # the D2H that last read this output set
+                torch.ops._C.rms_norm_dynamic_per_token_quant(dq1[b], dx[b], w, ds1[b], EPS, None, None)
+                torch.ops._C.silu_and_mul_per_block_quant(dq2[b], dgu[b], ds2[b], GROUP, None, False, False)
+                ev_k[b].record(st_k)
+            with torch.cuda.stream(st_out):
+                st_out.wait_event(ev_k[b])
+                hq1[b].copy_(dq1[b].view(torch.uint8), non_blocking=True)
+                hs1[b].copy_(ds1[b], non_blocking=True)
+                hq2[b].copy_(dq2[b].view(torch.uint8), non_blocking=True)
+                hs2[b].copy_(ds2[b], non_blocking=True)
+                ev_out[b].record(st_out)
+
+    cur = torch.cuda.current_stream()
+    e2e_steps = max(2, min(K, 10))
+    e2e_run(NB)
     barrier()
-    e0 = torch.cuda.Event(enable_timing=True)
-    e1 = torch.cuda.Event(enable_timing=True)
-    e0.record()
-    for _ in range(e2e_steps):
-        e2e_step()
-    e1.record()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(cur)
+    for s in (st_in, st_k, st_out):
+        s.wait_event(e0)
+    e2e_run(e2e_steps)
+    for s in (st_in, st_k, st_out):
+        cur.wait_stream(s)
+    e1.record(cur)
     barrier()
-    e2e_ms = torch.tensor([e0.elapsed_time(e1) / e2e_steps], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(e2e_ms, op=dist.ReduceOp.MAX)
-    e2e_val = world * step_bytes / (float(e2e_ms.item()) * 1e-3) / 1e9
-    h2d = hx.numel() * 2 + hgu.numel() * 2
-    d2h = hq1.numel() + hs1.numel() * 4 + hq2.numel() + hs2.numel() * 4
+    e2e_ms = max_over_ranks(e0.elapsed_time(e1) / e2e_steps)
+    e2e_val = world * step_bytes / (e2e_ms * 1e-3) / 1e9
+    same_as_device_path = bool(torch.equal(hq2[0], q2.view(torch.uint8).cpu()) and torch.equal(hs1[0], s1.cpu()))
+    h2d = hx[0].numel() * 2 + hgu[0].numel() * 2
+    d2h = hq1[0].numel() + hs1[0].numel() * 4 + hq2[0].numel() + hs2[0].numel() * 4
+    del hx, hgu, hq1, hq2, dx, dgu, dq1, dq2
 
-    # ---- GEMMs (Llama-3-70B shapes, N-sharded over the ranks) ----
-    gemm = None
-    try:
-        from bench_gemm import bench_gemms
-        gemm = bench_gemms(dev, rank, world, pk, steps=max(3, min(K, 20)))
-    except Exception as exc:  # GEMM section must never hide the quant numbers
-        gemm = {"error": f"{type(exc).__name__}: {exc}"[:300]}
+    # ---- GEMM half of the metric ----
+    gemm = e2e_g = reassembled = None
+    if not args.no_gemm:
+        try:
+            import bench_gemm
+            del x, gu, q1, q2
+            torch.cuda.empty_cache()
+            gemm = bench_gemm.bench_gemms(dev, rank, world, pk, launches=max(100, K), warmup=max(10, args.warmup))
+            e2e_g = bench_gemm.e2e_gemm(dev, rank, world)
+            if world > 1:
+                reassembled = bench_gemm.bench_reassembled(dev, rank, world)
+        except Exception as exc:  # the GEMM section must never hide the quant numbers
+            gemm = {"error": f"{type(exc).__name__}: {exc}"[:300]}
 
     if sampler:
         sampler.stop_flag.set()
@@ -276,53 +365,60 @@ def run_ours(args):
             dist.destroy_process_group()
         return
 
-    # ---- CPU baseline: the reference's torch CPU path on a bounded sample, rank 0 only at N=1 ----
+    # ---- CPU baseline: the reference's torch CPU path on a bounded sample, rank 0 only at N = 1 ----
     cpu_baseline = None
     if world == 1:
         threads = os.cpu_count() or 1
-        Tc = 256
-        cstep, cbytes = cpu_reference_step(Tc, threads)
-        cstep()
-        t0 = time.perf_counter()
-        reps = 3
-        for _ in range(reps):
-            cstep()
-        cdt = (time.perf_counter() - t0) / reps
-        cpu_baseline = {"value": cbytes / cdt / 1e9, "unit": "GB/s", "cores": threads, "kind": "port",
-                        "sample": f"{Tc} of {T} token rows of the same step (oracle/, torch CPU ops), "
-                                  f"{reps} timed passes"}
+        cpu_baseline = cpu_quant_baseline(threads, 256, 3)
+        if not args.no_gemm:
+            try:
+                import bench_gemm
+                cpu_baseline["gemm"] = bench_gemm.cpu_gemm_baseline(threads)
+            except Exception as exc:
+                cpu_baseline["gemm"] = {"error": f"{type(exc).__name__}: {exc}"[:200]}
 
     achieved = BYTES_SILU(T) / (silu_ms * 1e-3) / 1e9
-    traffic = None
+    traffic, traffic_src = None, None
     tp = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(tp):
         try:
-            traffic = json.load(open(tp)).get("silu_and_mul_per_block_quant_T8192")
+            tj = json.load(open(tp))
+            traffic = tj.get("silu_and_mul_per_block_quant_T8192")
+            traffic_src = tj.get("source", "profiles/traffic.json (ncu --set full capture, not measured in this run)")
         except Exception:
             traffic = None
+    rms_gbs = BYTES_RMS(T) / (rms_ms * 1e-3) / 1e9
+    a1_gbs = BYTES_A1(4096, 4096) / (a1_ms * 1e-3) / 1e9
+    roofline = {"bound": "hbm", "kernel": "flat_quant_kernel<bf16,e4m3,silu,div> (silu_and_mul_per_block_quant)",
+                "achieved": achieved, "peak": pk["hbm"], "unit": "GB/s", "frac": achieved / pk["hbm"],
+                "peak_source": pk["src"] + " copy bandwidth", "traffic": traffic, "traffic_source": traffic_src,
+                "ms_per_launch": silu_ms, "algorithmic_bytes_per_launch": BYTES_SILU(T),
+                "also": {"rms_norm_dynamic_per_token_quant": {
+                             "kernel": "row_quant_kernel<bf16,e4m3,token,rms> T=8192 H=4096", "achieved": rms_gbs,
+                             "ms_per_launch": rms_ms, "frac": rms_gbs / pk["hbm"],
+                             "algorithmic_bytes_per_launch": BYTES_RMS(T)},
+                         "config1_dynamic_per_token_fp8_4096x4096": {
+                             "kernel": "row_quant_kernel<bf16,e4m3,token> (tests/test_fp8_quant.py:48-83 shape)",
+                             "achieved": a1_gbs, "ms_per_launch": a1_ms, "frac": a1_gbs / pk["hbm"],
+                             "algorithmic_bytes_per_launch": BYTES_A1(4096, 4096),
+                             "launches": n_a1, "l2": "8 rotating buffer sets (403 MB) > L2"}},
+                "gemm": gemm}
+    if reassembled is not None:
+        roofline["gemm_reassembled"] = reassembled
     line = {
-        "metric": "quant-kernel HBM GB/s (Llama-3-8B fused rms_norm+FP8 / silu_mul+block-FP8 step)",
-        "value": value, "unit": "GB/s", "n_gpus": world, "steps": K, "warmup": max(args.warmup, 3) + extra_warm,
+        "metric": METRIC, "value": value, "unit": "GB/s", "n_gpus": world, "steps": K, "warmup": args.warmup,
         "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "bf16->e4m3", "data": "synthetic",
-        "config": {"workload": "llama3-8b fused quant step: rms_norm_dynamic_per_token_quant(Tx4096) + "
-                               "silu_and_mul_per_block_quant(Tx2x14336, G=128)",
-                   "tokens_per_gpu": T, "hidden": HIDDEN, "intermediate": INTER, "group": GROUP,
-                   "l2": "per-step working set 692 MB > 126 MB L2 (inputs larger than L2)",
-                   "parallelism": f"token rows sharded over {world} GPU(s), no collective"},
-        "roofline": {"bound": "hbm", "kernel": "flat_quant_kernel<bf16,e4m3,silu,div> (silu_and_mul_per_block_quant)",
-                     "achieved": achieved, "peak": pk["hbm"], "unit": "GB/s", "frac": achieved / pk["hbm"],
-                     "peak_source": pk["src"] + " copy bandwidth", "traffic": traffic,
-                     "ms_per_launch": silu_ms, "algorithmic_bytes_per_launch": BYTES_SILU(T),
-                     "also": {"rms_norm_dynamic_per_token_quant": {
-                         "achieved": BYTES_RMS(T) / (rms_ms * 1e-3) / 1e9, "ms_per_launch": rms_ms,
-                         "frac": BYTES_RMS(T) / (rms_ms * 1e-3) / 1e9 / pk["hbm"]}}},
+        "config": workload_config(world),
+        "roofline": roofline,
         "cpu_baseline": cpu_baseline,
         "e2e": {"value": e2e_val, "unit": "GB/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                "ms_per_step": float(e2e_ms.item())},
+                "ms_per_step": e2e_ms, "steps": e2e_steps,
+                "how": "pinned host buffers; H2D, kernels and D2H on three streams over two buffer sets "
+                       "(full-duplex PCIe); results equal the device-resident path: " + str(same_as_device_path),
+                "gemm": e2e_g},
         "gpu_launches": int(launches),
         "clocks": sampler.summary() if sampler else None,
-        "gemm": gemm,
     }
     print(json.dumps(line), flush=True)
     if world > 1:
@@ -335,6 +431,7 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-gemm", action="store_true", help="skip the GEMM half (quick runs)")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

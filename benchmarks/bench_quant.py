@@ -113,6 +113,16 @@ def case(name, T, H):
             x = torch.randn(T, 2 * H, dtype=bf, device=DEV) * SCALE; o = torch.empty(T, H // 2, dtype=torch.uint8, device=DEV)
             s = torch.empty(T, H // 32, device=DEV)
             return lambda: torch.ops._C.silu_and_mul_mxfp4_quant(o, x, s, 32, 1e-10)
+    elif name == "indexer_k_quant_cache":
+        # (f)#3: T tokens x head_dim H (bf16) -> e4m3 codes + one fp32 scale per 128 into the paged cache
+        nb = T * H * 3 + 4 * T * H // 128 + 8 * T
+        def mk():
+            bs = 64
+            nblk = (T + bs - 1) // bs
+            x = torch.randn(T, H, dtype=bf, device=DEV)
+            cache = torch.zeros(nblk, bs, H + 4 * (H // 128), dtype=torch.uint8, device=DEV)
+            slots = torch.randperm(nblk * bs, device=DEV)[:T]
+            return lambda: torch.ops._C_cache_ops.indexer_k_quant_and_cache(x, cache, slots, 128, "ue8m0")
     else:
         raise KeyError(name)
     fns = [mk() for _ in range(nsets(nb))]
@@ -123,7 +133,7 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--quick", action="store_true")
     ap.add_argument("--json", default=None)
-    ap.add_argument("--silu-fast", type=int, default=1)
+    ap.add_argument("--silu-fast", type=int, default=-1, help="-1 auto (default), 0 accurate, 1 approximate")
     ap.add_argument("--only", default=None, help="comma-separated op names")
     ap.add_argument("--T", type=int, default=None)
     ap.add_argument("--scale", type=float, default=1.0, help="multiply the random inputs (activation magnitude)")
@@ -136,16 +146,20 @@ def main():
     row_ops = ["dynamic_per_token_fp8", "static_fp8", "group_fp8_128", "group_mxfp4", "rms_token_fp8",
                "rms_token_fp8_res", "rms_block_fp8_128", "rms_mxfp4", "rms_static_fp8"]
     act_ops = ["silu_static_fp8", "silu_block_fp8_128", "silu_mxfp4"]
+    cache_ops = ["indexer_k_quant_cache"]
     Ts = [8192] if args.quick else [1, 16, 128, 1024, 4096, 8192]
     if args.T:
         Ts = [args.T]
+    cache_Ts = [Ts[-1] * 64]    # tokens of a long-context prefill chunk (head_dim is only 128)
     rows = []
-    for op in row_ops + act_ops:
+    for op in row_ops + act_ops + cache_ops:
         if args.only and op not in args.only.split(","):
             continue
         Hs = ([4096] if args.quick else [4096, 8192]) if op in row_ops else ([14336] if args.quick else [14336, 28672])
+        if op in cache_ops:
+            Hs = [128, 512]
         for H in Hs:
-            for T in Ts:
+            for T in (cache_Ts if op in cache_ops else Ts):
                 fns, nb = case(op, T, H)
                 ms = time_rot(fns, iters=5 if T >= 1024 else 20)
                 gbs = nb / ms / 1e6

@@ -43,8 +43,10 @@ int vxk_abi_version(void);
 const char* vxk_last_error(void);
 /* number of kernels this library has launched in this process (bench "gpu_launches") */
 uint64_t vxk_launch_count(void);
-/* silu evaluation in the fused silu_and_mul_* kernels: 0 (default) = expf + IEEE divide,
- * 1 = ex2.approx / rcp.approx.  Returns the previous setting.  Process-wide. */
+/* silu evaluation in the fused silu_and_mul_* kernels.  -1 (default) = auto: the cheapest form that is
+ * proven bit-identical to the reference on every input (ex2.approx / rcp.approx for bf16 a10 / a11 and
+ * for a12, expf + IEEE divide for f16 a10 / a11); 0 = expf + IEEE divide everywhere; 1 = approximate
+ * everywhere.  Returns the previous setting.  Process-wide. */
 int vxk_set_silu_fast(int on);
 /* Testing aid: out_t[i] = T(silu(in[i])) exactly as the fused silu_and_mul_* kernels evaluate it
  * (mode 0 / 1 as vxk_set_silu_fast; mode 2 = approximate form with caller constants c, beta);
@@ -247,6 +249,41 @@ int vxk_fp8_gemm_w8a16(void* D, const void* A, const void* B, const float* b_sca
                        int64_t b_stride_n, int64_t ldd, int b_scale_mode, int64_t group_k,
                        int64_t group_n, int64_t sb0, int64_t sb1, int act_dtype, int fp8_dtype,
                        int bias_dtype, int force_fallback, vxk_stream_t stream);
+
+/* ------------------------------------------------------- (f) next #3 ---
+ * Block-FP8 quantisation into / out of the paged indexer-K cache, and the FP8 cache conversion.
+ * Cache block layout (bytes): [block_size * head_dim e4m3 codes][block_size * head_dim / G fp32 scales].
+ *
+ * ref: indexer_k_quant_and_cache  csrc/cache.cpp:530-612, launcher :1558-1590,
+ *      schema csrc/torch_bindings.cpp:298-302 (library _C_cache_ops)
+ * k [num_tokens, head_dim] (row stride k_row_stride elements), slot_mapping [num_tokens] int64
+ * (negative = skip the token), kv_cache [num_blocks, cache_block_size, cache_stride] bytes with
+ * cache_block_stride_bytes between blocks.  s = max(amax, 1e-4) / 448 per 1 x quant_block_size group
+ * (use_ue8m0: rounded up to a power of two), q = e4m3(clamp(x / s)). */
+int vxk_indexer_k_quant_and_cache(const void* k, void* kv_cache, const int64_t* slot_mapping,
+                                  int64_t num_tokens, int64_t head_dim, int64_t k_row_stride,
+                                  int64_t quant_block_size, int64_t cache_block_size, int64_t cache_stride,
+                                  int64_t cache_block_stride_bytes, int use_ue8m0, int in_dtype,
+                                  vxk_stream_t stream);
+
+/* ref: cp_gather_indexer_k_quant_cache  csrc/cache.cpp:616-750, launcher :1625-1680,
+ *      schema csrc/torch_bindings.cpp:303-309
+ * Gathers the codes and scales of the tokens of `batch_size` sequences (cu_seq_lens [batch+1] int32,
+ * block_table [batch, max_blocks_per_seq] int32) from the paged cache into dst_k [num_tokens, head_dim]
+ * bytes and dst_scale [num_tokens, 4 * head_dim / quant_block_size] bytes (fp32 scales). */
+int vxk_cp_gather_indexer_k_quant_cache(const void* kv_cache, void* dst_k, void* dst_scale,
+                                        const int32_t* block_table, const int32_t* cu_seq_lens,
+                                        int64_t batch_size, int64_t max_blocks_per_seq, int64_t num_tokens,
+                                        int64_t head_dim, int64_t quant_block_size, int64_t cache_block_size,
+                                        int64_t cache_block_stride_bytes, int64_t dst_k_stride_bytes,
+                                        int64_t dst_scale_stride_bytes, vxk_stream_t stream);
+
+/* ref: convert_fp8  csrc/cache.cpp:1393-1540, schema csrc/torch_bindings.cpp:281-284
+ * n elements.  src_kind / dst_kind: VXK_F32 / VXK_F16 / VXK_BF16 or 3 = byte tensor (exactly one side).
+ * mode 1 ("fp8" / "fp8_e4m3"): bytes are e4m3 codes, quantise e4m3(clamp(x / scale)) or dequantise
+ * float(code) * scale by direction; mode 0 ("auto"): numeric cast of float(src) * scale. */
+int vxk_convert_fp8(void* dst, const void* src, double scale, int64_t n, int src_kind, int dst_kind,
+                    int mode, vxk_stream_t stream);
 
 #ifdef __cplusplus
 }

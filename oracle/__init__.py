@@ -22,4 +22,4 @@ The reference has no CPU *kernel* implementation of these ops (its device code
 is SYCL + oneDNN, neither buildable here), so there is no ``oracle/_ref``.
 """
 
-from . import formats, quant, gemm  # noqa: F401
+from . import formats, quant, gemm, cache  # noqa: F401

@@ -263,6 +263,41 @@ def main():
         cases.append(dict(kind="block", a=a, wq=u8(wq_b), scale=s_b, out=out_b))
     g["f1_fp8_gemm_w8a16"] = cases
 
+    # ---- (f)#3 indexer-K cache ops: the reference tests' own torch refs
+    # (tests/test_indexer_k_quant_and_cache.py:95-131, tests/test_cp_gather_indexer_k_quant_cache.py:34-86)
+    import tests.test_indexer_k_quant_and_cache as t_idx
+    import tests.test_cp_gather_indexer_k_quant_cache as t_gat
+    cases = []
+    for dtype in (torch.float32, torch.bfloat16):
+        for fmt in ("ue8m0", "fp8e4m3"):
+            for (seqs, hd, G, bs) in (([17], 128, 128, 16), ([3, 4], 256, 128, 4), ([7, 8, 5], 512, 128, 16),
+                                      ([5, 4], 24, 24, 4)):
+                torch.manual_seed(0)
+                T = sum(seqs)
+                k = torch.randn(T, hd, dtype=dtype)
+                groups = hd // G
+                cs = hd + groups * 4
+                # block table / slots as the reference test builds them (:117-150)
+                per = [(n + bs - 1) // bs for n in seqs]
+                maxb, nblk = max(per), sum(per)
+                table, slots, nxt = [], [], 0
+                for n, nb in zip(seqs, per):
+                    blocks = list(range(nxt, nxt + nb))
+                    nxt += nb
+                    table.append(blocks + [0] * (maxb - nb))
+                    slots += [blocks[p // bs] * bs + p % bs for p in range(n)]
+                block_table = torch.tensor(table, dtype=torch.int32)
+                slot_mapping = torch.tensor(slots, dtype=torch.int64)
+                cu = torch.tensor([0] + list(torch.tensor(seqs).cumsum(0)), dtype=torch.int32)
+                cache = torch.zeros(nblk, bs, cs, dtype=torch.uint8)
+                t_idx.ref_indexer_k_quant_and_cache(k, cache, slot_mapping, G, fmt)
+                dst_k = torch.zeros(T, hd, dtype=torch.uint8)
+                dst_s = torch.zeros(T, groups * 4, dtype=torch.uint8)
+                t_gat.ref_cp_gather_indexer_k_quant_cache(cache, dst_k, dst_s, block_table, cu)
+                cases.append(dict(k=k, G=G, block_size=bs, fmt=fmt, slot_mapping=slot_mapping, block_table=block_table,
+                                  cu_seq_lens=cu, cache=cache.clone(), dst_k=dst_k, dst_scale=dst_s))
+    g["f3_indexer_k_cache"] = cases
+
     # ---- silu on EVERY 16-bit input, through the reference's own ref function
     # (test_fused_quant_activation.py:28-40: ref_silu_and_mul_quant = F.silu(gate) * up in x.dtype;
     # with up = 1 and scale = 1 the e4m3 cast is the only other step, so the table is taken from

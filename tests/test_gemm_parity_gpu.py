@@ -399,7 +399,8 @@ def test_llama70b_mxfp4_full_m(ops, lib, kn):
     del x, w
     out = ops.fp4_gemm(xq, wq.t(), xs, ws, torch.bfloat16)
     rows = _rows_sample(m)
-    ref = _gpu_ref(_mx4_deq(xq[rows], xs[rows]), _mx4_deq(wq, ws), torch.bfloat16)
+    ref = _gpu_ref(_mx4_deq(xq.view(torch.uint8)[rows], xs.view(torch.uint8)[rows].view(E8)), _mx4_deq(wq, ws),
+                   torch.bfloat16)
     torch.testing.assert_close(out[rows].float(), ref.float(), atol=1e-2 * float(ref.float().abs().max()), rtol=1e-2)
     # linearity: doubling every weight scale (an exponent-byte increment) doubles the output exactly
     ws2 = (ws.view(torch.uint8) + 1).view(E8)

@@ -227,3 +227,38 @@ def test_silu_table_is_fp32_silu_rounded_once():
         mine = (allv.float() / (1.0 + e32)).to(dtype).view(torch.int16)
         assert torch.equal(mine[fin], tab[str(dtype)][fin])
         assert torch.equal(torch.nn.functional.silu(allv).view(torch.int16)[fin], tab[str(dtype)][fin])
+
+
+def test_f3_indexer_k_cache_golden():
+    """(f)#3: the oracle's cache scatter / gather equal the reference tests' torch refs byte for byte
+    (fp32-log2 exponent as the ref, and the exact-exponent form the CUDA kernels use)."""
+    from oracle import cache as ocache
+    for c in load("f3_indexer_k_cache"):
+        for exact in (False, True):
+            kv = torch.zeros_like(c["cache"])
+            ocache.indexer_k_quant_and_cache(c["k"], kv, c["slot_mapping"], c["G"], c["fmt"], exact_exponent=exact)
+            assert torch.equal(kv, c["cache"]), (c["fmt"], c["k"].dtype, exact)
+        dk = torch.zeros_like(c["dst_k"])
+        ds = torch.zeros_like(c["dst_scale"])
+        ocache.cp_gather_indexer_k_quant_cache(c["cache"], dk, ds, c["block_table"], c["cu_seq_lens"])
+        assert torch.equal(dk, c["dst_k"]) and torch.equal(ds, c["dst_scale"])
+
+
+def test_convert_fp8_oracle_round_trip():
+    """convert_fp8 has no torch ref in the reference (it IS the helper of tests/test_cache.py); its oracle
+    restates csrc/cache.cpp:1411-1435 and is pinned by properties: every e4m3 code survives
+    dequantise -> quantise at any power-of-two scale, and quantisation equals the a2 static-scale oracle."""
+    from oracle import cache as ocache
+    codes = torch.arange(256, dtype=torch.uint8)
+    finite = ~torch.isnan(codes.view(E4).float())
+    for scale in (1.0, 0.125, 4.0):
+        for dt in (torch.float32, torch.float16, torch.bfloat16):
+            deq = ocache.convert_fp8(codes, scale, "fp8", dt)
+            back = ocache.convert_fp8(deq, scale, "fp8_e4m3", torch.uint8)
+            same = back == codes
+            # -0 (0x80) may come back as 0x80 or 0x00 depending on the sign of zero surviving: it does
+            assert bool(same[finite].all()), (scale, dt)
+    x = torch.randn(64, 128, dtype=torch.bfloat16)
+    q = ocache.convert_fp8(x, 0.5, "fp8", torch.uint8)
+    ref = (x.float() / 0.5).clamp(-448, 448).to(E4).view(torch.uint8)
+    assert torch.equal(q, ref)

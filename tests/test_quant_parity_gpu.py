@@ -5,18 +5,13 @@ test_fused_norm_quant.py, test_fused_silu_mul_*_quant.py,
 test_fused_quant_activation.py), trimmed so the oracle finishes in seconds.
 
 Bars (DESIGN.md "Parity"):
-  * ops without a transcendental or a long reduction (a1-a5): codes, E8M0 bytes
-    and fp32 scales BIT-EXACT;
-  * rms-norm ops (a6-a9): the variance is a 64-16k term sum; torch's fp32 cascade
-    order differs between AVX2 / AVX-512 hosts, the kernel accumulates it in fp64
-    (correctly rounded mean).  A 1-ulp difference in the variance propagates
-    through rsqrt, two multiplies, the row max and the divide by fp8_max, so
-    scales are held to 4 ulp (2.4e-7 relative) and codes to "identical or
-    adjacent code" with a mismatch fraction <= 2e-4;
-  * silu ops (a10-a12): the sigmoid is a transcendental (torch CPU: Sleef exp,
-    here: ex2.approx / rcp.approx by default, expf + IEEE divide on request);
-    codes identical for >= 99.98 % of elements, never more than one code apart;
-    both modes are tested.
+  * a1-a5: codes, E8M0 bytes and fp32 scales BIT-EXACT;
+  * a6-a9 (rms_norm + quant): BIT-EXACT against the oracle with the variance reduced exactly (fp64 mean
+    rounded once -- the kernels accumulate the exact squares in fp64); against torch's own fp32 summation
+    order on this host: scales within TORCH_ORDER_MAX_ULP, codes at most one step apart on a measured
+    < 1e-5 of elements;
+  * a10 / a11 (silu_and_mul + static / per-block): BIT-EXACT, both input types;
+  * a12 (silu_and_mul + MXFP4, fp32 product): at most 1e-6 of codes one step apart, scale bytes equal.
 """
 import os
 
@@ -24,6 +19,7 @@ import pytest
 import torch
 
 from oracle import formats, quant
+from parity_util import code_stats, nibble_stats, scale_stats
 
 pytestmark = pytest.mark.gpu
 
@@ -269,6 +265,9 @@ def test_e2m1_hardware_conversion_matches_reference_on_every_bf16(ops):
 
 
 # ------------------------------------------------------------------ a6 .. a9
+# Bar: BIT-EXACT scales, E8M0 bytes, codes and residual against the oracle with the variance reduced
+# exactly (fp64 mean, rounded once -- oracle.quant.rms_norm_f32(exact_variance=True)); torch's own fp32
+# summation order on this host is the second, measured check (its variance is a few ulp off the exact one).
 def _norm_inputs(T, H, dtype, add_res, strided=False):
     seed()
     w = torch.empty(H, dtype=dtype).normal_(mean=1.0, std=0.1)
@@ -279,31 +278,41 @@ def _norm_inputs(T, H, dtype, add_res, strided=False):
 
 
 NORM_SHAPES = [(1, 64), (7, 128), (83, 1024), (7, 5120), (64, 4096), (5, 8192), (3, 1000), (2, 16384)]
+TORCH_ORDER_MAX_ULP = 8          # measured: <= 4 (profiles/parity_r02.txt)
+TORCH_ORDER_MAX_CODE_FRAC = 1e-3  # measured: <= 6e-6 at T = 8192
 
 
-@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+def _check_vs_torch_order(q, s, rq, rs, what, is_int8=False):
+    n, frac, d = code_stats(q, rq, is_int8)
+    assert d <= 1 and frac <= TORCH_ORDER_MAX_CODE_FRAC, f"{what}: {n} codes differ, max {d} steps"
+    if s is not None:
+        assert scale_stats(s, rs)[2] <= TORCH_ORDER_MAX_ULP, f"{what}: scales {scale_stats(s, rs)}"
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16, torch.float32])
 @pytest.mark.parametrize("qd", [E4, torch.int8])
 @pytest.mark.parametrize("T,H", NORM_SHAPES)
 @pytest.mark.parametrize("add_res", [False, True])
 def test_a6_rms_norm_dynamic_per_token(ops, dtype, qd, T, H, add_res):
     x, w, res = _norm_inputs(T, H, dtype, add_res)
-    rq, rs, rres = quant.rms_norm_dynamic_per_token_quant(x, w, 1e-6, qd, None, res)
     dres = res.clone().to(DEV) if add_res else None
     q, s = ops.rms_norm_dynamic_per_token_quant(x.to(DEV), w.to(DEV), 1e-6, qd, None, dres)
-    assert ulps(s, rs) <= 4
-    assert_codes_close(q, rq, 2e-4, "a6", is_int8=(qd == torch.int8))
+    rq, rs, rres = quant.rms_norm_dynamic_per_token_quant(x, w, 1e-6, qd, None, res, exact_variance=True)
+    assert torch.equal(s.cpu(), rs), f"scales: {scale_stats(s, rs)}"
+    assert torch.equal(u8(q), u8(rq)), f"codes: {code_stats(q, rq, qd == torch.int8)}"
     if add_res:
         assert torch.equal(dres.cpu(), rres)       # residual update is exact
+    tq, ts, _ = quant.rms_norm_dynamic_per_token_quant(x, w, 1e-6, qd, None, res, exact_variance=False)
+    _check_vs_torch_order(q, s, tq, ts, "a6 vs torch order", qd == torch.int8)
 
 
 def test_a6_scale_ub(ops):
     x, w, _ = _norm_inputs(83, 1024, torch.bfloat16, False)
-    normed, _ = quant.rms_norm_f32(x, w, 1e-6)
+    normed, _ = quant.rms_norm_f32(x, w, 1e-6, exact_variance=True)
     ub = torch.tensor(0.5 * float(normed.abs().max()))
-    rq, rs, _ = quant.rms_norm_dynamic_per_token_quant(x, w, 1e-6, E4, ub)
+    rq, rs, _ = quant.rms_norm_dynamic_per_token_quant(x, w, 1e-6, E4, ub, exact_variance=True)
     q, s = ops.rms_norm_dynamic_per_token_quant(x.to(DEV), w.to(DEV), 1e-6, E4, ub.to(DEV))
-    assert ulps(s, rs) <= 4
-    assert_codes_close(q, rq, 2e-4, "a6 ub")
+    assert torch.equal(s.cpu(), rs) and torch.equal(u8(q), u8(rq))
 
 
 @pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
@@ -314,16 +323,18 @@ def test_a6_scale_ub(ops):
 @pytest.mark.parametrize("transposed", [False, True])
 def test_a7_rms_norm_per_block(ops, dtype, qd, T, H, G, add_res, transposed):
     x, w, res = _norm_inputs(T, H, dtype, add_res)
-    rq, rs, rres = quant.rms_norm_per_block_quant(x, w, 1e-6, G, qd, res)
+    rq, rs, rres = quant.rms_norm_per_block_quant(x, w, 1e-6, G, qd, res, exact_variance=True)
     dres = res.clone().to(DEV) if add_res else None
     q, s = ops.rms_norm_per_block_quant(x.to(DEV), w.to(DEV), 1e-6, G, qd, dres, transposed)
     assert s.shape == (T, H // G)
     if transposed:
         assert s.stride(0) == 1
-    assert ulps(s, rs) <= 4
-    assert_codes_close(q, rq, 2e-4, "a7", is_int8=(qd == torch.int8))
+    assert torch.equal(s.contiguous().cpu(), rs), f"scales: {scale_stats(s, rs)}"
+    assert torch.equal(u8(q), u8(rq)), f"codes: {code_stats(q, rq, qd == torch.int8)}"
     if add_res:
         assert torch.equal(dres.cpu(), rres)
+    tq, ts, _ = quant.rms_norm_per_block_quant(x, w, 1e-6, G, qd, res, exact_variance=False)
+    _check_vs_torch_order(q, s, tq, ts, "a7 vs torch order", qd == torch.int8)
 
 
 @pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
@@ -331,14 +342,12 @@ def test_a7_rms_norm_per_block(ops, dtype, qd, T, H, G, add_res, transposed):
 @pytest.mark.parametrize("add_res", [False, True])
 def test_a7_mxfp8_ue8m0(ops, dtype, T, H, add_res):
     x, w, res = _norm_inputs(T, H, dtype, add_res)
-    rq, rs, _ = quant.rms_norm_per_block_quant(x, w, 1e-6, 32, E4, res, scale_ue8m0=True)
+    rq, rs, _ = quant.rms_norm_per_block_quant(x, w, 1e-6, 32, E4, res, scale_ue8m0=True, exact_variance=True)
     dres = res.clone().to(DEV) if add_res else None
     q, s = ops.rms_norm_per_block_quant(x.to(DEV), w.to(DEV), 1e-6, 32, E4, dres, False, True)
     log2 = torch.log2(s.cpu())
     assert torch.equal(log2, log2.round())                       # exact powers of two
-    assert (s.cpu() != rs).float().mean().item() <= 1e-3          # a 1-ulp amax can cross 2^k
-    same = (s.cpu() == rs).repeat_interleave(32, dim=1)
-    assert_codes_close(u8(q)[same], u8(rq)[same], 2e-4, "a7 ue8m0")
+    assert torch.equal(s.cpu(), rs) and torch.equal(u8(q), u8(rq))
 
 
 def test_a7_noncontiguous_rows(ops):
@@ -352,22 +361,20 @@ def test_a7_noncontiguous_rows(ops):
     q1, s1 = ops.rms_norm_per_block_quant(xnc, w, 1e-6, 128, E4)
     q2, s2 = ops.rms_norm_per_block_quant(xnc.contiguous(), w, 1e-6, 128, E4)
     assert torch.equal(s1, s2) and torch.equal(u8(q1), u8(q2))
+    rq, rs, _ = quant.rms_norm_per_block_quant(xnc.contiguous().cpu(), w.cpu(), 1e-6, 128, E4, exact_variance=True)
+    assert torch.equal(s1.cpu(), rs) and torch.equal(u8(q1), u8(rq))
 
 
 @pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
-@pytest.mark.parametrize("T,H", [(1, 128), (7, 1024), (83, 5120)])
+@pytest.mark.parametrize("T,H", [(1, 128), (7, 1024), (83, 5120), (64, 4096)])
 @pytest.mark.parametrize("add_res", [False, True])
 def test_a8_rms_norm_mxfp4(ops, dtype, T, H, add_res):
     x, w, res = _norm_inputs(T, H, dtype, add_res)
-    rq, rs, rres = quant.rms_norm_mxfp4_quant(x, w, 1e-6, res)
+    rq, rs, rres = quant.rms_norm_mxfp4_quant(x, w, 1e-6, res, exact_variance=True)
     dres = res.clone().to(DEV) if add_res else None
     q, s = ops.rms_norm_mxfp4_quant(x.to(DEV), w.to(DEV), 1e-6, dres)
-    log2 = torch.log2(s.cpu())
-    assert torch.equal(log2, log2.round())
-    assert (s.cpu() != rs).float().mean().item() <= 1e-3
-    same = (s.cpu() == rs).repeat_interleave(16, dim=1)
-    neq = (u8(q) != rq) & same
-    assert neq.float().mean().item() <= 2e-4
+    assert torch.equal(s.cpu(), rs), "E8M0 scales"
+    assert torch.equal(u8(q), rq), f"codes: {nibble_stats(q, rq)}"
     if add_res:
         assert torch.equal(dres.cpu(), rres)
 
@@ -380,7 +387,7 @@ def test_a9_rms_norm_static(ops, dtype, T, H, strided, add_res):
     x, w, res = _norm_inputs(T, H, dtype, add_res, strided)
     for sv in (1.0, 0.02):
         scale = torch.tensor(sv, dtype=torch.float32)
-        rq, rres = quant.rms_norm_static_fp8_quant(x, w, scale, 1e-6, res)
+        rq, rres = quant.rms_norm_static_fp8_quant(x, w, scale, 1e-6, res, exact_variance=True)
         dres = res.clone().to(DEV) if add_res else None
         xd = (torch.zeros(T, 2 * H, dtype=dtype, device=DEV) if strided else None)
         if strided:
@@ -390,50 +397,58 @@ def test_a9_rms_norm_static(ops, dtype, T, H, strided, add_res):
         else:
             xin = x.to(DEV)
         q = ops.rms_norm_static_fp8_quant(xin, w.to(DEV), scale.to(DEV), 1e-6, dres)
-        assert_codes_close(q, rq, 2e-4, "a9")
+        assert torch.equal(u8(q), u8(rq)), f"codes: {code_stats(q, rq)}"
         if add_res:
             assert torch.equal(dres.cpu(), rres)
 
 
 def test_a6_a9_golden(ops):
+    """The committed outputs of the reference's own functions (torch fp32 summation order of the build
+    container): the second, measured check."""
     for c in load("a6_a9_rms_norm"):
         x, w, res = c["x"], c["w"], c["res"]
         for qd in (E4, torch.int8):
             dres = res.clone().to(DEV) if res is not None else None
             q, s = ops.rms_norm_dynamic_per_token_quant(x.to(DEV), w.to(DEV), 1e-6, qd, None, dres)
             gq, gs = c[f"tok_{qd}"]
-            assert ulps(s, gs) <= 4
-            assert_codes_close(q, gq, 5e-4, "golden a6", is_int8=(qd == torch.int8))
+            _check_vs_torch_order(q, s, gq, gs, "golden a6", qd == torch.int8)
             if res is not None:
                 assert torch.equal(dres.cpu(), c["res_out"])
             for G in (64, 128):
                 dres = res.clone().to(DEV) if res is not None else None
                 q, s = ops.rms_norm_per_block_quant(x.to(DEV), w.to(DEV), 1e-6, G, qd, dres)
                 gq, gs = c[f"grp{G}_{qd}"]
-                assert ulps(s, gs) <= 4
-                assert_codes_close(q, gq, 5e-4, "golden a7", is_int8=(qd == torch.int8))
+                _check_vs_torch_order(q, s, gq, gs, "golden a7", qd == torch.int8)
         dres = res.clone().to(DEV) if res is not None else None
         q = ops.rms_norm_static_fp8_quant(x.to(DEV), w.to(DEV), torch.tensor(0.02, device=DEV), 1e-6, dres)
-        assert_codes_close(q, c["static_0p02"], 5e-4, "golden a9")
+        _check_vs_torch_order(q, None, c["static_0p02"], None, "golden a9")
         dres = res.clone().to(DEV) if res is not None else None
         q, s = ops.rms_norm_mxfp4_quant(x.to(DEV), w.to(DEV), 1e-6, dres)
         gq, ge = c["mxfp4"]
         assert (u8(s.to(torch.float8_e8m0fnu)) != ge).float().mean().item() <= 1e-3
-        assert (u8(q) != gq).float().mean().item() <= 2e-3
+        assert nibble_stats(q, gq)[1] <= 1e-3
 
 
 # ------------------------------------------------------------------ a10 .. a12
+# Bar: a10 / a11 BIT-EXACT (silu(gate) is rounded to the 16-bit input type at once, and
+# tests/test_silu_exhaustive_gpu.py proves the kernels' silu -> T equals torch's on all 65536 inputs of
+# either type); a12 keeps the fp32 product and is held to its measured worst case (profiles/parity_r02.txt:
+# at most 5 of 5.9e7 codes one step apart, no scale byte differs), stated here as <= 1e-6.
+A12_MAX_FRAC = 1e-6
+
+
 @pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
 @pytest.mark.parametrize("qd", [E4, E5])
 @pytest.mark.parametrize("T,d", [(1, 16), (7, 128), (83, 512), (512, 4096), (7, 100), (5, 14336)])
-def test_a10_silu_and_mul_quant(ops, dtype, qd, T, d):
+@pytest.mark.parametrize("mag", [1.0, 8.0])
+def test_a10_silu_and_mul_quant(ops, dtype, qd, T, d, mag):
     seed()
-    x = torch.randn(T, 2 * d, dtype=dtype)
+    x = torch.randn(T, 2 * d, dtype=dtype) * mag
     scale = torch.tensor([0.5], dtype=torch.float32)
     ref = quant.silu_and_mul_quant(x, scale, qd)
     out = torch.empty(T, d, dtype=qd, device=DEV)
     ops.silu_and_mul_quant(out, x.to(DEV), scale.to(DEV))
-    assert_codes_close(out, ref, 2e-4, "a10")
+    assert torch.equal(u8(out), u8(ref)), f"codes: {code_stats(out, ref)}"
 
 
 @pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
@@ -449,12 +464,20 @@ def test_a11_silu_and_mul_per_block(ops, dtype, qd, T, H, G, transposed):
     rq, rs = quant.silu_and_mul_per_block_quant(x, G, qd)
     q, s = ops.silu_and_mul_per_block_quant(x.to(DEV), G, qd, None, transposed)
     assert s.shape == (T, H // G)
-    sc = s.contiguous().cpu()
-    same = sc == rs
-    assert same.float().mean().item() >= 0.999
-    torch.testing.assert_close(sc, rs, rtol=1e-2, atol=0)
-    m = same.repeat_interleave(G, dim=1)
-    assert_codes_close(u8(q)[m], u8(rq)[m], 2e-4, "a11", is_int8=(qd == torch.int8))
+    assert torch.equal(s.contiguous().cpu(), rs), f"scales: {scale_stats(s, rs)}"
+    assert torch.equal(u8(q), u8(rq)), f"codes: {code_stats(q, rq, qd == torch.int8)}"
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("mag", [1.0, 1.0 / 64, 8.0])
+def test_a11_full_width_magnitudes(ops, dtype, mag):
+    """Llama-3-8B intermediate width, gate magnitudes from tiny to saturating."""
+    seed()
+    x = torch.randn(256, 2 * 14336, dtype=dtype) * mag
+    for qd in (E4, torch.int8):
+        rq, rs = quant.silu_and_mul_per_block_quant(x, 128, qd)
+        q, s = ops.silu_and_mul_per_block_quant(x.to(DEV), 128, qd)
+        assert torch.equal(s.cpu(), rs) and torch.equal(u8(q), u8(rq)), (scale_stats(s, rs), code_stats(q, rq))
 
 
 def test_a11_scale_ub_and_ue8m0(ops):
@@ -465,27 +488,31 @@ def test_a11_scale_ub_and_ue8m0(ops):
     ub = s0.median().reshape(1)
     rq, rs = quant.silu_and_mul_per_block_quant(x, G, E4, scale_ub=ub)
     q, s = ops.silu_and_mul_per_block_quant(x.to(DEV), G, E4, ub.to(DEV))
-    assert (s.cpu() == rs).float().mean().item() >= 0.999
+    assert torch.equal(s.cpu(), rs) and torch.equal(u8(q), u8(rq))
     rq, rs = quant.silu_and_mul_per_block_quant(x, G, E4, scale_ue8m0=True)
     q, s = ops.silu_and_mul_per_block_quant(x.to(DEV), G, E4, None, False, True)
-    assert (s.cpu() == rs).float().mean().item() >= 0.999
-    m = (s.cpu() == rs).repeat_interleave(G, dim=1)
-    assert_codes_close(u8(q)[m], u8(rq)[m], 2e-4, "a11 ue8m0")
+    assert torch.equal(s.cpu(), rs) and torch.equal(u8(q), u8(rq))
 
 
 @pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
 @pytest.mark.parametrize("T,H", [(1, 128), (7, 1024), (83, 5120), (2048, 1024), (2, 28672)])
-def test_a12_silu_and_mul_mxfp4(ops, dtype, T, H):
+@pytest.mark.parametrize("mag", [None, 1.0])
+def test_a12_silu_and_mul_mxfp4(ops, dtype, T, H, mag):
     seed()
-    x = torch.randn(T, 2 * H, dtype=dtype) * (1.0 / H)
+    x = torch.randn(T, 2 * H, dtype=dtype) * (mag if mag else 1.0 / H)
     rq, rs = quant.silu_and_mul_mxfp4_quant(x)
     q, s = ops.silu_and_mul_mxfp4_quant(x.to(DEV))
     log2 = torch.log2(s.cpu())
     assert torch.equal(log2, log2.round())
-    same = s.cpu() == rs
-    assert same.float().mean().item() >= 0.999
-    m = same.repeat_interleave(16, dim=1)
-    assert ((u8(q) != rq) & m).float().mean().item() <= 2e-4
+    n_s = int((s.cpu() != rs).sum())
+    n_c, frac_c, d_c = nibble_stats(q, rq)
+    assert n_s <= max(1, A12_MAX_FRAC * s.numel()), f"{n_s} scale bytes differ"
+    # a differing scale byte re-codes its whole group: compare against the formula with the kernel's scales
+    given = quant.mxfp4_codes_given_exponent(quant.silu_mul_f32(x), u8(s.to(torch.float8_e8m0fnu)))
+    n_g, frac_g, d_g = nibble_stats(q, given)
+    assert d_g <= 1 and n_g <= max(1, A12_MAX_FRAC * rq.numel() * 2), f"{n_g} codes differ (max {d_g} steps)"
+    if n_s == 0:
+        assert d_c <= 1 and n_c <= max(1, A12_MAX_FRAC * rq.numel() * 2)
 
 
 def test_a10_a12_golden(ops):
@@ -493,23 +520,22 @@ def test_a10_a12_golden(ops):
         qd = E4 if "e4m3" in c["qdtype"] else E5
         out = torch.empty(c["x"].shape[0], c["x"].shape[1] // 2, dtype=qd, device=DEV)
         ops.silu_and_mul_quant(out, c["x"].to(DEV), c["scale"].to(DEV))
-        assert_codes_close(out, c["q"], 5e-4, "golden a10")
+        assert torch.equal(u8(out), c["q"])
     for c in load("a11_silu_block"):
         qd = E4 if "e4m3" in c["qdtype"] else torch.int8
         q, s = ops.silu_and_mul_per_block_quant(c["x"].to(DEV), c["G"], qd)
-        torch.testing.assert_close(s.cpu(), c["s"], rtol=1e-2, atol=0)
-        m = (s.cpu() == c["s"]).repeat_interleave(c["G"], dim=1)
-        assert_codes_close(u8(q)[m], c["q"][m], 5e-4, "golden a11", is_int8=(qd == torch.int8))
+        assert torch.equal(s.cpu(), c["s"]) and torch.equal(u8(q), c["q"])
     for c in load("a12_silu_mxfp4"):
         q, s = ops.silu_and_mul_mxfp4_quant(c["x"].to(DEV))
-        assert (s.cpu() == c["s"]).float().mean().item() >= 0.999
-        assert (u8(q) != c["q"]).float().mean().item() <= 1e-3
+        assert torch.equal(s.cpu(), c["s"])
+        assert nibble_stats(q, c["q"])[0] <= 1
 
 
 @pytest.mark.parametrize("fast", [0, 1])
 @pytest.mark.parametrize("mag", [1.0, 1.0 / 64, 8.0])
-def test_silu_modes_stay_within_the_bar(ops, fast, mag):
-    """Both silu evaluations (approximate = default, expf + IEEE divide) meet the same bar."""
+def test_silu_modes_forced(ops, fast, mag):
+    """vxk_set_silu_fast(0 / 1) overrides the auto choice; both forms stay within one code step on a
+    vanishing fraction of elements (bf16: the two are identical, see the exhaustive test)."""
     from vllm_xpu_kernels_b200 import _loader
     lib = _loader.cdll()
     seed()
@@ -522,20 +548,14 @@ def test_silu_modes_stay_within_the_bar(ops, fast, mag):
         q4, s4 = ops.silu_and_mul_mxfp4_quant(x.to(DEV))
     finally:
         lib.vxk_set_silu_fast(prev)
-    same = s.cpu() == rs
-    assert same.float().mean().item() >= 0.999
-    m = same.repeat_interleave(128, dim=1)
-    assert_codes_close(u8(q)[m], u8(rq)[m], 2e-4, f"a11 fast={fast}")
-    same4 = s4.cpu() == rs4
-    assert same4.float().mean().item() >= 0.999
-    assert ((u8(q4) != r4) & same4.repeat_interleave(16, dim=1)).float().mean().item() <= 2e-4
+    assert torch.equal(s.cpu(), rs) and torch.equal(u8(q), u8(rq))
+    assert torch.equal(s4.cpu(), rs4)
+    n, frac, d = nibble_stats(q4, r4)
+    assert d <= 1 and n <= 2
 
 
-@pytest.mark.parametrize("fast", [0, 1])
-def test_silu_extreme_gates(ops, fast):
-    """Gates far outside the sigmoid's useful range (exp overflow side) next to ordinary ones: scales and codes still match the reference."""
-    from vllm_xpu_kernels_b200 import _loader
-    lib = _loader.cdll()
+def test_silu_extreme_gates(ops):
+    """Gates far outside the sigmoid's useful range (exp overflow side) next to ordinary ones."""
     seed()
     x = torch.randn(64, 2 * 1024, dtype=torch.bfloat16)
     x[:, 0:1024:7] = -60.0
@@ -543,17 +563,9 @@ def test_silu_extreme_gates(ops, fast):
     x[:, 2:1024:11] = 100.0
     x[3, :1024] = -80.0          # a whole row of vanishing silu values
     rq, rs = quant.silu_and_mul_per_block_quant(x, 128, E4)
-    prev = lib.vxk_set_silu_fast(fast)
-    try:
-        q, s = ops.silu_and_mul_per_block_quant(x.to(DEV), 128, E4)
-    finally:
-        lib.vxk_set_silu_fast(prev)
-    live = rs > 1e-12            # groups whose scale is not the tiny-value floor
-    same = (s.cpu() == rs) | ~live
-    assert same.float().mean().item() >= 0.999
-    m = (same & live).repeat_interleave(128, dim=1)
-    assert_codes_close(u8(q)[m], u8(rq)[m], 5e-4, f"a11 extreme fast={fast}")
+    q, s = ops.silu_and_mul_per_block_quant(x.to(DEV), 128, E4)
     assert torch.isfinite(s).all()
+    assert torch.equal(s.cpu(), rs) and torch.equal(u8(q), u8(rq))
 
 
 # ------------------------------------------------------------------ boundary behaviour

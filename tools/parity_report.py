@@ -102,7 +102,7 @@ def report_silu(T, H, dtype, mag, lib):
     xd = x.to(DEV)
     tag = f"T={T} H={H} {str(dtype)[6:]} gate~N(0,{mag:g})"
     yT = quant.silu_mul_T(x)
-    for fast in (0, 1):
+    for fast in (-1, 0, 1):
         prev = lib.vxk_set_silu_fast(fast)
         try:
             # a10

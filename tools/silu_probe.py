@@ -5,8 +5,11 @@ the approximate form's two constants for a variant with zero mismatches.  Run on
     python tools/silu_probe.py [out.pt]
 """
 import ctypes
+import os
 import struct
 import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 
 import torch
 import torch.nn.functional as F

@@ -33,6 +33,7 @@ CU_SOURCES = {
     "quant_row_f16.cu": ["-fmad=false"],
     "quant_row_bf16.cu": ["-fmad=false"],
     "quant_flat.cu": ["-fmad=false"],
+    "quant_cache.cu": ["-fmad=false"],
     "gemm_fallback.cu": [],
     "gemm_tc.cu": [],
     "gemm_w8a16.cu": [],

@@ -20,7 +20,14 @@
 
 namespace vxk {
 
-std::atomic<int> g_silu_fast{1};  // see DESIGN.md "silu": approx by default, vxk_set_silu_fast(0) for expf + IEEE divide
+// silu evaluation (see DESIGN.md "silu"): -1 = auto (default), 0 = expf + IEEE divide everywhere,
+// 1 = ex2.approx / rcp.approx everywhere.  Auto picks, per op and input type, the cheapest form that is
+// PROVEN bit-identical to the reference on every input: a10 / a11 round silu(gate) to the 16-bit input
+// type right away, so the function has 65536 inputs and tests/test_silu_exhaustive_gpu.py checks all of
+// them against torch -- the approximate form passes for bf16 (8-bit significand) and not for f16
+// (11-bit), which therefore takes the accurate form.  a12 keeps the fp32 product (no rounding to hide
+// the last bits; torch's own fp32 sigmoid differs between hosts there) and uses the approximate form.
+std::atomic<int> g_silu_fast{-1};
 
 enum Pro { PRO_NONE = 0, PRO_SILU_T = 1, PRO_SILU_F32 = 2 };
 enum Fmt { FMT_FP8_DIV = 0, FMT_MX8 = 1, FMT_MXFP4 = 2, FMT_STATIC = 3 };
@@ -83,6 +90,9 @@ __device__ __forceinline__ void raw_to_f32(const RawV<T>& r, float (&v)[8]) {
   }
 }
 
+// accurate silu, out of line (rare path of the approximate form, see prologue)
+__device__ __noinline__ float silu_slow(float x) { return silu_f32<0>(x); }
+
 // gate/up vectors -> the fp32 values to quantise (v) and, for 16-bit T, the same values still
 // packed two per word (yw) -- the sign bits of the packed words patch the fp8 codes after an
 // exact division (see pack_q8_signed).
@@ -97,12 +107,26 @@ __device__ __forceinline__ void prologue(const RawV<T>& g, const RawV<T>& up, fl
   } else if constexpr (PRO == PRO_SILU_T && sizeof(T) == 2) {
     const uint32_t gw[4] = {g.a.x, g.a.y, g.a.z, g.a.w};
     const uint32_t uw[4] = {up.a.x, up.a.y, up.a.z, up.a.w};
+    // The approximate form flushes 1 / (1 + e^-x) to zero once e^-x passes 2^126 (rcp.approx.ftz), i.e. for
+    // gates in (-88.72, -87.34]: three bf16 values (-87.5, -88, -88.5) whose silu is a tiny normal number in
+    // the reference.  A vector holding such a gate takes the accurate form (3 packed minima + 1 compare per
+    // 8 elements; the branch is never taken on real activations).  Everything else is proven identical by
+    // tests/test_silu_exhaustive_gpu.py.
+    bool deep = false;
+    if constexpr (FAST && std::is_same<T, __nv_bfloat16>::value) {
+      using V = typename Pair<T>::V;
+      const V m = __hmin2(__hmin2(*reinterpret_cast<const V*>(&gw[0]), *reinterpret_cast<const V*>(&gw[1])),
+                          __hmin2(*reinterpret_cast<const V*>(&gw[2]), *reinterpret_cast<const V*>(&gw[3])));
+      deep = !__hbgt2(m, __float2bfloat162_rn(-87.25f));       // some gate <= -87.25 (or NaN)
+    }
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
       const float2 f = Pair<T>::unpack(gw[i]);
       float s0, s1;
-      if constexpr (FAST) silu2_approx(f.x, f.y, s0, s1);
-      else { s0 = silu_f32<0>(f.x); s1 = silu_f32<0>(f.y); }
+      if constexpr (FAST) {
+        if (__builtin_expect(deep, 0)) { s0 = silu_slow(f.x); s1 = silu_slow(f.y); }
+        else silu2_approx(f.x, f.y, s0, s1);
+      } else { s0 = silu_f32<0>(f.x); s1 = silu_f32<0>(f.y); }
       const typename Pair<T>::V s2 = Pair<T>::pack(s0, s1);
       const typename Pair<T>::V y2 = __hmul2(s2, *reinterpret_cast<const typename Pair<T>::V*>(&uw[i]));
       yw[i] = *reinterpret_cast<const uint32_t*>(&y2);
@@ -520,7 +544,8 @@ static void launch_flat_ll(const FlatParams& p, int64_t row_blocks, int ncb, int
 template <typename T, int Q, int PRO, int FMT>
 static int launch_flat(FlatParams p, int64_t T_, int64_t H, int G, bool vec_ok, cudaStream_t st) {
   if (T_ == 0 || H == 0) return VXK_OK;
-  const int mode = (PRO != PRO_NONE) ? g_silu_fast.load(std::memory_order_relaxed) : 0;
+  int mode = (PRO != PRO_NONE) ? g_silu_fast.load(std::memory_order_relaxed) : 0;
+  if (mode < 0) mode = (PRO == PRO_SILU_F32 || std::is_same<T, __nv_bfloat16>::value) ? 1 : 0;   // auto
   p.T = T_;
   if (vec_ok) {
     constexpr int U = (PRO == PRO_NONE) ? 4 : 2;   // 4 x 16 B loads in flight per thread either way
@@ -589,8 +614,7 @@ static bool group_vec_ok(const void* in, const void* out, int64_t H, int64_t G, 
 using namespace vxk;
 
 extern "C" int vxk_set_silu_fast(int on) {
-  const int prev = g_silu_fast.exchange(on ? 1 : 0);
-  return prev;
+  return g_silu_fast.exchange(on < 0 ? -1 : (on ? 1 : 0));
 }
 
 extern "C" int vxk_per_token_group_fp8_quant(const void* in, void* out_q, float* out_s, int64_t T_,
@@ -765,7 +789,12 @@ __global__ void silu_probe_kernel(const T* __restrict__ in, T* out_t, float* out
     const float x = to_f32<T>(in[i]);
     float s;
     if (mode == 0) s = silu_f32<0>(x);
-    else if (mode == 1) s = silu_f32<1>(x);
+    else if (mode == 1) {
+      // the approximate form as the fused kernels use it: bf16 vectors holding a gate <= -87.25 take the
+      // accurate form (prologue<PRO_SILU_T, FAST>)
+      if (std::is_same<T, __nv_bfloat16>::value && !(x > -87.25f)) s = silu_f32<0>(x);
+      else s = silu_f32<1>(x);
+    }
     else s = (x * rcp_approx(1.0f + ex2_approx(x * c))) * beta;
     if (out_t) out_t[i] = from_f32<T>(s);
     if (out_f32) out_f32[i] = s;

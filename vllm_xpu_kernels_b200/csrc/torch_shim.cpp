@@ -12,6 +12,7 @@
 #include <torch/library.h>
 
 #include <optional>
+#include <string>
 #include <tuple>
 
 #include "../../include/vxk_b200.h"
@@ -59,7 +60,8 @@ template <typename... Rest>
 inline void same_device(const Tensor& ref, const std::optional<Tensor>& t, const Rest&... rest);
 template <typename... Rest>
 inline void same_device(const Tensor& ref, const Tensor& t, const Rest&... rest) {
-  TORCH_CHECK(!t.defined() || (t.is_cuda() && t.device() == ref.device()),
+  // (an empty tensor stands for "absent": the reference tests pass torch.Tensor() as "no bias")
+  TORCH_CHECK(!t.defined() || t.numel() == 0 || (t.is_cuda() && t.device() == ref.device()),
               "all tensor arguments must be on the same CUDA device (got ", t.device(), " and ", ref.device(), ")");
   same_device(ref, rest...);
 }
@@ -677,6 +679,88 @@ Tensor fp8_gemm_w8a16(const Tensor& A, const Tensor& B, const std::optional<Tens
   return result;
 }
 
+// ------------------------------------------------------------ _C_cache_ops
+// ref: csrc/cache.cpp:1558-1590
+void indexer_k_quant_and_cache(Tensor& k, Tensor& kv_cache, Tensor& slot_mapping, int64_t quant_block_size,
+                               const std::string& scale_fmt) {
+  check_cuda(k, "k");
+  TORCH_CHECK(k.device() == kv_cache.device(), "k and kv_cache must be on the same device");
+  TORCH_CHECK(k.device() == slot_mapping.device(), "k and slot_mapping must be on the same device");
+  TORCH_CHECK(k.dim() == 2 && kv_cache.dim() == 3, "k must be [num_tokens, head_dim], kv_cache [blocks, block_size, stride]");
+  TORCH_CHECK(kv_cache.element_size() == 1, "kv_cache must be a byte tensor (uint8 / fp8)");
+  TORCH_CHECK(slot_mapping.scalar_type() == at::kLong && slot_mapping.is_contiguous(), "slot_mapping must be contiguous int64");
+  const int64_t num_tokens = k.size(0), head_dim = k.size(1);
+  TORCH_CHECK(slot_mapping.numel() >= num_tokens, "slot_mapping must hold one slot per token");
+  TORCH_CHECK(quant_block_size > 0 && head_dim % quant_block_size == 0, "head_dim must be divisible by quant_block_size");
+  TORCH_CHECK(k.stride(1) == 1 && kv_cache.stride(2) == 1 && kv_cache.stride(1) == kv_cache.size(2),
+              "k rows and kv_cache blocks must be dense");
+  const c10::cuda::CUDAGuard guard(k.device());
+  check_rc(vxk_indexer_k_quant_and_cache(k.data_ptr(), kv_cache.data_ptr(), slot_mapping.data_ptr<int64_t>(), num_tokens,
+                                         head_dim, k.stride(0), quant_block_size, kv_cache.size(1), kv_cache.size(2),
+                                         kv_cache.stride(0), scale_fmt == "ue8m0" ? 1 : 0,
+                                         in_dtype_of(k, "indexer_k_quant_and_cache"), cur_stream()),
+           "indexer_k_quant_and_cache");
+}
+
+// ref: csrc/cache.cpp:1625-1680
+void cp_gather_indexer_k_quant_cache(const Tensor& kv_cache, Tensor& dst_k, Tensor& dst_scale, const Tensor& block_table,
+                                     const Tensor& cu_seq_lens) {
+  check_cuda(kv_cache, "kv_cache");
+  TORCH_CHECK(kv_cache.device() == dst_k.device(), "kv_cache and dst_k must be on the same device");
+  TORCH_CHECK(kv_cache.device() == dst_scale.device(), "kv_cache and dst_scale must be on the same device");
+  TORCH_CHECK(kv_cache.device() == block_table.device(), "kv_cache and block_table must be on the same device");
+  TORCH_CHECK(kv_cache.device() == cu_seq_lens.device(), "kv_cache and cu_seq_lens must be on the same device");
+  TORCH_CHECK(kv_cache.dim() == 3 && dst_k.dim() == 2 && dst_scale.dim() == 2 && block_table.dim() == 2,
+              "kv_cache [blocks, block_size, stride], dst_k [tokens, head_dim], dst_scale [tokens, 4 * groups], "
+              "block_table [batch, blocks]");
+  TORCH_CHECK(kv_cache.element_size() == 1 && dst_k.element_size() == 1 && dst_scale.element_size() == 1,
+              "kv_cache, dst_k and dst_scale must be byte tensors");
+  TORCH_CHECK(block_table.scalar_type() == at::kInt && cu_seq_lens.scalar_type() == at::kInt,
+              "block_table and cu_seq_lens must be int32");
+  TORCH_CHECK(block_table.stride(1) == 1 && cu_seq_lens.is_contiguous() && dst_k.stride(1) == 1 && dst_scale.stride(1) == 1 &&
+                  kv_cache.stride(2) == 1 && kv_cache.stride(1) == kv_cache.size(2),
+              "inner dimensions must be dense");
+  const int64_t batch = block_table.size(0), num_tokens = dst_k.size(0), head_dim = dst_k.size(1);
+  TORCH_CHECK(cu_seq_lens.numel() >= batch + 1, "cu_seq_lens must have batch_size + 1 entries");
+  TORCH_CHECK(dst_scale.size(1) > 0 && (head_dim * 4) % dst_scale.size(1) == 0, "dst_scale must be [tokens, 4 * head_dim / quant_block_size]");
+  const int64_t quant_block_size = head_dim * 4 / dst_scale.size(1);
+  TORCH_CHECK(head_dim % quant_block_size == 0, "head_dim must be divisible by quant_block_size");
+  TORCH_CHECK(block_table.stride(0) == block_table.size(1), "block_table rows must be dense");
+  const c10::cuda::CUDAGuard guard(kv_cache.device());
+  check_rc(vxk_cp_gather_indexer_k_quant_cache(kv_cache.data_ptr(), dst_k.data_ptr(), dst_scale.data_ptr(),
+                                               block_table.data_ptr<int32_t>(), cu_seq_lens.data_ptr<int32_t>(), batch,
+                                               block_table.size(1), num_tokens, head_dim, quant_block_size,
+                                               kv_cache.size(1), kv_cache.stride(0), dst_k.stride(0), dst_scale.stride(0),
+                                               cur_stream()),
+           "cp_gather_indexer_k_quant_cache");
+}
+
+// ref: csrc/cache.cpp:1478-1540
+void convert_fp8(Tensor& dst, const Tensor& src, double scale, const std::string& kv_cache_dtype) {
+  TORCH_CHECK(src.is_cuda(), "src must be on a CUDA device");
+  TORCH_CHECK(dst.is_cuda(), "dst must be on a CUDA device");
+  TORCH_CHECK(src.device() == dst.device(), "src and dst must be on the same device");
+  int mode;
+  if (kv_cache_dtype == "auto") mode = 0;
+  else if (kv_cache_dtype == "fp8" || kv_cache_dtype == "fp8_e4m3") mode = 1;
+  else TORCH_CHECK(false, "Unsupported data type: ", kv_cache_dtype);
+  auto kind = [](const Tensor& t) -> int {
+    switch (t.scalar_type()) {
+      case at::kFloat: return VXK_F32;
+      case at::kHalf: return VXK_F16;
+      case at::kBFloat16: return VXK_BF16;
+      default: return t.element_size() == 1 ? 3 : -1;
+    }
+  };
+  const int sk = kind(src), dk = kind(dst);
+  TORCH_CHECK(sk >= 0 && dk >= 0 && ((sk == 3) != (dk == 3)), "Unsupported data type combination for ", kv_cache_dtype,
+              " convert_fp8");
+  TORCH_CHECK(src.numel() == dst.numel(), "src and dst must have the same number of elements");
+  TORCH_CHECK(src.is_contiguous() && dst.is_contiguous(), "src and dst must be contiguous");
+  const c10::cuda::CUDAGuard guard(src.device());
+  check_rc(vxk_convert_fp8(dst.data_ptr(), src.data_ptr(), scale, src.numel(), sk, dk, mode, cur_stream()), "convert_fp8");
+}
+
 }  // namespace
 
 // Schemas verbatim from /root/reference/csrc/torch_bindings.cpp (line numbers in SURVEY.md 8b).
@@ -738,4 +822,20 @@ TORCH_LIBRARY_IMPL(_xpu_C, CUDA, xpu_ops) {
   xpu_ops.impl("fp8_gemm", &fp8_gemm);
   xpu_ops.impl("fp4_gemm", &fp4_gemm);
   xpu_ops.impl("fp8_gemm_w8a16", &fp8_gemm_w8a16);
+}
+
+// Schemas verbatim from /root/reference/csrc/torch_bindings.cpp:281-284,298-309 (library _C_cache_ops).
+TORCH_LIBRARY_FRAGMENT(_C_cache_ops, cache_ops) {
+  cache_ops.def("convert_fp8(Tensor! dst, Tensor src, "
+                "            float scale, str kv_cache_dtype) -> ()");
+  cache_ops.def("indexer_k_quant_and_cache(Tensor k, Tensor! kv_cache,"
+                "Tensor slot_mapping, int quant_block_size, str scale_fmt) -> ()");
+  cache_ops.def("cp_gather_indexer_k_quant_cache(Tensor kv_cache, Tensor! dst_k, "
+                "Tensor! dst_scale, Tensor block_table, Tensor cu_seq_lens) -> ()");
+}
+
+TORCH_LIBRARY_IMPL(_C_cache_ops, CUDA, cache_ops) {
+  cache_ops.impl("convert_fp8", &convert_fp8);
+  cache_ops.impl("indexer_k_quant_and_cache", &indexer_k_quant_and_cache);
+  cache_ops.impl("cp_gather_indexer_k_quant_cache", &cp_gather_indexer_k_quant_cache);
 }

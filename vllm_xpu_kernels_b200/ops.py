@@ -45,6 +45,19 @@ def fp4_gemm(input, weight, scale_act, scale_wei, out_dtype, bias=None):
     return torch.ops._xpu_C.fp4_gemm(input, weight, scale_act, scale_wei, out_dtype, bias)
 
 
+# ----------------------------------------------------------- cache ops (tests/register_ops.py:226-294)
+def indexer_k_quant_and_cache(k, kv_cache, slot_mapping, quant_block_size: int, scale_fmt: str) -> None:
+    torch.ops._C_cache_ops.indexer_k_quant_and_cache(k, kv_cache, slot_mapping, quant_block_size, scale_fmt)
+
+
+def cp_gather_indexer_k_quant_cache(kv_cache, dst_k, dst_scale, block_table, cu_seq_lens) -> None:
+    torch.ops._C_cache_ops.cp_gather_indexer_k_quant_cache(kv_cache, dst_k, dst_scale, block_table, cu_seq_lens)
+
+
+def convert_fp8(dst_cache, src_cache, scale: float, kv_dtype: str = "fp8") -> None:
+    torch.ops._C_cache_ops.convert_fp8(dst_cache, src_cache, scale, kv_dtype)
+
+
 # ------------------------------------------------- allocation helpers (tests/ops)
 def scaled_fp8_quant(
     input: torch.Tensor,
