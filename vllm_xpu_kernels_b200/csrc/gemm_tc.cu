@@ -2,6 +2,7 @@
 // canonicalisation, launch of the tcgen05 kernels (gemm_tc.cuh) or of the CUDA-core
 // fallback (gemm_fallback.cu), and the two C-ABI entry points.
 #include "gemm_tc2_blk.cuh"
+#include "gemm_tc2_blk4.cuh"
 #include "gemm_skinny.cuh"
 
 
@@ -145,10 +146,10 @@ static SfPack sf_pack_plan(int64_t M, int64_t N, int64_t K_elems, bool fp4) {
   return s;
 }
 
-static int max_cluster_pairs(const void* kernel, int smem_bytes) {
+static int max_cluster_pairs(const void* kernel, int smem_bytes, int threads = kTc2Threads) {
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = dim3(2 * sm_count());
-  cfg.blockDim = dim3(kTc2Threads);
+  cfg.blockDim = dim3(threads);
   cfg.dynamicSmemBytes = smem_bytes;
   cudaLaunchAttribute attr{};
   attr.id = cudaLaunchAttributeClusterDimension;
@@ -224,6 +225,28 @@ static int launch_tc2_blk(Tc2BlkParams tp, const CUtensorMap& ma, const CUtensor
   kernel<<<grid, kTc2Threads, L::kTotalBytes, st>>>(tp, ma, mb);
   g_gemm_tc_calls.fetch_add(1, std::memory_order_relaxed);
   return check_launch("gemm_tc2_blk");
+}
+
+static int launch_tc2_blk4(Tc2BlkParams tp, const CUtensorMap& ma, const CUtensorMap& mb, cudaStream_t st) {
+  using L = Blk4Smem;
+  auto kernel = gemm_tc2_blk4_kernel;
+  static PerDeviceOnce once;
+  const PerDeviceOnce::Entry cfg_once = once.get([&](PerDeviceOnce::Entry& x) {
+    x.err = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotalBytes);
+    if (x.err == cudaSuccess)
+      x.aux = max_cluster_pairs(reinterpret_cast<const void*>(kernel), L::kTotalBytes, kBlk4Threads);
+  });
+  const int pairs = cfg_once.aux;
+  if (cfg_once.err != cudaSuccess)
+    return fail(VXK_ERR_CUDA, "cudaFuncSetAttribute(smem=%d): %s", L::kTotalBytes, cudaGetErrorString(cfg_once.err));
+  static const int group_m = env_int("VXK_GEMM_GROUP_M", 16);
+  tp.b.debug = 0;
+  tp.group_m = group_m < 1 ? 1 : group_m;
+  const int tiles = tp.num_m_pairs * tp.num_n_blocks;
+  const int grid = 2 * (tiles < pairs ? tiles : pairs);
+  kernel<<<grid, kBlk4Threads, L::kTotalBytes, st>>>(tp, ma, mb);
+  g_gemm_tc_calls.fetch_add(1, std::memory_order_relaxed);
+  return check_launch("gemm_tc2_blk4");
 }
 
 // Two W tiles per K loop (NACC = 2) cut the L2 bytes per flop by a quarter but quantise the
@@ -531,6 +554,21 @@ extern "C" int vxk_fp8_gemm(void* D, const void* A, const void* B, const void* a
   if (operands_ok && a_scale_mode == 2 && scale_dtype == VXK_S_F32 && group_k % 128 == 0 && group_n % 32 == 0 &&
       K % group_k == 0) {
     // fp32 block scales: two-level accumulation (tensor core per K slice, CUDA cores across slices)
+    static const int blk_gen = env_int("VXK_BLK_GEN", 4);
+    if (blk_gen == 4) {
+      Tc2BlkParams t4{};
+      t4.b = tp;
+      t4.sa = static_cast<const float*>(a_scale);
+      t4.sb = static_cast<const float*>(b_scale);
+      t4.sa0 = sa0; t4.sa1 = sa1; t4.sb0 = sb0; t4.sb1 = sb1;
+      t4.group_k_blocks = (int)(group_k / 128);
+      t4.group_n = (int)group_n;
+      t4.num_m_pairs = (int)((M + 255) / 256);
+      t4.num_n_blocks = (int)((N + kBlk4N - 1) / kBlk4N);
+      if ((rc = make_map_2d_u8(&ma, A, K, M, lda, kBlockKBytes, kBlockM, true))) return rc;
+      if ((rc = make_map_2d_u8(&mb, B, K, N, b_stride_n, kBlockKBytes, kBlk4N / 2, true))) return rc;
+      return launch_tc2_blk4(t4, ma, mb, st);
+    }
     constexpr int BN = 192;
     Tc2BlkParams t2{};
     t2.b = tp;

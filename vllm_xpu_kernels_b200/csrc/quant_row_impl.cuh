@@ -206,6 +206,10 @@ __global__ void __launch_bounds__(512) row_quant_kernel(const RowParams p, const
   const bool sat = p.scale_in != nullptr;
   const int nvec = p.nvec;
   int slot = 0;
+  // Programmatic dependent launch: the next kernel in the stream may be scheduled as soon as this one's
+  // CTAs retire (its launch latency and index set-up overlap our tail); our own global accesses -- inputs
+  // AND outputs, which the previous kernel may still be reading -- start only after griddepcontrol.wait.
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
   if (tid < 64) {
     scratch[tid >> 5][tid & 31] = 0.0f;
     if constexpr (RMS) scratch64[tid >> 5][tid & 31] = 0.0;
@@ -231,6 +235,23 @@ __global__ void __launch_bounds__(512) row_quant_kernel(const RowParams p, const
 #pragma unroll
   for (int i = 0; i < VPT; ++i) ok[i] = FULL || (vidx[i] < nvec);
 
+  // per-thread element offsets of its vectors and row pointers that advance by a constant:
+  // no per-row 64-bit address arithmetic in the loop
+  int voff[VPT];
+#pragma unroll
+  for (int i = 0; i < VPT; ++i) voff[i] = vidx[i] * kVec;
+  const int64_t in_step = static_cast<int64_t>(gridDim.x) * p.in_row_stride;
+  const int64_t out_step = static_cast<int64_t>(gridDim.x) * (MODE == MODE_MXFP4 ? p.H / 2 : p.H);
+  const T* __restrict__ xnext = static_cast<const T*>(p.in) + static_cast<int64_t>(blockIdx.x) * p.in_row_stride;
+  uint8_t* orow = static_cast<uint8_t*>(p.out) + static_cast<int64_t>(blockIdx.x) * (MODE == MODE_MXFP4 ? p.H / 2 : p.H);
+
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+  // first row: requested before the weight staging below so that its HBM latency overlaps it
+  Raw8<T> raw[VPT];
+#pragma unroll
+  for (int i = 0; i < VPT; ++i)
+    raw[i] = (static_cast<int64_t>(blockIdx.x) < T_rows && ok[i]) ? load_raw<T, true>(xnext + voff[i]) : Raw8<T>{};
+
   // rms weight, staged once per CTA as fp32 in THREAD order: slot i * nthr + tid holds the weight
   // vector this thread multiplies its i-th vector with (two planes: elements 0-3 / 4-7), so the
   // per-row reads are conflict-free 128-bit loads whatever the vector-to-thread mapping is
@@ -245,21 +266,6 @@ __global__ void __launch_bounds__(512) row_quant_kernel(const RowParams p, const
     }
     __syncthreads();
   }
-
-  // per-thread element offsets of its vectors and row pointers that advance by a constant:
-  // no per-row 64-bit address arithmetic in the loop
-  int voff[VPT];
-#pragma unroll
-  for (int i = 0; i < VPT; ++i) voff[i] = vidx[i] * kVec;
-  const int64_t in_step = static_cast<int64_t>(gridDim.x) * p.in_row_stride;
-  const int64_t out_step = static_cast<int64_t>(gridDim.x) * (MODE == MODE_MXFP4 ? p.H / 2 : p.H);
-  const T* __restrict__ xnext = static_cast<const T*>(p.in) + static_cast<int64_t>(blockIdx.x) * p.in_row_stride;
-  uint8_t* orow = static_cast<uint8_t*>(p.out) + static_cast<int64_t>(blockIdx.x) * (MODE == MODE_MXFP4 ? p.H / 2 : p.H);
-
-  Raw8<T> raw[VPT];
-#pragma unroll
-  for (int i = 0; i < VPT; ++i)
-    raw[i] = (static_cast<int64_t>(blockIdx.x) < T_rows && ok[i]) ? load_raw<T, true>(xnext + voff[i]) : Raw8<T>{};
 
   for (int64_t row = blockIdx.x; row < T_rows; row += gridDim.x, orow += out_step) {
     float v[VPT][8];
@@ -585,7 +591,18 @@ inline int launch_row_vpt3(const RowParams& p, int64_t T_rows, int threads, cuda
   }
   const int64_t cap = static_cast<int64_t>(per_sm) * sm_count();
   const unsigned grid = static_cast<unsigned>(T_rows < cap ? T_rows : cap);
-  kernel<<<grid, threads, smem, st>>>(p, T_rows);
+  static const int pdl = [] { const char* e = getenv("VXK_ROW_PDL"); return e ? atoi(e) : 1; }();
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(static_cast<unsigned>(threads));
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr{};
+  attr.id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr.val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = &attr;
+  cfg.numAttrs = pdl ? 1 : 0;
+  cudaLaunchKernelEx(&cfg, kernel, p, T_rows);
   return 0;
 }
 template <typename T, int Q, int MODE, bool RMS, bool HAS_RES, int VPT, int VG>
@@ -622,14 +639,17 @@ int launch_row(const RowParams& p_in, int64_t T_rows, bool vec_ok, cudaStream_t 
   while (p.group > 0 && (kVec << p.gv_log2) < p.group) ++p.gv_log2;
   if (T_rows == 0 || p.H == 0) return VXK_OK;
   const int nvec = p.nvec;
-  // per-thread vectors: enough to keep one warp busy, 4 by default (two register
-  // copies of the row are live: current + prefetched), more only for long rows
+  // per-thread vectors: enough to keep one warp busy; two register copies of the row are live (current +
+  // prefetched).  rms kernels take 8 (the per-row scalar work -- reductions, 1/sqrt, scale arithmetic -- is paid
+  // per WARP, so fewer, fatter warps per row cut the instruction count: measured 45.9 -> 38.6 us at 8192 x 8192,
+  // profiles/r02_row_vpt_sweep.txt; 16 vectors per thread fill the register file and measured slower), the plain
+  // per-token kernel 4 (no difference there)
   constexpr int kMaxVpt = 8;
   static const int env_vpt = [] { const char* e = getenv("VXK_ROW_VPT"); return e ? atoi(e) : 0; }();
-  const int want = env_vpt > 0 ? env_vpt : 4;
+  const int want = env_vpt > 0 ? env_vpt : ((RMS && sizeof(T) == 2) ? 8 : 4);
   int vpt = 1;
-  while (vpt < want && nvec > 32 * vpt) vpt *= 2;
-  while ((nvec + vpt - 1) / vpt > 256 && vpt < kMaxVpt) vpt *= 2;  // long rows: up to 8 x 512 threads
+  while (vpt < want && vpt < kMaxVpt && nvec > 32 * vpt) vpt *= 2;
+  while ((nvec + vpt - 1) / vpt > 256 && vpt < 8) vpt *= 2;  // long rows: up to 8 x 512 threads
   if (vpt > kMaxVpt) vpt = kMaxVpt;
   const int threads = ((nvec + vpt - 1) / vpt + 31) / 32 * 32;
   // group modes: runs of vg vectors of one group per thread, 2^lanes_log2 adjacent lanes per group
