@@ -21,7 +21,7 @@
 extern "C" {
 #endif
 
-#define VXK_ABI_VERSION 4
+#define VXK_ABI_VERSION 5
 
 typedef struct CUstream_st* vxk_stream_t; /* == cudaStream_t */
 
@@ -229,6 +229,46 @@ int vxk_fp4_gemm_allgather(void* const* peer_out, int n_peers, int self_rank, in
  * it the call still runs, on the single-CTA kernel.
  * ref: the per-call scratchpad of fp4_gemm_w4a4.h:159-162. */
 int64_t vxk_fp4_gemm_workspace_bytes(int64_t M, int64_t N, int64_t K);
+
+/* ------------------------------------------------------- (f) next #2 ---
+ * MX scale factors in the tensor core's own layout ("packed": the 512-byte chunks that
+ * tcgen05.cp.32x128b.warpx4 copies into TMEM, DESIGN.md "Scale-factor layouts").  The reference has no
+ * counterpart: oneDNN re-orders scales inside the primitive on every call (fp4_gemm_w4a4.h:159-167,
+ * scratchpad); here the re-ordering can leave the hot path altogether --
+ *   weights:      vxk_mx_sf_pack once after loading, pass the result as b_scale_packed;
+ *   activations:  the *_sf variants of the MXFP4 quantisation kernels (a5 / a8 / a12) write the packed
+ *                 bytes themselves, next to the fp32 scales the reference API returns.
+ *   kind: 0 = FP8 with E8M0 block scales (K slices of 128), 1 = MXFP4 (K slices of 256)
+ *   operand: 0 = activations (rows = M), 1 = weights (rows = N)
+ * A packed buffer is device memory, 16-byte aligned, vxk_mx_sf_packed_bytes long.  When K is not a
+ * multiple of the K slice the caller zero-fills it before a *_sf quantisation kernel writes into it
+ * (the kernels only write real groups; vxk_mx_sf_pack writes every byte). */
+int64_t vxk_mx_sf_packed_bytes(int64_t rows, int64_t K, int kind, int operand);
+/* src: E8M0 bytes of (row r, 32-element K group g) at src[r*s_row + g*s_k]. */
+int vxk_mx_sf_pack(void* dst, const void* src, int64_t rows, int64_t K, int64_t s_row, int64_t s_k,
+                   int kind, int operand, vxk_stream_t stream);
+/* vxk_fp4_gemm with optional packed copies of either scale grid (nullable; the natural-layout
+ * pointers stay mandatory: small-M calls and the fallback read those).  With both packed copies no
+ * workspace is needed and the call issues no re-packing launch. */
+int vxk_fp4_gemm_sf(void* D, const void* A, const void* B, const void* a_scale, const void* b_scale,
+                    const void* a_scale_packed, const void* b_scale_packed, const void* bias,
+                    int64_t M, int64_t N, int64_t K, int64_t lda_bytes, int64_t ldb_bytes, int64_t ldd,
+                    int64_t sa0, int64_t sa1, int64_t sb0, int64_t sb1, int out_dtype, int bias_dtype,
+                    void* workspace, int64_t workspace_bytes, vxk_stream_t stream);
+/* a5 / a8 / a12 with the extra packed output (sf_packed nullable = the plain op; kind 1, operand 0,
+ * rows = T, K = H). */
+int vxk_per_token_group_quant_mxfp4_sf(const void* in, void* out_q, float* out_s, void* sf_packed,
+                                       int64_t T, int64_t H, int64_t group_size, double eps,
+                                       int64_t ss0, int64_t ss1, int in_dtype, vxk_stream_t stream);
+int vxk_rms_norm_mxfp4_quant_sf(void* out, const void* in, const void* weight, float* scales,
+                                void* sf_packed, double epsilon, void* residual, int64_t T, int64_t H,
+                                int64_t group_size, int64_t ss0, int64_t ss1, int in_dtype,
+                                vxk_stream_t stream);
+int vxk_silu_and_mul_mxfp4_quant_sf(void* out, const void* in, float* scales, void* sf_packed,
+                                    int64_t T, int64_t H, int64_t group_size, double eps, int64_t ss0,
+                                    int64_t ss1, int in_dtype, vxk_stream_t stream);
+/* Scale re-packing launches issued so far by the GEMM entry points (testing aid). */
+uint64_t vxk_sf_pack_launches(void);
 
 /* ------------------------------------------------------- (f) next #1 ---
  * ref: fp8_gemm_w8a16  csrc/xpu/onednn/onednn_matmul.cpp:81-99 -> dnnl_matmul_w8a16_fp8

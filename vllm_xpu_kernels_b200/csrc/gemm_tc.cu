@@ -2,7 +2,6 @@
 // canonicalisation, launch of the tcgen05 kernels (gemm_tc.cuh) or of the CUDA-core
 // fallback (gemm_fallback.cu), and the two C-ABI entry points.
 #include "gemm_tc2_blk.cuh"
-#include "gemm_tc2_blk4.cuh"
 #include "gemm_skinny.cuh"
 
 
@@ -130,6 +129,8 @@ __global__ void sf_pack_kernel(uint32_t* out, int64_t rows, int64_t groups32, in
   }
 }
 
+static std::atomic<uint64_t> g_sf_pack_calls{0};   // scale re-packing launches (tests: the packed entry points issue none)
+
 struct SfPack {
   int num_kb, sf_words, a_blocks, b_blocks;
   int64_t a_bytes, b_bytes;
@@ -227,28 +228,6 @@ static int launch_tc2_blk(Tc2BlkParams tp, const CUtensorMap& ma, const CUtensor
   return check_launch("gemm_tc2_blk");
 }
 
-static int launch_tc2_blk4(Tc2BlkParams tp, const CUtensorMap& ma, const CUtensorMap& mb, cudaStream_t st) {
-  using L = Blk4Smem;
-  auto kernel = gemm_tc2_blk4_kernel;
-  static PerDeviceOnce once;
-  const PerDeviceOnce::Entry cfg_once = once.get([&](PerDeviceOnce::Entry& x) {
-    x.err = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotalBytes);
-    if (x.err == cudaSuccess)
-      x.aux = max_cluster_pairs(reinterpret_cast<const void*>(kernel), L::kTotalBytes, kBlk4Threads);
-  });
-  const int pairs = cfg_once.aux;
-  if (cfg_once.err != cudaSuccess)
-    return fail(VXK_ERR_CUDA, "cudaFuncSetAttribute(smem=%d): %s", L::kTotalBytes, cudaGetErrorString(cfg_once.err));
-  static const int group_m = env_int("VXK_GEMM_GROUP_M", 16);
-  tp.b.debug = 0;
-  tp.group_m = group_m < 1 ? 1 : group_m;
-  const int tiles = tp.num_m_pairs * tp.num_n_blocks;
-  const int grid = 2 * (tiles < pairs ? tiles : pairs);
-  kernel<<<grid, kBlk4Threads, L::kTotalBytes, st>>>(tp, ma, mb);
-  g_gemm_tc_calls.fetch_add(1, std::memory_order_relaxed);
-  return check_launch("gemm_tc2_blk4");
-}
-
 // Two W tiles per K loop (NACC = 2) cut the L2 bytes per flop by a quarter but quantise the
 // work into tiles twice as large and expose part of the epilogue: take them when the last
 // wave of super-tiles is not much emptier than the last wave of single tiles.
@@ -333,24 +312,32 @@ static int run_pair_block_scaled(Tc2Params tp, const void* A, int64_t lda_bytes,
                                  int64_t M, int64_t N, int64_t K_elems, const uint8_t* a_scale, int64_t a_row_stride,
                                  int64_t a_kps, int64_t a_k_stride, const uint8_t* b_scale, int64_t b_row_div,
                                  int64_t b_row_stride, int64_t b_kps, int64_t b_k_stride, void* workspace,
-                                 cudaStream_t st) {
+                                 cudaStream_t st, const void* a_packed = nullptr, const void* b_packed = nullptr) {
   constexpr bool fp4 = KIND == KIND_MXF4;
   constexpr int BN = 192;
   const SfPack sp = sf_pack_plan(M, N, K_elems, fp4);
   uint8_t* ws = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(workspace) + 255) & ~uintptr_t(255));
-  uint32_t* sfa = reinterpret_cast<uint32_t*>(ws);
-  uint32_t* sfb = reinterpret_cast<uint32_t*>(ws + sp.a_bytes);
+  // a_packed / b_packed: the caller already holds that grid in tcgen05.cp order (vxk_mx_sf_pack, or written by
+  // the quantisation kernel that produced the operand): no re-packing launch for it
+  const uint32_t* sfa = a_packed ? static_cast<const uint32_t*>(a_packed) : reinterpret_cast<uint32_t*>(ws);
+  const uint32_t* sfb = b_packed ? static_cast<const uint32_t*>(b_packed) : reinterpret_cast<uint32_t*>(ws + sp.a_bytes);
   const int64_t groups32 = (K_elems + 31) / 32;
   const int blocks = 8 * sm_count();
   const int a_words = a_kps == 1 && a_k_stride == 1 && a_row_stride % 4 == 0 && reinterpret_cast<uintptr_t>(a_scale) % 4 == 0;
   const int b_words = b_kps == 1 && b_k_stride == 1 && b_row_stride % 4 == 0 && reinterpret_cast<uintptr_t>(b_scale) % 4 == 0;
   int rc;
-  sf_pack_kernel<<<blocks, 256, 0, st>>>(sfa, M, groups32, sp.num_kb, sp.a_blocks, sp.sf_words, a_scale, 1,
-                                         a_row_stride, a_kps, a_k_stride, a_words);
-  if ((rc = check_launch("sf_pack_a"))) return rc;
-  sf_pack_kernel<<<blocks, 256, 0, st>>>(sfb, N, groups32, sp.num_kb, sp.b_blocks, sp.sf_words, b_scale, b_row_div,
-                                         b_row_stride, b_kps, b_k_stride, b_words);
-  if ((rc = check_launch("sf_pack_b"))) return rc;
+  if (!a_packed) {
+    sf_pack_kernel<<<blocks, 256, 0, st>>>(const_cast<uint32_t*>(sfa), M, groups32, sp.num_kb, sp.a_blocks, sp.sf_words,
+                                           a_scale, 1, a_row_stride, a_kps, a_k_stride, a_words);
+    if ((rc = check_launch("sf_pack_a"))) return rc;
+    g_sf_pack_calls.fetch_add(1, std::memory_order_relaxed);
+  }
+  if (!b_packed) {
+    sf_pack_kernel<<<blocks, 256, 0, st>>>(const_cast<uint32_t*>(sfb), N, groups32, sp.num_kb, sp.b_blocks, sp.sf_words,
+                                           b_scale, b_row_div, b_row_stride, b_kps, b_k_stride, b_words);
+    if ((rc = check_launch("sf_pack_b"))) return rc;
+    g_sf_pack_calls.fetch_add(1, std::memory_order_relaxed);
+  }
   const bool two = prefer_two_acc(M, N, fp4 ? K_elems / 2 : K_elems, BN);
   const int tile_n = two ? 2 * BN : BN;
   tp.num_m_pairs = static_cast<int>((M + 255) / 256);
@@ -554,21 +541,7 @@ extern "C" int vxk_fp8_gemm(void* D, const void* A, const void* B, const void* a
   if (operands_ok && a_scale_mode == 2 && scale_dtype == VXK_S_F32 && group_k % 128 == 0 && group_n % 32 == 0 &&
       K % group_k == 0) {
     // fp32 block scales: two-level accumulation (tensor core per K slice, CUDA cores across slices)
-    static const int blk_gen = env_int("VXK_BLK_GEN", 4);
-    if (blk_gen == 4) {
-      Tc2BlkParams t4{};
-      t4.b = tp;
-      t4.sa = static_cast<const float*>(a_scale);
-      t4.sb = static_cast<const float*>(b_scale);
-      t4.sa0 = sa0; t4.sa1 = sa1; t4.sb0 = sb0; t4.sb1 = sb1;
-      t4.group_k_blocks = (int)(group_k / 128);
-      t4.group_n = (int)group_n;
-      t4.num_m_pairs = (int)((M + 255) / 256);
-      t4.num_n_blocks = (int)((N + kBlk4N - 1) / kBlk4N);
-      if ((rc = make_map_2d_u8(&ma, A, K, M, lda, kBlockKBytes, kBlockM, true))) return rc;
-      if ((rc = make_map_2d_u8(&mb, B, K, N, b_stride_n, kBlockKBytes, kBlk4N / 2, true))) return rc;
-      return launch_tc2_blk4(t4, ma, mb, st);
-    }
+    static const int blk_pipe = env_int("VXK_BLK_PIPE", 1);
     constexpr int BN = 192;
     Tc2BlkParams t2{};
     t2.b = tp;
@@ -581,7 +554,6 @@ extern "C" int vxk_fp8_gemm(void* D, const void* A, const void* B, const void* a
     t2.num_n_blocks = (int)((N + BN - 1) / BN);
     if ((rc = make_map_2d_u8(&ma, A, K, M, lda, kBlockKBytes, kBlockM, true))) return rc;
     if ((rc = make_map_2d_u8(&mb, B, K, N, b_stride_n, kBlockKBytes, BN / 2, true))) return rc;
-    static const int blk_pipe = env_int("VXK_BLK_PIPE", 1);
     return blk_pipe ? launch_tc2_blk<BN, true>(t2, ma, mb, st) : launch_tc2_blk<BN, false>(t2, ma, mb, st);
   }
   if (operands_ok && a_scale_mode == 2 && scale_dtype == VXK_S_E8M0 && group_k % 32 == 0 && workspace &&
@@ -647,11 +619,36 @@ extern "C" int vxk_fp8_gemm_allgather(void* const* peer_out, int n_peers, int se
   return rc;
 }
 
-extern "C" int vxk_fp4_gemm(void* D, const void* A, const void* B, const void* a_scale, const void* b_scale,
-                            const void* bias, int64_t M, int64_t N, int64_t K, int64_t lda_bytes, int64_t ldb_bytes,
-                            int64_t ldd, int64_t sa0, int64_t sa1, int64_t sb0, int64_t sb1, int out_dtype,
-                            int bias_dtype, void* workspace, int64_t workspace_bytes, vxk_stream_t stream) {
+extern "C" int64_t vxk_mx_sf_packed_bytes(int64_t rows, int64_t K, int kind, int operand) {
+  if (rows < 0 || K < 0 || (kind != 0 && kind != 1) || (operand != 0 && operand != 1)) return -1;
+  const SfPack sp = operand == 0 ? sf_pack_plan(rows, 0, K, kind == 1) : sf_pack_plan(0, rows, K, kind == 1);
+  return operand == 0 ? sp.a_bytes : sp.b_bytes;
+}
+
+extern "C" int vxk_mx_sf_pack(void* dst, const void* src, int64_t rows, int64_t K, int64_t s_row, int64_t s_k,
+                              int kind, int operand, vxk_stream_t stream) {
+  VXK_REQUIRE(dst && src, "null pointer");
+  VXK_REQUIRE(rows >= 0 && K >= 0 && K % 32 == 0, "rows >= 0 and K a multiple of 32");
+  VXK_REQUIRE((kind == 0 || kind == 1) && (operand == 0 || operand == 1), "kind / operand must be 0 or 1");
+  VXK_REQUIRE(reinterpret_cast<uintptr_t>(dst) % 16 == 0, "packed scale buffer must be 16-byte aligned");
+  const SfPack sp = operand == 0 ? sf_pack_plan(rows, 0, K, kind == 1) : sf_pack_plan(0, rows, K, kind == 1);
+  const int nblk = operand == 0 ? sp.a_blocks : sp.b_blocks;
+  const int words = s_k == 1 && s_row % 4 == 0 && reinterpret_cast<uintptr_t>(src) % 4 == 0;
+  sf_pack_kernel<<<8 * sm_count(), 256, 0, stream>>>(static_cast<uint32_t*>(dst), rows, K / 32, sp.num_kb, nblk,
+                                                     sp.sf_words, static_cast<const uint8_t*>(src), 1, s_row, 1, s_k, words);
+  return check_launch("mx_sf_pack");
+}
+
+extern "C" uint64_t vxk_sf_pack_launches(void) { return g_sf_pack_calls.load(std::memory_order_relaxed); }
+
+static int fp4_gemm_impl(void* D, const void* A, const void* B, const void* a_scale, const void* b_scale,
+                         const void* bias, int64_t M, int64_t N, int64_t K, int64_t lda_bytes, int64_t ldb_bytes,
+                         int64_t ldd, int64_t sa0, int64_t sa1, int64_t sb0, int64_t sb1, int out_dtype,
+                         int bias_dtype, void* workspace, int64_t workspace_bytes, vxk_stream_t stream,
+                         const void* a_packed, const void* b_packed) {
   VXK_REQUIRE(M >= 0 && N >= 0 && K >= 0, "negative shape");
+  VXK_REQUIRE(reinterpret_cast<uintptr_t>(a_packed) % 16 == 0 && reinterpret_cast<uintptr_t>(b_packed) % 16 == 0,
+              "packed scale buffers must be 16-byte aligned");
   VXK_REQUIRE(K % 32 == 0, "K must be a multiple of the MX block (32)");
   VXK_REQUIRE(out_dtype == VXK_BF16 || out_dtype == VXK_F16, "output must be bf16 or f16");
   VXK_REQUIRE(a_scale && b_scale, "scale pointers must not be null");
@@ -681,13 +678,14 @@ extern "C" int vxk_fp4_gemm(void* D, const void* A, const void* B, const void* a
   tp.num_k_blocks = (int)((K / 2 + kBlockKBytes - 1) / kBlockKBytes);
   tp.vec_store_ok = aligned16(D) && (ldd * 2) % 16 == 0;
   for (int i = 0; i < peers.n; ++i) tp.vec_store_ok = tp.vec_store_ok && aligned16(peers.ptr[i]);
-  if (!force_single() && (prefer_pair(M, N, bn, 192) || peers.n > 0) && workspace &&
-      workspace_bytes >= vxk_fp4_gemm_workspace_bytes(M, N, K)) {
+  const bool ws_ok = (a_packed && b_packed) || (workspace && workspace_bytes >= vxk_fp4_gemm_workspace_bytes(M, N, K));
+  if (!force_single() && (prefer_pair(M, N, bn, 192) || peers.n > 0) && ws_ok) {
     Tc2Params t2{};
     t2.b = tp;
     return run_pair_block_scaled<KIND_MXF4>(t2, A, lda_bytes, B, ldb_bytes, M, N, K,
                                             static_cast<const uint8_t*>(a_scale), sa0, 1, sa1,
-                                            static_cast<const uint8_t*>(b_scale), 1, sb0, 1, sb1, workspace, st);
+                                            static_cast<const uint8_t*>(b_scale), 1, sb0, 1, sb1, workspace, st,
+                                            a_packed, b_packed);
   }
   CUtensorMap ma, mb, msa, msb;
   int rc;
@@ -712,6 +710,23 @@ extern "C" int vxk_fp4_gemm(void* D, const void* A, const void* B, const void* a
   if ((rc = make_map_2d_u8(&msa, sfa, scales_direct ? K / 32 : pa, M, pa, 16, kBlockM, false))) return rc;
   if ((rc = make_map_2d_u8(&msb, sfb, scales_direct ? K / 32 : pb, N, pb, 16, bn, false))) return rc;
   return launch_tc_bn<KIND_MXF4>(bn, tp, ma, mb, msa, msb, st);
+}
+
+extern "C" int vxk_fp4_gemm(void* D, const void* A, const void* B, const void* a_scale, const void* b_scale,
+                            const void* bias, int64_t M, int64_t N, int64_t K, int64_t lda_bytes, int64_t ldb_bytes,
+                            int64_t ldd, int64_t sa0, int64_t sa1, int64_t sb0, int64_t sb1, int out_dtype,
+                            int bias_dtype, void* workspace, int64_t workspace_bytes, vxk_stream_t stream) {
+  return fp4_gemm_impl(D, A, B, a_scale, b_scale, bias, M, N, K, lda_bytes, ldb_bytes, ldd, sa0, sa1, sb0, sb1,
+                       out_dtype, bias_dtype, workspace, workspace_bytes, stream, nullptr, nullptr);
+}
+
+extern "C" int vxk_fp4_gemm_sf(void* D, const void* A, const void* B, const void* a_scale, const void* b_scale,
+                               const void* a_scale_packed, const void* b_scale_packed, const void* bias, int64_t M,
+                               int64_t N, int64_t K, int64_t lda_bytes, int64_t ldb_bytes, int64_t ldd, int64_t sa0,
+                               int64_t sa1, int64_t sb0, int64_t sb1, int out_dtype, int bias_dtype, void* workspace,
+                               int64_t workspace_bytes, vxk_stream_t stream) {
+  return fp4_gemm_impl(D, A, B, a_scale, b_scale, bias, M, N, K, lda_bytes, ldb_bytes, ldd, sa0, sa1, sb0, sb1,
+                       out_dtype, bias_dtype, workspace, workspace_bytes, stream, a_scale_packed, b_scale_packed);
 }
 
 extern "C" int vxk_fp4_gemm_allgather(void* const* peer_out, int n_peers, int self_rank, int64_t col_offset,

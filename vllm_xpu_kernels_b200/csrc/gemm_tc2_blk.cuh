@@ -12,11 +12,21 @@
 // chunk overlap the load of the next), hand the buffer back as soon as its last chunk has landed,
 // and fold it into their accumulators (96 columns per thread, packed fp32x2 FMAs).  The promotion
 // warps take 224 registers (setmaxnreg), the role warps give theirs up.
-// What bounds it (clock64 stamps per slice, round 1d): not TMEM bandwidth (tcgen05.ld 32x32b.x32
-// drains >= 340 B/clk/SM with 8 warps, scratch/tmem_bw.cu) and not the FMAs, but the LATENCY of the
-// hand-over loop  MMA retires -> commit -> promotion warps -> tcgen05.ld -> 16 arrivals (two CTAs)
-// -> MMA warp -> issue: ~1500 clk per buffer round trip against 384 clk of tensor work per slice.
-// A 4 x 128-column variant (more units in flight, more hand-overs) measured slower.
+// What bounds it (round 2, profiles/r02_blk_analysis.txt).  Per K slice and CTA pair at 8192 x 36864 x 7168:
+//   m  = 344 ns  MMA side alone (promotion warps hand every buffer straight back, VXK_GEMM_DEBUG=16): the L2 -> SM
+//                operand stream of a 256 x 192 tile, not the tensor pipe (278 ns at the measured FP8 peak)
+//   d  = 255 ns  draining 96 KB per CTA through tcgen05.ld: 223 B/clk/SM measured WITH the tensor pipe busy
+//                (253 idle, benchmarks/tmem_contention.cu) -- the full-rate FP8 MMA needs 256 B/clk/SM, so this
+//                algorithm can never pass ~85 % of the tensor peak on sm_100
+//   h  = 335 ns  the two hand-overs (commit -> mbarrier -> promotion warps, and sixteen arrivals across the
+//                pair -> MMA warp -> issue -> first MMA)
+// With two TMEM buffers every buffer goes round the loop MMA -> hand-over -> drain -> hand-over, so the period
+// per slice is (m + d + h) / 2 = 467 ns -- exactly what the kernel measures (1995 TFLOP/s, 0.60 of the FP8 peak).
+// More buffers would take h off the critical path, but the TMEM has 512 columns: four 128-column buffers
+// (256 x 128 tiles) were built and measured at 1200-1420 TFLOP/s (eight or sixteen promotion warps, register
+// double buffer) -- the 128-wide tile's MMA side alone reaches only 1515 TFLOP/s; 256-wide tiles leave no
+// registers for the staging buffers (128 accumulators per thread: 700 B of spills, 1860 TFLOP/s with 16-column
+// chunks).  192 x 2 is the measured optimum of this design space.
 // ref: fp8_gemm_w8a8.h:28-41,86-134 (block scale shapes), tests/test_fp8_gemm_onednn.py:270-358.
 #pragma once
 
@@ -140,8 +150,11 @@ gemm_tc2_blk_kernel(const Tc2BlkParams pp, const __grid_constant__ CUtensorMap m
     const int q = e & 3;                    // TMEM lane quarter
     const int h = e >> 2;                   // column half of the tile
     constexpr int kCols = BLOCK_N / 2;      // columns per thread
-    constexpr int kChunks = kCols / 32;
+    constexpr int CW = 32;                  // tcgen05.ld chunk (columns)
+    constexpr int kChunks = kCols / CW;
+    constexpr int kSc = kCols / 32;         // 32-column scale blocks per thread
     static_assert(kCols % 32 == 0, "column halves must be whole 32-column chunks");
+    const bool dbg_idle = p.debug & 16;     // timing experiment: hand every buffer straight back, no promotion
     const int row_in_tile = static_cast<int>(rank) * kBlockM + q * 32 + lane;
     // fused all-gather: needs 16-byte aligned output rows and N % 8 == 0 (else direct peer stores)
     const bool row_copy = p.n_peers > 0 && p.vec_store_ok && p.N % 8 == 0;
@@ -154,9 +167,9 @@ gemm_tc2_blk_kernel(const Tc2BlkParams pp, const __grid_constant__ CUtensorMap m
       const bool row_ok = m < p.M;
       const float* sa_row = pp.sa + static_cast<int64_t>(row_ok ? m : 0) * pp.sa0;
       // scale column groups of this thread's chunks (a 32-column chunk never straddles a group: group_n % 32 == 0)
-      int ng[kChunks];
+      int ng[kSc];
 #pragma unroll
-      for (int c = 0; c < kChunks; ++c) {
+      for (int c = 0; c < kSc; ++c) {
         const int n = n_first + c * 32;
         ng[c] = (n < p.N ? n : 0) / pp.group_n;
       }
@@ -166,17 +179,26 @@ gemm_tc2_blk_kernel(const Tc2BlkParams pp, const __grid_constant__ CUtensorMap m
       // Scales are fetched one slice ahead and kept RAW: the warp issues in order, so forming the
       // product sA * sW right after the loads would stall every slice on an L2 round trip (~600 clk,
       // measured with clock64 stamps); the product is formed when the slice is consumed.
-      struct RawScales { float a; float b[kChunks]; };
+      struct RawScales { float a; float b[kSc]; };
       auto load_scales = [&](int kb, RawScales& s) {
         const int kg = pp.group_k_blocks == 1 ? kb : kb / pp.group_k_blocks;
         s.a = row_ok ? __ldg(sa_row + static_cast<int64_t>(kg) * pp.sa1) : 0.0f;
 #pragma unroll
-        for (int c = 0; c < kChunks; ++c) s.b[c] = __ldg(pp.sb + kg * pp.sb0 + ng[c] * pp.sb1);
+        for (int c = 0; c < kSc; ++c) s.b[c] = __ldg(pp.sb + kg * pp.sb0 + ng[c] * pp.sb1);
       };
       RawScales s_next;
       load_scales(0, s_next);
       const uint32_t t_lane = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + h * kCols;
-      if constexpr (!PIPE) {
+      if (dbg_idle) {
+        for (int kb = 0; kb < KB; ++kb, ++g) {
+          const uint32_t buf = g & 1;
+          mbar_wait(&p_full_bar[buf], (g >> 1) & 1);
+          tc_fence_after();
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive_cluster(&p_empty_bar[buf], 0);
+        }
+      } else if constexpr (!PIPE) {
         // all chunks of a slice at once: shortest hand-back latency, no overlap of ld and FMAs inside the warp
         for (int kb = 0; kb < KB; ++kb, ++g) {
           const uint32_t buf = g & 1;
@@ -205,28 +227,29 @@ gemm_tc2_blk_kernel(const Tc2BlkParams pp, const __grid_constant__ CUtensorMap m
         // tcgen05.ld of the next chunk -- of the next slice after the last one -- is already in flight
         // (two rotating 32-register buffers; tcgen05.wait::ld has no finer granularity than "all").
         // A slice's TMEM buffer goes back to the MMA warp as soon as its last chunk has landed.
-        uint32_t r[2][32];
+        uint32_t r[2][CW];
         mbar_wait(&p_full_bar[g & 1], (g >> 1) & 1);
         tc_fence_after();
-        tmem_ld_32x32b_x32(t_lane + (g & 1) * kAccCols, r[0]);
+        tmem_ld_32x32b<CW>(t_lane + (g & 1) * kAccCols, r[0]);
         auto slice = [&](auto kp_tag, int kb) {
           constexpr int KP = decltype(kp_tag)::value;      // parity of the slice index within the tile
           const uint32_t buf = g & 1;
-          float s[kChunks];
+          float s[kSc];
           asm volatile("" : "+f"(s_next.a));
 #pragma unroll
-          for (int c = 0; c < kChunks; ++c) s[c] = s_next.a * s_next.b[c];
+          for (int c = 0; c < kSc; ++c) s[c] = s_next.a * s_next.b[c];
           const bool more = kb + 1 < KB;
 #pragma unroll
           for (int c = 0; c < kChunks; ++c) {
             constexpr int kOdd = kChunks & 1;              // chunks per slice odd: buffer roles flip every slice
             const int cur = (KP * kOdd + c) & 1;
+            const float sc = s[c * CW / 32];
             tmem_ld_wait();
 #pragma unroll
-            for (int j = 0; j < 32; ++j) asm volatile("" : "+r"(r[cur][j]));   // values are defined from here on
+            for (int j = 0; j < CW; ++j) asm volatile("" : "+r"(r[cur][j]));   // values are defined from here on
             bool issued = false;
             if (c + 1 < kChunks) {
-              tmem_ld_32x32b_x32(t_lane + buf * kAccCols + (c + 1) * 32, r[cur ^ 1]);
+              tmem_ld_32x32b<CW>(t_lane + buf * kAccCols + (c + 1) * CW, r[cur ^ 1]);
               issued = true;
             } else {
               tc_fence_before();
@@ -237,20 +260,19 @@ gemm_tc2_blk_kernel(const Tc2BlkParams pp, const __grid_constant__ CUtensorMap m
                 const uint32_t gn = g + 1;
                 if (__all_sync(0xffffffffu, mbar_try_wait(&p_full_bar[gn & 1], (gn >> 1) & 1))) {
                   tc_fence_after();
-                  tmem_ld_32x32b_x32(t_lane + (gn & 1) * kAccCols, r[cur ^ 1]);
+                  tmem_ld_32x32b<CW>(t_lane + (gn & 1) * kAccCols, r[cur ^ 1]);
                   issued = true;
                 }
               }
             }
 #pragma unroll
-            for (int j = 0; j < 32; j += 2)
-              fma2(acc[c * 32 + j], acc[c * 32 + j + 1], __uint_as_float(r[cur][j]), __uint_as_float(r[cur][j + 1]),
-                   s[c], s[c]);
+            for (int j = 0; j < CW; j += 2)
+              fma2(acc[c * CW + j], acc[c * CW + j + 1], __uint_as_float(r[cur][j]), __uint_as_float(r[cur][j + 1]), sc, sc);
             if (c + 1 == kChunks && more && !issued) {     // next slice was not ready: wait for it now
               const uint32_t gn = g + 1;
               mbar_wait(&p_full_bar[gn & 1], (gn >> 1) & 1);
               tc_fence_after();
-              tmem_ld_32x32b_x32(t_lane + (gn & 1) * kAccCols, r[cur ^ 1]);
+              tmem_ld_32x32b<CW>(t_lane + (gn & 1) * kAccCols, r[cur ^ 1]);
             }
           }
           ++g;
@@ -264,7 +286,7 @@ gemm_tc2_blk_kernel(const Tc2BlkParams pp, const __grid_constant__ CUtensorMap m
       }
       if (row_ok) {
 #pragma unroll
-        for (int c = 0; c < kChunks; ++c) {
+        for (int c = 0; c < kSc; ++c) {
           const int nbase = n_first + c * 32;
           if (nbase < p.N) {
             uint32_t bits[32];

@@ -46,6 +46,8 @@ struct FlatParams {
   // thread -> (row-in-block, column) mapping: tx column threads, rpb rows per block
   int tx, rpb;
   int ncb;               // column blocks per row = ceil(nvec / (tx * U)) = gridDim.y
+  uint8_t* sf_packed;    // MXFP4 only, nullable: E8M0 bytes also go here in the GEMM's tcgen05.cp order
+  int sf_nblk;           // 128-row blocks of that buffer (sf_pack_blocks(T, 0))
 };
 
 // ---- packed 16-bit helpers (bf16x2 / half2 held in a 32-bit register) ----
@@ -202,6 +204,9 @@ __global__ void __launch_bounds__(256) flat_quant_kernel(const FlatParams p) {
   const int nvec = p.nvec;
   const int c0 = blockIdx.y * (U * tx) + cx;
   const bool sat = p.scale_in != nullptr;
+  // programmatic dependent launch (see launch_pdl): nothing above touches global memory
+  pdl_launch_dependents();
+  pdl_wait();
   float r_static = 0.0f, ub = 0.0f;
   if constexpr (FMT == FMT_STATIC) r_static = __frcp_rn(__ldg(p.scale_in));
   else if (sat) ub = __ldg(p.scale_in);
@@ -264,7 +269,10 @@ __global__ void __launch_bounds__(256) flat_quant_kernel(const FlatParams p) {
         if constexpr (FMT == FMT_MXFP4) {
           const int e = rceil_e8m0(div_const<6>(gmax));
           const float d = e8m0_descale(e);
-          if (leader[u]) *sq = e8m0_scale(e);
+          if (leader[u]) {
+            *sq = e8m0_scale(e);
+            if (p.sf_packed) p.sf_packed[sf_packed_offset<2>(t, (c0 + u * tx) >> ll, p.sf_nblk)] = static_cast<uint8_t>(e);
+          }
           // (the reference's clamp to +-6 is what the saturating conversion does anyway)
 #pragma unroll
           for (int k = 0; k < 8; k += 2) {
@@ -371,7 +379,10 @@ __global__ void __launch_bounds__(256) flat_quant_generic(const FlatParams p, in
     if constexpr (FMT == FMT_MXFP4) {
       const int e = rceil_e8m0(__fdiv_rn(gmax, 6.0f));
       const float d = e8m0_descale(e);
-      if (lane == 0) *sp = e8m0_scale(e);
+      if (lane == 0) {
+        *sp = e8m0_scale(e);
+        if (p.sf_packed) p.sf_packed[sf_packed_offset<2>(t, g, p.sf_nblk)] = static_cast<uint8_t>(e);
+      }
       uint8_t* o = static_cast<uint8_t*>(p.out) + t * (H / 2);
       for (int h2 = g * G / 2 + lane; h2 < (g + 1) * G / 2; h2 += 32) {
         float c0 = fminf(fmaxf(value(t, 2 * h2) * d, -6.0f), 6.0f);
@@ -422,6 +433,8 @@ template <typename T, int Q>
 __global__ void __launch_bounds__(256) static_quant_vec_kernel(const StaticParams p) {
   const int nvec = static_cast<int>(p.H / kVec);
   const unsigned gm = static_cast<unsigned>(p.group_m), gnv = static_cast<unsigned>(p.group_n / kVec);
+  pdl_launch_dependents();
+  pdl_wait();   // the scale may come from the kernel right before this one (dynamic_scaled_fp8_quant)
   for (int64_t t = blockIdx.x; t < p.T; t += gridDim.x) {
     const T* __restrict__ xrow = static_cast<const T*>(p.in) + t * p.in_row_stride;
     uint8_t* orow = static_cast<uint8_t*>(p.out) + t * p.out_row_stride;
@@ -527,7 +540,7 @@ static void launch_flat_vec(const FlatParams& p, int64_t row_blocks, int ncb, in
   int64_t gx = static_cast<int64_t>(sm_count()) * o / ncb;
   if (gx < 1) gx = 1;
   if (gx > row_blocks) gx = row_blocks;
-  kernel<<<dim3(static_cast<unsigned>(gx), static_cast<unsigned>(ncb)), threads, 0, st>>>(p);
+  launch_pdl(kernel, dim3(static_cast<unsigned>(gx), static_cast<unsigned>(ncb)), dim3(threads), 0, st, p);
 }
 
 template <typename T, int Q, int PRO, int FMT, int FAST, int U>
@@ -638,18 +651,24 @@ extern "C" int vxk_per_token_group_fp8_quant(const void* in, void* out_q, float*
     return launch_flat<T, VXK_Q_E5M2, PRO_NONE, FMT_FP8_DIV>(p, T_, H, (int)G, v, stream));
 }
 
-extern "C" int vxk_per_token_group_quant_mxfp4(const void* in, void* out_q, float* out_s, int64_t T_,
-                                               int64_t H, int64_t G, double eps, int64_t ss0,
-                                               int64_t ss1, int in_dtype, vxk_stream_t stream) {
+extern "C" int vxk_per_token_group_quant_mxfp4_sf(const void* in, void* out_q, float* out_s, void* sf_packed,
+                                                  int64_t T_, int64_t H, int64_t G, double eps, int64_t ss0,
+                                                  int64_t ss1, int in_dtype, vxk_stream_t stream) {
   (void)eps;  // the torch reference (to_mxfp) has no epsilon; an all-zero group gets exponent byte 0
   VXK_REQUIRE(T_ >= 0 && H >= 0, "negative shape");
   VXK_REQUIRE(G == 32, "MXFP4 requires group_size == 32, got %lld", (long long)G);
   VXK_REQUIRE(H % 32 == 0, "the last dimension (%lld) must be divisible by 32", (long long)H);
   FlatParams p{};
   p.out = out_q; p.in = in; p.scales = out_s; p.ss0 = ss0; p.ss1 = ss1;
+  p.sf_packed = static_cast<uint8_t*>(sf_packed); p.sf_nblk = sf_pack_blocks(T_, 0);
   const bool v = group_vec_ok(in, out_q, H, G, in_dtype, true);
   VXK_DISPATCH_T(in_dtype,
     return launch_flat<T, VXK_Q_E4M3, PRO_NONE, FMT_MXFP4>(p, T_, H, 32, v, stream));
+}
+extern "C" int vxk_per_token_group_quant_mxfp4(const void* in, void* out_q, float* out_s, int64_t T_,
+                                               int64_t H, int64_t G, double eps, int64_t ss0,
+                                               int64_t ss1, int in_dtype, vxk_stream_t stream) {
+  return vxk_per_token_group_quant_mxfp4_sf(in, out_q, out_s, nullptr, T_, H, G, eps, ss0, ss1, in_dtype, stream);
 }
 
 extern "C" int vxk_silu_and_mul_quant(void* out, const void* in, const float* scale, int64_t T_,
@@ -694,6 +713,11 @@ extern "C" int vxk_silu_and_mul_per_block_quant(void* out, const void* in, float
 extern "C" int vxk_silu_and_mul_mxfp4_quant(void* out, const void* in, float* scales, int64_t T_,
                                             int64_t H, int64_t G, double eps, int64_t ss0, int64_t ss1,
                                             int in_dtype, vxk_stream_t stream) {
+  return vxk_silu_and_mul_mxfp4_quant_sf(out, in, scales, nullptr, T_, H, G, eps, ss0, ss1, in_dtype, stream);
+}
+extern "C" int vxk_silu_and_mul_mxfp4_quant_sf(void* out, const void* in, float* scales, void* sf_packed, int64_t T_,
+                                               int64_t H, int64_t G, double eps, int64_t ss0, int64_t ss1,
+                                               int in_dtype, vxk_stream_t stream) {
   (void)eps;
   VXK_REQUIRE(T_ >= 0 && H >= 0, "negative shape");
   VXK_REQUIRE(G == 32, "MXFP4 requires group_size == 32, got %lld", (long long)G);
@@ -701,6 +725,7 @@ extern "C" int vxk_silu_and_mul_mxfp4_quant(void* out, const void* in, float* sc
   VXK_REQUIRE(in_dtype == VXK_F16 || in_dtype == VXK_BF16, "input must be f16 / bf16");
   FlatParams p{};
   p.out = out; p.in = in; p.scales = scales; p.ss0 = ss0; p.ss1 = ss1;
+  p.sf_packed = static_cast<uint8_t*>(sf_packed); p.sf_nblk = sf_pack_blocks(T_, 0);
   const bool v = group_vec_ok(in, out, H, G, in_dtype, true);
   VXK_DISPATCH_T16(in_dtype,
     return launch_flat<T, VXK_Q_E4M3, PRO_SILU_F32, FMT_MXFP4>(p, T_, H, 32, v, stream));
@@ -712,7 +737,7 @@ static int launch_static(const StaticParams& p, bool vec, cudaStream_t st) {
     const int64_t cap = static_cast<int64_t>(sm_count()) * 8;
     const int nvec = static_cast<int>(p.H / kVec);
     const int threads = nvec >= 1024 ? 256 : (nvec >= 512 ? 128 : 64);
-    static_quant_vec_kernel<T, Q><<<static_cast<unsigned>(p.T < cap ? p.T : cap), threads, 0, st>>>(p);
+    launch_pdl(static_quant_vec_kernel<T, Q>, dim3(static_cast<unsigned>(p.T < cap ? p.T : cap)), dim3(threads), 0, st, p);
   } else {
     const int grid = flat_grid(p.T * p.H, 1024);
     static_quant_scalar_kernel<T, Q><<<grid, 256, 0, st>>>(p);

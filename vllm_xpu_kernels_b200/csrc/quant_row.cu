@@ -105,6 +105,13 @@ extern "C" int vxk_rms_norm_mxfp4_quant(void* out, const void* in, const void* w
                                         double epsilon, void* residual, int64_t T_, int64_t H,
                                         int64_t group_size, int64_t ss0, int64_t ss1, int in_dtype,
                                         vxk_stream_t stream) {
+  return vxk_rms_norm_mxfp4_quant_sf(out, in, weight, scales, nullptr, epsilon, residual, T_, H, group_size, ss0, ss1,
+                                     in_dtype, stream);
+}
+extern "C" int vxk_rms_norm_mxfp4_quant_sf(void* out, const void* in, const void* weight, float* scales,
+                                           void* sf_packed, double epsilon, void* residual, int64_t T_, int64_t H,
+                                           int64_t group_size, int64_t ss0, int64_t ss1, int in_dtype,
+                                           vxk_stream_t stream) {
   VXK_REQUIRE(T_ >= 0 && H >= 0, "negative shape");
   VXK_REQUIRE(group_size == 32, "MXFP4 requires group_size == 32, got %lld", (long long)group_size);
   VXK_REQUIRE(H % 32 == 0, "hidden_size must be divisible by group_size");
@@ -112,6 +119,7 @@ extern "C" int vxk_rms_norm_mxfp4_quant(void* out, const void* in, const void* w
   p.out = out; p.in = in; p.weight = weight; p.residual = residual; p.scales = scales;
   p.H = H; p.in_row_stride = H; p.nvec = static_cast<int>(H / kVec);
   p.group = 32; p.ss0 = ss0; p.ss1 = ss1; p.eps = static_cast<float>(epsilon);
+  p.sf_packed = static_cast<uint8_t*>(sf_packed); p.sf_nblk = sf_pack_blocks(T_, 0);
   const bool v = vec_path_ok(p, in_dtype, /*packed4=*/true);
   return row_dispatch(in_dtype, ROW_A8, VXK_Q_E4M3, p, T_, v, stream);
 }

@@ -24,6 +24,8 @@ struct RowParams {
   float eps;
   int exact_var;        // rms: variance from an fp64 sum of squares (correctly rounded mean), see row_variance()
   double inv_H;         // 1.0 / H
+  uint8_t* sf_packed;   // MODE_MXFP4, nullable: E8M0 bytes also go here in the GEMM's tcgen05.cp order
+  int sf_nblk;          // 128-row blocks of that buffer (sf_pack_blocks(T, 0))
 };
 
 // Raw (still packed) copy of 8 input elements: 4 registers for bf16/f16, 8 for f32.
@@ -209,7 +211,7 @@ __global__ void __launch_bounds__(512) row_quant_kernel(const RowParams p, const
   // Programmatic dependent launch: the next kernel in the stream may be scheduled as soon as this one's
   // CTAs retire (its launch latency and index set-up overlap our tail); our own global accesses -- inputs
   // AND outputs, which the previous kernel may still be reading -- start only after griddepcontrol.wait.
-  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  pdl_launch_dependents();
   if (tid < 64) {
     scratch[tid >> 5][tid & 31] = 0.0f;
     if constexpr (RMS) scratch64[tid >> 5][tid & 31] = 0.0;
@@ -245,7 +247,7 @@ __global__ void __launch_bounds__(512) row_quant_kernel(const RowParams p, const
   const T* __restrict__ xnext = static_cast<const T*>(p.in) + static_cast<int64_t>(blockIdx.x) * p.in_row_stride;
   uint8_t* orow = static_cast<uint8_t*>(p.out) + static_cast<int64_t>(blockIdx.x) * (MODE == MODE_MXFP4 ? p.H / 2 : p.H);
 
-  asm volatile("griddepcontrol.wait;" ::: "memory");
+  pdl_wait();
   // first row: requested before the weight staging below so that its HBM latency overlaps it
   Raw8<T> raw[VPT];
 #pragma unroll
@@ -393,7 +395,10 @@ __global__ void __launch_bounds__(512) row_quant_kernel(const RowParams p, const
         if constexpr (MODE == MODE_MXFP4) {
           const int e = rceil_e8m0(div_const<6>(gmax));
           const float d = e8m0_descale(e);
-          if (leader) p.scales[row * p.ss0 + g * p.ss1] = e8m0_scale(e);
+          if (leader) {
+            p.scales[row * p.ss0 + g * p.ss1] = e8m0_scale(e);
+            if (p.sf_packed) p.sf_packed[sf_packed_offset<2>(row, g, p.sf_nblk)] = static_cast<uint8_t>(e);
+          }
           uint32_t code[VG];
 #pragma unroll
           for (int i = i0; i < i0 + VG; ++i) {
@@ -526,7 +531,10 @@ __global__ void __launch_bounds__(256) row_quant_generic(const RowParams p) {
       if constexpr (MODE == MODE_MXFP4) {
         const int e = rceil_e8m0(__fdiv_rn(gmax, 6.0f));
         const float d = e8m0_descale(e);
-        if (lane == 0) p.scales[row * p.ss0 + g * p.ss1] = e8m0_scale(e);
+        if (lane == 0) {
+          p.scales[row * p.ss0 + g * p.ss1] = e8m0_scale(e);
+          if (p.sf_packed) p.sf_packed[sf_packed_offset<2>(row, g, p.sf_nblk)] = static_cast<uint8_t>(e);
+        }
         uint8_t* o = static_cast<uint8_t*>(p.out) + row * (p.H / 2);
         for (int h2 = g * G / 2 + lane; h2 < (g + 1) * G / 2; h2 += 32) {
           float c0 = fminf(fmaxf(value(2 * h2) * d, -6.0f), 6.0f);
@@ -591,18 +599,7 @@ inline int launch_row_vpt3(const RowParams& p, int64_t T_rows, int threads, cuda
   }
   const int64_t cap = static_cast<int64_t>(per_sm) * sm_count();
   const unsigned grid = static_cast<unsigned>(T_rows < cap ? T_rows : cap);
-  static const int pdl = [] { const char* e = getenv("VXK_ROW_PDL"); return e ? atoi(e) : 1; }();
-  cudaLaunchConfig_t cfg{};
-  cfg.gridDim = dim3(grid);
-  cfg.blockDim = dim3(static_cast<unsigned>(threads));
-  cfg.dynamicSmemBytes = smem;
-  cfg.stream = st;
-  cudaLaunchAttribute attr{};
-  attr.id = cudaLaunchAttributeProgrammaticStreamSerialization;
-  attr.val.programmaticStreamSerializationAllowed = 1;
-  cfg.attrs = &attr;
-  cfg.numAttrs = pdl ? 1 : 0;
-  cudaLaunchKernelEx(&cfg, kernel, p, T_rows);
+  launch_pdl(kernel, dim3(grid), dim3(static_cast<unsigned>(threads)), smem, st, p, T_rows);
   return 0;
 }
 template <typename T, int Q, int MODE, bool RMS, bool HAS_RES, int VPT, int VG>

@@ -207,8 +207,19 @@ void per_token_group_fp8_quant(const Tensor& input, Tensor& output_q, Tensor& ou
 }
 
 // ref: csrc/quantization/fp4/mxfp4_quant.cpp:24-126
-void per_token_group_quant_mxfp4(const Tensor& input, Tensor& output_q, Tensor& output_s, int64_t group_size,
-                                 double eps) {
+// packed scale-factor buffer of an activation tensor [T, H] (include/vxk_b200.h "(f) next #2"); nullptr when absent
+void* sf_packed_ptr(const std::optional<Tensor>& sf, int64_t rows, int64_t K, int operand, const Tensor& like) {
+  if (!sf.has_value() || !sf->defined()) return nullptr;
+  TORCH_CHECK(sf->scalar_type() == at::kByte && sf->is_contiguous(), "packed scale buffer must be contiguous uint8");
+  TORCH_CHECK(sf->device() == like.device(), "packed scale buffer must be on the operands' device");
+  TORCH_CHECK(sf->numel() >= vxk_mx_sf_packed_bytes(rows, K, /*kind=*/1, operand),
+              "packed scale buffer too small: ", sf->numel(), " < ", vxk_mx_sf_packed_bytes(rows, K, 1, operand));
+  TORCH_CHECK(reinterpret_cast<uintptr_t>(sf->data_ptr()) % 16 == 0, "packed scale buffer must be 16-byte aligned");
+  return sf->data_ptr();
+}
+
+void per_token_group_quant_mxfp4_impl(const Tensor& input, Tensor& output_q, Tensor& output_s, int64_t group_size,
+                                      double eps, const std::optional<Tensor>& sf_packed) {
   TORCH_CHECK(input.is_contiguous(), "input must be contiguous");
   TORCH_CHECK(output_q.is_contiguous(), "output_q must be contiguous");
   TORCH_CHECK(group_size == 32, "MXFP4 requires group_size == 32, got ", group_size);
@@ -228,10 +239,19 @@ void per_token_group_quant_mxfp4(const Tensor& input, Tensor& output_q, Tensor& 
   TORCH_CHECK(H % group_size == 0 && output_s.size(1) == H / group_size,
               "output_s must have shape [num_tokens, hidden / 32]");
   const c10::cuda::CUDAGuard guard(input.device());
-  check_rc(vxk_per_token_group_quant_mxfp4(input.data_ptr(), output_q.data_ptr(), output_s.data_ptr<float>(),
-                                           T, H, group_size, eps, output_s.stride(0), output_s.stride(1),
-                                           in_dtype_of(input, "per_token_group_quant_mxfp4"), cur_stream()),
+  check_rc(vxk_per_token_group_quant_mxfp4_sf(input.data_ptr(), output_q.data_ptr(), output_s.data_ptr<float>(),
+                                              sf_packed_ptr(sf_packed, T, H, 0, input), T, H, group_size, eps,
+                                              output_s.stride(0), output_s.stride(1),
+                                              in_dtype_of(input, "per_token_group_quant_mxfp4"), cur_stream()),
            "per_token_group_quant_mxfp4");
+}
+void per_token_group_quant_mxfp4(const Tensor& input, Tensor& output_q, Tensor& output_s, int64_t group_size,
+                                 double eps) {
+  per_token_group_quant_mxfp4_impl(input, output_q, output_s, group_size, eps, std::nullopt);
+}
+void per_token_group_quant_mxfp4_sf(const Tensor& input, Tensor& output_q, Tensor& output_s, Tensor& sf_packed,
+                                    int64_t group_size, double eps) {
+  per_token_group_quant_mxfp4_impl(input, output_q, output_s, group_size, eps, sf_packed);
 }
 
 void check_residual(const std::optional<Tensor>& residual, const Tensor& input) {
@@ -308,8 +328,9 @@ void rms_norm_per_block_quant(Tensor& out, const Tensor& input, const Tensor& we
 }
 
 // ref: layernorm_quant.cpp:1172-1219
-void rms_norm_mxfp4_quant(Tensor& out, const Tensor& input, const Tensor& weight, Tensor& scales,
-                          double epsilon, std::optional<Tensor> residual, int64_t group_size) {
+void rms_norm_mxfp4_quant_impl(Tensor& out, const Tensor& input, const Tensor& weight, Tensor& scales,
+                               double epsilon, std::optional<Tensor> residual, int64_t group_size,
+                               const std::optional<Tensor>& sf_packed) {
   TORCH_CHECK(input.is_contiguous(), "input must be contiguous");
   TORCH_CHECK(out.is_contiguous(), "out must be contiguous");
   TORCH_CHECK(weight.dtype() == input.dtype(), "weight and input must have the same dtype");
@@ -327,11 +348,20 @@ void rms_norm_mxfp4_quant(Tensor& out, const Tensor& input, const Tensor& weight
   TORCH_CHECK(scales.size(0) == T && scales.size(1) == H / group_size, "scales must be [num_tokens, hidden/32]");
   TORCH_CHECK(weight.numel() == H && weight.is_contiguous(), "weight must be a contiguous [hidden] tensor");
   const c10::cuda::CUDAGuard guard(input.device());
-  check_rc(vxk_rms_norm_mxfp4_quant(out.data_ptr(), input.data_ptr(), weight.data_ptr(), scales.data_ptr<float>(),
-                                    epsilon, residual.has_value() ? residual->data_ptr() : nullptr, T, H,
-                                    group_size, scales.stride(0), scales.stride(1),
-                                    in_dtype_of(input, "rms_norm_mxfp4_quant"), cur_stream()),
+  check_rc(vxk_rms_norm_mxfp4_quant_sf(out.data_ptr(), input.data_ptr(), weight.data_ptr(), scales.data_ptr<float>(),
+                                       sf_packed_ptr(sf_packed, T, H, 0, input), epsilon,
+                                       residual.has_value() ? residual->data_ptr() : nullptr, T, H, group_size,
+                                       scales.stride(0), scales.stride(1),
+                                       in_dtype_of(input, "rms_norm_mxfp4_quant"), cur_stream()),
            "rms_norm_mxfp4_quant");
+}
+void rms_norm_mxfp4_quant(Tensor& out, const Tensor& input, const Tensor& weight, Tensor& scales,
+                          double epsilon, std::optional<Tensor> residual, int64_t group_size) {
+  rms_norm_mxfp4_quant_impl(out, input, weight, scales, epsilon, residual, group_size, std::nullopt);
+}
+void rms_norm_mxfp4_quant_sf(Tensor& out, const Tensor& input, const Tensor& weight, Tensor& scales, Tensor& sf_packed,
+                             double epsilon, std::optional<Tensor> residual, int64_t group_size) {
+  rms_norm_mxfp4_quant_impl(out, input, weight, scales, epsilon, residual, group_size, sf_packed);
 }
 
 void rms_norm_static_impl(Tensor& out, const Tensor& input, Tensor* residual, const Tensor& weight,
@@ -431,7 +461,8 @@ void silu_and_mul_per_block_quant(Tensor& out, const Tensor& input, Tensor& scal
 }
 
 // ref: fused_silu_mul_mxfp4_quant.cpp:134-209
-void silu_and_mul_mxfp4_quant(Tensor& out, const Tensor& input, Tensor& scales, int64_t group_size, double eps) {
+void silu_and_mul_mxfp4_quant_impl(Tensor& out, const Tensor& input, Tensor& scales, int64_t group_size, double eps,
+                                   const std::optional<Tensor>& sf_packed) {
   TORCH_CHECK(input.dtype() == at::kHalf || input.dtype() == at::kBFloat16,
               "input must be float16 or bfloat16");
   TORCH_CHECK(out.scalar_type() == at::ScalarType::Byte, "out must be uint8 (packed FP4)");
@@ -453,10 +484,18 @@ void silu_and_mul_mxfp4_quant(Tensor& out, const Tensor& input, Tensor& scales, 
   check_cuda(input, "input");
   same_device(input, out, scales);
   const c10::cuda::CUDAGuard guard(input.device());
-  check_rc(vxk_silu_and_mul_mxfp4_quant(out.data_ptr(), input.data_ptr(), scales.data_ptr<float>(), T, H,
-                                        group_size, eps, scales.stride(0), scales.stride(1),
-                                        in_dtype_of(input, "silu_and_mul_mxfp4_quant"), cur_stream()),
+  check_rc(vxk_silu_and_mul_mxfp4_quant_sf(out.data_ptr(), input.data_ptr(), scales.data_ptr<float>(),
+                                           sf_packed_ptr(sf_packed, T, H, 0, input), T, H, group_size, eps,
+                                           scales.stride(0), scales.stride(1),
+                                           in_dtype_of(input, "silu_and_mul_mxfp4_quant"), cur_stream()),
            "silu_and_mul_mxfp4_quant");
+}
+void silu_and_mul_mxfp4_quant(Tensor& out, const Tensor& input, Tensor& scales, int64_t group_size, double eps) {
+  silu_and_mul_mxfp4_quant_impl(out, input, scales, group_size, eps, std::nullopt);
+}
+void silu_and_mul_mxfp4_quant_sf(Tensor& out, const Tensor& input, Tensor& scales, Tensor& sf_packed,
+                                 int64_t group_size, double eps) {
+  silu_and_mul_mxfp4_quant_impl(out, input, scales, group_size, eps, sf_packed);
 }
 
 // --------------------------------------------------------------- _xpu_C ops
@@ -574,8 +613,9 @@ Tensor fp8_gemm(const Tensor& A, const Tensor& B, std::optional<c10::ScalarType>
 }
 
 // ref: onednn_matmul.cpp:101-123, fp4_gemm_w4a4.h:12-167
-Tensor fp4_gemm(const Tensor& A, const Tensor& B, const Tensor& A_scale, const Tensor& B_scale,
-                std::optional<c10::ScalarType> out_dtype, const std::optional<Tensor>& bias_) {
+Tensor fp4_gemm_impl(const Tensor& A, const Tensor& B, const Tensor& A_scale, const Tensor& B_scale,
+                     std::optional<c10::ScalarType> out_dtype, const std::optional<Tensor>& bias_,
+                     const std::optional<Tensor>& A_sf_packed, const std::optional<Tensor>& B_sf_packed) {
   const c10::cuda::CUDAGuard guard(A.device());
   Tensor result = check_and_create_output_tensor(A, B, out_dtype);
   const auto a_st = A.scalar_type(), b_st = B.scalar_type();
@@ -606,17 +646,47 @@ Tensor fp4_gemm(const Tensor& A, const Tensor& B, const Tensor& A_scale, const T
     bias = bias_->data_ptr();
     bias_dtype = bias_dtype_of(*bias_);
   }
-  // per-call scratch, like the reference's scratchpad tensor (fp4_gemm_w4a4.h:159-162)
-  const int64_t ws_bytes = vxk_fp4_gemm_workspace_bytes(r.M, N, K);
+  const void* a_packed = sf_packed_ptr(A_sf_packed, r.M, K, 0, A);
+  const void* b_packed = sf_packed_ptr(B_sf_packed, N, K, 1, A);
+  // per-call scratch, like the reference's scratchpad tensor (fp4_gemm_w4a4.h:159-162); none when both scale
+  // grids arrive in the tensor core's layout
+  const int64_t ws_bytes = (a_packed && b_packed) ? 0 : vxk_fp4_gemm_workspace_bytes(r.M, N, K);
   Tensor ws;
   if (ws_bytes > 0) ws = at::empty({ws_bytes}, A.options().dtype(at::kByte));
-  check_rc(vxk_fp4_gemm(result.data_ptr(), A.data_ptr(), B.data_ptr(), A_scale.data_ptr(), B_scale.data_ptr(), bias,
-                        r.M, N, K, r.lda, B.stride(1), r.ldd, A_scale.stride(0), A_scale.stride(1),
-                        B_scale.stride(0), B_scale.stride(1),
-                        result.scalar_type() == at::kBFloat16 ? VXK_BF16 : VXK_F16, bias_dtype,
-                        ws_bytes > 0 ? ws.data_ptr() : nullptr, ws_bytes, cur_stream()),
+  check_rc(vxk_fp4_gemm_sf(result.data_ptr(), A.data_ptr(), B.data_ptr(), A_scale.data_ptr(), B_scale.data_ptr(),
+                           a_packed, b_packed, bias, r.M, N, K, r.lda, B.stride(1), r.ldd, A_scale.stride(0),
+                           A_scale.stride(1), B_scale.stride(0), B_scale.stride(1),
+                           result.scalar_type() == at::kBFloat16 ? VXK_BF16 : VXK_F16, bias_dtype,
+                           ws_bytes > 0 ? ws.data_ptr() : nullptr, ws_bytes, cur_stream()),
            "fp4_gemm");
   return result;
+}
+Tensor fp4_gemm(const Tensor& A, const Tensor& B, const Tensor& A_scale, const Tensor& B_scale,
+                std::optional<c10::ScalarType> out_dtype, const std::optional<Tensor>& bias_) {
+  return fp4_gemm_impl(A, B, A_scale, B_scale, out_dtype, bias_, std::nullopt, std::nullopt);
+}
+// extension (no reference counterpart): scale grids also handed over in tcgen05.cp order
+Tensor fp4_gemm_sf(const Tensor& A, const Tensor& B, const Tensor& A_scale, const Tensor& B_scale,
+                   std::optional<c10::ScalarType> out_dtype, const std::optional<Tensor>& bias_,
+                   const std::optional<Tensor>& A_sf_packed, const std::optional<Tensor>& B_sf_packed) {
+  return fp4_gemm_impl(A, B, A_scale, B_scale, out_dtype, bias_, A_sf_packed, B_sf_packed);
+}
+int64_t mx_sf_packed_bytes(int64_t rows, int64_t K, bool fp4, bool is_weight) {
+  const int64_t n = vxk_mx_sf_packed_bytes(rows, K, fp4 ? 1 : 0, is_weight ? 1 : 0);
+  TORCH_CHECK(n >= 0, "mx_sf_packed_bytes: bad arguments");
+  return n;
+}
+// scale: [rows, K/32] float8_e8m0fnu (any strides) -> packed uint8 buffer, every byte written
+Tensor mx_sf_pack(const Tensor& scale, bool fp4, bool is_weight) {
+  TORCH_CHECK(scale.dim() == 2 && scale.scalar_type() == at::kFloat8_e8m0fnu, "scale must be a 2-D float8_e8m0fnu tensor");
+  check_cuda(scale, "scale");
+  const c10::cuda::CUDAGuard guard(scale.device());
+  const int64_t rows = scale.size(0), K = scale.size(1) * 32;
+  Tensor out = at::empty({mx_sf_packed_bytes(rows, K, fp4, is_weight)}, scale.options().dtype(at::kByte));
+  check_rc(vxk_mx_sf_pack(out.data_ptr(), scale.data_ptr(), rows, K, scale.stride(0), scale.stride(1), fp4 ? 1 : 0,
+                          is_weight ? 1 : 0, cur_stream()),
+           "mx_sf_pack");
+  return out;
 }
 
 // ref: onednn_matmul.cpp:81-99, fp8_gemm_w8a16.h:13-145
@@ -822,6 +892,27 @@ TORCH_LIBRARY_IMPL(_xpu_C, CUDA, xpu_ops) {
   xpu_ops.impl("fp8_gemm", &fp8_gemm);
   xpu_ops.impl("fp4_gemm", &fp4_gemm);
   xpu_ops.impl("fp8_gemm_w8a16", &fp8_gemm_w8a16);
+}
+
+// Extensions without a reference counterpart (scale factors in the tensor core's layout).
+TORCH_LIBRARY_FRAGMENT(_vxk, vxk_ops) {
+  vxk_ops.def("mx_sf_packed_bytes(int rows, int K, bool fp4, bool is_weight) -> int", &mx_sf_packed_bytes);
+  vxk_ops.def("mx_sf_pack(Tensor scale, bool fp4, bool is_weight) -> Tensor");
+  vxk_ops.def("per_token_group_quant_mxfp4_sf(Tensor input, Tensor! output_q, Tensor! output_s, Tensor! sf_packed, "
+              "int group_size, float eps) -> ()");
+  vxk_ops.def("rms_norm_mxfp4_quant_sf(Tensor! result, Tensor input, Tensor weight, Tensor! scale, Tensor! sf_packed, "
+              "float epsilon, Tensor!? residual, int group_size) -> ()");
+  vxk_ops.def("silu_and_mul_mxfp4_quant_sf(Tensor! out, Tensor input, Tensor! scales, Tensor! sf_packed, int group_size, "
+              "float eps=1e-10) -> ()");
+  vxk_ops.def("fp4_gemm_sf(Tensor A, Tensor B, Tensor A_scale, Tensor B_scale, ScalarType? out_dtype, Tensor? bias_, "
+              "Tensor? A_sf_packed, Tensor? B_sf_packed) -> Tensor");
+}
+TORCH_LIBRARY_IMPL(_vxk, CUDA, vxk_ops) {
+  vxk_ops.impl("mx_sf_pack", &mx_sf_pack);
+  vxk_ops.impl("per_token_group_quant_mxfp4_sf", &per_token_group_quant_mxfp4_sf);
+  vxk_ops.impl("rms_norm_mxfp4_quant_sf", &rms_norm_mxfp4_quant_sf);
+  vxk_ops.impl("silu_and_mul_mxfp4_quant_sf", &silu_and_mul_mxfp4_quant_sf);
+  vxk_ops.impl("fp4_gemm_sf", &fp4_gemm_sf);
 }
 
 // Schemas verbatim from /root/reference/csrc/torch_bindings.cpp:281-284,298-309 (library _C_cache_ops).

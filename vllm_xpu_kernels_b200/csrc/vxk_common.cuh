@@ -14,6 +14,7 @@
 #include <atomic>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <mutex>
 
 #include "../../include/vxk_b200.h"
@@ -50,6 +51,45 @@ int sm_count();  // cached cudaDevAttrMultiProcessorCount of the current device
 // One-time per-DEVICE configuration of a kernel (cudaFuncSetAttribute is per device: a process that
 // calls an op on cuda:0 and then on cuda:1 must configure both).  One static instance per kernel
 // instantiation; `init(entry)` runs once for each device ordinal that reaches it.
+// MX scale factors in the layout tcgen05.cp.32x128b.warpx4 consumes ("packed", see sf_pack_kernel in gemm_tc.cu):
+// 512-byte chunks [32 lanes][4 words]; word (lane, c) of chunk (kb, blk, w) holds the four E8M0 bytes of row
+// blk * 128 + c * 32 + lane for the 32-element K groups kb * 4 * SF_WORDS + 4 w .. + 3; chunks ordered [kb][blk][w].
+// SF_WORDS = 2 for MXFP4 (a K slice of 256 elements = 8 groups), 1 for MXFP8 (128 elements = 4 groups).
+// nblk: 128-row blocks in the buffer = ceil(rows / 128) + 1 for activations, + 2 for weights (sf_pack_blocks).
+inline int sf_pack_blocks(int64_t rows, int operand) { return static_cast<int>((rows + 127) / 128) + (operand ? 2 : 1); }
+template <int SF_WORDS>
+__host__ __device__ __forceinline__ int64_t sf_packed_offset(int64_t row, int g, int nblk) {
+  constexpr int kGroups = 4 * SF_WORDS;
+  const int kb = g / kGroups, w = (g % kGroups) >> 2, b = g & 3;
+  const int64_t chunk = (static_cast<int64_t>(kb) * nblk + (row >> 7)) * SF_WORDS + w;
+  return ((chunk * 128 + (row & 31) * 4 + ((row >> 5) & 3)) << 2) + b;
+}
+
+// Launch with the programmatic-stream-serialisation attribute (PDL): the kernel may be scheduled while the
+// previous kernel in the stream is still draining; it must execute griddepcontrol.wait before its first global
+// access that can depend on (or be read by) that kernel.  VXK_PDL=0 turns the attribute off everywhere.
+inline bool pdl_enabled() {
+  static const int on = [] { const char* e = getenv("VXK_PDL"); return e ? atoi(e) : 1; }();
+  return on != 0;
+}
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st,
+                              Args&&... args) {
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr{};
+  attr.id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr.val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = &attr;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
 struct PerDeviceOnce {
   struct Entry { bool done = false; cudaError_t err = cudaSuccess; int aux = 0; size_t smem = 0; };
   std::mutex mu;

@@ -229,3 +229,53 @@ def rms_norm_static_fp8_quant(x, weight, scale, eps, residual=None, quant_dtype=
     else:
         torch.ops._C.fused_add_rms_norm_static_fp8_quant(out, x, residual, weight, scale, eps)
     return out
+
+
+# ------------------------------------------------- extensions: MX scale factors in the tensor core's layout
+# (include/vxk_b200.h "(f) next #2"; no reference counterpart -- the reference API above stays the drop-in)
+def mx_sf_buffer(rows: int, K: int, device, fp4: bool = True, is_weight: bool = False) -> torch.Tensor:
+    """Packed scale-factor buffer for a [rows, K] operand, to be filled by one of the *_sf quantisation ops.
+    Zero-filled only when K has a partial K slice (the kernels write real groups only)."""
+    n = torch.ops._vxk.mx_sf_packed_bytes(rows, K, fp4, is_weight)
+    slice_k = 256 if fp4 else 128
+    return (torch.zeros if K % slice_k else torch.empty)(n, dtype=torch.uint8, device=device)
+
+
+def mx_sf_pack(scale_e8m0: torch.Tensor, fp4: bool = True, is_weight: bool = True) -> torch.Tensor:
+    """[rows, K/32] float8_e8m0fnu -> packed uint8 buffer (once per weight, after loading)."""
+    return torch.ops._vxk.mx_sf_pack(scale_e8m0, fp4, is_weight)
+
+
+def per_token_group_quant_mxfp4_sf(x: torch.Tensor, group_size: int = 32, eps: float = 1e-10):
+    """per_token_group_quant_mxfp4 that also returns the packed scale factors: (q, e8m0 scales, packed)."""
+    M, N = x.shape
+    out_q = torch.empty(M, N // 2, device=x.device, dtype=torch.uint8)
+    out_s = torch.empty(M, N // group_size, device=x.device, dtype=torch.float32)
+    sf = mx_sf_buffer(M, N, x.device)
+    torch.ops._vxk.per_token_group_quant_mxfp4_sf(x.contiguous(), out_q, out_s, sf, group_size, eps)
+    return out_q.view(torch.float4_e2m1fn_x2), out_s.to(torch.float8_e8m0fnu), sf
+
+
+def rms_norm_mxfp4_quant_sf(x, weight, eps, residual=None, group_size: int = 32):
+    x = x.contiguous()
+    H = x.shape[-1]
+    T = x.numel() // H
+    out = torch.empty(T, H // 2, device=x.device, dtype=torch.uint8)
+    scales = torch.empty(T, H // group_size, device=x.device, dtype=torch.float32)
+    sf = mx_sf_buffer(T, H, x.device)
+    torch.ops._vxk.rms_norm_mxfp4_quant_sf(out, x, weight, scales, sf, eps, residual, group_size)
+    return out, scales, sf
+
+
+def silu_and_mul_mxfp4_quant_sf(input: torch.Tensor, group_size: int = 32, eps: float = 1e-10):
+    T = input.shape[0]
+    H = input.shape[-1] // 2
+    out = torch.empty(T, H // 2, dtype=torch.uint8, device=input.device)
+    scales = torch.empty(T, H // group_size, dtype=torch.float32, device=input.device)
+    sf = mx_sf_buffer(T, H, input.device)
+    torch.ops._vxk.silu_and_mul_mxfp4_quant_sf(out, input.contiguous(), scales, sf, group_size, eps)
+    return out, scales, sf
+
+
+def fp4_gemm_sf(input, weight, scale_act, scale_wei, out_dtype, bias=None, act_sf_packed=None, wei_sf_packed=None):
+    return torch.ops._vxk.fp4_gemm_sf(input, weight, scale_act, scale_wei, out_dtype, bias, act_sf_packed, wei_sf_packed)
