@@ -236,25 +236,42 @@ def run_ours(args):
         sampler.start()
 
     # ---- timed region: exactly K steps, CUDA events on the launching (current) stream ----
+    # Only the two ends of the region carry an event: a timestamp between two kernels drains the stream and
+    # exposes a full launch latency per kernel (measured: +5..8 us each), which neither a serving engine's
+    # stream nor the reference's own benchmark has.
     K = args.steps
-    ev = [[torch.cuda.Event(enable_timing=True) for _ in range(3)] for _ in range(K)]
     n_launch0 = _loader.launch_count()
     barrier()
     t_start = torch.cuda.Event(enable_timing=True)
     t_end = torch.cuda.Event(enable_timing=True)
     t_start.record()
     for i in range(K):
-        ev[i][0].record()
-        torch.ops._C.rms_norm_dynamic_per_token_quant(q1, x, w, s1, EPS, None, None)
-        ev[i][1].record()
-        torch.ops._C.silu_and_mul_per_block_quant(q2, gu, s2, GROUP, None, False, False)
-        ev[i][2].record()
+        step()
     t_end.record()
     barrier()
     launches = _loader.launch_count() - n_launch0
-    rms_ms = sum(e[0].elapsed_time(e[1]) for e in ev) / K
-    silu_ms = sum(e[1].elapsed_time(e[2]) for e in ev) / K
     ms_per_step = max_over_ranks(t_start.elapsed_time(t_end)) / K
+
+    # ---- per-kernel launch durations (roofline): K back-to-back launches of ONE kernel, events at both ends.
+    # silu: one buffer set (587 MB) already exceeds L2; rms: four rotating sets (4 x 101 MB).
+    def timed_loop(fn, n):
+        fn(0)
+        torch.cuda.synchronize()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for i in range(n):
+            fn(i)
+        b.record()
+        torch.cuda.synchronize()
+        return a.elapsed_time(b) / n
+
+    n_k = max(K, 20)
+    silu_ms = timed_loop(lambda i: torch.ops._C.silu_and_mul_per_block_quant(q2, gu, s2, GROUP, None, False, False), n_k)
+    rms_sets = [(x, q1, s1)] + [(torch.randn_like(x) / HIDDEN, torch.empty_like(q1), torch.empty_like(s1)) for _ in range(3)]
+    rms_ms = timed_loop(lambda i: torch.ops._C.rms_norm_dynamic_per_token_quant(
+        rms_sets[i % 4][1], rms_sets[i % 4][0], w, rms_sets[i % 4][2], EPS, None, None), 4 * n_k)
+    del rms_sets
+    launches_kernel_loops = 5 * n_k + 2
     step_bytes = BYTES_RMS(T) + BYTES_SILU(T)
     value = world * step_bytes / (ms_per_step * 1e-3) / 1e9
 
@@ -393,10 +410,14 @@ def run_ours(args):
                 "achieved": achieved, "peak": pk["hbm"], "unit": "GB/s", "frac": achieved / pk["hbm"],
                 "peak_source": pk["src"] + " copy bandwidth", "traffic": traffic, "traffic_source": traffic_src,
                 "ms_per_launch": silu_ms, "algorithmic_bytes_per_launch": BYTES_SILU(T),
+                "timing": f"{n_k} back-to-back launches of this kernel between two CUDA events on the launching stream "
+                          f"(one 587 MB buffer set > L2); the interleaved step itself is ms_per_step "
+                          f"(sum of the two per-kernel figures: {silu_ms + rms_ms:.4f} ms)",
                 "also": {"rms_norm_dynamic_per_token_quant": {
                              "kernel": "row_quant_kernel<bf16,e4m3,token,rms> T=8192 H=4096", "achieved": rms_gbs,
                              "ms_per_launch": rms_ms, "frac": rms_gbs / pk["hbm"],
-                             "algorithmic_bytes_per_launch": BYTES_RMS(T)},
+                             "algorithmic_bytes_per_launch": BYTES_RMS(T), "launches": 4 * n_k,
+                             "l2": "4 rotating buffer sets (403 MB) > L2"},
                          "config1_dynamic_per_token_fp8_4096x4096": {
                              "kernel": "row_quant_kernel<bf16,e4m3,token> (tests/test_fp8_quant.py:48-83 shape)",
                              "achieved": a1_gbs, "ms_per_launch": a1_ms, "frac": a1_gbs / pk["hbm"],
@@ -418,6 +439,7 @@ def run_ours(args):
                        "(full-duplex PCIe); results equal the device-resident path: " + str(same_as_device_path),
                 "gemm": e2e_g},
         "gpu_launches": int(launches),
+        "gpu_launches_kernel_loops": int(launches_kernel_loops),
         "clocks": sampler.summary() if sampler else None,
     }
     print(json.dumps(line), flush=True)
