@@ -36,6 +36,8 @@ KERNEL_OF = {   # dominant kernel of each kind at large M (vllm_xpu_kernels_b200
     "mxfp4": "gemm_tc2_kernel<KIND_MXF4,192,*> (tcgen05 kind::mxf4.block_scale, cta_group::2)",
     "fp8_w8a16": "gemm_w8a16_kernel (tcgen05 kind::f16, FP8 widened in the main loop)",
     "block_fp8": "gemm_tc2_blk_kernel<192> (tcgen05 kind::f8f6f4 per K slice + fp32 promotion)",
+    "mxfp4_sf": "gemm_tc2_kernel<KIND_MXF4,192,*> via torch.ops._vxk.fp4_gemm_sf (pre-packed scale factors, no sf_pack launches)",
+    "mxfp4 (M <= 128)": "gemm_skinny_mx4_kernel (swap-AB, split-K over a cluster, natural-layout scales re-tiled in the kernel)",
 }
 
 
@@ -64,6 +66,17 @@ def make_case(kind, M, K, nloc, dev, copies):
             w = torch.randint(0, 256, (nloc, K // 2), dtype=torch.uint8, device=dev).view(torch.float4_e2m1fn_x2)
             sw = torch.randint(118, 130, (nloc, K // 32), dtype=torch.uint8, device=dev).view(E8)
             fns.append(lambda w=w, sw=sw: torch.ops._xpu_C.fp4_gemm(a, w.t(), sa, sw, torch.bfloat16, None))
+        nbytes = M * K // 2 + K * nloc // 2 + 2 * M * nloc + (M + nloc) * K // 32
+    elif kind == "mxfp4_sf":
+        # the extension path: weight scales pre-packed once, activation scales packed by the quant kernel
+        a = torch.randint(0, 256, (M, K // 2), dtype=torch.uint8, device=dev).view(torch.float4_e2m1fn_x2)
+        sa = torch.randint(118, 130, (M, K // 32), dtype=torch.uint8, device=dev).view(E8)
+        sa_p = torch.ops._vxk.mx_sf_pack(sa, True, False)
+        for _ in range(copies):
+            w = torch.randint(0, 256, (nloc, K // 2), dtype=torch.uint8, device=dev).view(torch.float4_e2m1fn_x2)
+            sw = torch.randint(118, 130, (nloc, K // 32), dtype=torch.uint8, device=dev).view(E8)
+            sw_p = torch.ops._vxk.mx_sf_pack(sw, True, True)
+            fns.append(lambda w=w, sw=sw, sw_p=sw_p: torch.ops._vxk.fp4_gemm_sf(a, w.t(), sa, sw, torch.bfloat16, None, sa_p, sw_p))
         nbytes = M * K // 2 + K * nloc // 2 + 2 * M * nloc + (M + nloc) * K // 32
     elif kind == "block_fp8":
         a = (torch.randn(M, K, device=dev) / 4).to(E4)
@@ -119,7 +132,7 @@ def time_case(kind, M, K, N, dev, rank, world, pk, launches, warmup):
     from vllm_xpu_kernels_b200 import shard
     n0, n1 = shard.column_shard(N, rank, world)
     nloc = n1 - n0
-    wbytes = K * max(nloc, 1) // (2 if kind == "mxfp4" else 1)
+    wbytes = K * max(nloc, 1) // (2 if kind.startswith("mxfp4") else 1)
     setbytes = wbytes + M * K + 2 * M * max(nloc, 1)
     copies = 1 if setbytes > 2 * L2_BYTES else max(2, min(16, int(2 * L2_BYTES // setbytes) + 1))
     graph = M <= 256
@@ -137,7 +150,7 @@ def time_case(kind, M, K, N, dev, rank, world, pk, launches, warmup):
         dist.all_reduce(ts, op=dist.ReduceOp.SUM)
         ms, nbytes = float(tm[0].item()), float(ts[1].item())
     torch.cuda.empty_cache()
-    peak_tf = {"fp8_w8a8": 2.0, "block_fp8": 2.0, "mxfp4": 4.0, "fp8_w8a16": 1.0}[kind] * pk["bf16"] * world
+    peak_tf = {"fp8_w8a8": 2.0, "block_fp8": 2.0, "mxfp4": 4.0, "mxfp4_sf": 4.0, "fp8_w8a16": 1.0}[kind] * pk["bf16"] * world
     flops = 2.0 * M * N * K
     t_tensor = flops / (peak_tf * 1e12)
     t_hbm = nbytes / (pk["hbm"] * world * 1e9)
@@ -162,11 +175,17 @@ def bench_gemms(dev, rank, world, pk, launches=100, warmup=10, m_tokens=8192, se
 
     torch.manual_seed(1234)
     M = m_tokens
-    rows70, rows5, rows3 = [], [], []
+    rows70, rows5, rows3, rows4 = [], [], [], []
     if "70b" in sets:
         for (K, N) in LLAMA70B_KN:
             for kind in ("fp8_w8a8", "mxfp4", "fp8_w8a16"):
                 rows70.append(time_case(kind, M, K, N, dev, rank, world, pk, launches, warmup))
+        # the same MXFP4 GEMM with both scale grids already in the tensor core's layout (no re-packing launches)
+        rows70.append(time_case("mxfp4_sf", M, LLAMA70B_KN[0][0], LLAMA70B_KN[0][1], dev, rank, world, pk, launches, warmup))
+        # config 4 in the decode regime (swap-AB split-K MXFP4 kernel)
+        for (K, N) in LLAMA70B_KN:
+            for m in (1, 64):
+                rows4.append(time_case("mxfp4", m, K, N, dev, rank, world, pk, launches, warmup))
     if "dsv3" in sets:
         for (K, N) in DSV3_KN:
             rows5.append(time_case("block_fp8", M, K, N, dev, rank, world, pk, launches, warmup))
@@ -175,7 +194,8 @@ def bench_gemms(dev, rank, world, pk, launches=100, warmup=10, m_tokens=8192, se
             for m in (1, 256, M):
                 rows3.append(time_case("fp8_w8a8", m, K, N, dev, rank, world, pk, launches, warmup))
     tc, fb = stats()
-    return {"llama70b_m8192": rows70, "dsv3_block_fp8_m8192": rows5, "llama8b_w8a8_m_sweep": rows3,
+    return {"llama70b_m8192": rows70, "llama70b_mxfp4_decode": rows4, "dsv3_block_fp8_m8192": rows5,
+            "llama8b_w8a8_m_sweep": rows3,
             "kernels": KERNEL_OF, "tensor_core_calls": tc, "fallback_calls": fb,
             "peak_source": pk["src"] + " bf16 cuBLAS x2 (fp8) / x4 (fp4) / x1 (fp8_w8a16: bf16 MMA); "
                            "hbm = " + pk["src"] + " copy bandwidth",

@@ -498,3 +498,26 @@ def test_ops_on_second_device_after_first(ops):
         q, s = ops.rms_norm_dynamic_per_token_quant(xr, wr, 1e-6, E4)
         rq, rs, _ = oq.rms_norm_dynamic_per_token_quant(xr.cpu(), wr.cpu(), 1e-6, E4, exact_variance=True)
         assert torch.equal(s.cpu(), rs)
+
+
+@pytest.mark.parametrize("k", [1024, 1280, 4096, 8192])
+@pytest.mark.parametrize("n", [128, 1000, 4096])
+@pytest.mark.parametrize("m", [1, 7, 33, 64, 100, 128])
+def test_mxfp4_skinny_decode_kernel(ops, lib, m, n, k):
+    """M <= 128: the swap-AB split-K MXFP4 kernel (gemm_skinny_mx4.cuh) straight from the natural scale tensors;
+    ragged N, K slices that do not fill the last ring stage (1280 = 5 x 256), bias, both output types."""
+    torch.manual_seed(m * 131 + n + k)
+    x = torch.randn(m, k, dtype=torch.bfloat16, device=DEV)
+    w = torch.randn(n, k, dtype=torch.bfloat16, device=DEV) * 0.05
+    xq, xs = ops.per_token_group_quant_mxfp4(x)
+    wq, ws = ops.per_token_group_quant_mxfp4(w)
+    bias = torch.randn(n, dtype=torch.bfloat16, device=DEV)
+    tc0, fb0 = gemm_stats(lib)
+    out = ops.fp4_gemm(xq, wq.t(), xs, ws, torch.bfloat16, bias)
+    out16 = ops.fp4_gemm(xq, wq.t(), xs, ws, torch.float16)
+    tc1, fb1 = gemm_stats(lib)
+    assert (tc1, fb1) == (tc0 + 2, fb0)
+    ref = _mx4_deq(xq, xs).double() @ _mx4_deq(wq, ws).double().t()
+    tol = 1e-2 * float(ref.abs().max())
+    torch.testing.assert_close(out.double(), (ref + bias.double()).to(torch.bfloat16).double(), atol=tol, rtol=1e-2)
+    torch.testing.assert_close(out16.double(), ref.to(torch.float16).double(), atol=tol, rtol=1e-2)

@@ -2,6 +2,7 @@
 // canonicalisation, launch of the tcgen05 kernels (gemm_tc.cuh) or of the CUDA-core
 // fallback (gemm_fallback.cu), and the two C-ABI entry points.
 #include "gemm_tc2_blk.cuh"
+#include "gemm_skinny_mx4.cuh"
 #include "gemm_skinny.cuh"
 
 
@@ -427,6 +428,75 @@ static int run_skinny_f8(const TcParams& tp, const void* A, const void* W, int64
   }
 }
 
+// Small-M MXFP4 GEMM (M <= 128).  See gemm_skinny_mx4.cuh.
+template <int MT>
+static int launch_skinny_mx4(SkinnyMx4Params sp, const CUtensorMap& mw, const CUtensorMap& ma, const CUtensorMap& msw,
+                             const CUtensorMap& msa, int n_tiles, cudaStream_t st) {
+  using L = SkinnyMx4Smem<MT>;
+  auto kernel = gemm_skinny_mx4_kernel<MT>;
+  static PerDeviceOnce once;
+  const cudaError_t attr_err = once.get([&](PerDeviceOnce::Entry& x) {
+    x.err = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotalBytes);
+  }).err;
+  if (attr_err != cudaSuccess)
+    return fail(VXK_ERR_CUDA, "cudaFuncSetAttribute(smem=%d): %s", L::kTotalBytes, cudaGetErrorString(attr_err));
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(n_tiles, sp.splits, 1);
+  cfg.blockDim = dim3(kSkinnyThreads);
+  cfg.dynamicSmemBytes = L::kTotalBytes;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[2];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 1;
+  attr[0].val.clusterDim.y = sp.splits;
+  attr[0].val.clusterDim.z = 1;
+  static const int pdl = env_int("VXK_SKINNY_PDL", 1);
+  attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[1].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl ? 2 : 1;
+  const cudaError_t e = cudaLaunchKernelEx(&cfg, kernel, sp, mw, ma, msw, msa);
+  if (e != cudaSuccess) return fail(VXK_ERR_CUDA, "gemm_skinny_mx4 launch: %s", cudaGetErrorString(e));
+  g_gemm_tc_calls.fetch_add(1, std::memory_order_relaxed);
+  return check_launch("gemm_skinny_mx4");
+}
+
+// A: [M, K/2] bytes, W: [N, K/2] bytes, scales natural [rows, K/32] bytes with 16-byte aligned rows
+static int run_skinny_mx4(const TcParams& tp, const void* A, const void* W, const void* sa, const void* sw, int64_t M,
+                          int64_t N, int64_t K, int64_t lda, int64_t ldw, int64_t sa0, int64_t sw0, cudaStream_t st) {
+  SkinnyMx4Params sp{};
+  sp.D = tp.D; sp.bias = tp.bias; sp.M = (int)M; sp.N = (int)N; sp.ldd = tp.ldd;
+  sp.out_dtype = tp.out_dtype; sp.bias_dtype = tp.bias_dtype;
+  sp.num_k_blocks = tp.num_k_blocks;
+  const int n_tiles = (int)((N + 127) / 128);
+  static const int env_splits = env_int("VXK_SKINNY_SPLITS", 0);
+  const int mt = M <= 32 ? 32 : (M <= 64 ? 64 : 128);
+  constexpr int ks = 2;
+  int splits = sm_count() / n_tiles;
+  if (splits > 8) splits = 8;
+  if (env_splits > 0) splits = env_splits > 8 ? 8 : env_splits;
+  const int max_by_k = sp.num_k_blocks / (2 * ks);
+  if (splits > max_by_k) splits = max_by_k;
+  if (splits < 1) splits = 1;
+  while (splits & (splits - 1)) --splits;   // cluster sizes 1 / 2 / 4 / 8
+  int per = (sp.num_k_blocks + splits - 1) / splits;
+  per = (per + ks - 1) / ks * ks;
+  splits = (sp.num_k_blocks + per - 1) / per;          // no empty rank
+  sp.kb_per_split = per;
+  sp.splits = splits;
+  CUtensorMap mw, ma, msw, msa;
+  int rc;
+  if ((rc = make_map_2d_u8(&mw, W, K / 2, N, ldw, kBlockKBytes, 128, true))) return rc;
+  if ((rc = make_map_2d_u8(&ma, A, K / 2, M, lda, kBlockKBytes, mt, true))) return rc;
+  if ((rc = make_map_2d_u8(&msw, sw, K / 32, N, sw0, 16, 128, false))) return rc;
+  if ((rc = make_map_2d_u8(&msa, sa, K / 32, M, sa0, 16, mt, false))) return rc;
+  switch (mt) {
+    case 32: return launch_skinny_mx4<32>(sp, mw, ma, msw, msa, n_tiles, st);
+    case 64: return launch_skinny_mx4<64>(sp, mw, ma, msw, msa, n_tiles, st);
+    default: return launch_skinny_mx4<128>(sp, mw, ma, msw, msa, n_tiles, st);
+  }
+}
+
 }  // namespace vxk
 
 using namespace vxk;
@@ -678,6 +748,11 @@ static int fp4_gemm_impl(void* D, const void* A, const void* B, const void* a_sc
   tp.num_k_blocks = (int)((K / 2 + kBlockKBytes - 1) / kBlockKBytes);
   tp.vec_store_ok = aligned16(D) && (ldd * 2) % 16 == 0;
   for (int i = 0; i < peers.n; ++i) tp.vec_store_ok = tp.vec_store_ok && aligned16(peers.ptr[i]);
+  // decode regime: swap-AB split-K kernel straight from the caller's scale tensors
+  static const int skinny_mx4 = env_int("VXK_SKINNY_MX4", 1);
+  // (65..128 tokens: only while the 128-row weight tiles fit one wave -- measured, profiles/r02_mxfp4_smallm.txt)
+  if (skinny_mx4 && peers.n == 0 && K >= 1024 && scales_direct && (M <= 64 || (M <= 128 && (N + 127) / 128 <= sm_count())))
+    return run_skinny_mx4(tp, A, B, a_scale, b_scale, M, N, K, lda_bytes, ldb_bytes, sa0, sb0, st);
   const bool ws_ok = (a_packed && b_packed) || (workspace && workspace_bytes >= vxk_fp4_gemm_workspace_bytes(M, N, K));
   if (!force_single() && (prefer_pair(M, N, bn, 192) || peers.n > 0) && ws_ok) {
     Tc2Params t2{};
