@@ -21,7 +21,7 @@
 extern "C" {
 #endif
 
-#define VXK_ABI_VERSION 5
+#define VXK_ABI_VERSION 6
 
 typedef struct CUstream_st* vxk_stream_t; /* == cudaStream_t */
 
@@ -269,6 +269,33 @@ int vxk_silu_and_mul_mxfp4_quant_sf(void* out, const void* in, float* scales, vo
                                     int64_t ss1, int in_dtype, vxk_stream_t stream);
 /* Scale re-packing launches issued so far by the GEMM entry points (testing aid). */
 uint64_t vxk_sf_pack_launches(void);
+
+/* ------------------------------------------------------- (f) next #4 ---
+ * MoE grouped GEMM.
+ * ref: cutlass_grouped_gemm_interface  csrc/xpu/grouped_gemm/grouped_gemm_interface.cpp:12-59
+ *      -> cutlass_grouped_gemm_xe2_impl  csrc/xpu/grouped_gemm/xe_2/grouped_gemm_xe2_interface.hpp:160-357,
+ *      schema csrc/xpu/torch_bindings.cpp:41-53, recipes vllm_xpu_kernels/fused_moe_interface.py:32-45
+ *
+ *   for every expert e (rows of A / D are grouped by expert, in expert order):
+ *     D[r0_e : r0_e + rows_per_expert[e], :] = A[same rows, :] x dequant(B[e]) (+ bias[e, :])
+ *   A [total_m, K] and D [total_m, N] contiguous, act_dtype (VXK_BF16 / VXK_F16); fp32 accumulation.
+ *   rows_per_expert: int32 [num_experts] ON THE DEVICE (never read by the host); rows past the sum are left
+ *   untouched.
+ *   weight_kind / B / scales:
+ *     VXK_MOE_W16       B [E, K, N] of act_dtype, scales ignored                        (recipe "bf16")
+ *     VXK_MOE_FP8_E4M3 / _E5M2   B [E, K, N] FP8 bytes, scales fp32 [E] (per expert)       (recipe "fp8")
+ *     VXK_MOE_MXFP4     B [E, N, K/2] packed E2M1 (even k in the low nibble), scales uint8 E8M0 [E, N, K/32];
+ *                       a weight is table(code) * 2^(s-127), both factors and the product in act_dtype
+ *                       (tests/fused_moe/test_grouped_gemm.py:341-377)                   (recipe "mxfp4")
+ *   bias: nullable, [E, N] of act_dtype.  N % 8 == 0 (grouped_gemm_xe2_interface.hpp:178).
+ *   The INT4 recipe of the reference op is out of scope (INT4 GEMMs).
+ *   force_fallback: testing aid, non-zero routes the call to the CUDA-core kernel.
+ */
+enum { VXK_MOE_W16 = 0, VXK_MOE_FP8_E4M3 = 1, VXK_MOE_FP8_E5M2 = 2, VXK_MOE_MXFP4 = 3 };
+int vxk_moe_grouped_gemm(void* D, const void* A, const void* B, const void* scales, const void* bias,
+                         const int32_t* rows_per_expert, int64_t total_m, int64_t N, int64_t K,
+                         int64_t num_experts, int act_dtype, int weight_kind, int force_fallback,
+                         vxk_stream_t stream);
 
 /* ------------------------------------------------------- (f) next #1 ---
  * ref: fp8_gemm_w8a16  csrc/xpu/onednn/onednn_matmul.cpp:81-99 -> dnnl_matmul_w8a16_fp8

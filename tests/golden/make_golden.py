@@ -298,6 +298,65 @@ def main():
                                   cu_seq_lens=cu, cache=cache.clone(), dst_k=dst_k, dst_scale=dst_s))
     g["f3_indexer_k_cache"] = cases
 
+    # ---- (f)#4 MoE grouped GEMM: the reference test's own dequantize_mxfp4 (tests/fused_moe/test_grouped_gemm.py:341-377)
+    # called unmodified (its device="xpu" constants redirected to the CPU), and the literal expected-output loops of
+    # test_xe_grouped_gemm / _fp8 / _mxfp4 (:131-146, :175-218, :424-442)
+    fmi = types.ModuleType("vllm_xpu_kernels.fused_moe_interface")
+    fmi.cutlass_grouped_gemm = fmi.cutlass_grouped_gemm_xe2 = None
+    sys.modules["vllm_xpu_kernels.fused_moe_interface"] = fmi
+    import tests.fused_moe.test_grouped_gemm as t_gg
+
+    class _CpuTorch:
+        def __getattr__(self, name):
+            return getattr(torch, name)
+
+        @staticmethod
+        def tensor(*a, **kw):
+            kw.pop("device", None)
+            return torch.tensor(*a, **kw)
+    t_gg.torch = _CpuTorch()
+
+    def expected(a, w_kn, bias, rows):
+        ref, pre = [], 0
+        for i in range(len(rows)):
+            r = int(rows[i])
+            if r == 0:
+                continue
+            acc = a[pre:pre + r].to(torch.float32) @ w_kn[i].to(torch.float32)
+            if bias is not None:
+                acc += bias[i]
+            ref.append(acc.to(a.dtype))
+            pre += r
+        return torch.cat(ref, dim=0)
+
+    cases = []
+    for dtype in (torch.bfloat16, torch.float16):
+        for has_bias in (False, True):
+            torch.manual_seed(7)
+            E, m, n, k = 4, 24, 64, 128
+            rows = torch.tensor([5, 0, 12, 7], dtype=torch.int32)
+            a = torch.randn(m, k, dtype=dtype)
+            bias = torch.randn(E, n, dtype=dtype) * 100 if has_bias else None
+            # bf16 recipe
+            b16 = torch.randn(E, k, n, dtype=dtype)
+            cases.append(dict(kind="bf16", a=a, b=b16, scales=None, bias=bias, rows=rows,
+                              out=expected(a, b16, bias, rows)))
+            # fp8 recipe: static quant x * (1/s) (scaled_fp8_quant with a given scale), power-of-two scales (:176-190)
+            for qd in (E4, E5):
+                sc = torch.pow(2.0, torch.randint(-3, 4, (E,)).float())
+                bq = torch.stack([(b16[i].float() * (1.0 / sc[i])).clamp(-torch.finfo(qd).max, torch.finfo(qd).max).to(qd)
+                                  for i in range(E)])
+                deq = torch.stack([(bq[i].to(torch.float32) * sc[i]).to(dtype) for i in range(E)])
+                cases.append(dict(kind="fp8", qdtype=str(qd), a=a, b=u8(bq), scales=sc, bias=bias, rows=rows,
+                                  out=expected(a, deq, bias, rows)))
+            # mxfp4 recipe (:392-442)
+            bq4 = torch.randint(0, 0xff, (E, n, k // 2)).to(torch.uint8)
+            sc4 = torch.randint(0, 0x7f, (E, n, k // 32), dtype=torch.uint8)
+            w16 = torch.stack([t_gg.dequantize_mxfp4(bq4[i], sc4[i], 32, dtype) for i in range(E)])
+            cases.append(dict(kind="mxfp4", a=a, b=bq4, scales=sc4, bias=bias, rows=rows, w16=w16,
+                              out=expected(a, w16.transpose(1, 2), bias, rows)))
+    g["f4_grouped_gemm"] = cases
+
     # ---- silu on EVERY 16-bit input, through the reference's own ref function
     # (test_fused_quant_activation.py:28-40: ref_silu_and_mul_quant = F.silu(gate) * up in x.dtype;
     # with up = 1 and scale = 1 the e4m3 cast is the only other step, so the table is taken from

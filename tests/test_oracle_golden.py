@@ -262,3 +262,23 @@ def test_convert_fp8_oracle_round_trip():
     q = ocache.convert_fp8(x, 0.5, "fp8", torch.uint8)
     ref = (x.float() / 0.5).clamp(-448, 448).to(E4).view(torch.uint8)
     assert torch.equal(q, ref)
+
+
+def test_f4_grouped_gemm_golden():
+    """(f)#4: oracle/moe.py equals the reference test's expected outputs bit for bit
+    (tests/fused_moe/test_grouped_gemm.py: dequantize_mxfp4 called unmodified, the three expected-output loops)."""
+    from oracle import moe
+    for c in load("f4_grouped_gemm"):
+        a, rows = c["a"], c["rows"]
+        n_used = int(rows.sum())
+        if c["kind"] == "fp8":
+            qd = E4 if "e4m3" in c["qdtype"] else E5
+            out = moe.grouped_gemm(a, c["b"].view(qd), c["scales"], c["bias"], rows, "fp8")
+        else:
+            out = moe.grouped_gemm(a, c["b"], c["scales"], c["bias"], rows, c["kind"])
+        if c["kind"] == "mxfp4":
+            for e in range(c["b"].shape[0]):
+                w = moe.dequantize_mxfp4(c["b"][e], c["scales"][e], 32, a.dtype)
+                assert torch.equal(w.view(torch.int16), c["w16"][e].view(torch.int16))
+        assert torch.equal(out[:n_used].view(torch.int16), c["out"].view(torch.int16)), (c["kind"], a.dtype)
+        assert not out[n_used:].any()

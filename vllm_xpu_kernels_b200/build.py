@@ -37,6 +37,7 @@ CU_SOURCES = {
     "gemm_fallback.cu": [],
     "gemm_tc.cu": [],
     "gemm_w8a16.cu": [],
+    "gemm_grouped.cu": [],
 }
 # every header under csrc/ feeds every object's digest (a header missing here means stale objects)
 HEADERS = sorted(f for f in os.listdir(CSRC) if f.endswith((".cuh", ".h"))) + [os.path.join(ROOT, "include", "vxk_b200.h")]

@@ -1,0 +1,403 @@
+// MoE grouped GEMM on tcgen05 (device side): for every expert e
+//
+//   D[rows of e, :] = A[rows of e, :] * dequant(B[e]) (+ bias[e])          A, D: bf16 / f16, fp32 accumulate
+//
+//   ref: cutlass_grouped_gemm_interface  csrc/xpu/grouped_gemm/grouped_gemm_interface.cpp:12-59
+//        -> cutlass_grouped_gemm_xe2_impl  csrc/xpu/grouped_gemm/xe_2/grouped_gemm_xe2_interface.hpp:160-357
+//        recipes (vllm_xpu_kernels/fused_moe_interface.py:32-45): "bf16" (16-bit weights [E, K, N]),
+//        "fp8" (e4m3 / e5m2 weights [E, K, N] + one fp32 scale per expert), "mxfp4" (packed E2M1 weights
+//        [E, N, K/2] + E8M0 scale bytes [E, N, K/32]); activations stay 16-bit in all of them.
+//
+// rows_per_expert lives on the device (no host sync), so the tile list is built inside the kernel: every CTA
+// scans rows_per_expert once (warp 3), and all roles walk the same persistent tile sequence
+//   tile = (expert e, token tile t of MT rows, weight tile of 128 output columns)
+// ordered so that consecutive CTAs share the weight tile (t fastest).
+//
+// Operands are swapped like the small-M kernels (UMMA M = 128 weight rows, UMMA N = MT tokens, the accumulator is
+// D^T): a token tile may start at any row (TMA box at an arbitrary row coordinate; rows of the next expert that
+// ride along are computed and never stored), MT is chosen from the average rows per expert like the reference's
+// policies (grouped_gemm_xe2_interface.hpp:275-357), and a warp's D^T rows are consecutive output columns, so the
+// epilogue's stores are contiguous.
+//
+//   warp 0      TMA producer: weight tile + MT x 64 activation box of one 64-deep K slice per ring stage
+//   warp 1      MMA issuer: tcgen05.mma.kind::f16 128 x MT x 16, four per stage, two TMEM accumulators
+//   warp 2      TMEM allocator          warp 3  tile-list scan
+//   warps 4-7   epilogue: tcgen05.ld, per-expert scale, bias, 16-bit, lane pairs swap so a lane stores 2 columns
+//   warps 8-15  converters (fp8 / mxfp4 only): raw tile -> 16-bit operand tile (exact widening)
+//
+// Weight operand layouts:
+//   [E, K, N] weights (16-bit, fp8) are N-contiguous = "MN-major" for the tensor core: the operand tile is
+//   [2 blocks of 64 columns][64 k rows][128 B], SWIZZLE_128B; for 16-bit weights TMA writes it directly
+//   (two boxes), for fp8 the converters write it from a raw 64 x 128 B box.
+//   [E, N, K/2] mxfp4 weights are K-contiguous: raw box 128 rows x 32 B, widened into the usual K-major tile; the
+//   E8M0 scale is folded into the widening (value * 2^(s-127) is exact in bf16; for f16 the product is rounded
+//   the way the reference test dequantises, tests/fused_moe/test_grouped_gemm.py:341-377).
+#pragma once
+
+#include "gemm_w8a16.cuh"
+
+namespace vxk {
+
+constexpr int GW_16 = 0, GW_FP8 = 1, GW_MX4 = 2;
+constexpr int kGgBlockK = 64;
+constexpr int kGgMaxExperts = 1024;
+
+struct GroupedParams {
+  void* D;
+  const void* bias;        // [E, N] activation dtype, or null
+  const float* w_scale;    // GW_FP8: [E]
+  const uint8_t* w_sf;     // GW_MX4: [E, N, K / 32]
+  const int32_t* rows;     // [E]
+  int total_m, N, K, E;
+  int num_kb, num_nt;
+  int64_t ldd;
+};
+
+__device__ __forceinline__ void tma_load_3d(void* smem_dst, const CUtensorMap* m, uint64_t* bar, int c0, int c1,
+                                            int c2) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+      ::"r"(smem_u32(smem_dst)), "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2)
+      : "memory");
+}
+
+// MN-major operand tile, SWIZZLE_128B: 64-element column blocks `lbo` bytes apart, groups of 8 k rows 1024 B apart
+__device__ __forceinline__ uint64_t make_mnmajor_sw128_desc(uint32_t smem_addr, uint32_t lbo) {
+  uint64_t d = 0;
+  d |= static_cast<uint64_t>((smem_addr >> 4) & 0x3fffu);
+  d |= static_cast<uint64_t>((lbo >> 4) & 0x3fffu) << 16;
+  d |= static_cast<uint64_t>(1024u >> 4) << 32;
+  d |= static_cast<uint64_t>(1) << 46;
+  d |= static_cast<uint64_t>(2) << 61;
+  return d;
+}
+
+// 8 E2M1 codes (one 32-bit word, even element in the low nibble) -> four packed 16-bit pairs, times the group
+// scale `sc2` (packed pair of the activation type)
+template <bool BF16>
+__device__ __forceinline__ void e2m1x8_widen(uint32_t word, uint32_t sc2, uint32_t (&w)[4]) {
+  uint32_t h[4];
+  asm("{\n\t.reg .b8 b0, b1, b2, b3;\n\tmov.b32 {b0, b1, b2, b3}, %4;\n\t"
+      "cvt.rn.f16x2.e2m1x2 %0, b0;\n\tcvt.rn.f16x2.e2m1x2 %1, b1;\n\t"
+      "cvt.rn.f16x2.e2m1x2 %2, b2;\n\tcvt.rn.f16x2.e2m1x2 %3, b3;\n\t}"
+      : "=r"(h[0]), "=r"(h[1]), "=r"(h[2]), "=r"(h[3])
+      : "r"(word));
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    if constexpr (BF16) {
+      // f16 -> bf16 bit positions (every E2M1 value is a normal f16 or zero), re-bias by 2^112, then the scale
+      const uint32_t t = ((h[i] >> 3) & 0x0fff0fffu) | (h[i] & 0x80008000u);
+      uint32_t u;
+      asm("mul.rn.bf16x2 %0, %1, %2;" : "=r"(u) : "r"(t), "r"(0x77807780u));
+      asm("mul.rn.bf16x2 %0, %1, %2;" : "=r"(w[i]) : "r"(u), "r"(sc2));
+    } else {
+      asm("mul.rn.f16x2 %0, %1, %2;" : "=r"(w[i]) : "r"(h[i]), "r"(sc2));
+    }
+  }
+}
+
+template <int MT, int WKIND>
+struct GgSmem {
+  static constexpr bool kConv = WKIND != GW_16;
+  static constexpr int kOpBytes = 128 * 128;            // 128 weight rows x 64 elements of 16 bits
+  static constexpr int kRawW = WKIND == GW_16 ? kOpBytes : (WKIND == GW_FP8 ? 64 * 128 : 128 * 32);
+  static constexpr int kABox = MT * 128;
+  static constexpr int kStageBytes = (kRawW + kABox + 1023) / 1024 * 1024;
+  static constexpr int kTxBytes = kRawW + kABox;
+  static constexpr int kConvSlots = kConv ? 3 : 0;
+  static constexpr int kSchedBytes = 2 * (kGgMaxExperts + 1) * 4;
+  static constexpr int kStagesRaw = (220 * 1024 - kConvSlots * kOpBytes - kSchedBytes) / kStageBytes;
+  static constexpr int kStages = kStagesRaw > 10 ? 10 : kStagesRaw;
+  static constexpr int kBarrierBytes = (2 * kStages + 2 * 3 + 4) * 8 + 16;
+  static constexpr int kTotalBytes = kStages * kStageBytes + kConvSlots * kOpBytes + kBarrierBytes + kSchedBytes + 1024;
+  static_assert(kStages >= 3, "ring too shallow");
+};
+
+struct GgTile { int e, row0, rows, n0; };
+
+template <int MT>
+__device__ __forceinline__ GgTile gg_tile(const int* tile_start, const int* row_start, int E, int num_nt, int idx) {
+  int lo = 0, hi = E - 1;                     // smallest e whose linear range ends after idx
+  while (lo < hi) {
+    const int mid = (lo + hi) >> 1;
+    if (tile_start[mid + 1] * num_nt > idx) hi = mid; else lo = mid + 1;
+  }
+  const int e = lo;
+  const int te = tile_start[e + 1] - tile_start[e];
+  const int local = idx - tile_start[e] * num_nt;
+  const int nt = local / te, t = local - nt * te;
+  const int rows_e = row_start[e + 1] - row_start[e];
+  GgTile r;
+  r.e = e;
+  r.row0 = row_start[e] + t * MT;
+  r.rows = min(MT, rows_e - t * MT);
+  r.n0 = nt * 128;
+  return r;
+}
+
+template <int MT, int WKIND, bool BF16, bool E5M2>
+__global__ void __launch_bounds__(WKIND == GW_16 ? 256 : 512, 1)
+gemm_grouped_kernel(const GroupedParams p, const __grid_constant__ CUtensorMap map_w,
+                    const __grid_constant__ CUtensorMap map_a) {
+  using L = GgSmem<MT, WKIND>;
+  constexpr int S = L::kStages;
+  constexpr int C = L::kConv ? L::kConvSlots : 1;
+  constexpr bool kMnMajor = WKIND != GW_MX4;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  auto stage_w = [&](int s) { return smem + s * L::kStageBytes; };
+  auto stage_a = [&](int s) { return smem + s * L::kStageBytes + L::kRawW; };
+  uint8_t* conv_base = smem + S * L::kStageBytes;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(conv_base + L::kConvSlots * L::kOpBytes);
+  uint64_t* full_bar = bars;
+  uint64_t* empty_bar = bars + S;
+  uint64_t* conv_full = bars + 2 * S;
+  uint64_t* conv_empty = bars + 2 * S + 3;
+  uint64_t* tmem_full_bar = bars + 2 * S + 6;
+  uint64_t* tmem_empty_bar = bars + 2 * S + 8;
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(bars + 2 * S + 10);
+  int* tile_start = reinterpret_cast<int*>(reinterpret_cast<uint8_t*>(bars) + L::kBarrierBytes);
+  int* row_start = tile_start + (kGgMaxExperts + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&map_w);
+    tma_prefetch_desc(&map_a);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int i = 0; i < S; ++i) {
+      mbar_init(&full_bar[i], 1);
+      mbar_init(&empty_bar[i], 1);
+    }
+    for (int i = 0; i < 3; ++i) {
+      mbar_init(&conv_full[i], 8);
+      mbar_init(&conv_empty[i], 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&tmem_full_bar[i], 1);
+      mbar_init(&tmem_empty_bar[i], 128);
+    }
+    fence_barrier_init();
+  }
+  constexpr uint32_t kCols = 2 * MT < 32 ? 32 : 2 * MT;
+  if (warp == 2) tmem_alloc<kCols>(tmem_ptr_smem);
+  if (warp == 3) {
+    // exclusive prefix sums of rows and of token tiles per expert
+    int carry_r = 0, carry_t = 0;
+    for (int base = 0; base < p.E; base += 32) {
+      const int e = base + lane;
+      int r = e < p.E ? __ldg(p.rows + e) : 0;
+      r = r < 0 ? 0 : r;
+      int sr = r, stl = (r + MT - 1) / MT;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const int a = __shfl_up_sync(0xffffffffu, sr, o), b = __shfl_up_sync(0xffffffffu, stl, o);
+        if (lane >= o) { sr += a; stl += b; }
+      }
+      if (e < p.E) {
+        row_start[e + 1] = carry_r + sr;
+        tile_start[e + 1] = carry_t + stl;
+      }
+      carry_r += __shfl_sync(0xffffffffu, sr, 31);
+      carry_t += __shfl_sync(0xffffffffu, stl, 31);
+    }
+    if (lane == 0) { row_start[0] = 0; tile_start[0] = 0; }
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr_smem;
+  const int num_tiles = tile_start[p.E] * p.num_nt;
+
+  if (warp == 0) {
+    // ===================== TMA producer =====================
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int idx = blockIdx.x; idx < num_tiles; idx += gridDim.x) {
+      const GgTile t = gg_tile<MT>(tile_start, row_start, p.E, p.num_nt, idx);
+      for (int kb = 0; kb < p.num_kb; ++kb) {
+        mbar_wait(&empty_bar[stage], phase ^ 1);
+        if (elect_one()) {
+          mbar_arrive_expect_tx(&full_bar[stage], L::kTxBytes);
+          if constexpr (WKIND == GW_16) {        // byte coordinates: (column bytes, k, expert)
+            tma_load_3d(stage_w(stage), &map_w, &full_bar[stage], t.n0 * 2, kb * kGgBlockK, t.e);
+            tma_load_3d(stage_w(stage) + 8192, &map_w, &full_bar[stage], t.n0 * 2 + 128, kb * kGgBlockK, t.e);
+          } else if constexpr (WKIND == GW_FP8) {
+            tma_load_3d(stage_w(stage), &map_w, &full_bar[stage], t.n0, kb * kGgBlockK, t.e);
+          } else {                                // (k bytes, weight row, expert)
+            tma_load_3d(stage_w(stage), &map_w, &full_bar[stage], kb * (kGgBlockK / 2), t.n0, t.e);
+          }
+          tma_load_2d(stage_a(stage), &map_a, &full_bar[stage], kb * 128, t.row0);
+        }
+        __syncwarp();
+        if (++stage == S) { stage = 0; phase ^= 1; }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer: D^T[128 x MT] += W16[128 x 16] * A[MT x 16]^T =====================
+    const uint32_t idesc = make_idesc_f16(BF16 ? 1 : 0, 128, MT) | (kMnMajor ? (1u << 15) : 0u);
+    int stage = 0, cs = 0, iter = 0;
+    uint32_t phase = 0, cphase = 0;
+    for (int idx = blockIdx.x; idx < num_tiles; idx += gridDim.x, ++iter) {
+      const int as = iter & 1;
+      const uint32_t aphase = (iter >> 1) & 1;
+      mbar_wait(&tmem_empty_bar[as], aphase ^ 1);
+      tc_fence_after();
+      const uint32_t tmem_d = tmem_base + as * MT;
+      for (int kb = 0; kb < p.num_kb; ++kb) {
+        mbar_wait(&full_bar[stage], phase);
+        if constexpr (L::kConv) mbar_wait(&conv_full[cs], cphase);
+        tc_fence_after();
+        if (elect_one()) {
+          const uint32_t w_addr = L::kConv ? smem_u32(conv_base + cs * L::kOpBytes) : smem_u32(stage_w(stage));
+          const uint64_t dw = kMnMajor ? make_mnmajor_sw128_desc(w_addr, 8192) : make_kmajor_sw128_desc(w_addr);
+          const uint64_t da = make_kmajor_sw128_desc(smem_u32(stage_a(stage)));
+#pragma unroll
+          for (int k = 0; k < 4; ++k)             // 16 k per MMA: 2 groups of 8 k rows (MN-major) / 32 B (K-major)
+            umma_f16(tmem_d, dw + static_cast<uint64_t>(kMnMajor ? 128 * k : 2 * k), da + static_cast<uint64_t>(2 * k),
+                     idesc, (kb > 0 || k > 0) ? 1u : 0u);
+          if constexpr (L::kConv) umma_commit(&conv_empty[cs]);
+          umma_commit(&empty_bar[stage]);
+          if (kb == p.num_kb - 1) umma_commit(&tmem_full_bar[as]);
+        }
+        __syncwarp();
+        if constexpr (L::kConv) { if (++cs == C) { cs = 0; cphase ^= 1; } }
+        if (++stage == S) { stage = 0; phase ^= 1; }
+      }
+    }
+  } else if (warp >= 8) {
+    // ===================== converters =====================
+    if constexpr (L::kConv) {
+      const int ct = threadIdx.x - 256;          // 0..255
+      int stage = 0, cs = 0;
+      uint32_t phase = 0, cphase = 0;
+      for (int idx = blockIdx.x; idx < num_tiles; idx += gridDim.x) {
+        const GgTile t = gg_tile<MT>(tile_start, row_start, p.E, p.num_nt, idx);
+        const uint8_t* sfp = nullptr;
+        if constexpr (WKIND == GW_MX4) {
+          const int n = min(t.n0 + (ct >> 1), p.N - 1);
+          sfp = p.w_sf + (static_cast<int64_t>(t.e) * p.N + n) * (p.K / 32) + (ct & 1);
+        }
+        for (int kb = 0; kb < p.num_kb; ++kb) {
+          uint32_t sc2 = 0;
+          if constexpr (WKIND == GW_MX4) {
+            const uint32_t s = __ldg(sfp + kb * 2);
+            uint32_t h;
+            if constexpr (BF16) {
+              h = s << 7;                        // bf16 bits of 2^(s-127): the reference's (scale << 7).view(bf16)
+            } else {
+              const __half x = __float2half_rn(__uint_as_float(s << 23));
+              h = *reinterpret_cast<const uint16_t*>(&x);
+            }
+            sc2 = h | (h << 16);
+          }
+          mbar_wait(&full_bar[stage], phase);
+          const uint32_t raw = smem_u32(stage_w(stage));
+          if constexpr (WKIND == GW_FP8) {
+            // raw: 64 k rows x 128 column bytes (SWIZZLE_128B); this thread: 16 columns at k0 and k0 + 32
+            const int j = ct & 7, k0 = ct >> 3, sw = k0 & 7;
+            const uint4 v0 = lds128(raw + k0 * 128 + ((j ^ sw) << 4));
+            const uint4 v1 = lds128(raw + (k0 + 32) * 128 + ((j ^ sw) << 4));
+            uint32_t w0[8], w1[8];
+            widen16<BF16, E5M2, false>(v0, 1.0f, w0);
+            widen16<BF16, E5M2, false>(v1, 1.0f, w1);
+            mbar_wait(&conv_empty[cs], cphase ^ 1);
+            const uint32_t dst = smem_u32(conv_base + cs * L::kOpBytes) + (j >> 2) * 8192 + k0 * 128;
+            const uint32_t c0 = ((((j & 3) * 2) ^ sw) << 4), c1 = ((((j & 3) * 2 + 1) ^ sw) << 4);
+            sts128(dst + c0, w0[0], w0[1], w0[2], w0[3]);
+            sts128(dst + c1, w0[4], w0[5], w0[6], w0[7]);
+            sts128(dst + 32 * 128 + c0, w1[0], w1[1], w1[2], w1[3]);
+            sts128(dst + 32 * 128 + c1, w1[4], w1[5], w1[6], w1[7]);
+          } else {
+            // raw: 128 weight rows x 32 bytes (64 codes), linear; this thread: one 32-code scale group
+            const int row = ct >> 1, half = ct & 1, sw = row & 7;
+            const uint4 v = lds128(raw + row * 32 + half * 16);
+            uint32_t w[4][4];
+            e2m1x8_widen<BF16>(v.x, sc2, w[0]);
+            e2m1x8_widen<BF16>(v.y, sc2, w[1]);
+            e2m1x8_widen<BF16>(v.z, sc2, w[2]);
+            e2m1x8_widen<BF16>(v.w, sc2, w[3]);
+            mbar_wait(&conv_empty[cs], cphase ^ 1);
+            const uint32_t dst = smem_u32(conv_base + cs * L::kOpBytes) + row * 128;
+#pragma unroll
+            for (int q = 0; q < 4; ++q)
+              sts128(dst + (((half * 4 + q) ^ sw) << 4), w[q][0], w[q][1], w[q][2], w[q][3]);
+          }
+          fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&conv_full[cs]);
+          if (++cs == C) { cs = 0; cphase ^= 1; }
+          if (++stage == S) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp >= 4) {
+    // ===================== epilogue =====================
+    const int q = warp & 3;
+    const int col = q * 32 + lane;               // D^T row = output column within the tile
+    int iter = 0;
+    for (int idx = blockIdx.x; idx < num_tiles; idx += gridDim.x, ++iter) {
+      const GgTile t = gg_tile<MT>(tile_start, row_start, p.E, p.num_nt, idx);
+      const int as = iter & 1;
+      const uint32_t aphase = (iter >> 1) & 1;
+      const int n = t.n0 + col;
+      const bool n_ok = n < p.N;
+      float sc = 1.0f, bv = 0.0f;
+      if constexpr (WKIND == GW_FP8) sc = __ldg(p.w_scale + t.e);
+      if (p.bias && n_ok) {
+        const int64_t bi = static_cast<int64_t>(t.e) * p.N + n;
+        bv = BF16 ? __bfloat162float(static_cast<const __nv_bfloat16*>(p.bias)[bi])
+                  : __half2float(static_cast<const __half*>(p.bias)[bi]);
+      }
+      // lane pairs (2i, 2i+1) swap so that the even lane stores columns (n, n+1) of even token rows and the odd
+      // lane the same two columns of odd token rows: 4-byte stores, 64 contiguous bytes per row per warp
+      const int n2 = n & ~1;
+      const bool pair_ok = n2 + 1 < p.N;
+      uint16_t* dbase = static_cast<uint16_t*>(p.D) + n2;
+      mbar_wait_backoff(&tmem_full_bar[as], aphase);
+      tc_fence_after();
+#pragma unroll 1
+      for (int c = 0; c < MT / 32; ++c) {
+        if (c * 32 >= t.rows) break;
+        uint32_t r[32];
+        tmem_ld_32x32b_x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * MT + c * 32, r);
+        tmem_ld_wait();
+        uint32_t hv[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+          const float v = fmaf(__uint_as_float(r[j]), sc, bv);
+          if constexpr (BF16) {
+            const __nv_bfloat16 x = __float2bfloat16_rn(v);
+            hv[j] = *reinterpret_cast<const uint16_t*>(&x);
+          } else {
+            const __half x = __float2half_rn(v);
+            hv[j] = *reinterpret_cast<const uint16_t*>(&x);
+          }
+        }
+#pragma unroll
+        for (int j = 0; j < 32; j += 2) {
+          const uint32_t give = (lane & 1) ? hv[j] : hv[j + 1];
+          const uint32_t got = __shfl_xor_sync(0xffffffffu, give, 1);
+          const int tr = c * 32 + j + (lane & 1);            // token row within the tile
+          const uint32_t packed = (lane & 1) ? (got | (hv[j + 1] << 16)) : (hv[j] | (got << 16));
+          if (tr < t.rows && n_ok) {
+            uint16_t* d = dbase + static_cast<int64_t>(t.row0 + tr) * p.ldd;
+            if (pair_ok) *reinterpret_cast<uint32_t*>(d) = packed;
+            else d[0] = static_cast<uint16_t>(packed);
+          }
+        }
+      }
+      tc_fence_before();
+      mbar_arrive(&tmem_empty_bar[as]);
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc<kCols>(tmem_base);
+  }
+}
+
+}  // namespace vxk

@@ -749,6 +749,74 @@ Tensor fp8_gemm_w8a16(const Tensor& A, const Tensor& B, const std::optional<Tens
   return result;
 }
 
+// ref: cutlass_grouped_gemm_interface  csrc/xpu/grouped_gemm/grouped_gemm_interface.cpp:12-59,
+//      argument checks csrc/xpu/grouped_gemm/xe_2/grouped_gemm_xe2_interface.hpp:160-246,303-311,339-341
+Tensor cutlass_grouped_gemm_interface(Tensor ptr_A, Tensor ptr_B, const std::optional<Tensor>& ptr_scales,
+                                      const std::optional<Tensor>& ptr_bias, Tensor ptr_D, Tensor rows_per_expert,
+                                      int64_t N, int64_t K, int64_t num_experts) {
+  check_cuda(ptr_A, "ptr_A");
+  same_device(ptr_A, ptr_B, ptr_scales, ptr_bias);
+  TORCH_CHECK(ptr_D.device() == ptr_A.device() && rows_per_expert.device() == ptr_A.device(),
+              "ptr_D and rows_per_expert must be on ptr_A's device");
+  const c10::cuda::CUDAGuard guard(ptr_A.device());
+  const auto a_st = ptr_A.scalar_type(), b_st = ptr_B.scalar_type();
+  TORCH_CHECK(a_st == at::kBFloat16 || a_st == at::kHalf, "activations must be bfloat16 or float16, got ", a_st);
+  TORCH_CHECK(ptr_D.scalar_type() == a_st, "ptr_D must have the activation dtype");
+  const bool has_scales = ptr_scales.has_value() && ptr_scales->defined();
+  const bool is_fp8 = b_st == at::kFloat8_e4m3fn || b_st == at::kFloat8_e5m2;
+  const bool is_mxfp4 = b_st == at::kFloat4_e2m1fn_x2 && has_scales;
+  TORCH_CHECK(!(b_st == at::kChar && has_scales),
+              "the int4 recipe of cutlass_grouped_gemm_interface is not implemented in the B200 build");
+  TORCH_CHECK(N % 8 == 0, "N must be divisible by 8");
+  TORCH_CHECK(ptr_A.dim() == 2, "ptr_A must be 2D [Total_M, K]");
+  TORCH_CHECK(ptr_B.dim() == 3, "ptr_B must be 3D [num_experts, K, N]");
+  TORCH_CHECK(ptr_D.dim() == 2, "ptr_D must be 2D [Total_M, N]");
+  TORCH_CHECK(ptr_A.is_contiguous() && ptr_B.is_contiguous() && ptr_D.is_contiguous(),
+              "ptr_A, ptr_B and ptr_D must be contiguous");
+  const void* bias = nullptr;
+  if (ptr_bias.has_value() && ptr_bias->defined()) {
+    TORCH_CHECK(ptr_bias->dim() == 2, "ptr_bias must be 2D [num_experts, N]");
+    TORCH_CHECK(ptr_bias->is_contiguous(), "ptr_bias must be contiguous");
+    TORCH_CHECK(ptr_bias->size(0) == num_experts && ptr_bias->size(1) == N, "ptr_bias must be [num_experts, N]");
+    TORCH_CHECK(ptr_bias->scalar_type() == a_st, "ptr_bias must have the activation dtype");
+    bias = ptr_bias->data_ptr();
+  }
+  int64_t B_K = ptr_B.size(1), B_N = ptr_B.size(2);
+  if (is_mxfp4) { B_K = ptr_B.size(2) * 2; B_N = ptr_B.size(1); }      // [E, N, K/2]
+  TORCH_CHECK(ptr_B.size(0) == num_experts, "ptr_B.size(0) must match num_experts");
+  TORCH_CHECK(ptr_A.size(0) == ptr_D.size(0), "ptr_A.size(0) must match ptr_D.size(0)");
+  TORCH_CHECK(ptr_A.size(1) == B_K && B_K == K, "ptr_A.size(1) must match ptr_B.size(1)");
+  TORCH_CHECK(B_N == ptr_D.size(1) && B_N == N, "ptr_B.size(2) must match ptr_D.size(1)");
+  TORCH_CHECK(rows_per_expert.scalar_type() == at::kInt && rows_per_expert.is_contiguous() &&
+                  rows_per_expert.numel() >= num_experts,
+              "rows_per_expert must be a contiguous int32 tensor with num_experts entries");
+  int kind = VXK_MOE_W16;
+  const void* scales = nullptr;
+  if (is_mxfp4) {
+    TORCH_CHECK(ptr_scales->is_contiguous() && ptr_scales->dim() == 3, "ptr_scales must be contiguous [num_experts, N, K / 32]");
+    TORCH_CHECK(ptr_scales->size(0) == num_experts && ptr_scales->size(1) == N && ptr_scales->size(2) * 32 == K,
+                "mxfp4 ptr_scales must be [num_experts, N, K / 32] (group size 32)");
+    TORCH_CHECK(ptr_scales->element_size() == 1, "mxfp4 ptr_scales must be E8M0 bytes (uint8 / float8_e8m0fnu)");
+    kind = VXK_MOE_MXFP4;
+    scales = ptr_scales->data_ptr();
+  } else if (is_fp8) {
+    TORCH_CHECK(has_scales, "w8a16 grouped gemm must have scales");
+    TORCH_CHECK(ptr_scales->is_contiguous() && ptr_scales->dim() == 1 && ptr_scales->size(0) == num_experts,
+                "ptr_scales of fp8 must be 1D [num_experts]");
+    TORCH_CHECK(ptr_scales->scalar_type() == at::kFloat, "ptr_scales must be float");
+    kind = b_st == at::kFloat8_e4m3fn ? VXK_MOE_FP8_E4M3 : VXK_MOE_FP8_E5M2;
+    scales = ptr_scales->data_ptr();
+  } else {
+    TORCH_CHECK(b_st == a_st, "w16a16 grouped gemm: ptr_B must have the activation dtype, got ", b_st);
+    TORCH_CHECK(!has_scales, "w16a16 grouped gemm must not have scales");
+  }
+  check_rc(vxk_moe_grouped_gemm(ptr_D.data_ptr(), ptr_A.data_ptr(), ptr_B.data_ptr(), scales, bias,
+                                rows_per_expert.data_ptr<int32_t>(), ptr_A.size(0), N, K, num_experts,
+                                a_st == at::kBFloat16 ? VXK_BF16 : VXK_F16, kind, 0, cur_stream()),
+           "cutlass_grouped_gemm_interface");
+  return ptr_D;
+}
+
 // ------------------------------------------------------------ _C_cache_ops
 // ref: csrc/cache.cpp:1558-1590
 void indexer_k_quant_and_cache(Tensor& k, Tensor& kv_cache, Tensor& slot_mapping, int64_t quant_block_size,
@@ -886,12 +954,16 @@ TORCH_LIBRARY_FRAGMENT(_xpu_C, xpu_ops) {
   xpu_ops.def("fp8_gemm_w8a16(Tensor A, Tensor B, Tensor? B_scale_, Tensor? bias_) -> Tensor");
   xpu_ops.def("fp4_gemm(Tensor A, Tensor B, Tensor A_scale, Tensor B_scale, ScalarType? out_dtype, "
               "Tensor? bias_) -> Tensor");
+  // csrc/xpu/torch_bindings.cpp:41-53
+  xpu_ops.def("cutlass_grouped_gemm_interface(Tensor ptr_A, Tensor ptr_B, Tensor? ptr_scales, Tensor? ptr_bias, "
+              "Tensor ptr_D, Tensor rows_per_expert, int N, int K, int num_experts) -> Tensor");
 }
 
 TORCH_LIBRARY_IMPL(_xpu_C, CUDA, xpu_ops) {
   xpu_ops.impl("fp8_gemm", &fp8_gemm);
   xpu_ops.impl("fp4_gemm", &fp4_gemm);
   xpu_ops.impl("fp8_gemm_w8a16", &fp8_gemm_w8a16);
+  xpu_ops.impl("cutlass_grouped_gemm_interface", &cutlass_grouped_gemm_interface);
 }
 
 // Extensions without a reference counterpart (scale factors in the tensor core's layout).
