@@ -93,7 +93,7 @@ static int launch_gg(const GroupedParams& gp, const CUtensorMap& mw, const CUten
   if (attr_err != cudaSuccess)
     return fail(VXK_ERR_CUDA, "cudaFuncSetAttribute(smem=%d): %s", L::kTotalBytes, cudaGetErrorString(attr_err));
   const int grid = max_tiles < sm_count() ? static_cast<int>(max_tiles) : sm_count();
-  kernel<<<grid, WKIND == GW_16 ? 256 : 512, L::kTotalBytes, st>>>(gp, mw, ma);
+  kernel<<<grid, WKIND == GW_16 ? 256 : kGgConvThreads, L::kTotalBytes, st>>>(gp, mw, ma);
   g_gemm_tc_calls.fetch_add(1, std::memory_order_relaxed);
   return check_launch("gemm_grouped");
 }
@@ -167,6 +167,9 @@ extern "C" int vxk_moe_grouped_gemm(void* D, const void* A, const void* B, const
   gp.num_kb = static_cast<int>((K + kGgBlockK - 1) / kGgBlockK);
   gp.num_nt = static_cast<int>((N + 127) / 128);
   gp.ldd = N;
+  gp.sf_vec = wkind == GW_MX4 && (K / 32) % 16 == 0 && aligned16(scales);
+  static const int env_dbg = gg_env_int("VXK_GG_DEBUG", 0);
+  gp.dbg = env_dbg;
   const int64_t max_tiles = ((total_m + mt - 1) / mt + num_experts) * gp.num_nt;
   if (max_tiles >= (1LL << 31)) return fail(VXK_ERR_UNSUPPORTED, "grouped GEMM: too many tiles");
 

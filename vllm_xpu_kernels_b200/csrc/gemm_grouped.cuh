@@ -23,7 +23,7 @@
 //   warp 1      MMA issuer: tcgen05.mma.kind::f16 128 x MT x 16, four per stage, two TMEM accumulators
 //   warp 2      TMEM allocator          warp 3  tile-list scan
 //   warps 4-7   epilogue: tcgen05.ld, per-expert scale, bias, 16-bit, lane pairs swap so a lane stores 2 columns
-//   warps 8-15  converters (fp8 / mxfp4 only): raw tile -> 16-bit operand tile (exact widening)
+//   warps 8-23  converters (fp8 / mxfp4 only): raw tile -> 16-bit operand tile (exact widening)
 //
 // Weight operand layouts:
 //   [E, K, N] weights (16-bit, fp8) are N-contiguous = "MN-major" for the tensor core: the operand tile is
@@ -40,7 +40,15 @@ namespace vxk {
 
 constexpr int GW_16 = 0, GW_FP8 = 1, GW_MX4 = 2;
 constexpr int kGgBlockK = 64;
-constexpr int kGgMaxExperts = 1024;
+#ifndef VXK_GG_STAGE_CAP
+#define VXK_GG_STAGE_CAP 10
+#endif
+#ifndef VXK_GG_CONV_SLOTS
+#define VXK_GG_CONV_SLOTS 3
+#endif
+constexpr int kGgMaxExperts = 512;
+constexpr int kGgConvWarps = 16;          // 4 per scheduler: the widening chains are latency bound with fewer
+constexpr int kGgConvThreads = 256 + 32 * kGgConvWarps;
 
 struct GroupedParams {
   void* D;
@@ -51,6 +59,8 @@ struct GroupedParams {
   int total_m, N, K, E;
   int num_kb, num_nt;
   int64_t ldd;
+  int sf_vec;              // GW_MX4: scale rows are 16-byte aligned and K / 32 is a multiple of 16
+  int dbg;                 // VXK_GG_DEBUG (profiling only): 1 = converters skip the widening, 2 = skip the proxy fence
 };
 
 __device__ __forceinline__ void tma_load_3d(void* smem_dst, const CUtensorMap* m, uint64_t* bar, int c0, int c1,
@@ -75,7 +85,7 @@ __device__ __forceinline__ uint64_t make_mnmajor_sw128_desc(uint32_t smem_addr, 
 // 8 E2M1 codes (one 32-bit word, even element in the low nibble) -> four packed 16-bit pairs, times the group
 // scale `sc2` (packed pair of the activation type)
 template <bool BF16>
-__device__ __forceinline__ void e2m1x8_widen(uint32_t word, uint32_t sc2, uint32_t (&w)[4]) {
+__device__ __forceinline__ void e2m1x8_widen(uint32_t word, uint32_t sc2, bool fused, uint32_t (&w)[4]) {
   uint32_t h[4];
   asm("{\n\t.reg .b8 b0, b1, b2, b3;\n\tmov.b32 {b0, b1, b2, b3}, %4;\n\t"
       "cvt.rn.f16x2.e2m1x2 %0, b0;\n\tcvt.rn.f16x2.e2m1x2 %1, b1;\n\t"
@@ -85,11 +95,18 @@ __device__ __forceinline__ void e2m1x8_widen(uint32_t word, uint32_t sc2, uint32
 #pragma unroll
   for (int i = 0; i < 4; ++i) {
     if constexpr (BF16) {
-      // f16 -> bf16 bit positions (every E2M1 value is a normal f16 or zero), re-bias by 2^112, then the scale
+      // f16 -> bf16 bit positions (every E2M1 value is a normal f16 or zero): the pattern reads value * 2^-112.
+      // `fused`: sc2 already carries the 2^112 re-bias (2^(s-15) is a normal bf16 for 1 <= s <= 142); otherwise
+      // re-bias first, then the scale (s = 0 is a zero scale in the reference's dequantisation, s > 142 would
+      // overflow the fused factor)
       const uint32_t t = ((h[i] >> 3) & 0x0fff0fffu) | (h[i] & 0x80008000u);
-      uint32_t u;
-      asm("mul.rn.bf16x2 %0, %1, %2;" : "=r"(u) : "r"(t), "r"(0x77807780u));
-      asm("mul.rn.bf16x2 %0, %1, %2;" : "=r"(w[i]) : "r"(u), "r"(sc2));
+      if (fused) {
+        asm("mul.rn.bf16x2 %0, %1, %2;" : "=r"(w[i]) : "r"(t), "r"(sc2));
+      } else {
+        uint32_t u;
+        asm("mul.rn.bf16x2 %0, %1, %2;" : "=r"(u) : "r"(t), "r"(0x77807780u));
+        asm("mul.rn.bf16x2 %0, %1, %2;" : "=r"(w[i]) : "r"(u), "r"(sc2));
+      }
     } else {
       asm("mul.rn.f16x2 %0, %1, %2;" : "=r"(w[i]) : "r"(h[i]), "r"(sc2));
     }
@@ -104,11 +121,17 @@ struct GgSmem {
   static constexpr int kABox = MT * 128;
   static constexpr int kStageBytes = (kRawW + kABox + 1023) / 1024 * 1024;
   static constexpr int kTxBytes = kRawW + kABox;
-  static constexpr int kConvSlots = kConv ? 3 : 0;
+  // Ring depth / operand slots were swept (10 / 15 / 24 stages, 2 / 3 / 6 / 8 slots, 8 / 16 converter warps): no
+  // effect.  What bounds the small-MT shapes is the tensor core's read of the 128-row operand from shared memory:
+  // 4 KB per tcgen05.mma at ~32 B / clk = ~128 clk per 16-deep step whatever MT is, i.e. 16 weights / clk / SM
+  // (measured: 550-600 clk per 64-deep stage with the converters doing nothing, for 16-bit, fp8 and mxfp4 alike;
+  // profiles/r02_grouped_gemm.txt).  16-bit weights therefore sit at the HBM roofline (32 B / clk / SM), fp8 is
+  // capped at ~4.5 TB/s and mxfp4 at ~2.4 TB/s of weight stream; the way past it is the widened operand in TMEM.
+  static constexpr int kConvSlots = !kConv ? 0 : VXK_GG_CONV_SLOTS;
   static constexpr int kSchedBytes = 2 * (kGgMaxExperts + 1) * 4;
   static constexpr int kStagesRaw = (220 * 1024 - kConvSlots * kOpBytes - kSchedBytes) / kStageBytes;
-  static constexpr int kStages = kStagesRaw > 10 ? 10 : kStagesRaw;
-  static constexpr int kBarrierBytes = (2 * kStages + 2 * 3 + 4) * 8 + 16;
+  static constexpr int kStages = kStagesRaw > VXK_GG_STAGE_CAP ? VXK_GG_STAGE_CAP : kStagesRaw;   // bytes in flight are what the HBM-bound shapes need
+  static constexpr int kBarrierBytes = (2 * kStages + 2 * 8 + 4) * 8 + 16;
   static constexpr int kTotalBytes = kStages * kStageBytes + kConvSlots * kOpBytes + kBarrierBytes + kSchedBytes + 1024;
   static_assert(kStages >= 3, "ring too shallow");
 };
@@ -136,7 +159,7 @@ __device__ __forceinline__ GgTile gg_tile(const int* tile_start, const int* row_
 }
 
 template <int MT, int WKIND, bool BF16, bool E5M2>
-__global__ void __launch_bounds__(WKIND == GW_16 ? 256 : 512, 1)
+__global__ void __launch_bounds__(WKIND == GW_16 ? 256 : kGgConvThreads, 1)
 gemm_grouped_kernel(const GroupedParams p, const __grid_constant__ CUtensorMap map_w,
                     const __grid_constant__ CUtensorMap map_a) {
   using L = GgSmem<MT, WKIND>;
@@ -152,10 +175,10 @@ gemm_grouped_kernel(const GroupedParams p, const __grid_constant__ CUtensorMap m
   uint64_t* full_bar = bars;
   uint64_t* empty_bar = bars + S;
   uint64_t* conv_full = bars + 2 * S;
-  uint64_t* conv_empty = bars + 2 * S + 3;
-  uint64_t* tmem_full_bar = bars + 2 * S + 6;
-  uint64_t* tmem_empty_bar = bars + 2 * S + 8;
-  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(bars + 2 * S + 10);
+  uint64_t* conv_empty = bars + 2 * S + 8;
+  uint64_t* tmem_full_bar = bars + 2 * S + 16;
+  uint64_t* tmem_empty_bar = bars + 2 * S + 18;
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(bars + 2 * S + 20);
   int* tile_start = reinterpret_cast<int*>(reinterpret_cast<uint8_t*>(bars) + L::kBarrierBytes);
   int* row_start = tile_start + (kGgMaxExperts + 1);
 
@@ -169,8 +192,8 @@ gemm_grouped_kernel(const GroupedParams p, const __grid_constant__ CUtensorMap m
       mbar_init(&full_bar[i], 1);
       mbar_init(&empty_bar[i], 1);
     }
-    for (int i = 0; i < 3; ++i) {
-      mbar_init(&conv_full[i], 8);
+    for (int i = 0; i < 8; ++i) {
+      mbar_init(&conv_full[i], kGgConvWarps);
       mbar_init(&conv_empty[i], 1);
     }
     for (int i = 0; i < 2; ++i) {
@@ -235,6 +258,8 @@ gemm_grouped_kernel(const GroupedParams p, const __grid_constant__ CUtensorMap m
     }
   } else if (warp == 1) {
     // ===================== MMA issuer: D^T[128 x MT] += W16[128 x 16] * A[MT x 16]^T =====================
+    // (a_format != b_format -- f16 weights against bf16 activations, which would make the fp8 widening one cvt per
+    // two codes -- is rejected by the hardware: illegal instruction, measured)
     const uint32_t idesc = make_idesc_f16(BF16 ? 1 : 0, 128, MT) | (kMnMajor ? (1u << 15) : 0u);
     int stage = 0, cs = 0, iter = 0;
     uint32_t phase = 0, cphase = 0;
@@ -268,23 +293,48 @@ gemm_grouped_kernel(const GroupedParams p, const __grid_constant__ CUtensorMap m
   } else if (warp >= 8) {
     // ===================== converters =====================
     if constexpr (L::kConv) {
-      const int ct = threadIdx.x - 256;          // 0..255
+      const int ct = threadIdx.x - 256;          // 0..511
       int stage = 0, cs = 0;
       uint32_t phase = 0, cphase = 0;
       for (int idx = blockIdx.x; idx < num_tiles; idx += gridDim.x) {
         const GgTile t = gg_tile<MT>(tile_start, row_start, p.E, p.num_nt, idx);
+        // mxfp4: this thread's scale bytes, 8 K slices (16 bytes of the row, every other one is this half's) per
+        // fetch, fetched one group ahead so the load latency never sits in the per-stage chain
         const uint8_t* sfp = nullptr;
+        uint4 sf_nxt = make_uint4(0, 0, 0, 0);
+        uint32_t sf_lo = 0, sf_hi = 0;            // this thread's 8 scale bytes of the current group, next one lowest
+        auto sf_load = [&](int kb) {
+          if (p.sf_vec) return __ldg(reinterpret_cast<const uint4*>(sfp + kb * 2));
+          uint32_t wv[4] = {0, 0, 0, 0};
+          for (int i = 0; i < 16; ++i)
+            if (kb * 2 + i < p.K / 32) wv[i >> 2] |= static_cast<uint32_t>(__ldg(sfp + kb * 2 + i)) << (8 * (i & 3));
+          return make_uint4(wv[0], wv[1], wv[2], wv[3]);
+        };
         if constexpr (WKIND == GW_MX4) {
-          const int n = min(t.n0 + (ct >> 1), p.N - 1);
-          sfp = p.w_sf + (static_cast<int64_t>(t.e) * p.N + n) * (p.K / 32) + (ct & 1);
+          const int n = min(t.n0 + (ct >> 2), p.N - 1);
+          sfp = p.w_sf + (static_cast<int64_t>(t.e) * p.N + n) * (p.K / 32);
+          sf_nxt = sf_load(0);
         }
         for (int kb = 0; kb < p.num_kb; ++kb) {
           uint32_t sc2 = 0;
+          bool sf_fused = true;
           if constexpr (WKIND == GW_MX4) {
-            const uint32_t s = __ldg(sfp + kb * 2);
+            if ((kb & 7) == 0) {
+              const uint32_t sel = (ct & 2) ? 0x7531u : 0x6420u;          // odd / even bytes: this half's groups
+              sf_lo = __byte_perm(sf_nxt.x, sf_nxt.y, sel);
+              sf_hi = __byte_perm(sf_nxt.z, sf_nxt.w, sel);
+              if (kb + 8 < p.num_kb) sf_nxt = sf_load(kb + 8);
+            }
+            const uint32_t s = sf_lo & 0xffu;
+            sf_lo = __funnelshift_r(sf_lo, sf_hi, 8);
+            sf_hi >>= 8;
             uint32_t h;
             if constexpr (BF16) {
-              h = s << 7;                        // bf16 bits of 2^(s-127): the reference's (scale << 7).view(bf16)
+              // fused factor 2^(s-127) * 2^112 (the widening's re-bias): a normal bf16 for 1 <= s <= 142; s = 0 is a
+              // zero scale in the reference's dequantisation ((0 << 7).view(bf16) = 0.0), which the fused path
+              // reproduces with a zero factor; only s > 142 takes the two-multiply path (warp-uniform branch)
+              sf_fused = !__any_sync(0xffffffffu, s > 142u);
+              h = sf_fused ? (s == 0 ? 0u : (s + 112u) << 7) : s << 7;
             } else {
               const __half x = __float2half_rn(__uint_as_float(s << 23));
               h = *reinterpret_cast<const uint16_t*>(&x);
@@ -293,37 +343,47 @@ gemm_grouped_kernel(const GroupedParams p, const __grid_constant__ CUtensorMap m
           }
           mbar_wait(&full_bar[stage], phase);
           const uint32_t raw = smem_u32(stage_w(stage));
-          if constexpr (WKIND == GW_FP8) {
-            // raw: 64 k rows x 128 column bytes (SWIZZLE_128B); this thread: 16 columns at k0 and k0 + 32
+          if (p.dbg & 4) {
+            mbar_wait(&conv_empty[cs], cphase ^ 1);
+          } else if constexpr (WKIND == GW_FP8) {
+            // raw: 64 k rows x 128 column bytes (SWIZZLE_128B); this thread: 16 columns of k row k0
             const int j = ct & 7, k0 = ct >> 3, sw = k0 & 7;
             const uint4 v0 = lds128(raw + k0 * 128 + ((j ^ sw) << 4));
-            const uint4 v1 = lds128(raw + (k0 + 32) * 128 + ((j ^ sw) << 4));
-            uint32_t w0[8], w1[8];
-            widen16<BF16, E5M2, false>(v0, 1.0f, w0);
-            widen16<BF16, E5M2, false>(v1, 1.0f, w1);
+            uint32_t w0[8];
+            if (p.dbg & 1) {
+#pragma unroll
+              for (int i = 0; i < 8; ++i) w0[i] = v0.x;
+            } else {
+              widen16<BF16, E5M2, false>(v0, 1.0f, w0);
+            }
             mbar_wait(&conv_empty[cs], cphase ^ 1);
+            // a quarter warp (one k row, j = 0..7) writes both 64-column blocks; j >= 4 stores its odd chunk first
+            // so that the eight 16-byte stores of one instruction fall on eight different bank groups
             const uint32_t dst = smem_u32(conv_base + cs * L::kOpBytes) + (j >> 2) * 8192 + k0 * 128;
-            const uint32_t c0 = ((((j & 3) * 2) ^ sw) << 4), c1 = ((((j & 3) * 2 + 1) ^ sw) << 4);
-            sts128(dst + c0, w0[0], w0[1], w0[2], w0[3]);
-            sts128(dst + c1, w0[4], w0[5], w0[6], w0[7]);
-            sts128(dst + 32 * 128 + c0, w1[0], w1[1], w1[2], w1[3]);
-            sts128(dst + 32 * 128 + c1, w1[4], w1[5], w1[6], w1[7]);
+            const uint32_t f = j >> 2;
+            const uint32_t c0 = ((((j & 3) * 2 + f) ^ sw) << 4), c1 = ((((j & 3) * 2 + (f ^ 1)) ^ sw) << 4);
+            if (f) {
+              sts128(dst + c0, w0[4], w0[5], w0[6], w0[7]);
+              sts128(dst + c1, w0[0], w0[1], w0[2], w0[3]);
+            } else {
+              sts128(dst + c0, w0[0], w0[1], w0[2], w0[3]);
+              sts128(dst + c1, w0[4], w0[5], w0[6], w0[7]);
+            }
           } else {
-            // raw: 128 weight rows x 32 bytes (64 codes), linear; this thread: one 32-code scale group
-            const int row = ct >> 1, half = ct & 1, sw = row & 7;
-            const uint4 v = lds128(raw + row * 32 + half * 16);
-            uint32_t w[4][4];
-            e2m1x8_widen<BF16>(v.x, sc2, w[0]);
-            e2m1x8_widen<BF16>(v.y, sc2, w[1]);
-            e2m1x8_widen<BF16>(v.z, sc2, w[2]);
-            e2m1x8_widen<BF16>(v.w, sc2, w[3]);
+            // raw: 128 weight rows x 32 bytes (64 codes), linear; this thread: 16 codes (half a scale group)
+            const int row = ct >> 2, qtr = ct & 3, sw = row & 7;
+            uint32_t v0, v1;
+            asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(v0), "=r"(v1) : "r"(raw + row * 32 + qtr * 8));
+            uint32_t w[2][4];
+            e2m1x8_widen<BF16>(v0, sc2, sf_fused, w[0]);
+            e2m1x8_widen<BF16>(v1, sc2, sf_fused, w[1]);
             mbar_wait(&conv_empty[cs], cphase ^ 1);
             const uint32_t dst = smem_u32(conv_base + cs * L::kOpBytes) + row * 128;
 #pragma unroll
-            for (int q = 0; q < 4; ++q)
-              sts128(dst + (((half * 4 + q) ^ sw) << 4), w[q][0], w[q][1], w[q][2], w[q][3]);
+            for (int q = 0; q < 2; ++q)
+              sts128(dst + (((qtr * 2 + q) ^ sw) << 4), w[q][0], w[q][1], w[q][2], w[q][3]);
           }
-          fence_proxy_async_smem();
+          if (!(p.dbg & 2)) fence_proxy_async_smem();
           __syncwarp();
           if (lane == 0) mbar_arrive(&conv_full[cs]);
           if (++cs == C) { cs = 0; cphase ^= 1; }
