@@ -1,2 +1,2 @@
-for d in 0 4 6; do echo "== VXK_GG_DEBUG=$d"; VXK_GG_DEBUG=$d python benchmarks/bench_grouped_gemm.py --graph --Ms 256 --kinds fp8,mxfp4; done
-python benchmarks/bench_grouped_gemm.py --graph --Ms 256 --kinds bf16
+python benchmarks/bench_grouped_gemm.py --graph --Ms 16,256,1024,8192 --kinds fp8,mxfp4
+python benchmarks/bench_gemm_sweep.py --graph --sets llama8b_w8a16 --Ms 1,16,64,8192

@@ -11,7 +11,7 @@ static int gg_env_int(const char* name, int dflt) {
 }
 
 int make_map_3d_u8(CUtensorMap* map, const void* base, uint64_t d0_bytes, uint64_t d1, uint64_t d2, uint64_t pitch1,
-                   uint64_t pitch2, uint32_t box0, uint32_t box1, bool swizzle128);
+                   uint64_t pitch2, uint32_t box0, uint32_t box1, int swizzle_bytes);
 
 // ---- CUDA-core path: one thread per output, any N / K; also the cross-check of the tensor-core kernel ----
 struct GgFallbackParams {
@@ -107,6 +107,11 @@ static int launch_gg_types(const GroupedParams& gp, const CUtensorMap& mw, const
   if (wkind == GW_MX4)
     return bf16 ? launch_gg<MT, GW_MX4, true, false>(gp, mw, ma, max_tiles, st)
                 : launch_gg<MT, GW_MX4, false, false>(gp, mw, ma, max_tiles, st);
+  if constexpr (MT <= 128) {
+    if (wkind == GW_MX4T)
+      return bf16 ? launch_gg<MT, GW_MX4T, true, false>(gp, mw, ma, max_tiles, st)
+                  : launch_gg<MT, GW_MX4T, false, false>(gp, mw, ma, max_tiles, st);
+  }
   if (bf16)
     return e5m2 ? launch_gg<MT, GW_FP8, true, true>(gp, mw, ma, max_tiles, st)
                 : launch_gg<MT, GW_FP8, true, false>(gp, mw, ma, max_tiles, st);
@@ -158,13 +163,19 @@ extern "C" int vxk_moe_grouped_gemm(void* D, const void* A, const void* B, const
   int mt = avg <= 32 ? 32 : (avg <= 64 ? 64 : (avg <= 128 ? 128 : 256));
   if (env_mt == 32 || env_mt == 64 || env_mt == 128 || env_mt == 256) mt = env_mt;
 
+  // mxfp4 with the widened operand in TMEM (token tiles up to 128 rows; 256-row tiles are tensor bound either way)
+  static const int env_ta = gg_env_int("VXK_GG_TMEM_A", 1);
+  int launch_kind = wkind;
+  if (wkind == GW_MX4 && env_ta && mt <= 128 && K % 128 == 0) launch_kind = GW_MX4T;
+  const int block_k = launch_kind == GW_MX4T ? 128 : kGgBlockK;
+
   GroupedParams gp{};
   gp.D = D; gp.bias = bias; gp.rows = rows_per_expert;
   gp.w_scale = wkind == GW_FP8 ? static_cast<const float*>(scales) : nullptr;
   gp.w_sf = wkind == GW_MX4 ? static_cast<const uint8_t*>(scales) : nullptr;
   gp.total_m = static_cast<int>(total_m); gp.N = static_cast<int>(N); gp.K = static_cast<int>(K);
   gp.E = static_cast<int>(num_experts);
-  gp.num_kb = static_cast<int>((K + kGgBlockK - 1) / kGgBlockK);
+  gp.num_kb = static_cast<int>((K + block_k - 1) / block_k);
   gp.num_nt = static_cast<int>((N + 127) / 128);
   gp.ldd = N;
   gp.sf_vec = wkind == GW_MX4 && (K / 32) % 16 == 0 && aligned16(scales);
@@ -178,14 +189,15 @@ extern "C" int vxk_moe_grouped_gemm(void* D, const void* A, const void* B, const
   if ((rc = make_map_2d_u8(&ma, A, static_cast<uint64_t>(K) * 2, total_m, static_cast<uint64_t>(K) * 2, 128, mt, true)))
     return rc;
   if (wkind == GW_MX4)
-    rc = make_map_3d_u8(&mw, B, K / 2, N, num_experts, K / 2, N * (K / 2), kGgBlockK / 2, 128, false);
+    rc = make_map_3d_u8(&mw, B, K / 2, N, num_experts, K / 2, N * (K / 2), block_k / 2, 128,
+                        launch_kind == GW_MX4T ? 64 : 0);
   else
-    rc = make_map_3d_u8(&mw, B, wpitch, K, num_experts, wpitch, K * wpitch, 128, kGgBlockK, true);
+    rc = make_map_3d_u8(&mw, B, wpitch, K, num_experts, wpitch, K * wpitch, 128, kGgBlockK, 128);
   if (rc) return rc;
   switch (mt) {
-    case 32: return launch_gg_types<32>(gp, mw, ma, max_tiles, wkind, bf16, e5m2, st);
-    case 64: return launch_gg_types<64>(gp, mw, ma, max_tiles, wkind, bf16, e5m2, st);
-    case 128: return launch_gg_types<128>(gp, mw, ma, max_tiles, wkind, bf16, e5m2, st);
-    default: return launch_gg_types<256>(gp, mw, ma, max_tiles, wkind, bf16, e5m2, st);
+    case 32: return launch_gg_types<32>(gp, mw, ma, max_tiles, launch_kind, bf16, e5m2, st);
+    case 64: return launch_gg_types<64>(gp, mw, ma, max_tiles, launch_kind, bf16, e5m2, st);
+    case 128: return launch_gg_types<128>(gp, mw, ma, max_tiles, launch_kind, bf16, e5m2, st);
+    default: return launch_gg_types<256>(gp, mw, ma, max_tiles, launch_kind, bf16, e5m2, st);
   }
 }

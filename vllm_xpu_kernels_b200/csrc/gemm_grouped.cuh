@@ -38,7 +38,7 @@
 
 namespace vxk {
 
-constexpr int GW_16 = 0, GW_FP8 = 1, GW_MX4 = 2;
+constexpr int GW_16 = 0, GW_FP8 = 1, GW_MX4 = 2, GW_MX4T = 3;   // MX4T: mxfp4 with the widened operand in TMEM
 constexpr int kGgBlockK = 64;
 #ifndef VXK_GG_STAGE_CAP
 #define VXK_GG_STAGE_CAP 10
@@ -71,6 +71,27 @@ __device__ __forceinline__ void tma_load_3d(void* smem_dst, const CUtensorMap* m
       : "memory");
 }
 
+// D[tmem] (+)= A[tmem] * B[smem]: the 128-row operand is read from tensor memory (lane = row, one 32-bit column =
+// two consecutive k), which takes it off the shared-memory read path that bounds the small token tiles
+__device__ __forceinline__ void umma_f16_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t desc_b, uint32_t idesc,
+                                            uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}" ::"r"(tmem_d),
+      "r"(tmem_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// registers -> TMEM: this warp's 32 lanes x 16 consecutive columns
+__device__ __forceinline__ void tmem_st_32x32b_x16(uint32_t taddr, const uint32_t (&r)[16]) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], "
+      "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16};" ::"r"(taddr),
+      "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]), "r"(r[9]),
+      "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15])
+      : "memory");
+}
+__device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+
 // MN-major operand tile, SWIZZLE_128B: 64-element column blocks `lbo` bytes apart, groups of 8 k rows 1024 B apart
 __device__ __forceinline__ uint64_t make_mnmajor_sw128_desc(uint32_t smem_addr, uint32_t lbo) {
   uint64_t d = 0;
@@ -85,7 +106,7 @@ __device__ __forceinline__ uint64_t make_mnmajor_sw128_desc(uint32_t smem_addr, 
 // 8 E2M1 codes (one 32-bit word, even element in the low nibble) -> four packed 16-bit pairs, times the group
 // scale `sc2` (packed pair of the activation type)
 template <bool BF16>
-__device__ __forceinline__ void e2m1x8_widen(uint32_t word, uint32_t sc2, bool fused, uint32_t (&w)[4]) {
+__device__ __forceinline__ void e2m1x8_widen(uint32_t word, uint32_t sc2, uint32_t (&w)[4]) {
   uint32_t h[4];
   asm("{\n\t.reg .b8 b0, b1, b2, b3;\n\tmov.b32 {b0, b1, b2, b3}, %4;\n\t"
       "cvt.rn.f16x2.e2m1x2 %0, b0;\n\tcvt.rn.f16x2.e2m1x2 %1, b1;\n\t"
@@ -95,18 +116,13 @@ __device__ __forceinline__ void e2m1x8_widen(uint32_t word, uint32_t sc2, bool f
 #pragma unroll
   for (int i = 0; i < 4; ++i) {
     if constexpr (BF16) {
-      // f16 -> bf16 bit positions (every E2M1 value is a normal f16 or zero): the pattern reads value * 2^-112.
-      // `fused`: sc2 already carries the 2^112 re-bias (2^(s-15) is a normal bf16 for 1 <= s <= 142); otherwise
-      // re-bias first, then the scale (s = 0 is a zero scale in the reference's dequantisation, s > 142 would
-      // overflow the fused factor)
-      const uint32_t t = ((h[i] >> 3) & 0x0fff0fffu) | (h[i] & 0x80008000u);
-      if (fused) {
-        asm("mul.rn.bf16x2 %0, %1, %2;" : "=r"(w[i]) : "r"(t), "r"(sc2));
-      } else {
-        uint32_t u;
-        asm("mul.rn.bf16x2 %0, %1, %2;" : "=r"(u) : "r"(t), "r"(0x77807780u));
-        asm("mul.rn.bf16x2 %0, %1, %2;" : "=r"(w[i]) : "r"(u), "r"(sc2));
-      }
+      // f16 -> f32 (two conversions on the FMA pipe) -> packed bf16 (one pack), all exact.  Moving the f16 fields
+      // into bf16 positions with shift / mask / merge + a re-bias multiply is one instruction shorter but all of it
+      // sits on the half-rate ALU pipe, which is what bounds the converters (69 % busy, profiles/r02_grouped_mx4t.csv):
+      // measured 190 -> 173 us at M = 256.  sc2 = bf16 bits of 2^(s-127), the reference's own factor.
+      const float2 f = __half22float2(*reinterpret_cast<const __half2*>(&h[i]));
+      const __nv_bfloat162 b = __floats2bfloat162_rn(f.x, f.y);
+      asm("mul.rn.bf16x2 %0, %1, %2;" : "=r"(w[i]) : "r"(*reinterpret_cast<const uint32_t*>(&b)), "r"(sc2));
     } else {
       asm("mul.rn.f16x2 %0, %1, %2;" : "=r"(w[i]) : "r"(h[i]), "r"(sc2));
     }
@@ -115,25 +131,31 @@ __device__ __forceinline__ void e2m1x8_widen(uint32_t word, uint32_t sc2, bool f
 
 template <int MT, int WKIND>
 struct GgSmem {
+  static constexpr bool kTmemA = WKIND == GW_MX4T;
   static constexpr bool kConv = WKIND != GW_16;
+  static constexpr int kBlockK = kTmemA ? 128 : kGgBlockK;          // K elements per ring stage
   static constexpr int kOpBytes = 128 * 128;            // 128 weight rows x 64 elements of 16 bits
-  static constexpr int kRawW = WKIND == GW_16 ? kOpBytes : (WKIND == GW_FP8 ? 64 * 128 : 128 * 32);
-  static constexpr int kABox = MT * 128;
-  static constexpr int kStageBytes = (kRawW + kABox + 1023) / 1024 * 1024;
-  static constexpr int kTxBytes = kRawW + kABox;
+  static constexpr int kRawW = WKIND == GW_16 ? kOpBytes : WKIND == GW_FP8 ? 64 * 128 : kTmemA ? 128 * 64 : 128 * 32;
+  static constexpr int kABox = MT * 128;                // one 64-deep activation slice
+  static constexpr int kABoxes = kBlockK / 64;
+  static constexpr int kStageBytes = (kRawW + kABoxes * kABox + 1023) / 1024 * 1024;
+  static constexpr int kTxBytes = kRawW + kABoxes * kABox;
   // Ring depth / operand slots were swept (10 / 15 / 24 stages, 2 / 3 / 6 / 8 slots, 8 / 16 converter warps): no
   // effect.  What bounds the small-MT shapes is the tensor core's read of the 128-row operand from shared memory:
   // 4 KB per tcgen05.mma at ~32 B / clk = ~128 clk per 16-deep step whatever MT is, i.e. 16 weights / clk / SM
   // (measured: 550-600 clk per 64-deep stage with the converters doing nothing, for 16-bit, fp8 and mxfp4 alike;
   // profiles/r02_grouped_gemm.txt).  16-bit weights therefore sit at the HBM roofline (32 B / clk / SM), fp8 is
-  // capped at ~4.5 TB/s and mxfp4 at ~2.4 TB/s of weight stream; the way past it is the widened operand in TMEM.
-  static constexpr int kConvSlots = !kConv ? 0 : VXK_GG_CONV_SLOTS;
+  // capped at ~4.5 TB/s and mxfp4 at ~2.4 TB/s of weight stream; the way past it is the widened operand in TMEM
+  // (GW_MX4T: the converters write tensor memory, four 64-column slots next to the accumulators).
+  static constexpr int kConvSlots = !kConv ? 0 : kTmemA ? 4 : VXK_GG_CONV_SLOTS;
+  static constexpr int kConvSmemBytes = (kConv && !kTmemA) ? kConvSlots * kOpBytes : 0;
   static constexpr int kSchedBytes = 2 * (kGgMaxExperts + 1) * 4;
-  static constexpr int kStagesRaw = (220 * 1024 - kConvSlots * kOpBytes - kSchedBytes) / kStageBytes;
-  static constexpr int kStages = kStagesRaw > VXK_GG_STAGE_CAP ? VXK_GG_STAGE_CAP : kStagesRaw;   // bytes in flight are what the HBM-bound shapes need
+  static constexpr int kStagesRaw = (220 * 1024 - kConvSmemBytes - kSchedBytes) / kStageBytes;
+  static constexpr int kStages = kStagesRaw > VXK_GG_STAGE_CAP ? VXK_GG_STAGE_CAP : kStagesRaw;
   static constexpr int kBarrierBytes = (2 * kStages + 2 * 8 + 4) * 8 + 16;
-  static constexpr int kTotalBytes = kStages * kStageBytes + kConvSlots * kOpBytes + kBarrierBytes + kSchedBytes + 1024;
+  static constexpr int kTotalBytes = kStages * kStageBytes + kConvSmemBytes + kBarrierBytes + kSchedBytes + 1024;
   static_assert(kStages >= 3, "ring too shallow");
+  static_assert(!kTmemA || MT <= 128, "TMEM: 2 x MT accumulator columns + 4 x 64 operand columns");
 };
 
 struct GgTile { int e, row0, rows, n0; };
@@ -165,13 +187,15 @@ gemm_grouped_kernel(const GroupedParams p, const __grid_constant__ CUtensorMap m
   using L = GgSmem<MT, WKIND>;
   constexpr int S = L::kStages;
   constexpr int C = L::kConv ? L::kConvSlots : 1;
-  constexpr bool kMnMajor = WKIND != GW_MX4;
+  constexpr bool kMnMajor = WKIND == GW_16 || WKIND == GW_FP8;
+  constexpr bool kTmemA = L::kTmemA;
+  constexpr uint32_t kASlotCol = 256;           // TMEM-A: operand slots live in columns [256, 512)
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   auto stage_w = [&](int s) { return smem + s * L::kStageBytes; };
   auto stage_a = [&](int s) { return smem + s * L::kStageBytes + L::kRawW; };
   uint8_t* conv_base = smem + S * L::kStageBytes;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(conv_base + L::kConvSlots * L::kOpBytes);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(conv_base + L::kConvSmemBytes);
   uint64_t* full_bar = bars;
   uint64_t* empty_bar = bars + S;
   uint64_t* conv_full = bars + 2 * S;
@@ -202,7 +226,7 @@ gemm_grouped_kernel(const GroupedParams p, const __grid_constant__ CUtensorMap m
     }
     fence_barrier_init();
   }
-  constexpr uint32_t kCols = 2 * MT < 32 ? 32 : 2 * MT;
+  constexpr uint32_t kCols = kTmemA ? 512 : (2 * MT < 32 ? 32 : 2 * MT);
   if (warp == 2) tmem_alloc<kCols>(tmem_ptr_smem);
   if (warp == 3) {
     // exclusive prefix sums of rows and of token tiles per expert
@@ -248,9 +272,11 @@ gemm_grouped_kernel(const GroupedParams p, const __grid_constant__ CUtensorMap m
           } else if constexpr (WKIND == GW_FP8) {
             tma_load_3d(stage_w(stage), &map_w, &full_bar[stage], t.n0, kb * kGgBlockK, t.e);
           } else {                                // (k bytes, weight row, expert)
-            tma_load_3d(stage_w(stage), &map_w, &full_bar[stage], kb * (kGgBlockK / 2), t.n0, t.e);
+            tma_load_3d(stage_w(stage), &map_w, &full_bar[stage], kb * (L::kBlockK / 2), t.n0, t.e);
           }
-          tma_load_2d(stage_a(stage), &map_a, &full_bar[stage], kb * 128, t.row0);
+#pragma unroll
+          for (int h = 0; h < L::kABoxes; ++h)
+            tma_load_2d(stage_a(stage) + h * L::kABox, &map_a, &full_bar[stage], (kb * L::kABoxes + h) * 128, t.row0);
         }
         __syncwarp();
         if (++stage == S) { stage = 0; phase ^= 1; }
@@ -273,7 +299,22 @@ gemm_grouped_kernel(const GroupedParams p, const __grid_constant__ CUtensorMap m
         mbar_wait(&full_bar[stage], phase);
         if constexpr (L::kConv) mbar_wait(&conv_full[cs], cphase);
         tc_fence_after();
-        if (elect_one()) {
+        if constexpr (kTmemA) {
+          if (elect_one()) {
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+              const uint64_t da = make_kmajor_sw128_desc(smem_u32(stage_a(stage) + h * L::kABox));
+#pragma unroll
+              for (int k = 0; k < 4; ++k)         // 16 k = 8 TMEM columns of the operand slot per MMA
+                umma_f16_ts((p.dbg & 16) ? tmem_base + ((k & 1) ? MT : 0) : tmem_d,
+                            tmem_base + kASlotCol + cs * 64 + (h * 4 + k) * 8, da + static_cast<uint64_t>(2 * k),
+                            idesc, (kb > 0 || h > 0 || k > 0) ? 1u : 0u);
+            }
+            umma_commit(&conv_empty[cs]);
+            umma_commit(&empty_bar[stage]);
+            if (kb == p.num_kb - 1) umma_commit(&tmem_full_bar[as]);
+          }
+        } else if (elect_one()) {
           const uint32_t w_addr = L::kConv ? smem_u32(conv_base + cs * L::kOpBytes) : smem_u32(stage_w(stage));
           const uint64_t dw = kMnMajor ? make_mnmajor_sw128_desc(w_addr, 8192) : make_kmajor_sw128_desc(w_addr);
           const uint64_t da = make_kmajor_sw128_desc(smem_u32(stage_a(stage)));
@@ -292,7 +333,74 @@ gemm_grouped_kernel(const GroupedParams p, const __grid_constant__ CUtensorMap m
     }
   } else if (warp >= 8) {
     // ===================== converters =====================
-    if constexpr (L::kConv) {
+    if constexpr (kTmemA) {
+      // mxfp4, operand in TMEM: a warp can only write the 32 TMEM lanes of its quadrant (warp % 4), so thread
+      // (quadrant q, lane l) owns weight row 32 q + l; the four warps of a quadrant split the stage's 128 k into the
+      // four 32-code scale groups.  raw: 128 rows x 64 B, SWIZZLE_64B (16-byte chunk ^= (row >> 1) & 3): eight
+      // consecutive rows reading the same logical chunk hit eight different bank groups.
+      const int q = warp & 3, j = (warp - 8) >> 2, row = q * 32 + lane;
+      int stage = 0, cs = 0;
+      uint32_t phase = 0, cphase = 0;
+      for (int idx = blockIdx.x; idx < num_tiles; idx += gridDim.x) {
+        const GgTile t = gg_tile<MT>(tile_start, row_start, p.E, p.num_nt, idx);
+        const int n = min(t.n0 + row, p.N - 1);
+        const uint8_t* sfp = p.w_sf + (static_cast<int64_t>(t.e) * p.N + n) * (p.K / 32);
+        // scale bytes: 16 per fetch = 4 stages x 4 groups, this thread's group j of each; fetched one group ahead
+        auto sf_load = [&](int kb) {
+          if (p.sf_vec) return __ldg(reinterpret_cast<const uint4*>(sfp + kb * 4));
+          uint32_t wv[4] = {0, 0, 0, 0};
+          for (int i = 0; i < 16; ++i)
+            if (kb * 4 + i < p.K / 32) wv[i >> 2] |= static_cast<uint32_t>(__ldg(sfp + kb * 4 + i)) << (8 * (i & 3));
+          return make_uint4(wv[0], wv[1], wv[2], wv[3]);
+        };
+        uint4 sf_nxt = sf_load(0);
+        uint32_t sf4 = 0;
+        for (int kb = 0; kb < p.num_kb; ++kb) {
+          if ((kb & 3) == 0) {
+            const uint32_t sel = 0x4000u | (static_cast<uint32_t>(4 + j) << 4) | static_cast<uint32_t>(j);
+            const uint32_t lo = __byte_perm(sf_nxt.x, sf_nxt.y, sel), hi = __byte_perm(sf_nxt.z, sf_nxt.w, sel);
+            sf4 = __byte_perm(lo, hi, 0x5410u);
+            if (kb + 4 < p.num_kb) sf_nxt = sf_load(kb + 4);
+          }
+          const uint32_t sb = sf4 & 0xffu;
+          sf4 >>= 8;
+          uint32_t h;
+          if constexpr (BF16) {
+            h = sb << 7;                          // bf16 bits of 2^(sb-127): the reference's (scale << 7).view(bf16)
+          } else {
+            const __half x = __float2half_rn(__uint_as_float(sb << 23));
+            h = *reinterpret_cast<const uint16_t*>(&x);
+          }
+          const uint32_t sc2 = h | (h << 16);
+          mbar_wait(&full_bar[stage], phase);
+          const uint4 v = lds128(smem_u32(stage_w(stage)) + row * 64 + ((j ^ ((row >> 1) & 3)) << 4));
+          uint32_t w[16];
+          if (p.dbg & 4) {
+#pragma unroll
+            for (int i = 0; i < 16; ++i) w[i] = v.x;
+          } else {
+            uint32_t t4[4];
+            const uint32_t vv[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+              e2m1x8_widen<BF16>(vv[i], sc2, t4);
+              w[4 * i] = t4[0]; w[4 * i + 1] = t4[1]; w[4 * i + 2] = t4[2]; w[4 * i + 3] = t4[3];
+            }
+          }
+          mbar_wait(&conv_empty[cs], cphase ^ 1);
+          tc_fence_after();
+          if (!(p.dbg & 8)) {
+            tmem_st_32x32b_x16(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + kASlotCol + cs * 64 + j * 16, w);
+            tmem_st_wait();
+          }
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&conv_full[cs]);
+          if (++cs == C) { cs = 0; cphase ^= 1; }
+          if (++stage == S) { stage = 0; phase ^= 1; }
+        }
+      }
+    } else if constexpr (L::kConv) {
       const int ct = threadIdx.x - 256;          // 0..511
       int stage = 0, cs = 0;
       uint32_t phase = 0, cphase = 0;
@@ -317,7 +425,6 @@ gemm_grouped_kernel(const GroupedParams p, const __grid_constant__ CUtensorMap m
         }
         for (int kb = 0; kb < p.num_kb; ++kb) {
           uint32_t sc2 = 0;
-          bool sf_fused = true;
           if constexpr (WKIND == GW_MX4) {
             if ((kb & 7) == 0) {
               const uint32_t sel = (ct & 2) ? 0x7531u : 0x6420u;          // odd / even bytes: this half's groups
@@ -330,11 +437,7 @@ gemm_grouped_kernel(const GroupedParams p, const __grid_constant__ CUtensorMap m
             sf_hi >>= 8;
             uint32_t h;
             if constexpr (BF16) {
-              // fused factor 2^(s-127) * 2^112 (the widening's re-bias): a normal bf16 for 1 <= s <= 142; s = 0 is a
-              // zero scale in the reference's dequantisation ((0 << 7).view(bf16) = 0.0), which the fused path
-              // reproduces with a zero factor; only s > 142 takes the two-multiply path (warp-uniform branch)
-              sf_fused = !__any_sync(0xffffffffu, s > 142u);
-              h = sf_fused ? (s == 0 ? 0u : (s + 112u) << 7) : s << 7;
+              h = s << 7;                        // bf16 bits of 2^(s-127): the reference's (scale << 7).view(bf16)
             } else {
               const __half x = __float2half_rn(__uint_as_float(s << 23));
               h = *reinterpret_cast<const uint16_t*>(&x);
@@ -375,8 +478,8 @@ gemm_grouped_kernel(const GroupedParams p, const __grid_constant__ CUtensorMap m
             uint32_t v0, v1;
             asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(v0), "=r"(v1) : "r"(raw + row * 32 + qtr * 8));
             uint32_t w[2][4];
-            e2m1x8_widen<BF16>(v0, sc2, sf_fused, w[0]);
-            e2m1x8_widen<BF16>(v1, sc2, sf_fused, w[1]);
+            e2m1x8_widen<BF16>(v0, sc2, w[0]);
+            e2m1x8_widen<BF16>(v1, sc2, w[1]);
             mbar_wait(&conv_empty[cs], cphase ^ 1);
             const uint32_t dst = smem_u32(conv_base + cs * L::kOpBytes) + row * 128;
 #pragma unroll

@@ -47,7 +47,7 @@ int make_map_2d_u8(CUtensorMap* map, const void* base, uint64_t cols_bytes, uint
 
 // 3-D byte tensor [d2][d1][d0 bytes] (expert-stacked weights of the grouped GEMM), box [1][box1][box0]
 int make_map_3d_u8(CUtensorMap* map, const void* base, uint64_t d0_bytes, uint64_t d1, uint64_t d2, uint64_t pitch1,
-                   uint64_t pitch2, uint32_t box0, uint32_t box1, bool swizzle128) {
+                   uint64_t pitch2, uint32_t box0, uint32_t box1, int swizzle_bytes) {
   EncodeTiledFn fn = encode_tiled_fn();
   if (!fn) return fail(VXK_ERR_CUDA, "cuTensorMapEncodeTiled entry point not available");
   const cuuint64_t dims[3] = {d0_bytes, d1, d2};
@@ -56,7 +56,8 @@ int make_map_3d_u8(CUtensorMap* map, const void* base, uint64_t d0_bytes, uint64
   const cuuint32_t estr[3] = {1, 1, 1};
   const CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, const_cast<void*>(base), dims, strides, box, estr,
                         CU_TENSOR_MAP_INTERLEAVE_NONE,
-                        swizzle128 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_NONE,
+                        swizzle_bytes == 128 ? CU_TENSOR_MAP_SWIZZLE_128B
+                        : swizzle_bytes == 64 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_NONE,
                         CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS)
     return fail(VXK_ERR_CUDA, "cuTensorMapEncodeTiled failed (%d) for [%llu x %llu x %llu] box [%u x %u]",

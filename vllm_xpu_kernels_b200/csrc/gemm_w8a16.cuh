@@ -24,6 +24,10 @@
 
 #include "gemm_tc.cuh"
 
+#ifndef VXK_W16_BF16_VIA_F32
+#define VXK_W16_BF16_VIA_F32 1
+#endif
+
 namespace vxk {
 
 constexpr int kW16Threads = 512;
@@ -119,7 +123,19 @@ __device__ __forceinline__ void widen16(const uint4& raw, float s, uint32_t (&w)
         }
       }
     } else if constexpr (BF16) {
+#if VXK_W16_BF16_VIA_F32
+      // fp8 -> f16 (one cvt per pair) -> f32 (FMA pipe) -> packed bf16: 2 ALU-pipe + 2 FMA-pipe instructions per pair
+      // against 3.5 + 1 for the bit-placement form; the converters are bound by the half-rate ALU pipe
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        const uint32_t f16 = fp8x2_to_f16x2<E5M2>(in[i] >> (16 * h));
+        const float2 f = __half22float2(*reinterpret_cast<const __half2*>(&f16));
+        const __nv_bfloat162 o = __floats2bfloat162_rn(f.x, f.y);
+        w[2 * i + h] = *reinterpret_cast<const uint32_t*>(&o);
+      }
+#else
       fp8x4_to_bf16x4<E5M2>(in[i], w[2 * i], w[2 * i + 1]);
+#endif
     } else {
       w[2 * i] = fp8x2_to_f16x2<E5M2>(in[i]);
       w[2 * i + 1] = fp8x2_to_f16x2<E5M2>(in[i] >> 16);
