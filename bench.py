@@ -368,6 +368,10 @@ def run_ours(args):
             torch.cuda.empty_cache()
             gemm = bench_gemm.bench_gemms(dev, rank, world, pk, launches=max(100, K), warmup=max(10, args.warmup))
             e2e_g = bench_gemm.e2e_gemm(dev, rank, world)
+            try:    # MoE grouped GEMM: per-rank work, no collective
+                gemm["moe_grouped"] = bench_gemm.bench_moe_grouped(dev, pk, launches=max(100, K), warmup=max(10, args.warmup))
+            except Exception as exc:
+                gemm["moe_grouped"] = {"error": f"{type(exc).__name__}: {exc}"[:300]}
             if world > 1:
                 reassembled = bench_gemm.bench_reassembled(dev, rank, world)
         except Exception as exc:  # the GEMM section must never hide the quant numbers

@@ -38,6 +38,8 @@ KERNEL_OF = {   # dominant kernel of each kind at large M (vllm_xpu_kernels_b200
     "block_fp8": "gemm_tc2_blk_kernel<192> (tcgen05 kind::f8f6f4 per K slice + fp32 promotion)",
     "mxfp4_sf": "gemm_tc2_kernel<KIND_MXF4,192,*> via torch.ops._vxk.fp4_gemm_sf (pre-packed scale factors, no sf_pack launches)",
     "mxfp4 (M <= 128)": "gemm_skinny_mx4_kernel (swap-AB, split-K over a cluster, natural-layout scales re-tiled in the kernel)",
+    "moe_bf16 / moe_fp8 / moe_mxfp4": "gemm_grouped_kernel<MT,kind,*> (tcgen05 kind::f16, swap-AB, device-side tile list; "
+                                      "fp8 widened into shared memory, mxfp4 into tensor memory)",
 }
 
 
@@ -201,6 +203,56 @@ def bench_gemms(dev, rank, world, pk, launches=100, warmup=10, m_tokens=8192, se
                            "hbm = " + pk["src"] + " copy bandwidth",
             "method": f">= {warmup} warm-up + {launches} timed launches per case, CUDA events, max over ranks, "
                       "weights rotated through > 2 x L2 unless one set already exceeds it"}
+
+
+# ---------------------------------------------------------------------------------------------
+# MoE grouped GEMM: the reference test's shape, decode and prefill token counts
+# ---------------------------------------------------------------------------------------------
+def bench_moe_grouped(dev, pk, launches=100, warmup=10):
+    """torch.ops._xpu_C.cutlass_grouped_gemm_interface on tests/fused_moe/test_grouped_gemm.py:14-21 (N = 5120,
+    K = 8192, 16 experts, top-1), bf16 activations, the three recipes.  rows_per_expert is redrawn per launch so
+    that consecutive launches read different experts (HBM numbers, not L2 numbers).  Roofline time =
+    max(2MNK / bf16 dense peak, (weights of the experts that own rows + activations + output) / HBM peak)."""
+    from vllm_xpu_kernels_b200.fused_moe_interface import cutlass_grouped_gemm_xe2
+    E, N, K = 16, 5120, 8192
+    rows_out = []
+    for kind in ("bf16", "fp8", "mxfp4"):
+        if kind == "bf16":
+            b, sc, wb = torch.randn(E, K, N, device=dev, dtype=torch.bfloat16) / 8, None, 2.0
+        elif kind == "fp8":
+            b = torch.empty(E, K, N, device=dev, dtype=E4)
+            for e in range(E):
+                b[e] = (torch.randn(K, N, device=dev) / 4).to(E4)
+            sc, wb = torch.rand(E, device=dev) + 0.5, 1.0
+        else:
+            b = torch.randint(0, 256, (E, N, K // 2), dtype=torch.uint8, device=dev).view(torch.float4_e2m1fn_x2)
+            sc, wb = torch.randint(118, 130, (E, N, K // 32), dtype=torch.uint8, device=dev), 0.5 + 1.0 / 32
+        for M in (16, 256, 8192):
+            a = torch.randn(M, K, device=dev, dtype=torch.bfloat16) / 8
+            d = torch.empty(M, N, device=dev, dtype=torch.bfloat16)
+            copies = 8 if M < 1024 else 2
+            fns, act = [], 0.0
+            for i in range(copies):
+                g = torch.Generator().manual_seed(100 + i)
+                rows = torch.bincount(torch.rand(M, E, generator=g).argmax(dim=1), minlength=E).to(torch.int32)
+                act += float((rows > 0).sum()) / copies
+                r = rows.to(dev)
+                fns.append(lambda r=r, a=a, d=d: cutlass_grouped_gemm_xe2(a, b, sc, None, d, r, N, K, E))
+            try:
+                ms, graph = _time_graph(fns, launches, warmup), True
+            except Exception:
+                ms, graph = _time_eager(fns, launches, warmup), False
+            flops = 2.0 * M * N * K
+            nbytes = act * N * K * wb + 2.0 * M * K + 2.0 * M * N
+            t_tensor, t_hbm = flops / (pk["bf16"] * 1e12), nbytes / (pk["hbm"] * 1e9)
+            rows_out.append({"kind": "moe_" + kind, "M": M, "N": N, "K": K, "experts": E, "active_experts": act,
+                             "ms": ms, "tflops": flops / (ms * 1e-3) / 1e12, "gbs": nbytes / (ms * 1e-3) / 1e9,
+                             "bound": "tensor" if t_tensor > t_hbm else "hbm",
+                             "frac": max(t_tensor, t_hbm) * 1e3 / ms,
+                             "timed": "cuda-graph replay" if graph else "eager torch.ops launches"})
+        del b, sc
+        torch.cuda.empty_cache()
+    return rows_out
 
 
 # ---------------------------------------------------------------------------------------------
