@@ -120,11 +120,11 @@ static bool w16_force_fallback() {
 }
 
 // ---- small-M path (M <= 128): operands swapped, K split over a cluster.  See gemm_w8a16_skinny.cuh ----
-template <int MT, bool BF16, bool E5M2, bool SCALED>
-static int launch_w16_skinny(const W16SkinnyParams& sp, const CUtensorMap& mw, const CUtensorMap& ma, int n_tiles,
+template <int MT, bool BF16, bool E5M2, bool SCALED, bool TA>
+static int launch_w16_skinny_impl(const W16SkinnyParams& sp, const CUtensorMap& mw, const CUtensorMap& ma, int n_tiles,
                              cudaStream_t st) {
-  using L = W16SkinnySmem<MT>;
-  auto kernel = gemm_w8a16_skinny_kernel<MT, BF16, E5M2, SCALED>;
+  using L = W16SkinnySmem<MT, TA>;
+  auto kernel = gemm_w8a16_skinny_kernel<MT, BF16, E5M2, SCALED, TA>;
   static PerDeviceOnce once;
   const cudaError_t attr_err = once.get([&](PerDeviceOnce::Entry& x) {
     x.err = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotalBytes);
@@ -150,6 +150,15 @@ static int launch_w16_skinny(const W16SkinnyParams& sp, const CUtensorMap& mw, c
   if (e != cudaSuccess) return fail(VXK_ERR_CUDA, "gemm_w8a16_skinny launch: %s", cudaGetErrorString(e));
   g_gemm_tc_calls.fetch_add(1, std::memory_order_relaxed);
   return check_launch("gemm_w8a16_skinny");
+}
+
+// widened operand in tensor memory (default) or in shared memory (VXK_W16_TMEM_A=0): see gemm_w8a16_skinny.cuh
+template <int MT, bool BF16, bool E5M2, bool SCALED>
+static int launch_w16_skinny(const W16SkinnyParams& sp, const CUtensorMap& mw, const CUtensorMap& ma, int n_tiles,
+                             cudaStream_t st) {
+  static const int ta = [] { const char* e = getenv("VXK_W16_TMEM_A"); return e ? atoi(e) : 1; }();
+  return ta ? launch_w16_skinny_impl<MT, BF16, E5M2, SCALED, true>(sp, mw, ma, n_tiles, st)
+            : launch_w16_skinny_impl<MT, BF16, E5M2, SCALED, false>(sp, mw, ma, n_tiles, st);
 }
 
 template <int MT>

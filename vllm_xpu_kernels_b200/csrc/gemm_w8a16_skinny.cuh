@@ -23,6 +23,7 @@
 
 #include "gemm_skinny.cuh"
 #include "gemm_w8a16.cuh"
+#include "gemm_grouped.cuh"   // umma_f16_ts, tmem_st_32x32b_x16
 
 namespace vxk {
 
@@ -53,33 +54,40 @@ __device__ __forceinline__ void tma_prefetch_2d(const CUtensorMap* m, int c0, in
                : "memory");
 }
 
-template <int MT>
+// TA = the widened operand lives in TENSOR MEMORY instead of shared memory: a tcgen05.mma that reads its 128-row
+// operand from shared memory takes ~130-150 clk per 16-deep step whatever the token count (measured on the grouped
+// GEMM, profiles/r02_grouped_gemm.txt) = 16 weights / clk / SM = 4.5 TB/s of FP8 weight stream at best; from TMEM it
+// is ~80 clk.  The converters write their 32 lanes with tcgen05.st (no proxy fence, no shared-memory round trip),
+// four 64-column operand slots sit next to the accumulator, and the shared memory the slots used goes to the ring.
+template <int MT, bool TA = false>
 struct W16SkinnySmem {
   static constexpr int kRawW = 128 * kW16SkBlockK;          // 16 KB
   static constexpr int kABox = MT * 128;                    // one 64-element activation slice
   static constexpr int kRawStage = kRawW + 2 * kABox;
   static constexpr int kConvSlot = 2 * 128 * 128;           // two operand tiles (128 rows x 64 elements each), 32 KB
-  static constexpr int kConvSlots = 2;
-  static constexpr int kStagesRaw = (196 * 1024 - kConvSlots * kConvSlot) / kRawStage;
-  static constexpr int kStages = kStagesRaw > 8 ? 8 : kStagesRaw;
+  static constexpr int kConvSlots = TA ? 4 : 2;
+  static constexpr int kConvSmem = TA ? 0 : kConvSlots * kConvSlot;
+  static constexpr int kStagesRaw = (196 * 1024 - kConvSmem) / kRawStage;
+  static constexpr int kStages = kStagesRaw > (TA ? 10 : 8) ? (TA ? 10 : 8) : kStagesRaw;
   static constexpr int kBarrierBytes = (2 * kStages + 2 * kConvSlots + 1) * 8 + 16;
-  static constexpr int kTotalBytes = kStages * kRawStage + kConvSlots * kConvSlot + kBarrierBytes + 1024;
+  static constexpr int kTotalBytes = kStages * kRawStage + kConvSmem + kBarrierBytes + 1024;
   static_assert(kRawStage % 1024 == 0, "SWIZZLE_128B tiles need 1024-byte alignment");
   static_assert(kStages >= 2, "ring too shallow");
-  static_assert(kStages * kRawStage + kConvSlots * kConvSlot >= MT * 128 * 4, "the partial tile is parked in the rings");
+  static_assert(kStages * kRawStage + kConvSmem >= MT * 128 * 4, "the partial tile is parked in the rings");
 };
 
-template <int MT, bool BF16, bool E5M2, bool SCALED>
+template <int MT, bool BF16, bool E5M2, bool SCALED, bool TA = false>
 __global__ void __launch_bounds__(kW16SkThreads, 1)
 gemm_w8a16_skinny_kernel(const W16SkinnyParams p, const __grid_constant__ CUtensorMap map_w,
                          const __grid_constant__ CUtensorMap map_a) {
-  using L = W16SkinnySmem<MT>;
+  using L = W16SkinnySmem<MT, TA>;
+  constexpr uint32_t kASlotCol = 256;        // TA: operand slots in TMEM columns [256, 512)
   constexpr int S = L::kStages;
   constexpr int C = L::kConvSlots;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* conv_base = smem + S * L::kRawStage;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(conv_base + C * L::kConvSlot);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(conv_base + L::kConvSmem);
   uint64_t* full_bar = bars;                 // raw stage landed (TMA)
   uint64_t* empty_bar = bars + S;            // raw stage free (MMA commit)
   uint64_t* conv_full = bars + 2 * S;        // conv slot written (converter warps)
@@ -110,7 +118,7 @@ gemm_w8a16_skinny_kernel(const W16SkinnyParams p, const __grid_constant__ CUtens
     mbar_init(acc_bar, 1);
     fence_barrier_init();
   }
-  constexpr uint32_t kCols = MT < 32 ? 32 : MT;
+  constexpr uint32_t kCols = TA ? 512 : (MT < 32 ? 32 : MT);
   if (warp == 2) tmem_alloc<kCols>(tmem_ptr_smem);
   tc_fence_before();
   __syncthreads();
@@ -164,7 +172,22 @@ gemm_w8a16_skinny_kernel(const W16SkinnyParams p, const __grid_constant__ CUtens
       mbar_wait(&full_bar[stage], phase);      // activation boxes
       mbar_wait(&conv_full[cs], cphase);       // widened weight tiles
       tc_fence_after();
-      if (elect_one()) {
+      if constexpr (TA) {
+        if (elect_one()) {
+          const uint32_t a_addr = smem_u32(smem + stage * L::kRawStage + L::kRawW);
+#pragma unroll
+          for (int h = 0; h < 2; ++h) {
+            const uint64_t da = make_kmajor_sw128_desc(a_addr + h * L::kABox);
+#pragma unroll
+            for (int k = 0; k < 4; ++k)          // 16 k = 8 TMEM columns of the operand slot per MMA
+              umma_f16_ts(tmem_base, tmem_base + kASlotCol + cs * 64 + (h * 4 + k) * 8, da + static_cast<uint64_t>(2 * k),
+                          idesc, (it > 0 || h > 0 || k > 0) ? 1u : 0u);
+          }
+          umma_commit(&conv_empty[cs]);
+          umma_commit(&empty_bar[stage]);
+          if (it == nk - 1) umma_commit(acc_bar);
+        }
+      } else if (elect_one()) {
         const uint32_t w_addr = smem_u32(conv_base + cs * L::kConvSlot);
         const uint32_t a_addr = smem_u32(smem + stage * L::kRawStage + L::kRawW);
 #pragma unroll
@@ -188,7 +211,9 @@ gemm_w8a16_skinny_kernel(const W16SkinnyParams p, const __grid_constant__ CUtens
     // ===================== converters =====================
     const int ct = threadIdx.x - 256;          // 0..511: weight row ct / 4, 16-byte chunks jq and 4 + jq of its 128 bytes
     constexpr bool scaled = SCALED;
-    const int row = ct >> 2, jq = ct & 3, sw = row & 7;
+    // TA: a warp writes the 32 TMEM lanes of its quadrant (warp % 4): row = 32 q + lane, the four warps of a quadrant
+    // take the four 32-byte quarters of the 128-byte raw row (chunks 2 jq, 2 jq + 1)
+    const int row = TA ? (warp & 3) * 32 + lane : ct >> 2, jq = TA ? (warp - 8) >> 2 : ct & 3, sw = row & 7;
     int stage = 0, cs = 0;
     uint32_t phase = 0, cphase = 0;
     for (int it = 0; it < nk; ++it) {
@@ -196,7 +221,7 @@ gemm_w8a16_skinny_kernel(const W16SkinnyParams p, const __grid_constant__ CUtens
       const uint32_t raw = smem_u32(smem + stage * L::kRawStage) + row * 128;   // SWIZZLE_128B as TMA wrote it
       uint4 v[2];
 #pragma unroll
-      for (int h = 0; h < 2; ++h) v[h] = lds128(raw + (((h * 4 + jq) ^ sw) << 4));
+      for (int h = 0; h < 2; ++h) v[h] = lds128(raw + (((TA ? 2 * jq + h : h * 4 + jq) ^ sw) << 4));
       float sc = 1.0f;
       if constexpr (scaled) {
         const int n = min(n0 + row, p.N - 1);
@@ -207,13 +232,23 @@ gemm_w8a16_skinny_kernel(const W16SkinnyParams p, const __grid_constant__ CUtens
 #pragma unroll
       for (int h = 0; h < 2; ++h) widen16<BF16, E5M2, SCALED>(v[h], sc, w[h]);
       mbar_wait(&conv_empty[cs], cphase ^ 1);
-      const uint32_t dst = smem_u32(conv_base + cs * L::kConvSlot) + row * 128;
+      if constexpr (TA) {
+        tc_fence_after();
+        uint32_t wv[16];
 #pragma unroll
-      for (int h = 0; h < 2; ++h) {
-        sts128(dst + h * (128 * 128) + (((2 * jq) ^ sw) << 4), w[h][0], w[h][1], w[h][2], w[h][3]);
-        sts128(dst + h * (128 * 128) + (((2 * jq + 1) ^ sw) << 4), w[h][4], w[h][5], w[h][6], w[h][7]);
+        for (int i = 0; i < 16; ++i) wv[i] = w[i >> 3][i & 7];
+        tmem_st_32x32b_x16(tmem_base + (static_cast<uint32_t>((warp & 3) * 32) << 16) + kASlotCol + cs * 64 + jq * 16, wv);
+        tmem_st_wait();
+        tc_fence_before();
+      } else {
+        const uint32_t dst = smem_u32(conv_base + cs * L::kConvSlot) + row * 128;
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+          sts128(dst + h * (128 * 128) + (((2 * jq) ^ sw) << 4), w[h][0], w[h][1], w[h][2], w[h][3]);
+          sts128(dst + h * (128 * 128) + (((2 * jq + 1) ^ sw) << 4), w[h][4], w[h][5], w[h][6], w[h][7]);
+        }
+        fence_proxy_async_smem();
       }
-      fence_proxy_async_smem();
       __syncwarp();
       if (lane == 0) mbar_arrive(&conv_full[cs]);
       if (++cs == C) { cs = 0; cphase ^= 1; }
