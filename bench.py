@@ -18,7 +18,8 @@ are independent).
                `also`: the other kernel of the step and BASELINE config 1 (4096 x 4096 per-token FP8),
                `gemm`: the GEMM half of the metric -- FP8 / MXFP4 / fp8_w8a16 at the Llama-3-70B shapes,
                DeepSeek-V3 block-scaled FP8 (config 5) and a Llama-3-8B W8A8 M sweep (config 3), each row with
-               its own tensor / HBM roofline fraction (bench_gemm.py)
+               its own tensor / HBM roofline fraction, and `moe_grouped`: the MoE grouped GEMM on the reference
+               test's Llama-4-scout shape, three recipes x decode / prefill token counts (bench_gemm.py)
   cpu_baseline the reference's torch CPU path (oracle/) on a bounded sample, host cores stated; `gemm`: the
                GEMM test formula (dequantise -> fp32 matmul) at M = 512
   e2e          the same step through torch.ops with pinned HOST buffers, double-buffered over three streams

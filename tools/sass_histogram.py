@@ -16,13 +16,14 @@ FAMILIES = [
     ("gemm_tc2_kernel (CTA-pair FP8 / MXFP8 / MXFP4)", r"gemm_tc2_kernel"),
     ("gemm_tc2_blk_kernel (fp32-block FP8)", r"gemm_tc2_blk_kernel"),
     ("gemm_tc_kernel (single CTA)", r"gemm_tc_kernel"),
-    ("gemm_skinny (small-M FP8)", r"skinny"),
+    ("gemm_grouped_kernel (MoE grouped GEMM)", r"gemm_grouped"),
     ("gemm_w8a16", r"w8a16|w16"),
+    ("gemm_skinny (small-M FP8 / MXFP4)", r"skinny"),
     ("row_quant_kernel (a1, a6-a9)", r"row_quant_kernel"),
     ("flat_quant_kernel (a4, a5, a10-a12)", r"flat_quant_kernel"),
     ("cache ops (f3)", r"indexer|cp_gather|convert_fp8"),
 ]
-KEY = ["UTCHMMA", "UTCQMMA", "UTCOMMA", "UTCIMMA", "UTCCP", "UTCBAR", "UTMALDG", "UBLKCP", "LDTM", "SYNCS", "HMMA", "IMMA",
+KEY = ["UTCHMMA", "UTCQMMA", "UTCOMMA", "UTCIMMA", "UTCCP", "UTCBAR", "UTMALDG", "UBLKCP", "LDTM", "STTM", "SYNCS", "HMMA", "IMMA",
        "FFMA2", "FMUL2", "FADD2", "F2FP", "F2F", "DFMA", "MUFU", "LDG", "STG", "LDS", "STS", "SHFL", "BAR", "ACQBULK",
        "ELECT", "UCGABAR_ARV", "UCGABAR_WAIT", "USETMAXREG"]
 
