@@ -69,6 +69,20 @@ def main():
     src = torch.randn(4, 64, 32, dtype=bf, device=DEV)
     dst = torch.empty(4, 64, 32, dtype=torch.uint8, device=DEV)
     ops.convert_fp8(dst, src, 2.0, "fp8"); n += 1
+    # MoE grouped GEMM: 16-bit / fp8 (shared-memory operand) / mxfp4 (TMEM operand and, at 256-row tiles, shared memory)
+    from vllm_xpu_kernels_b200.fused_moe_interface import cutlass_grouped_gemm_xe2
+    for rows in ([5, 0, 40, 19], [300, 290, 310, 324]):
+        E, N, K = 4, 264, 256
+        r = torch.tensor(rows, dtype=torch.int32, device=DEV)
+        a = torch.randn(sum(rows) + 2, K, dtype=bf, device=DEV)
+        d = torch.empty(a.shape[0], N, dtype=bf, device=DEV)
+        bias = torch.randn(E, N, dtype=bf, device=DEV)
+        cutlass_grouped_gemm_xe2(a, torch.randn(E, K, N, dtype=bf, device=DEV), None, bias, d, r, N, K, E); n += 1
+        cutlass_grouped_gemm_xe2(a, torch.randn(E, K, N, device=DEV).to(E4), torch.rand(E, device=DEV) + 0.5, bias, d, r,
+                                 N, K, E); n += 1
+        b4 = torch.randint(0, 255, (E, N, K // 2), dtype=torch.uint8, device=DEV).view(torch.float4_e2m1fn_x2)
+        s4 = torch.randint(110, 130, (E, N, K // 32), dtype=torch.uint8, device=DEV)
+        cutlass_grouped_gemm_xe2(a, b4, s4, bias, d, r, N, K, E); n += 1
     torch.cuda.synchronize()
     print(f"sanitize_smoke: {n} op calls completed")
 
