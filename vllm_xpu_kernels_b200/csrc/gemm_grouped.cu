@@ -112,11 +112,44 @@ static int launch_gg_types(const GroupedParams& gp, const CUtensorMap& mw, const
       return bf16 ? launch_gg<MT, GW_MX4T, true, false>(gp, mw, ma, max_tiles, st)
                   : launch_gg<MT, GW_MX4T, false, false>(gp, mw, ma, max_tiles, st);
   }
+  if (wkind == GW_FP8T) {
+    if (bf16)
+      return e5m2 ? launch_gg<MT, GW_FP8T, true, true>(gp, mw, ma, max_tiles, st)
+                  : launch_gg<MT, GW_FP8T, true, false>(gp, mw, ma, max_tiles, st);
+    return e5m2 ? launch_gg<MT, GW_FP8T, false, true>(gp, mw, ma, max_tiles, st)
+                : launch_gg<MT, GW_FP8T, false, false>(gp, mw, ma, max_tiles, st);
+  }
   if (bf16)
     return e5m2 ? launch_gg<MT, GW_FP8, true, true>(gp, mw, ma, max_tiles, st)
                 : launch_gg<MT, GW_FP8, true, false>(gp, mw, ma, max_tiles, st);
   return e5m2 ? launch_gg<MT, GW_FP8, false, true>(gp, mw, ma, max_tiles, st)
               : launch_gg<MT, GW_FP8, false, false>(gp, mw, ma, max_tiles, st);
+}
+
+// Dense fp8_gemm_w8a16 at large M through the grouped kernel (one expert owning every row, weights W[N, K]
+// K-contiguous, widened operand in TMEM, 256-token tiles): see gemm_w8a16.cu for why.
+int run_w8a16_dense_tmem(void* D, const void* A, const void* W, const float* scale, int per_channel, const void* bias,
+                         int64_t M, int64_t N, int64_t K, int64_t lda, int64_t ldw, int64_t ldd, bool bf16, bool e5m2,
+                         cudaStream_t st) {
+  const int mt = M <= 32 ? 32 : (M <= 64 ? 64 : (M <= 128 ? 128 : 256));
+  const int block_k = mt <= 128 ? 128 : kGgBlockK;
+  GroupedParams gp{};
+  gp.D = D; gp.bias = bias; gp.rows = nullptr; gp.w_scale = scale; gp.scale_per_channel = per_channel;
+  gp.total_m = static_cast<int>(M); gp.N = static_cast<int>(N); gp.K = static_cast<int>(K); gp.E = 1;
+  gp.num_kb = static_cast<int>((K + block_k - 1) / block_k);
+  gp.num_nt = static_cast<int>((N + 127) / 128);
+  gp.ldd = ldd;
+  const int64_t max_tiles = ((M + mt - 1) / mt) * gp.num_nt;
+  CUtensorMap mw, ma;
+  int rc;
+  if ((rc = make_map_2d_u8(&ma, A, static_cast<uint64_t>(K) * 2, M, static_cast<uint64_t>(lda) * 2, 128, mt, true))) return rc;
+  if ((rc = make_map_3d_u8(&mw, W, K, N, 1, ldw, N * ldw, block_k, 128, block_k))) return rc;
+  switch (mt) {
+    case 32: return launch_gg_types<32>(gp, mw, ma, max_tiles, GW_FP8T, bf16, e5m2, st);
+    case 64: return launch_gg_types<64>(gp, mw, ma, max_tiles, GW_FP8T, bf16, e5m2, st);
+    case 128: return launch_gg_types<128>(gp, mw, ma, max_tiles, GW_FP8T, bf16, e5m2, st);
+    default: return launch_gg_types<256>(gp, mw, ma, max_tiles, GW_FP8T, bf16, e5m2, st);
+  }
 }
 
 }  // namespace vxk

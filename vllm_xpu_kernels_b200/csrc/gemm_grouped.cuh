@@ -38,7 +38,9 @@
 
 namespace vxk {
 
-constexpr int GW_16 = 0, GW_FP8 = 1, GW_MX4 = 2, GW_MX4T = 3;   // MX4T: mxfp4 with the widened operand in TMEM
+constexpr int GW_16 = 0, GW_FP8 = 1, GW_MX4 = 2;
+constexpr int GW_MX4T = 3;   // mxfp4 with the widened operand in TMEM
+constexpr int GW_FP8T = 4;   // fp8 weights [E, N, K] (K-contiguous: the dense fp8_gemm_w8a16 layout), operand in TMEM
 constexpr int kGgBlockK = 64;
 #ifndef VXK_GG_STAGE_CAP
 #define VXK_GG_STAGE_CAP 10
@@ -55,7 +57,8 @@ struct GroupedParams {
   const void* bias;        // [E, N] activation dtype, or null
   const float* w_scale;    // GW_FP8: [E]
   const uint8_t* w_sf;     // GW_MX4: [E, N, K / 32]
-  const int32_t* rows;     // [E]
+  const int32_t* rows;     // [E]; null: one expert owning all total_m rows (dense call)
+  int scale_per_channel;   // GW_FP8T: w_scale is [E, N] (per output channel) instead of [E]
   int total_m, N, K, E;
   int num_kb, num_nt;
   int64_t ldd;
@@ -131,11 +134,14 @@ __device__ __forceinline__ void e2m1x8_widen(uint32_t word, uint32_t sc2, uint32
 
 template <int MT, int WKIND>
 struct GgSmem {
-  static constexpr bool kTmemA = WKIND == GW_MX4T;
+  static constexpr bool kTmemA = WKIND == GW_MX4T || WKIND == GW_FP8T;
   static constexpr bool kConv = WKIND != GW_16;
-  static constexpr int kBlockK = kTmemA ? 128 : kGgBlockK;          // K elements per ring stage
+  // K elements per ring stage: 128 with the operand in TMEM, 64 otherwise and for 256-token tiles (whose
+  // activation boxes are 32 KB per 64 k)
+  static constexpr int kBlockK = (kTmemA && MT <= 128) ? 128 : kGgBlockK;
   static constexpr int kOpBytes = 128 * 128;            // 128 weight rows x 64 elements of 16 bits
-  static constexpr int kRawW = WKIND == GW_16 ? kOpBytes : WKIND == GW_FP8 ? 64 * 128 : kTmemA ? 128 * 64 : 128 * 32;
+  static constexpr int kRawW = WKIND == GW_16 ? kOpBytes : WKIND == GW_FP8 ? 64 * 128
+                               : WKIND == GW_FP8T ? 128 * kBlockK : WKIND == GW_MX4T ? 128 * 64 : 128 * 32;
   static constexpr int kABox = MT * 128;                // one 64-deep activation slice
   static constexpr int kABoxes = kBlockK / 64;
   static constexpr int kStageBytes = (kRawW + kABoxes * kABox + 1023) / 1024 * 1024;
@@ -155,7 +161,10 @@ struct GgSmem {
   static constexpr int kBarrierBytes = (2 * kStages + 2 * 8 + 4) * 8 + 16;
   static constexpr int kTotalBytes = kStages * kStageBytes + kConvSmemBytes + kBarrierBytes + kSchedBytes + 1024;
   static_assert(kStages >= 3, "ring too shallow");
-  static_assert(!kTmemA || MT <= 128, "TMEM: 2 x MT accumulator columns + 4 x 64 operand columns");
+  // TMEM-A: operand slots in columns [256, 512), accumulators in [0, 256): two buffers up to MT = 128, one at 256
+  static constexpr int kAccBufs = (kTmemA && MT > 128) ? 1 : 2;
+  static constexpr int kSlotCols = kBlockK / 2;         // one TMEM column = two consecutive k
+  static_assert(WKIND != GW_MX4T || MT <= 128, "mxfp4 with 256-token tiles keeps the shared-memory operand");
 };
 
 struct GgTile { int e, row0, rows, n0; };
@@ -233,7 +242,7 @@ gemm_grouped_kernel(const GroupedParams p, const __grid_constant__ CUtensorMap m
     int carry_r = 0, carry_t = 0;
     for (int base = 0; base < p.E; base += 32) {
       const int e = base + lane;
-      int r = e < p.E ? __ldg(p.rows + e) : 0;
+      int r = e < p.E ? (p.rows ? __ldg(p.rows + e) : p.total_m) : 0;
       r = r < 0 ? 0 : r;
       int sr = r, stl = (r + MT - 1) / MT;
 #pragma unroll
@@ -271,7 +280,9 @@ gemm_grouped_kernel(const GroupedParams p, const __grid_constant__ CUtensorMap m
             tma_load_3d(stage_w(stage) + 8192, &map_w, &full_bar[stage], t.n0 * 2 + 128, kb * kGgBlockK, t.e);
           } else if constexpr (WKIND == GW_FP8) {
             tma_load_3d(stage_w(stage), &map_w, &full_bar[stage], t.n0, kb * kGgBlockK, t.e);
-          } else {                                // (k bytes, weight row, expert)
+          } else if constexpr (WKIND == GW_FP8T) {   // (k bytes, weight row, expert)
+            tma_load_3d(stage_w(stage), &map_w, &full_bar[stage], kb * L::kBlockK, t.n0, t.e);
+          } else {                                // (k bytes, weight row, expert), two codes per byte
             tma_load_3d(stage_w(stage), &map_w, &full_bar[stage], kb * (L::kBlockK / 2), t.n0, t.e);
           }
 #pragma unroll
@@ -290,8 +301,8 @@ gemm_grouped_kernel(const GroupedParams p, const __grid_constant__ CUtensorMap m
     int stage = 0, cs = 0, iter = 0;
     uint32_t phase = 0, cphase = 0;
     for (int idx = blockIdx.x; idx < num_tiles; idx += gridDim.x, ++iter) {
-      const int as = iter & 1;
-      const uint32_t aphase = (iter >> 1) & 1;
+      const int as = iter % L::kAccBufs;
+      const uint32_t aphase = (iter / L::kAccBufs) & 1;
       mbar_wait(&tmem_empty_bar[as], aphase ^ 1);
       tc_fence_after();
       const uint32_t tmem_d = tmem_base + as * MT;
@@ -302,13 +313,12 @@ gemm_grouped_kernel(const GroupedParams p, const __grid_constant__ CUtensorMap m
         if constexpr (kTmemA) {
           if (elect_one()) {
 #pragma unroll
-            for (int h = 0; h < 2; ++h) {
+            for (int h = 0; h < L::kABoxes; ++h) {
               const uint64_t da = make_kmajor_sw128_desc(smem_u32(stage_a(stage) + h * L::kABox));
 #pragma unroll
               for (int k = 0; k < 4; ++k)         // 16 k = 8 TMEM columns of the operand slot per MMA
-                umma_f16_ts((p.dbg & 16) ? tmem_base + ((k & 1) ? MT : 0) : tmem_d,
-                            tmem_base + kASlotCol + cs * 64 + (h * 4 + k) * 8, da + static_cast<uint64_t>(2 * k),
-                            idesc, (kb > 0 || h > 0 || k > 0) ? 1u : 0u);
+                umma_f16_ts(tmem_d, tmem_base + kASlotCol + cs * L::kSlotCols + (h * 4 + k) * 8,
+                            da + static_cast<uint64_t>(2 * k), idesc, (kb > 0 || h > 0 || k > 0) ? 1u : 0u);
             }
             umma_commit(&conv_empty[cs]);
             umma_commit(&empty_bar[stage]);
@@ -333,7 +343,49 @@ gemm_grouped_kernel(const GroupedParams p, const __grid_constant__ CUtensorMap m
     }
   } else if (warp >= 8) {
     // ===================== converters =====================
-    if constexpr (kTmemA) {
+    if constexpr (WKIND == GW_FP8T) {
+      // fp8 [N, K] weights, operand in TMEM: thread (quadrant q = warp % 4, lane) owns weight row 32 q + lane, the
+      // four warps of a quadrant split the stage's K.  raw: 128 rows x kBlockK bytes, swizzled with a span of one row
+      // (SWIZZLE_128B / SWIZZLE_64B): consecutive rows reading the same logical chunk hit different bank groups.
+      constexpr int kBK = L::kBlockK;
+      constexpr int kChunks = kBK / 64;            // 16-byte chunks per thread and stage (2 or 1)
+      const int q = warp & 3, j = (warp - 8) >> 2, row = q * 32 + lane;
+      const int sw = kBK == 128 ? (row & 7) : ((row >> 1) & 3);
+      int stage = 0, cs = 0;
+      uint32_t phase = 0, cphase = 0;
+      for (int idx = blockIdx.x; idx < num_tiles; idx += gridDim.x) {
+        for (int kb = 0; kb < p.num_kb; ++kb) {
+          mbar_wait(&full_bar[stage], phase);
+          const uint32_t raw = smem_u32(stage_w(stage)) + row * kBK;
+          uint32_t w[kChunks * 8];
+#pragma unroll
+          for (int c = 0; c < kChunks; ++c) {
+            const uint4 v = lds128(raw + (((kChunks * j + c) ^ sw) << 4));
+            uint32_t t8[8];
+            widen16<BF16, E5M2, false>(v, 1.0f, t8);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) w[c * 8 + i] = t8[i];
+          }
+          mbar_wait(&conv_empty[cs], cphase ^ 1);
+          tc_fence_after();
+          const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + kASlotCol + cs * L::kSlotCols +
+                                 j * (kChunks * 8);
+          if constexpr (kChunks == 2) {
+            tmem_st_32x32b_x16(taddr, w);
+          } else {
+            asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"r"(taddr),
+                         "r"(w[0]), "r"(w[1]), "r"(w[2]), "r"(w[3]), "r"(w[4]), "r"(w[5]), "r"(w[6]), "r"(w[7])
+                         : "memory");
+          }
+          tmem_st_wait();
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&conv_full[cs]);
+          if (++cs == C) { cs = 0; cphase ^= 1; }
+          if (++stage == S) { stage = 0; phase ^= 1; }
+        }
+      }
+    } else if constexpr (kTmemA) {
       // mxfp4, operand in TMEM: a warp can only write the 32 TMEM lanes of its quadrant (warp % 4), so thread
       // (quadrant q, lane l) owns weight row 32 q + l; the four warps of a quadrant split the stage's 128 k into the
       // four 32-code scale groups.  raw: 128 rows x 64 B, SWIZZLE_64B (16-byte chunk ^= (row >> 1) & 3): eight
@@ -501,12 +553,15 @@ gemm_grouped_kernel(const GroupedParams p, const __grid_constant__ CUtensorMap m
     int iter = 0;
     for (int idx = blockIdx.x; idx < num_tiles; idx += gridDim.x, ++iter) {
       const GgTile t = gg_tile<MT>(tile_start, row_start, p.E, p.num_nt, idx);
-      const int as = iter & 1;
-      const uint32_t aphase = (iter >> 1) & 1;
+      const int as = iter % L::kAccBufs;
+      const uint32_t aphase = (iter / L::kAccBufs) & 1;
       const int n = t.n0 + col;
       const bool n_ok = n < p.N;
       float sc = 1.0f, bv = 0.0f;
       if constexpr (WKIND == GW_FP8) sc = __ldg(p.w_scale + t.e);
+      if constexpr (WKIND == GW_FP8T)
+        sc = p.scale_per_channel ? (n_ok ? __ldg(p.w_scale + static_cast<int64_t>(t.e) * p.N + n) : 0.0f)
+                                 : __ldg(p.w_scale + t.e);
       if (p.bias && n_ok) {
         const int64_t bi = static_cast<int64_t>(t.e) * p.N + n;
         bv = BF16 ? __bfloat162float(static_cast<const __nv_bfloat16*>(p.bias)[bi])

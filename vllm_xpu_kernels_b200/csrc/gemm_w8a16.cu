@@ -7,6 +7,10 @@
 
 namespace vxk {
 
+int run_w8a16_dense_tmem(void* D, const void* A, const void* W, const float* scale, int per_channel, const void* bias,
+                         int64_t M, int64_t N, int64_t K, int64_t lda, int64_t ldw, int64_t ldd, bool bf16, bool e5m2,
+                         cudaStream_t st);
+
 // ---- CUDA-core path: any strides, any K / N; 32 x 32 outputs per CTA, fp32 accumulation ----
 struct W16FallbackParams {
   void* D; const void* A; const uint8_t* B; const float* b_scale; const void* bias;
@@ -259,6 +263,21 @@ extern "C" int vxk_fp8_gemm_w8a16(void* D, const void* A, const void* B, const f
       if (rc) return rc;
     }
     return VXK_OK;
+  }
+
+  // Large M: the swap-AB kernel with the widened weight tile in TENSOR memory (gemm_grouped.cuh, GW_FP8T, one
+  // "expert").  The kernel below keeps tokens on the 128-row side and the widened 256-column weight tile in shared
+  // memory: per 64-deep step that is 128 KB of shared-memory traffic (TMA writes 32, converter reads 16 + writes
+  // 32, MMA reads 48) in the 512 clk the MMAs take = 250 B/clk against the SM's 128 B/clk -- shared-memory bound
+  // at 0.51 of the bf16 peak, which is where it measured (0.53-0.56).  With the weights on the 128-row side in TMEM
+  // and 256 tokens as the N operand the same step moves 80 KB (156 B/clk).
+  static const int dense_ta = [] { const char* e = getenv("VXK_W16_DENSE_TMEM_A"); return e ? atoi(e) : 1; }();
+  const int want_bias_dtype = act_dtype == VXK_BF16 ? VXK_BF16 : VXK_F16;
+  if (dense_ta && b_scale_mode != 2 && K % 64 == 0 && (!bias || bias_dtype == want_bias_dtype) && ldd % 2 == 0 &&
+      N % 2 == 0 && (reinterpret_cast<uintptr_t>(D) & 3) == 0) {
+    const int rc = run_w8a16_dense_tmem(D, A, B, b_scale, b_scale_mode == 1, bias, M, N, K, lda, b_stride_n, ldd,
+                                        act_dtype == VXK_BF16, fp8_dtype == VXK_Q_E5M2, st);
+    return rc;
   }
 
   W16Params wp{};
