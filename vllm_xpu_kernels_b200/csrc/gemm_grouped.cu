@@ -107,11 +107,9 @@ static int launch_gg_types(const GroupedParams& gp, const CUtensorMap& mw, const
   if (wkind == GW_MX4)
     return bf16 ? launch_gg<MT, GW_MX4, true, false>(gp, mw, ma, max_tiles, st)
                 : launch_gg<MT, GW_MX4, false, false>(gp, mw, ma, max_tiles, st);
-  if constexpr (MT <= 128) {
-    if (wkind == GW_MX4T)
-      return bf16 ? launch_gg<MT, GW_MX4T, true, false>(gp, mw, ma, max_tiles, st)
-                  : launch_gg<MT, GW_MX4T, false, false>(gp, mw, ma, max_tiles, st);
-  }
+  if (wkind == GW_MX4T)
+    return bf16 ? launch_gg<MT, GW_MX4T, true, false>(gp, mw, ma, max_tiles, st)
+                : launch_gg<MT, GW_MX4T, false, false>(gp, mw, ma, max_tiles, st);
   if (wkind == GW_FP8T) {
     if (bf16)
       return e5m2 ? launch_gg<MT, GW_FP8T, true, true>(gp, mw, ma, max_tiles, st)
@@ -196,11 +194,12 @@ extern "C" int vxk_moe_grouped_gemm(void* D, const void* A, const void* B, const
   int mt = avg <= 32 ? 32 : (avg <= 64 ? 64 : (avg <= 128 ? 128 : 256));
   if (env_mt == 32 || env_mt == 64 || env_mt == 128 || env_mt == 256) mt = env_mt;
 
-  // mxfp4 with the widened operand in TMEM (token tiles up to 128 rows; 256-row tiles are tensor bound either way)
-  static const int env_ta = gg_env_int("VXK_GG_TMEM_A", 1);
+  // mxfp4 with the widened operand in TMEM: 128-deep stages up to 128-token tiles, 64-deep at 256 (VXK_GG_TMEM_A=0:
+  // the shared-memory operand everywhere; =1: TMEM only up to 128-token tiles)
+  static const int env_ta = gg_env_int("VXK_GG_TMEM_A", 2);
   int launch_kind = wkind;
-  if (wkind == GW_MX4 && env_ta && mt <= 128 && K % 128 == 0) launch_kind = GW_MX4T;
-  const int block_k = launch_kind == GW_MX4T ? 128 : kGgBlockK;
+  if (wkind == GW_MX4 && env_ta && (mt <= 128 ? K % 128 == 0 : env_ta >= 2)) launch_kind = GW_MX4T;
+  const int block_k = (launch_kind == GW_MX4T && mt <= 128) ? 128 : kGgBlockK;
 
   GroupedParams gp{};
   gp.D = D; gp.bias = bias; gp.rows = rows_per_expert;
@@ -223,7 +222,7 @@ extern "C" int vxk_moe_grouped_gemm(void* D, const void* A, const void* B, const
     return rc;
   if (wkind == GW_MX4)
     rc = make_map_3d_u8(&mw, B, K / 2, N, num_experts, K / 2, N * (K / 2), block_k / 2, 128,
-                        launch_kind == GW_MX4T ? 64 : 0);
+                        (launch_kind == GW_MX4T && mt <= 128) ? 64 : 0);
   else
     rc = make_map_3d_u8(&mw, B, wpitch, K, num_experts, wpitch, K * wpitch, 128, kGgBlockK, 128);
   if (rc) return rc;

@@ -141,7 +141,7 @@ struct GgSmem {
   static constexpr int kBlockK = (kTmemA && MT <= 128) ? 128 : kGgBlockK;
   static constexpr int kOpBytes = 128 * 128;            // 128 weight rows x 64 elements of 16 bits
   static constexpr int kRawW = WKIND == GW_16 ? kOpBytes : WKIND == GW_FP8 ? 64 * 128
-                               : WKIND == GW_FP8T ? 128 * kBlockK : WKIND == GW_MX4T ? 128 * 64 : 128 * 32;
+                               : WKIND == GW_FP8T ? 128 * kBlockK : WKIND == GW_MX4T ? 128 * (kBlockK / 2) : 128 * 32;
   static constexpr int kABox = MT * 128;                // one 64-deep activation slice
   static constexpr int kABoxes = kBlockK / 64;
   static constexpr int kStageBytes = (kRawW + kABoxes * kABox + 1023) / 1024 * 1024;
@@ -164,7 +164,6 @@ struct GgSmem {
   // TMEM-A: operand slots in columns [256, 512), accumulators in [0, 256): two buffers up to MT = 128, one at 256
   static constexpr int kAccBufs = (kTmemA && MT > 128) ? 1 : 2;
   static constexpr int kSlotCols = kBlockK / 2;         // one TMEM column = two consecutive k
-  static_assert(WKIND != GW_MX4T || MT <= 128, "mxfp4 with 256-token tiles keeps the shared-memory operand");
 };
 
 struct GgTile { int e, row0, rows, n0; };
@@ -297,10 +296,14 @@ gemm_grouped_kernel(const GroupedParams p, const __grid_constant__ CUtensorMap m
     // ===================== MMA issuer: D^T[128 x MT] += W16[128 x 16] * A[MT x 16]^T =====================
     // (a_format != b_format -- f16 weights against bf16 activations, which would make the fp8 widening one cvt per
     // two codes -- is rejected by the hardware: illegal instruction, measured)
-    const uint32_t idesc = make_idesc_f16(BF16 ? 1 : 0, 128, MT) | (kMnMajor ? (1u << 15) : 0u);
     int stage = 0, cs = 0, iter = 0;
     uint32_t phase = 0, cphase = 0;
     for (int idx = blockIdx.x; idx < num_tiles; idx += gridDim.x, ++iter) {
+      // UMMA N = the token rows this tile really has, rounded up to 16: the last token tile of an expert is partial
+      // (half a tile wasted per expert on average), and the MMA time scales with N
+      const GgTile t = gg_tile<MT>(tile_start, row_start, p.E, p.num_nt, idx);
+      const int umma_n = min(MT, max(32, (t.rows + 15) & ~15));   // (N = 16 measured slower than 32 on the fp8 path)
+      const uint32_t idesc = make_idesc_f16(BF16 ? 1 : 0, 128, umma_n) | (kMnMajor ? (1u << 15) : 0u);
       const int as = iter % L::kAccBufs;
       const uint32_t aphase = (iter / L::kAccBufs) & 1;
       mbar_wait(&tmem_empty_bar[as], aphase ^ 1);
@@ -387,35 +390,48 @@ gemm_grouped_kernel(const GroupedParams p, const __grid_constant__ CUtensorMap m
       }
     } else if constexpr (kTmemA) {
       // mxfp4, operand in TMEM: a warp can only write the 32 TMEM lanes of its quadrant (warp % 4), so thread
-      // (quadrant q, lane l) owns weight row 32 q + l; the four warps of a quadrant split the stage's 128 k into the
-      // four 32-code scale groups.  raw: 128 rows x 64 B, SWIZZLE_64B (16-byte chunk ^= (row >> 1) & 3): eight
-      // consecutive rows reading the same logical chunk hit eight different bank groups.
+      // (quadrant q, lane l) owns weight row 32 q + l; the four warps of a quadrant split the stage's K.
+      //   128-deep stages (MT <= 128): raw 128 rows x 64 B, SWIZZLE_64B (16-byte chunk ^= (row >> 1) & 3: eight
+      //     consecutive rows reading the same logical chunk hit eight bank groups); a thread takes one 32-code group
+      //   64-deep stages (MT = 256): raw 128 rows x 32 B, linear; a thread takes 16 codes (half a scale group)
+      constexpr int kBK = L::kBlockK;
+      constexpr int kWords = kBK / 8;              // 16-bit pairs (= TMEM columns) per thread and stage: 16 or 8
+      constexpr int kGrp = kBK / 32;               // scale groups per stage: 4 or 2
       const int q = warp & 3, j = (warp - 8) >> 2, row = q * 32 + lane;
+      const int grp = kBK == 128 ? j : (j >> 1);   // this thread's scale group within the stage
       int stage = 0, cs = 0;
       uint32_t phase = 0, cphase = 0;
       for (int idx = blockIdx.x; idx < num_tiles; idx += gridDim.x) {
         const GgTile t = gg_tile<MT>(tile_start, row_start, p.E, p.num_nt, idx);
         const int n = min(t.n0 + row, p.N - 1);
         const uint8_t* sfp = p.w_sf + (static_cast<int64_t>(t.e) * p.N + n) * (p.K / 32);
-        // scale bytes: 16 per fetch = 4 stages x 4 groups, this thread's group j of each; fetched one group ahead
+        // scale bytes: 16 per fetch = 16 / kGrp stages, this thread's group of each; fetched one batch ahead
+        constexpr int kBatch = 16 / kGrp;          // stages per fetch: 4 or 8
         auto sf_load = [&](int kb) {
-          if (p.sf_vec) return __ldg(reinterpret_cast<const uint4*>(sfp + kb * 4));
+          if (p.sf_vec) return __ldg(reinterpret_cast<const uint4*>(sfp + kb * kGrp));
           uint32_t wv[4] = {0, 0, 0, 0};
           for (int i = 0; i < 16; ++i)
-            if (kb * 4 + i < p.K / 32) wv[i >> 2] |= static_cast<uint32_t>(__ldg(sfp + kb * 4 + i)) << (8 * (i & 3));
+            if (kb * kGrp + i < p.K / 32) wv[i >> 2] |= static_cast<uint32_t>(__ldg(sfp + kb * kGrp + i)) << (8 * (i & 3));
           return make_uint4(wv[0], wv[1], wv[2], wv[3]);
         };
         uint4 sf_nxt = sf_load(0);
-        uint32_t sf4 = 0;
+        uint32_t sf_lo = 0, sf_hi = 0;             // this thread's next scale bytes, the next one lowest
         for (int kb = 0; kb < p.num_kb; ++kb) {
-          if ((kb & 3) == 0) {
-            const uint32_t sel = 0x4000u | (static_cast<uint32_t>(4 + j) << 4) | static_cast<uint32_t>(j);
-            const uint32_t lo = __byte_perm(sf_nxt.x, sf_nxt.y, sel), hi = __byte_perm(sf_nxt.z, sf_nxt.w, sel);
-            sf4 = __byte_perm(lo, hi, 0x5410u);
-            if (kb + 4 < p.num_kb) sf_nxt = sf_load(kb + 4);
+          if ((kb & (kBatch - 1)) == 0) {
+            if constexpr (kGrp == 4) {
+              const uint32_t sel = 0x4000u | (static_cast<uint32_t>(4 + grp) << 4) | static_cast<uint32_t>(grp);
+              const uint32_t lo = __byte_perm(sf_nxt.x, sf_nxt.y, sel), hi = __byte_perm(sf_nxt.z, sf_nxt.w, sel);
+              sf_lo = __byte_perm(lo, hi, 0x5410u);
+            } else {
+              const uint32_t sel = grp ? 0x7531u : 0x6420u;
+              sf_lo = __byte_perm(sf_nxt.x, sf_nxt.y, sel);
+              sf_hi = __byte_perm(sf_nxt.z, sf_nxt.w, sel);
+            }
+            if (kb + kBatch < p.num_kb) sf_nxt = sf_load(kb + kBatch);
           }
-          const uint32_t sb = sf4 & 0xffu;
-          sf4 >>= 8;
+          const uint32_t sb = sf_lo & 0xffu;
+          sf_lo = __funnelshift_r(sf_lo, sf_hi, 8);
+          sf_hi >>= 8;
           uint32_t h;
           if constexpr (BF16) {
             h = sb << 7;                          // bf16 bits of 2^(sb-127): the reference's (scale << 7).view(bf16)
@@ -425,26 +441,32 @@ gemm_grouped_kernel(const GroupedParams p, const __grid_constant__ CUtensorMap m
           }
           const uint32_t sc2 = h | (h << 16);
           mbar_wait(&full_bar[stage], phase);
-          const uint4 v = lds128(smem_u32(stage_w(stage)) + row * 64 + ((j ^ ((row >> 1) & 3)) << 4));
-          uint32_t w[16];
-          if (p.dbg & 4) {
-#pragma unroll
-            for (int i = 0; i < 16; ++i) w[i] = v.x;
+          uint32_t vv[kWords / 4];
+          if constexpr (kBK == 128) {
+            const uint4 v = lds128(smem_u32(stage_w(stage)) + row * 64 + ((j ^ ((row >> 1) & 3)) << 4));
+            vv[0] = v.x; vv[1] = v.y; vv[2] = v.z; vv[3] = v.w;
           } else {
-            uint32_t t4[4];
-            const uint32_t vv[4] = {v.x, v.y, v.z, v.w};
+            asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(vv[0]), "=r"(vv[1])
+                         : "r"(smem_u32(stage_w(stage)) + row * 32 + j * 8));
+          }
+          uint32_t w[kWords];
 #pragma unroll
-            for (int i = 0; i < 4; ++i) {
-              e2m1x8_widen<BF16>(vv[i], sc2, t4);
-              w[4 * i] = t4[0]; w[4 * i + 1] = t4[1]; w[4 * i + 2] = t4[2]; w[4 * i + 3] = t4[3];
-            }
+          for (int i = 0; i < kWords / 4; ++i) {
+            uint32_t t4[4];
+            e2m1x8_widen<BF16>(vv[i], sc2, t4);
+            w[4 * i] = t4[0]; w[4 * i + 1] = t4[1]; w[4 * i + 2] = t4[2]; w[4 * i + 3] = t4[3];
           }
           mbar_wait(&conv_empty[cs], cphase ^ 1);
           tc_fence_after();
-          if (!(p.dbg & 8)) {
-            tmem_st_32x32b_x16(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + kASlotCol + cs * 64 + j * 16, w);
-            tmem_st_wait();
+          const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + kASlotCol + cs * L::kSlotCols + j * kWords;
+          if constexpr (kWords == 16) {
+            tmem_st_32x32b_x16(taddr, w);
+          } else {
+            asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"r"(taddr),
+                         "r"(w[0]), "r"(w[1]), "r"(w[2]), "r"(w[3]), "r"(w[4]), "r"(w[5]), "r"(w[6]), "r"(w[7])
+                         : "memory");
           }
+          tmem_st_wait();
           tc_fence_before();
           __syncwarp();
           if (lane == 0) mbar_arrive(&conv_full[cs]);
