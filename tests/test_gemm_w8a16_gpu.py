@@ -82,7 +82,10 @@ def test_fp8_gemm_w8a16(ops, lib, fp8, dtype, trans_wei, is_mbk, batch, mnk):
 @pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
 @pytest.mark.parametrize("is_nt", [True, False])
 @pytest.mark.parametrize("scale_layout", ["flat_1d", "row_2d"])
-@pytest.mark.parametrize("mnk", MNK_FACTORS + [(100, 200, 2048), (257, 129, 1040), (128, 128, 16), (3, 40, 72)])
+@pytest.mark.parametrize("mnk", MNK_FACTORS + [(100, 200, 2048), (257, 129, 1040), (128, 128, 16), (3, 40, 72),
+                                               # M > 256: the swap-AB TMEM-operand kernel (256-token tiles, 64-deep stages):
+                                               # token tail, N tail (200 = 128 + 72), K = 17 x 64
+                                               (300, 200, 1088), (777, 264, 4160), (1025, 8, 64)])
 @pytest.mark.parametrize("bias", [False, True])
 def test_fp8_gemm_w8a16_per_channel(ops, fp8, dtype, is_nt, scale_layout, mnk, bias):
     """tests/test_fp8_gemm_onednn.py:224-267: per-channel weight scales as [N] or [1, N]."""
