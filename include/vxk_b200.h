@@ -43,6 +43,14 @@ int vxk_abi_version(void);
 const char* vxk_last_error(void);
 /* number of kernels this library has launched in this process (bench "gpu_launches") */
 uint64_t vxk_launch_count(void);
+/* Small-M GEMMs (M <= 128 .. 256 of vxk_fp8_gemm / vxk_fp4_gemm / vxk_fp8_gemm_w8a16) are launched with programmatic
+ * stream serialisation and request their first WEIGHT tiles before griddepcontrol.wait, i.e. while the previous
+ * kernel on the stream is still draining -- the point being that the kernel producing the activations overlaps the
+ * weight prefetch.  PRECONDITION (default on): the weight tensor B and its scales must not be written by work that
+ * is still in flight on the same stream when the GEMM is enqueued (static model weights satisfy this; quantising a
+ * weight and multiplying with it back to back does not).  vxk_set_early_weight_loads(0) (or VXK_SKINNY_PDL=0 in the
+ * environment) launches these kernels as ordinary stream-ordered kernels.  Returns the previous setting. */
+int vxk_set_early_weight_loads(int on);
 /* silu evaluation in the fused silu_and_mul_* kernels.  -1 (default) = auto: the cheapest form that is
  * proven bit-identical to the reference on every input (ex2.approx / rcp.approx for bf16 a10 / a11 and
  * for a12, expf + IEEE divide for f16 a10 / a11); 0 = expf + IEEE divide everywhere; 1 = approximate

@@ -521,3 +521,32 @@ def test_mxfp4_skinny_decode_kernel(ops, lib, m, n, k):
     tol = 1e-2 * float(ref.abs().max())
     torch.testing.assert_close(out.double(), (ref + bias.double()).to(torch.bfloat16).double(), atol=tol, rtol=1e-2)
     torch.testing.assert_close(out16.double(), ref.to(torch.float16).double(), atol=tol, rtol=1e-2)
+
+
+def test_weight_written_right_before_small_m_gemm(ops, lib):
+    """the small-M kernels request weight tiles before griddepcontrol.wait, so a weight written by the
+    kernel just before them on the same stream must be fenced off by the caller -- or the early loads switched off
+    (vxk_set_early_weight_loads(0), include/vxk_b200.h).  With the switch off, 200 back-to-back
+    (rewrite weight -> GEMM) pairs on one stream must all see the new weight."""
+    torch.manual_seed(3)
+    m, n, k = 8, 1024, 4096
+    x = (torch.randn(m, k, device=DEV) / 4).to(E4)
+    xs = torch.ones(m, 1, device=DEV)
+    ws = torch.ones(n, 1, device=DEV)
+    wa = (torch.randn(n, k, device=DEV) / 4).to(E4)
+    wb = (torch.randn(n, k, device=DEV) / 4).to(E4)
+    ref = [ops.fp8_gemm(x, w.t(), torch.bfloat16, xs, ws, None).clone() for w in (wa, wb)]
+    torch.cuda.synchronize()
+    assert not torch.equal(ref[0], ref[1])
+    w = torch.empty_like(wa)
+    prev = lib.vxk_set_early_weight_loads(0)
+    try:
+        outs = []
+        for i in range(200):
+            w.copy_(wb if i % 2 else wa)                         # the producer of the weight, same stream
+            outs.append(ops.fp8_gemm(x, w.t(), torch.bfloat16, xs, ws, None))
+        torch.cuda.synchronize()
+        for i, o in enumerate(outs):
+            assert torch.equal(o, ref[i % 2]), i
+    finally:
+        lib.vxk_set_early_weight_loads(prev)

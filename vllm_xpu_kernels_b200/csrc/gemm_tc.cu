@@ -400,7 +400,7 @@ static int launch_skinny(SkinnyParams sp, const CUtensorMap& mw, const CUtensorM
   attr[0].val.clusterDim.y = sp.splits;
   attr[0].val.clusterDim.z = 1;
   // programmatic dependent launch: prologue + weight prefetch overlap the previous kernel's tail
-  static const int pdl = env_int("VXK_SKINNY_PDL", 1);
+  const int pdl = g_early_weight_loads.load(std::memory_order_relaxed);
   attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
   attr[1].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
@@ -471,7 +471,7 @@ static int launch_skinny_mx4(SkinnyMx4Params sp, const CUtensorMap& mw, const CU
   attr[0].val.clusterDim.x = 1;
   attr[0].val.clusterDim.y = sp.splits;
   attr[0].val.clusterDim.z = 1;
-  static const int pdl = env_int("VXK_SKINNY_PDL", 1);
+  const int pdl = g_early_weight_loads.load(std::memory_order_relaxed);
   attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
   attr[1].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;

@@ -145,7 +145,7 @@ static int launch_w16_skinny_impl(const W16SkinnyParams& sp, const CUtensorMap& 
   attr[0].val.clusterDim.x = 1;
   attr[0].val.clusterDim.y = sp.splits;
   attr[0].val.clusterDim.z = 1;
-  static const int pdl = [] { const char* e = getenv("VXK_SKINNY_PDL"); return e ? atoi(e) : 1; }();
+  const int pdl = g_early_weight_loads.load(std::memory_order_relaxed);
   attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
   attr[1].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;

@@ -4,6 +4,8 @@
 namespace vxk {
 thread_local char g_last_error[512] = {0};
 std::atomic<uint64_t> g_launches{0};
+// small-M GEMMs: programmatic dependent launch with the weight loads issued before griddepcontrol.wait
+std::atomic<int> g_early_weight_loads{[] { const char* e = getenv("VXK_SKINNY_PDL"); return e ? atoi(e) : 1; }()};
 
 int sm_count() {
   static thread_local int cached_dev = -1, cached = 0;
@@ -22,3 +24,4 @@ int sm_count() {
 extern "C" int vxk_abi_version(void) { return VXK_ABI_VERSION; }
 extern "C" const char* vxk_last_error(void) { return vxk::g_last_error; }
 extern "C" uint64_t vxk_launch_count(void) { return vxk::g_launches.load(); }
+extern "C" int vxk_set_early_weight_loads(int on) { return vxk::g_early_weight_loads.exchange(on ? 1 : 0); }

@@ -24,6 +24,7 @@ namespace vxk {
 // ------------------------------------------------------------------ host side
 extern thread_local char g_last_error[512];
 extern std::atomic<uint64_t> g_launches;
+extern std::atomic<int> g_early_weight_loads;
 
 inline int fail(int code, const char* fmt, ...) {
   va_list ap;
