@@ -21,7 +21,7 @@
 extern "C" {
 #endif
 
-#define VXK_ABI_VERSION 6
+#define VXK_ABI_VERSION 7
 
 typedef struct CUstream_st* vxk_stream_t; /* == cudaStream_t */
 
@@ -277,6 +277,23 @@ int vxk_silu_and_mul_mxfp4_quant_sf(void* out, const void* in, float* scales, vo
                                     int64_t ss1, int in_dtype, vxk_stream_t stream);
 /* Scale re-packing launches issued so far by the GEMM entry points (testing aid). */
 uint64_t vxk_sf_pack_launches(void);
+
+/* ------------------------------------------------------- (f) next #2 ---
+ * Quantisation fused into the GEMM's neighbour (no reference counterpart): the gate_up
+ * projection with silu_and_mul and the 1 x 128 block FP8 quantisation in its epilogue.
+ *
+ *   t      = fp8_gemm(A, W^T) as vxk_fp8_gemm would round it to mid_dtype (bf16 / f16):  [M, 2 * inter],
+ *            W [2 * inter, K] K-contiguous (row stride ldb bytes): gate rows first, then up rows
+ *   out_q, out_s = silu_and_mul_per_block_quant(t, group 128, e4m3): codes [M, inter] contiguous, scale of
+ *            (row m, group g) at out_s[m * ss0 + g * ss1]
+ * Bit-identical to the two calls, without writing / re-reading the [M, 2 * inter] intermediate.
+ * a_scale_mode / b_scale_mode: 0 scalar, 1 per token [M] / per channel [2 * inter].  bias nullable, [2 * inter].
+ * Returns VXK_ERR_UNSUPPORTED when inter % 128 != 0 or an operand is not TMA-expressible (16-byte aligned rows).
+ */
+int vxk_fp8_gemm_silu_mul_quant(void* out_q, float* out_s, const void* A, const void* B, const float* a_scale,
+                                const float* b_scale, const void* bias, int64_t M, int64_t inter, int64_t K,
+                                int64_t lda, int64_t ldb, int a_scale_mode, int b_scale_mode, int64_t ss0,
+                                int64_t ss1, int fp8_dtype, int mid_dtype, int bias_dtype, vxk_stream_t stream);
 
 /* ------------------------------------------------------- (f) next #4 ---
  * MoE grouped GEMM.

@@ -196,11 +196,11 @@ static int pair_count_hint() {   // SM pairs a cluster launch can keep resident 
   return sm_count() / 2;
 }
 
-template <int KIND, int BLOCK_N, int NACC>
+template <int KIND, int BLOCK_N, int NACC, int FUSE = 0>
 static int launch_tc2(Tc2Params tp, const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& msa,
                       const CUtensorMap& msb, cudaStream_t st) {
   using L = Tc2Smem<KIND, BLOCK_N, NACC>;
-  auto kernel = gemm_tc2_kernel<KIND, BLOCK_N, NACC>;
+  auto kernel = gemm_tc2_kernel<KIND, BLOCK_N, NACC, FUSE>;
   static PerDeviceOnce once;
   const PerDeviceOnce::Entry cfg_once = once.get([&](PerDeviceOnce::Entry& x) {
     x.err = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotalBytes);
@@ -553,6 +553,45 @@ extern "C" int64_t vxk_fp4_gemm_workspace_bytes(int64_t M, int64_t N, int64_t K)
     need = c > need ? c : need;
   }
   return need;               // 0: the single-CTA kernel reads the caller's scale tensors directly
+}
+
+// Fused gate_up projection: fp8_gemm -> silu_and_mul -> 1 x 128 block FP8 quantisation in one kernel (SURVEY 8f #2,
+// second half).  See include/vxk_b200.h.  Returns VXK_ERR_UNSUPPORTED for shapes the fused kernel does not take (the
+// torch shim then runs the two ops one after the other).
+extern "C" int vxk_fp8_gemm_silu_mul_quant(void* out_q, float* out_s, const void* A, const void* B, const float* a_scale,
+                                           const float* b_scale, const void* bias, int64_t M, int64_t inter, int64_t K,
+                                           int64_t lda, int64_t ldb, int a_scale_mode, int b_scale_mode, int64_t ss0,
+                                           int64_t ss1, int fp8_dtype, int mid_dtype, int bias_dtype, vxk_stream_t stream) {
+  VXK_REQUIRE(M >= 0 && inter >= 0 && K >= 0, "negative shape");
+  VXK_REQUIRE(fp8_dtype == VXK_Q_E4M3 || fp8_dtype == VXK_Q_E5M2, "operands must be e4m3 or e5m2");
+  VXK_REQUIRE(mid_dtype == VXK_BF16 || mid_dtype == VXK_F16, "intermediate type must be bf16 or f16");
+  VXK_REQUIRE(a_scale && b_scale, "scale pointers must not be null");
+  VXK_REQUIRE(a_scale_mode >= 0 && a_scale_mode <= 1 && b_scale_mode >= 0 && b_scale_mode <= 1,
+              "per-tensor / per-token / per-channel scales only");
+  if (M == 0 || inter == 0) return VXK_OK;
+  const int64_t N = 2 * inter;
+  if (force_fallback() || inter % 128 != 0 || !tma_ok(A, lda) || !tma_ok(B, ldb) || K < 32 || !aligned16(out_q) ||
+      M >= (1LL << 31) || N >= (1LL << 31) || K >= (1LL << 31))
+    return fail(VXK_ERR_UNSUPPORTED, "fused gate_up kernel needs inter %% 128 == 0 and TMA-expressible operands");
+  TcParams tp{};
+  tp.D = nullptr; tp.bias = bias; tp.M = (int)M; tp.N = (int)N; tp.K_bytes = (int)K; tp.ldd = N;
+  tp.a_scale_mode = a_scale_mode; tp.b_scale_mode = b_scale_mode; tp.out_dtype = mid_dtype;
+  tp.bias_dtype = bias_dtype; tp.fp8_fmt = fp8_dtype == VXK_Q_E5M2 ? 1 : 0;
+  tp.num_m_blocks = (int)((M + kBlockM - 1) / kBlockM);
+  tp.num_k_blocks = (int)((K + kBlockKBytes - 1) / kBlockKBytes);
+  tp.a_scale = a_scale; tp.b_scale = b_scale;
+  tp.fuse_q = out_q; tp.fuse_s = out_s; tp.fuse_ss0 = ss0; tp.fuse_ss1 = ss1; tp.fuse_inter = (int)inter;
+  Tc2Params t2{};
+  t2.b = tp;
+  t2.num_m_pairs = (int)((M + 255) / 256);
+  t2.num_n_blocks = (int)(inter / 128);
+  CUtensorMap ma, mb, msa{}, msb{};
+  int rc;
+  if ((rc = make_map_2d_u8(&ma, A, K, M, lda, kBlockKBytes, kBlockM, true))) return rc;
+  if ((rc = make_map_2d_u8(&mb, B, K, N, ldb, kBlockKBytes, 128, true))) return rc;
+  cudaStream_t st = stream;
+  return mid_dtype == VXK_BF16 ? launch_tc2<KIND_F8, 256, 1, 1>(t2, ma, mb, msa, msb, st)
+                               : launch_tc2<KIND_F8, 256, 1, 2>(t2, ma, mb, msa, msb, st);
 }
 
 extern "C" int vxk_fp8_gemm(void* D, const void* A, const void* B, const void* a_scale, const void* b_scale,

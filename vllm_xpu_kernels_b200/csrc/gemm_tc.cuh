@@ -46,13 +46,20 @@ struct TcParams {
   void* peer_D[8];        //      peer-mapped [M, N_total] outputs (offset to this rank's columns, row stride ldd like D)
   int peer_multicast;     // 1: peer_D[0] is an NVLS multicast mapping of all ranks' outputs (one multimem.st reaches all)
   int debug;              // bring-up switches (env VXK_GEMM_DEBUG): 1 skip tcgen05.cp, 2 plain MMA, 4 skip re-tiler
+  // fused gate_up GEMM -> silu_and_mul -> 1x128 block FP8 quantisation (gemm_tc2.cuh, FUSE): W is [2 * inter, K] (gate rows,
+  // then up rows), N = 2 * inter; D is not written, the e4m3 codes [M, inter] and fp32 scales go to fuse_q / fuse_s
+  void* fuse_q;
+  float* fuse_s;          // scale of (row m, group g) at fuse_s[m * fuse_ss0 + g * fuse_ss1]
+  int64_t fuse_ss0, fuse_ss1;
+  int fuse_inter;
 };
 
 // One thread's 32 consecutive accumulator columns of output row m: scales, bias, conversion
 // to bf16 / f16 and the stores (128-bit when the row is 16-byte aligned and the chunk is whole).
 // Every array index is a compile-time constant (no local memory).
-__device__ __forceinline__ void epilogue_store_32(const TcParams& p, const uint32_t (&r)[32], int m, int nbase,
-                                                  float row_scale, bool per_col, bool direct_peers = true) {
+// (the arithmetic half: 32 accumulator columns -> 16 packed words of the output type)
+__device__ __forceinline__ void epilogue_pack_32(const TcParams& p, const uint32_t (&r)[32], int nbase, float row_scale,
+                                                 bool per_col, uint32_t (&w)[16]) {
   float v[32];
   const bool whole = nbase + 32 <= p.N;
 #pragma unroll
@@ -82,7 +89,6 @@ __device__ __forceinline__ void epilogue_store_32(const TcParams& p, const uint3
     }
   }
   const bool bf = p.out_dtype == VXK_BF16;
-  uint32_t w[16];
 #pragma unroll
   for (int t = 0; t < 16; ++t) {
     if (bf) {
@@ -93,6 +99,13 @@ __device__ __forceinline__ void epilogue_store_32(const TcParams& p, const uint3
       w[t] = *reinterpret_cast<uint32_t*>(&h);
     }
   }
+}
+
+__device__ __forceinline__ void epilogue_store_32(const TcParams& p, const uint32_t (&r)[32], int m, int nbase,
+                                                  float row_scale, bool per_col, bool direct_peers = true) {
+  uint32_t w[16];
+  epilogue_pack_32(p, r, nbase, row_scale, per_col, w);
+  const bool whole = nbase + 32 <= p.N;
   const int64_t off = static_cast<int64_t>(m) * p.ldd + nbase;
   if (p.n_peers > 0 && direct_peers) {
     // fused all-gather, simple form: the 32-column piece is stored straight into every other rank's output

@@ -29,6 +29,7 @@
 #pragma once
 
 #include "gemm_tc.cuh"
+#include "quant_silu.cuh"
 
 namespace vxk {
 
@@ -208,7 +209,15 @@ __device__ __forceinline__ void tile_coords(int tile, int num_m, int num_n, int 
   nt = r / rows;
 }
 
-template <int KIND, int BLOCK_N, int NACC>
+// FUSE (KIND_F8, 256-wide tiles, NACC = 1 only): 0 = plain GEMM; 1 / 2 = the gate_up projection with silu_and_mul and the
+// 1 x 128 block FP8 quantisation in the epilogue (bf16 / f16 intermediate type).  The pair's tile is 128 gate columns
+// (CTA 0's half of W: rows [g0, g0 + 128)) next to the 128 up columns they multiply (CTA 1's half: rows
+// [inter + g0, + 128)), so every epilogue thread holds whole (gate, up) pairs of its output row: it rounds both to the
+// intermediate type exactly as the plain epilogue would have stored them, runs the SAME prologue / division helpers
+// as silu_and_mul_per_block_quant (quant_silu.cuh) and stores 64 e4m3 codes; the two warps that share a row exchange
+// their 64-column maxima through shared memory.  Bit-identical to fp8_gemm followed by silu_and_mul_per_block_quant,
+// without the [M, 2 inter] 16-bit round trip through HBM.
+template <int KIND, int BLOCK_N, int NACC, int FUSE = 0>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTc2Threads, 1)
 gemm_tc2_kernel(const Tc2Params pp, const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
                 const __grid_constant__ CUtensorMap map_sfa, const __grid_constant__ CUtensorMap map_sfb) {
@@ -277,7 +286,8 @@ gemm_tc2_kernel(const Tc2Params pp, const __grid_constant__ CUtensorMap map_a, c
       tile_coords(tile, pp.num_m_pairs, pp.num_n_blocks, pp.group_m, mt, nt);
       const int m0 = mt * (2 * kBlockM) + static_cast<int>(rank) * kBlockM;
       const int n0 = nt * kTileN;
-      const int nb = n0 + static_cast<int>(rank) * (BLOCK_N / 2);
+      const int nb = FUSE ? nt * (BLOCK_N / 2) + static_cast<int>(rank) * p.fuse_inter
+                          : n0 + static_cast<int>(rank) * (BLOCK_N / 2);
       for (int kb = 0; kb < p.num_k_blocks; ++kb) {
         mbar_wait(&empty_bar[stage], phase ^ 1);
         if (elect_one()) {
@@ -394,6 +404,77 @@ gemm_tc2_kernel(const Tc2Params pp, const __grid_constant__ CUtensorMap map_a, c
         if (p.b_scale_mode == 0) row_scale *= __ldg(p.b_scale);
       }
       const bool per_col = (KIND == KIND_F8) && (p.b_scale_mode == 1);
+      if constexpr (FUSE != 0) {
+        static_assert(FUSE == 0 || (KIND == KIND_F8 && BLOCK_N == 256 && NACC == 1), "fused epilogue: FP8, 256-wide, NACC 1");
+        using T = std::conditional_t<FUSE == 1, __nv_bfloat16, __half>;
+        constexpr int kFast = FUSE == 1 ? 1 : 0;      // the silu auto mode of quant_flat.cu: bf16 approximate (guarded), f16 exact
+        __shared__ float xchg[2][2][kBlockM];          // [tile parity][column half][row of this CTA]
+        const int g0 = nt * 128;                       // first of this tile's 128 output columns
+        const int rl = q * 32 + lane;                  // row within this CTA
+        // this warp: output columns [g0 + 64 h, + 64): gate accumulator columns 64 h .., up columns 128 + 64 h ..
+        uint32_t gw[2][16], uw[2][16];
+#pragma unroll
+        for (int c = 0; c < 2; ++c) {
+          uint32_t r[32];
+          const uint32_t tbase = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * kAccCols + h * 64 + c * 32;
+          tmem_ld_32x32b_x32(tbase, r);
+          tmem_ld_wait();
+          epilogue_pack_32(p, r, g0 + h * 64 + c * 32, row_scale, per_col, gw[c]);
+          tmem_ld_32x32b_x32(tbase + 128, r);
+          tmem_ld_wait();
+          epilogue_pack_32(p, r, p.fuse_inter + g0 + h * 64 + c * 32, row_scale, per_col, uw[c]);
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive_cluster(&tmem_empty_bar[as], 0);     // accumulator handed back before the arithmetic
+        uint32_t yw[8][4];
+        float gmax = 0.0f;
+#pragma unroll
+        for (int vv = 0; vv < 8; ++vv) {
+          const int c = vv >> 2, o = (vv & 3) * 4;
+          RawV<T> gr, ur;
+          gr.a = make_uint4(gw[c][o], gw[c][o + 1], gw[c][o + 2], gw[c][o + 3]);
+          ur.a = make_uint4(uw[c][o], uw[c][o + 1], uw[c][o + 2], uw[c][o + 3]);
+          float v[8];
+          prologue<T, PRO_SILU_T, kFast>(gr, ur, v, yw[vv]);
+#pragma unroll
+          for (int k = 0; k < 8; ++k) gmax = fmaxf(gmax, fabsf(v[k]));
+        }
+        xchg[iter & 1][h][rl] = gmax;
+        asm volatile("bar.sync 1, 256;" ::: "memory");
+        gmax = fmaxf(gmax, xchg[iter & 1][h ^ 1][rl]);
+        // silu_and_mul_per_block_quant (quant_flat.cu, PRO_SILU_T / FMT_FP8_DIV, e4m3): s = max(gmax, FLT_MIN) / 448
+        const float sc = div_qmax<VXK_Q_E4M3>(fmaxf(gmax, 1.17549435e-38f));
+        const float rc = __frcp_rn(sc);
+        if (m < p.M) {
+          if (h == 0) p.fuse_s[static_cast<int64_t>(m) * p.fuse_ss0 + static_cast<int64_t>(nt) * p.fuse_ss1] = sc;
+          uint8_t* orow = static_cast<uint8_t*>(p.fuse_q) + static_cast<int64_t>(m) * p.fuse_inter + g0 + h * 64;
+#pragma unroll
+          for (int vv = 0; vv < 8; vv += 2) {
+            uint2 pk[2];
+#pragma unroll
+            for (int t2 = 0; t2 < 2; ++t2) {
+              float v[8];
+#pragma unroll
+              for (int k = 0; k < 4; ++k) {
+                const float2 f = Pair<T>::unpack(yw[vv + t2][k]);
+                v[2 * k] = f.x;
+                v[2 * k + 1] = f.y;
+              }
+              if (__builtin_expect(!(rc <= 3.402823466e+38f), 0)) {
+                float qv[8];
+#pragma unroll
+                for (int k = 0; k < 8; ++k) qv[k] = slow_div(v[k], sc);
+                pk[t2] = pack_q8<VXK_Q_E4M3>(qv);
+              } else {
+                pk[t2] = div_pack_fp8_signed<VXK_Q_E4M3>(v, yw[vv + t2], sc, rc);
+              }
+            }
+            *reinterpret_cast<uint4*>(orow + vv * 8) = make_uint4(pk[0].x, pk[0].y, pk[1].x, pk[1].y);
+          }
+        }
+        continue;
+      }
       // columns [col0, col0 + 32 kChunks) of the tile; TMEM column = same offset from buffer `as`
       const int col0 = NACC == 2 ? h * BLOCK_N : h * (BLOCK_N / 2);
 #pragma unroll 1

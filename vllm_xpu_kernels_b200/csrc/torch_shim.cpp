@@ -967,6 +967,56 @@ TORCH_LIBRARY_IMPL(_xpu_C, CUDA, xpu_ops) {
 }
 
 // Extensions without a reference counterpart (scale factors in the tensor core's layout).
+// SURVEY 8f #2, second half (no reference counterpart): gate_up projection with silu_and_mul and the 1 x 128 block FP8
+// quantisation fused into the GEMM's epilogue.  Equals
+//   t = fp8_gemm(A, B, mid_dtype, A_scale, B_scale, bias);  silu_and_mul_per_block_quant(out_q, t, out_s, 128)
+// bit for bit; shapes the fused kernel does not take run exactly those two ops.
+void fp8_gemm_silu_mul_quant(const Tensor& A, const Tensor& B, const Tensor& A_scale, const Tensor& B_scale,
+                             const std::optional<Tensor>& bias_, at::ScalarType mid_dtype, Tensor& out_q, Tensor& out_s) {
+  check_cuda(A, "A");
+  same_device(A, B, A_scale, B_scale, bias_);
+  TORCH_CHECK(out_q.device() == A.device() && out_s.device() == A.device(), "outputs must be on A's device");
+  const c10::cuda::CUDAGuard guard(A.device());
+  TORCH_CHECK(A.dim() == 2 && B.dim() == 2, "A must be [M, K], B the [K, 2 * inter] view of W[2 * inter, K]");
+  TORCH_CHECK(mid_dtype == at::kBFloat16 || mid_dtype == at::kHalf, "mid_dtype must be bfloat16 or float16");
+  const auto st = A.scalar_type();
+  TORCH_CHECK((st == at::kFloat8_e4m3fn || st == at::kFloat8_e5m2) && B.scalar_type() == st,
+              "A and B must be float8_e4m3fn or float8_e5m2, same type");
+  const int64_t M = A.size(0), K = A.size(1), N = B.size(1);
+  TORCH_CHECK(B.size(0) == K && N % 2 == 0, "B must be [K, 2 * inter]");
+  const int64_t inter = N / 2;
+  TORCH_CHECK(out_q.scalar_type() == at::kFloat8_e4m3fn && out_q.is_contiguous() && out_q.dim() == 2 &&
+                  out_q.size(0) == M && out_q.size(1) == inter, "out_q must be contiguous float8_e4m3fn [M, inter]");
+  TORCH_CHECK(inter % 128 == 0, "inter must be a multiple of the group size 128");
+  TORCH_CHECK(out_s.scalar_type() == at::kFloat && out_s.dim() == 2 && out_s.size(0) == M && out_s.size(1) == inter / 128,
+              "out_s must be float32 [M, inter / 128]");
+  TORCH_CHECK(A_scale.scalar_type() == at::kFloat && B_scale.scalar_type() == at::kFloat, "scales must be float32");
+  const int a_mode = A_scale.numel() == 1 ? 0 : 1, b_mode = B_scale.numel() == 1 ? 0 : 1;
+  if (a_mode == 1) TORCH_CHECK(A_scale.numel() == M && A_scale.is_contiguous(), "A_scale must be [M] / [M,1]");
+  if (b_mode == 1) TORCH_CHECK(B_scale.numel() == N && B_scale.is_contiguous(), "B_scale must be [N] / [N,1]");
+  if (M == 0 || inter == 0) return;
+  const void* bias = nullptr;
+  int bias_dtype = VXK_F32;
+  if (bias_.has_value() && bias_->defined() && bias_->numel() > 0) {
+    TORCH_CHECK(bias_->numel() == N && bias_->is_contiguous(), "only a contiguous [N] bias is supported");
+    bias = bias_->data_ptr();
+    bias_dtype = bias_dtype_of(*bias_);
+  }
+  int rc = VXK_ERR_UNSUPPORTED;
+  if (B.stride(0) == 1 && A.stride(1) == 1)
+    rc = vxk_fp8_gemm_silu_mul_quant(out_q.data_ptr(), out_s.data_ptr<float>(), A.data_ptr(), B.data_ptr(),
+                                     A_scale.data_ptr<float>(), B_scale.data_ptr<float>(), bias, M, inter, K, A.stride(0),
+                                     B.stride(1), a_mode, b_mode, out_s.stride(0), out_s.stride(1),
+                                     st == at::kFloat8_e4m3fn ? VXK_Q_E4M3 : VXK_Q_E5M2,
+                                     mid_dtype == at::kBFloat16 ? VXK_BF16 : VXK_F16, bias_dtype, cur_stream());
+  if (rc == VXK_ERR_UNSUPPORTED) {
+    Tensor t = fp8_gemm(A, B, mid_dtype, A_scale, B_scale, bias_);
+    silu_and_mul_per_block_quant(out_q, t, out_s, 128, std::nullopt, out_s.stride(0) == 1 && out_s.size(1) > 1, false);
+    return;
+  }
+  check_rc(rc, "fp8_gemm_silu_mul_quant");
+}
+
 TORCH_LIBRARY_FRAGMENT(_vxk, vxk_ops) {
   vxk_ops.def("mx_sf_packed_bytes(int rows, int K, bool fp4, bool is_weight) -> int", &mx_sf_packed_bytes);
   vxk_ops.def("mx_sf_pack(Tensor scale, bool fp4, bool is_weight) -> Tensor");
@@ -978,6 +1028,8 @@ TORCH_LIBRARY_FRAGMENT(_vxk, vxk_ops) {
               "float eps=1e-10) -> ()");
   vxk_ops.def("fp4_gemm_sf(Tensor A, Tensor B, Tensor A_scale, Tensor B_scale, ScalarType? out_dtype, Tensor? bias_, "
               "Tensor? A_sf_packed, Tensor? B_sf_packed) -> Tensor");
+  vxk_ops.def("fp8_gemm_silu_mul_quant(Tensor A, Tensor B, Tensor A_scale, Tensor B_scale, Tensor? bias_, "
+              "ScalarType mid_dtype, Tensor! out_q, Tensor! out_s) -> ()");
 }
 TORCH_LIBRARY_IMPL(_vxk, CUDA, vxk_ops) {
   vxk_ops.impl("mx_sf_pack", &mx_sf_pack);
@@ -985,6 +1037,7 @@ TORCH_LIBRARY_IMPL(_vxk, CUDA, vxk_ops) {
   vxk_ops.impl("rms_norm_mxfp4_quant_sf", &rms_norm_mxfp4_quant_sf);
   vxk_ops.impl("silu_and_mul_mxfp4_quant_sf", &silu_and_mul_mxfp4_quant_sf);
   vxk_ops.impl("fp4_gemm_sf", &fp4_gemm_sf);
+  vxk_ops.impl("fp8_gemm_silu_mul_quant", &fp8_gemm_silu_mul_quant);
 }
 
 // Schemas verbatim from /root/reference/csrc/torch_bindings.cpp:281-284,298-309 (library _C_cache_ops).

@@ -279,3 +279,19 @@ def silu_and_mul_mxfp4_quant_sf(input: torch.Tensor, group_size: int = 32, eps: 
 
 def fp4_gemm_sf(input, weight, scale_act, scale_wei, out_dtype, bias=None, act_sf_packed=None, wei_sf_packed=None):
     return torch.ops._vxk.fp4_gemm_sf(input, weight, scale_act, scale_wei, out_dtype, bias, act_sf_packed, wei_sf_packed)
+
+
+def fp8_gemm_silu_mul_quant(input, weight, scale_act, scale_wei, bias=None, mid_dtype=torch.bfloat16,
+                            is_scale_transposed=False):
+    """Gate_up projection + silu_and_mul + 1x128 block FP8 quantisation in one kernel (no reference
+    counterpart).  `weight` is the [K, 2 * inter] transposed view of W[2 * inter, K] (gate rows, then up rows).
+    Returns (codes [M, inter] float8_e4m3fn, scales [M, inter / 128] float32), bit-identical to
+    fp8_gemm(..., mid_dtype) followed by silu_and_mul_per_block_quant(group 128)."""
+    M, inter = input.shape[0], weight.shape[1] // 2
+    out_q = torch.empty(M, inter, dtype=torch.float8_e4m3fn, device=input.device)
+    if is_scale_transposed:
+        out_s = torch.empty(inter // 128, M, dtype=torch.float32, device=input.device).t()
+    else:
+        out_s = torch.empty(M, inter // 128, dtype=torch.float32, device=input.device)
+    torch.ops._vxk.fp8_gemm_silu_mul_quant(input, weight, scale_act, scale_wei, bias, mid_dtype, out_q, out_s)
+    return out_q, out_s
