@@ -19,7 +19,8 @@ are independent).
                `gemm`: the GEMM half of the metric -- FP8 / MXFP4 / fp8_w8a16 at the Llama-3-70B shapes,
                DeepSeek-V3 block-scaled FP8 (config 5) and a Llama-3-8B W8A8 M sweep (config 3), each row with
                its own tensor / HBM roofline fraction, and `moe_grouped`: the MoE grouped GEMM on the reference
-               test's Llama-4-scout shape, three recipes x decode / prefill token counts (bench_gemm.py)
+               test's Llama-4-scout shape, three recipes x decode / prefill token counts, and `fused_gate_up`: the
+               gate_up GEMM with silu_and_mul + block quantisation in its epilogue vs the two ops (bench_gemm.py)
   cpu_baseline the reference's torch CPU path (oracle/) on a bounded sample, host cores stated; `gemm`: the
                GEMM test formula (dequantise -> fp32 matmul) at M = 512
   e2e          the same step through torch.ops with pinned HOST buffers, double-buffered over three streams
@@ -373,6 +374,11 @@ def run_ours(args):
                 gemm["moe_grouped"] = bench_gemm.bench_moe_grouped(dev, pk, launches=max(100, K), warmup=max(10, args.warmup))
             except Exception as exc:
                 gemm["moe_grouped"] = {"error": f"{type(exc).__name__}: {exc}"[:300]}
+            try:    # fused gate_up projection: GEMM + silu_and_mul + block quant in one kernel
+                gemm["fused_gate_up"] = bench_gemm.bench_fused_gate_up(dev, pk, launches=max(100, K),
+                                                                        warmup=max(10, args.warmup))
+            except Exception as exc:
+                gemm["fused_gate_up"] = {"error": f"{type(exc).__name__}: {exc}"[:300]}
             if world > 1:
                 reassembled = bench_gemm.bench_reassembled(dev, rank, world)
         except Exception as exc:  # the GEMM section must never hide the quant numbers

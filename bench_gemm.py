@@ -256,6 +256,38 @@ def bench_moe_grouped(dev, pk, launches=100, warmup=10):
 
 
 # ---------------------------------------------------------------------------------------------
+# fused gate_up projection: GEMM -> silu_and_mul -> 1x128 block FP8 quant in one kernel
+# ---------------------------------------------------------------------------------------------
+def bench_fused_gate_up(dev, pk, launches=100, warmup=10, m_tokens=8192):
+    """torch.ops._vxk.fp8_gemm_silu_mul_quant against the two reference-surface ops it replaces
+    (torch.ops._xpu_C.fp8_gemm + torch.ops._C.silu_and_mul_per_block_quant), Llama-3-8B and -70B MLP shapes."""
+    from vllm_xpu_kernels_b200 import ops
+    rows = []
+    for name, K, inter in (("llama3-8b", 4096, 14336), ("llama3-70b", 8192, 28672)):
+        M = m_tokens
+        a = (torch.randn(M, K, device=dev) / 4).to(E4)
+        sa = torch.rand(M, 1, device=dev) * 0.01 + 0.001
+        ws = [(torch.randn(2 * inter, K, device=dev) / 4).to(E4) for _ in range(2)]
+        sw = torch.rand(2 * inter, 1, device=dev) * 0.01 + 0.001
+        two = [lambda w=w: ops.silu_and_mul_per_block_quant(
+            torch.ops._xpu_C.fp8_gemm(a, w.t(), torch.bfloat16, sa, sw, None), 128, E4) for w in ws]
+        fused = [lambda w=w: ops.fp8_gemm_silu_mul_quant(a, w.t(), sa, sw, None, torch.bfloat16) for w in ws]
+        q0, s0 = two[0]()
+        q1, s1 = fused[0]()
+        same = bool(torch.equal(q0.view(torch.uint8), q1.view(torch.uint8)) and torch.equal(s0, s1))
+        t2, tf = _time_graph(two, launches, warmup), _time_graph(fused, launches, warmup)
+        flops = 2.0 * M * 2 * inter * K
+        rows.append({"kind": "fp8_gemm_silu_mul_quant", "model": name, "M": M, "K": K, "inter": inter,
+                     "ms_two_ops": t2, "ms_fused": tf, "speedup": t2 / tf, "tflops_fused": flops / (tf * 1e-3) / 1e12,
+                     "frac_of_fp8_peak": flops / (tf * 1e-3) / 1e12 / (2.0 * pk["bf16"]),
+                     "bit_identical_to_two_ops": same,
+                     "hbm_bytes_saved": 2 * 2 * M * 2 * inter})      # the bf16 intermediate: written once, read once
+        del ws
+        torch.cuda.empty_cache()
+    return rows
+
+
+# ---------------------------------------------------------------------------------------------
 # e2e: one GEMM call through torch.ops._xpu_C with HOST activations and a HOST result
 # ---------------------------------------------------------------------------------------------
 def e2e_gemm(dev, rank, world, steps=5):
