@@ -224,6 +224,27 @@ def test_tc_matches_fallback(kind):
     torch.testing.assert_close(out.cpu().float(), c["ref"].float(), rtol=2e-2, atol=1e-2)
 
 
+@pytest.mark.parametrize("kind", ["bf16", "fp8"])
+def test_k_tail_and_overlong_row_counts(kind):
+    """K % 64 != 0 (TMA zero-fills the last K slice of both operands) and a rows_per_expert whose sum exceeds the
+    rows of A / D: the surplus rows are never written (no out-of-bounds store)."""
+    rows = torch.tensor([5, 3, 9], dtype=torch.int32)
+    m, n, k = 17, 136, 72
+    c = make_case(kind, torch.bfloat16, 3, m, n, k, True, seed=21, rows=rows)
+    check(run_op(c, n, k), c, rtol=2e-2)
+    # claim 40 rows for the last expert while A / D have 17: rows 8..16 belong to it, nothing past row 16 exists
+    dev = "cuda"
+    a, b = c["a"].to(dev), c["b"].to(dev)
+    sc = None if c["scales"] is None else c["scales"].to(dev)
+    guard = torch.full((m + 64, n), 7.0, dtype=torch.bfloat16, device=dev)        # D is the first m rows of this
+    d = guard[:m]
+    over = torch.tensor([5, 3, 40], dtype=torch.int32, device=dev)
+    _iface().cutlass_grouped_gemm_xe2(a, b, sc, c["bias"].to(dev), d, over, n, k, 3)
+    torch.cuda.synchronize()
+    assert bool((guard[m:] == 7.0).all()), "store past the last row of D"
+    torch.testing.assert_close(d.cpu().float(), c["ref"].float(), rtol=2e-2, atol=1e-2)
+
+
 def test_argument_errors():
     dev = "cuda"
     f = _iface().cutlass_grouped_gemm_xe2

@@ -620,7 +620,7 @@ gemm_grouped_kernel(const GroupedParams p, const __grid_constant__ CUtensorMap m
           const uint32_t got = __shfl_xor_sync(0xffffffffu, give, 1);
           const int tr = c * 32 + j + (lane & 1);            // token row within the tile
           const uint32_t packed = (lane & 1) ? (got | (hv[j + 1] << 16)) : (hv[j] | (got << 16));
-          if (tr < t.rows && n_ok) {
+          if (tr < t.rows && n_ok && t.row0 + tr < p.total_m) {      // (sum(rows_per_expert) may exceed the rows of A / D)
             uint16_t* d = dbase + static_cast<int64_t>(t.row0 + tr) * p.ldd;
             if (pair_ok) *reinterpret_cast<uint32_t*>(d) = packed;
             else d[0] = static_cast<uint16_t>(packed);
