@@ -63,7 +63,8 @@ struct GroupedParams {
   int num_kb, num_nt;
   int64_t ldd;
   int sf_vec;              // GW_MX4: scale rows are 16-byte aligned and K / 32 is a multiple of 16
-  int dbg;                 // VXK_GG_DEBUG (profiling only): 1 = converters skip the widening, 2 = skip the proxy fence
+  int dbg;                 // VXK_GG_DEBUG (profiling only, shared-memory operand paths; results are garbage): 1 = no widening
+                           // arithmetic, 2 = no proxy fence, 4 = converters only pass the barriers on
 };
 
 __device__ __forceinline__ void tma_load_3d(void* smem_dst, const CUtensorMap* m, uint64_t* bar, int c0, int c1,
