@@ -216,9 +216,14 @@ def bench_moe_grouped(dev, pk, launches=100, warmup=10):
     from vllm_xpu_kernels_b200.fused_moe_interface import cutlass_grouped_gemm_xe2
     E, N, K = 16, 5120, 8192
     rows_out = []
-    for kind in ("bf16", "fp8", "mxfp4"):
+    for kind in ("bf16", "fp8", "fp8_nk", "mxfp4"):
         if kind == "bf16":
             b, sc, wb = torch.randn(E, K, N, device=dev, dtype=torch.bfloat16) / 8, None, 2.0
+        elif kind == "fp8_nk":    # extension: the fp8 recipe with the weights stored [E, N, K] (transposed view handed over)
+            b = torch.empty(E, N, K, device=dev, dtype=E4)
+            for e in range(E):
+                b[e] = (torch.randn(N, K, device=dev) / 4).to(E4)
+            b, sc, wb = b.transpose(1, 2), torch.rand(E, device=dev) + 0.5, 1.0
         elif kind == "fp8":
             b = torch.empty(E, K, N, device=dev, dtype=E4)
             for e in range(E):

@@ -35,6 +35,11 @@ def make_weights(kind, E, N, K):
         for e in range(E):
             b[e] = (torch.randn(K, N, device=DEV) / 4).to(E4)
         return b, torch.rand(E, device=DEV) + 0.5, 1.0
+    if kind == "fp8_nk":      # extension: fp8 weights stored [E, N, K], handed over as the transposed view
+        b = torch.empty(E, N, K, device=DEV, dtype=E4)
+        for e in range(E):
+            b[e] = (torch.randn(N, K, device=DEV) / 4).to(E4)
+        return b.transpose(1, 2), torch.rand(E, device=DEV) + 0.5, 1.0
     b = torch.randint(0, 256, (E, N, K // 2), dtype=torch.uint8, device=DEV).view(torch.float4_e2m1fn_x2)
     sc = torch.randint(118, 130, (E, N, K // 32), dtype=torch.uint8, device=DEV)
     return b, sc, 0.5 + 1.0 / 32

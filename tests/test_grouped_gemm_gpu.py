@@ -67,10 +67,13 @@ def make_case(kind, dtype, E, m, n, k, has_bias, seed=7, qd=E4, rows=None, weigh
     return dict(a=a, b=b, scales=scales, bias=bias, rows=rows, ref=ref, kind=kind)
 
 
-def run_op(c, n, k):
+def run_op(c, n, k, fp8_nk=False):
     dev = "cuda"
     a = c["a"].to(dev)
     b = c["b"].to(dev)
+    if fp8_nk:      # extension: the same [E, K, N] weight handed over as the transposed view of a contiguous [E, N, K] copy
+        b = b.view(torch.uint8).transpose(1, 2).contiguous().transpose(1, 2).view(c["b"].dtype)
+        assert not b.is_contiguous() and b.shape == c["b"].shape
     if c["kind"] == "mxfp4":
         b = b.view(torch.float4_e2m1fn_x2)
     scales = None if c["scales"] is None else c["scales"].to(dev)
@@ -222,6 +225,26 @@ def test_tc_matches_fallback(kind):
     torch.cuda.synchronize()
     torch.testing.assert_close(out.cpu().float(), out_tc.float(), rtol=1e-2, atol=1e-2)
     torch.testing.assert_close(out.cpu().float(), c["ref"].float(), rtol=2e-2, atol=1e-2)
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("qd", [E4, E5])
+@pytest.mark.parametrize("rows,n,k", [
+    ([1, 0, 2, 1], 128, 128), ([33, 0, 31, 64, 1], 384, 256), ([0, 700, 0], 136, 208), ([129, 127, 256, 255, 257], 264, 320),
+    ([5, 4000, 91], 1024, 512), ([300] * 12, 512, 128), ([40] * 16, 5120, 8192),
+])
+def test_fp8_weights_stored_nk(dtype, qd, rows, n, k):
+    """Extension (VXK_MOE_FP8_*_NK): the fp8 recipe with the weights stored [E, N, K] and passed as the transposed view --
+    same op, same results as the [E, K, N] layout (bit for bit: same widening, same accumulation order), widened tile in
+    tensor memory; every token-tile width, N / K tails."""
+    rows_t = torch.tensor(rows, dtype=torch.int32)
+    m = int(rows_t.sum()) + 1
+    c = make_case("fp8", dtype, len(rows), m, n, k, True, seed=13, qd=qd, rows=rows_t)
+    out_kn = run_op(c, n, k)
+    out_nk = run_op(c, n, k, fp8_nk=True)
+    check(out_nk, c, rtol=1e-2)
+    used = int(rows_t.sum())
+    torch.testing.assert_close(out_nk[:used].float(), out_kn[:used].float(), rtol=1e-2, atol=1e-2)
 
 
 @pytest.mark.parametrize("kind", ["bf16", "fp8"])

@@ -160,7 +160,42 @@ extern "C" int vxk_moe_grouped_gemm(void* D, const void* A, const void* B, const
                                     vxk_stream_t stream) {
   VXK_REQUIRE(total_m >= 0 && N >= 0 && K >= 0 && num_experts >= 0, "negative shape");
   VXK_REQUIRE(act_dtype == VXK_BF16 || act_dtype == VXK_F16, "activations must be bf16 or f16");
-  VXK_REQUIRE(weight_kind >= VXK_MOE_W16 && weight_kind <= VXK_MOE_MXFP4, "unknown weight_kind");
+  VXK_REQUIRE(weight_kind >= VXK_MOE_W16 && weight_kind <= VXK_MOE_FP8_E5M2_NK, "unknown weight_kind");
+  if (weight_kind == VXK_MOE_FP8_E4M3_NK || weight_kind == VXK_MOE_FP8_E5M2_NK) {
+    // fp8 weights [E, N, K]: the TMEM-operand kernel (GW_FP8T)
+    VXK_REQUIRE(N % 8 == 0, "N must be divisible by 8");
+    VXK_REQUIRE(scales && rows_per_expert, "fp8 grouped gemm must have scales and rows_per_expert");
+    if (total_m == 0 || N == 0 || num_experts == 0) return VXK_OK;
+    VXK_REQUIRE(K > 0, "K must be positive");
+    VXK_REQUIRE(!force_fallback && num_experts <= kGgMaxExperts && aligned16(A) && aligned16(B) && K % 16 == 0 &&
+                    (reinterpret_cast<uintptr_t>(D) & 3) == 0 && total_m < (1LL << 30) && N < (1LL << 30) && K < (1LL << 30),
+                "fp8 [E, N, K] grouped gemm needs K %% 16 == 0, 16-byte aligned operands and at most 512 experts");
+    const int64_t avg = (total_m + num_experts - 1) / num_experts;
+    const int mt = avg <= 32 ? 32 : (avg <= 64 ? 64 : (avg <= 128 ? 128 : 256));
+    const int block_k = mt <= 128 ? 128 : kGgBlockK;
+    GroupedParams gp{};
+    gp.D = D; gp.bias = bias; gp.rows = rows_per_expert; gp.w_scale = static_cast<const float*>(scales);
+    gp.total_m = static_cast<int>(total_m); gp.N = static_cast<int>(N); gp.K = static_cast<int>(K);
+    gp.E = static_cast<int>(num_experts);
+    gp.num_kb = static_cast<int>((K + block_k - 1) / block_k);
+    gp.num_nt = static_cast<int>((N + 127) / 128);
+    gp.ldd = N;
+    const int64_t max_tiles = ((total_m + mt - 1) / mt + num_experts) * gp.num_nt;
+    if (max_tiles >= (1LL << 31)) return fail(VXK_ERR_UNSUPPORTED, "grouped GEMM: too many tiles");
+    CUtensorMap mw, ma;
+    int rc;
+    if ((rc = make_map_2d_u8(&ma, A, static_cast<uint64_t>(K) * 2, total_m, static_cast<uint64_t>(K) * 2, 128, mt, true)))
+      return rc;
+    if ((rc = make_map_3d_u8(&mw, B, K, N, num_experts, K, N * K, block_k, 128, block_k))) return rc;
+    const bool bf = act_dtype == VXK_BF16, e5 = weight_kind == VXK_MOE_FP8_E5M2_NK;
+    cudaStream_t s2 = stream;
+    switch (mt) {
+      case 32: return launch_gg_types<32>(gp, mw, ma, max_tiles, GW_FP8T, bf, e5, s2);
+      case 64: return launch_gg_types<64>(gp, mw, ma, max_tiles, GW_FP8T, bf, e5, s2);
+      case 128: return launch_gg_types<128>(gp, mw, ma, max_tiles, GW_FP8T, bf, e5, s2);
+      default: return launch_gg_types<256>(gp, mw, ma, max_tiles, GW_FP8T, bf, e5, s2);
+    }
+  }
   VXK_REQUIRE(N % 8 == 0, "N must be divisible by 8");
   const int wkind = weight_kind == VXK_MOE_W16 ? GW_16 : (weight_kind == VXK_MOE_MXFP4 ? GW_MX4 : GW_FP8);
   if (wkind != GW_16) VXK_REQUIRE(scales, "fp8 / mxfp4 grouped gemm must have scales");

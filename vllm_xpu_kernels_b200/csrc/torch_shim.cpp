@@ -771,7 +771,10 @@ Tensor cutlass_grouped_gemm_interface(Tensor ptr_A, Tensor ptr_B, const std::opt
   TORCH_CHECK(ptr_A.dim() == 2, "ptr_A must be 2D [Total_M, K]");
   TORCH_CHECK(ptr_B.dim() == 3, "ptr_B must be 3D [num_experts, K, N]");
   TORCH_CHECK(ptr_D.dim() == 2, "ptr_D must be 2D [Total_M, N]");
-  TORCH_CHECK(ptr_A.is_contiguous() && ptr_B.is_contiguous() && ptr_D.is_contiguous(),
+  // extension: fp8 weights may be the transposed VIEW of a contiguous [E, N, K] tensor (the widened tile then goes to
+  // tensor memory, include/vxk_b200.h VXK_MOE_FP8_*_NK); everything else must be contiguous like the reference
+  const bool fp8_nk = is_fp8 && !ptr_B.is_contiguous() && ptr_B.dim() == 3 && ptr_B.transpose(1, 2).is_contiguous();
+  TORCH_CHECK(ptr_A.is_contiguous() && (ptr_B.is_contiguous() || fp8_nk) && ptr_D.is_contiguous(),
               "ptr_A, ptr_B and ptr_D must be contiguous");
   const void* bias = nullptr;
   if (ptr_bias.has_value() && ptr_bias->defined()) {
@@ -804,7 +807,8 @@ Tensor cutlass_grouped_gemm_interface(Tensor ptr_A, Tensor ptr_B, const std::opt
     TORCH_CHECK(ptr_scales->is_contiguous() && ptr_scales->dim() == 1 && ptr_scales->size(0) == num_experts,
                 "ptr_scales of fp8 must be 1D [num_experts]");
     TORCH_CHECK(ptr_scales->scalar_type() == at::kFloat, "ptr_scales must be float");
-    kind = b_st == at::kFloat8_e4m3fn ? VXK_MOE_FP8_E4M3 : VXK_MOE_FP8_E5M2;
+    kind = b_st == at::kFloat8_e4m3fn ? (fp8_nk ? VXK_MOE_FP8_E4M3_NK : VXK_MOE_FP8_E4M3)
+                                      : (fp8_nk ? VXK_MOE_FP8_E5M2_NK : VXK_MOE_FP8_E5M2);
     scales = ptr_scales->data_ptr();
   } else {
     TORCH_CHECK(b_st == a_st, "w16a16 grouped gemm: ptr_B must have the activation dtype, got ", b_st);
