@@ -550,3 +550,30 @@ def test_weight_written_right_before_small_m_gemm(ops, lib):
             assert torch.equal(o, ref[i % 2]), i
     finally:
         lib.vxk_set_early_weight_loads(prev)
+
+
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+@pytest.mark.parametrize("m", [1, 3, 17, 33, 64])
+@pytest.mark.parametrize("nk,gk,gn", [((1536, 7168), 128, 128), ((7168, 2048), 128, 128), ((576, 1024), 128, 64),
+                                      ((1000, 1536), 256, 8), ((384, 1024), 512, 128), ((24576, 1536), 128, 128)])
+@pytest.mark.parametrize("bias,col_major_sa", [(False, False), (True, True)])
+def test_block_fp8_small_m_kernel(ops, lib, dtype, m, nk, gk, gn, bias, col_major_sa):
+    """fp32 block scales at M <= 64 (BASELINE config 5 in the decode regime): gemm_skinny_kernel<MT, BLK> -- swap-AB,
+    cluster split-K, per-slice promotion.  DeepSeek shapes, N tails (576, 1000), group_k 128 / 256 / 512, group_n
+    8 ... 128, row- and column-major activation scales, bias; float64 oracle, atol = rtol = 1e-2; deterministic."""
+    n, k = nk
+    g = torch.Generator().manual_seed(m * 31 + n)
+    xq = (torch.randn(m, k, generator=g) / 4).to(E4)
+    wq = (torch.randn(n, k, generator=g) / 4).to(E4)
+    xs = torch.rand(m, k // gk, generator=g) * 0.02 + 0.005
+    ws = torch.rand(k // gk, n // gn, generator=g) * 0.02 + 0.005
+    b = torch.randn(n, generator=g).to(dtype) if bias else None
+    xs_d = xs.to(DEV)
+    if col_major_sa:
+        xs_d = xs.t().contiguous().to(DEV).t()          # logical [m, k/gk], column-major storage
+    tc0, fb0 = gemm_stats(lib)
+    out = ops.fp8_gemm(xq.to(DEV), wq.to(DEV).t(), dtype, xs_d, ws.to(DEV), b.to(DEV) if bias else torch.Tensor())
+    assert gemm_stats(lib) == (tc0 + 1, fb0), "tensor-core path"
+    close(out, og.fp8_gemm_ref(xq, wq.t(), dtype, xs, ws, b))
+    out2 = ops.fp8_gemm(xq.to(DEV), wq.to(DEV).t(), dtype, xs_d, ws.to(DEV), b.to(DEV) if bias else torch.Tensor())
+    assert torch.equal(out, out2)

@@ -38,6 +38,11 @@ struct SkinnyParams {
   int num_k_blocks;       // 128-byte K slices in total
   int kb_per_split;       // slices per cluster rank (a multiple of the slices per stage)
   int splits;             // cluster size along y
+  // BLK (fp32 block scales, DeepSeek-V3 1 x 128 / 128 x 128; fp8_gemm_w8a8.h:28-41,86-134):
+  const float* blk_sa;    // sA[m, k / group_k] at blk_sa[m * sa0 + kg * sa1]
+  const float* blk_sb;    // sW[k / group_k, n / group_n] at blk_sb[kg * sb0 + ng * sb1]
+  int64_t sa0, sa1, sb0, sb1;
+  int group_k, group_n;   // group_k % 128 == 0
 };
 
 // slices per ring stage: two for MT <= 128, one for the 256-token tile (its A slice alone is 32 KB)
@@ -48,7 +53,7 @@ struct SkinnySmem {
   static constexpr int kASlice = MT * kBlockKBytes;
   static constexpr int kStageBytes = kKS * (kWSlice + kASlice);
   static constexpr int kStages = (196 * 1024) / kStageBytes > 8 ? 8 : (196 * 1024) / kStageBytes;
-  static constexpr int kBarrierBytes = (2 * kStages + 1) * 8 + 16;
+  static constexpr int kBarrierBytes = (2 * kStages + 5) * 8 + 16;
   static constexpr int kTotalBytes = kStages * kStageBytes + kBarrierBytes + 1024;
   static_assert(kStageBytes % 1024 == 0, "SWIZZLE_128B tiles need 1024-byte alignment");
   static_assert(kStages * kStageBytes >= MT * 128 * 4, "the partial tile is parked in the ring");
@@ -65,10 +70,17 @@ __device__ __forceinline__ uint32_t mapa_u32(uint32_t cta_addr, uint32_t rank) {
   return r;
 }
 
-template <int MT>
+// BLK: fp32 block scales (BASELINE config 5 in the decode regime).  Non-power-of-two scales have no tcgen05 mode, so
+// every 128-deep K slice is a fresh accumulation into one of two TMEM buffers; the four epilogue warps pull each
+// partial product into registers (thread = output column, MT token columns), fold it into fp32 accumulators with
+// sA[m, kb] * sW[kb, n / group_n] (lane j fetches token j's scale one slice ahead, the warp shuffles it out) and hand the
+// buffer back, while the MMA warp is on the next slice.  The register accumulators are then parked and reduced over
+// the cluster exactly like the plain kernel's TMEM tile.
+template <int MT, bool BLK = false>
 __global__ void __launch_bounds__(kSkinnyThreads, 1)
 gemm_skinny_kernel(const SkinnyParams p, const __grid_constant__ CUtensorMap map_w,
                    const __grid_constant__ CUtensorMap map_a) {
+  static_assert(!BLK || MT <= 128, "block-scaled small-M kernel: two MT-column TMEM buffers, MT register accumulators");
   using L = SkinnySmem<MT>;
   constexpr int S = L::kStages;
   constexpr int kSkinnyKS = L::kKS;
@@ -78,7 +90,9 @@ gemm_skinny_kernel(const SkinnyParams p, const __grid_constant__ CUtensorMap map
   uint64_t* full_bar = bars;
   uint64_t* empty_bar = bars + S;
   uint64_t* acc_bar = bars + 2 * S;
-  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(bars + 2 * S + 1);
+  uint64_t* pfull = bars + 2 * S + 1;       // BLK: partial product of a K slice landed in TMEM buffer i
+  uint64_t* pempty = bars + 2 * S + 3;      // BLK: buffer i drained into registers
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(bars + 2 * S + 5);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int n0 = blockIdx.x * 128;
@@ -97,9 +111,13 @@ gemm_skinny_kernel(const SkinnyParams p, const __grid_constant__ CUtensorMap map
       mbar_init(&empty_bar[i], 1);
     }
     mbar_init(acc_bar, 1);
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&pfull[i], 1);
+      mbar_init(&pempty[i], 128);
+    }
     fence_barrier_init();
   }
-  constexpr uint32_t kCols = MT < 32 ? 32 : MT;      // TMEM allocation: power of two >= 32
+  constexpr uint32_t kCols = BLK ? (2 * MT < 32 ? 32 : 2 * MT) : (MT < 32 ? 32 : MT);   // TMEM allocation: power of two >= 32
   if (warp == 2) tmem_alloc<kCols>(tmem_ptr_smem);
   tc_fence_before();
   __syncthreads();
@@ -162,13 +180,24 @@ gemm_skinny_kernel(const SkinnyParams p, const __grid_constant__ CUtensorMap map
         for (int s = 0; s < ns; ++s) {
           const uint64_t dw = make_kmajor_sw128_desc(st + s * L::kWSlice);
           const uint64_t da = make_kmajor_sw128_desc(st + kSkinnyKS * L::kWSlice + s * L::kASlice);
+          if constexpr (BLK) {
+            const int sl = it * kSkinnyKS + s, buf = sl & 1;         // slice counter of this CTA
+            mbar_wait(&pempty[buf], ((sl >> 1) & 1) ^ 1);
+            tc_fence_after();
 #pragma unroll
-          for (int k = 0; k < kBlockKBytes / kUmmaKBytes; ++k)
-            umma_f8f6f4(tmem_base, dw + static_cast<uint64_t>(k * (kUmmaKBytes >> 4)),
-                        da + static_cast<uint64_t>(k * (kUmmaKBytes >> 4)), idesc, (it > 0 || s > 0 || k > 0) ? 1u : 0u);
+            for (int k = 0; k < kBlockKBytes / kUmmaKBytes; ++k)
+              umma_f8f6f4(tmem_base + buf * MT, dw + static_cast<uint64_t>(k * (kUmmaKBytes >> 4)),
+                          da + static_cast<uint64_t>(k * (kUmmaKBytes >> 4)), idesc, k > 0 ? 1u : 0u);
+            umma_commit(&pfull[buf]);
+          } else {
+#pragma unroll
+            for (int k = 0; k < kBlockKBytes / kUmmaKBytes; ++k)
+              umma_f8f6f4(tmem_base, dw + static_cast<uint64_t>(k * (kUmmaKBytes >> 4)),
+                          da + static_cast<uint64_t>(k * (kUmmaKBytes >> 4)), idesc, (it > 0 || s > 0 || k > 0) ? 1u : 0u);
+          }
         }
         umma_commit(&empty_bar[stage]);
-        if (it == num_stages_k - 1) umma_commit(acc_bar);
+        if (!BLK && it == num_stages_k - 1) umma_commit(acc_bar);
       }
       __syncwarp();
       if (++stage == S) { stage = 0; phase ^= 1; }
@@ -180,9 +209,58 @@ gemm_skinny_kernel(const SkinnyParams p, const __grid_constant__ CUtensorMap map
   // the fp32 tile is parked in the drained ring as [token][128 columns]
   asm volatile("griddepcontrol.wait;" ::: "memory");   // scales / bias / D may depend on the previous kernel
   const bool bf = p.out_dtype == VXK_BF16;
-  const float sa_all = (p.a_scale_mode == 1) ? 1.0f : __ldg(p.a_scale);
+  const float sa_all = (BLK || p.a_scale_mode == 1) ? 1.0f : __ldg(p.a_scale);
   float* park = reinterpret_cast<float*>(smem);
-  if (warp >= 4) {
+  if (BLK && warp >= 4) {
+    if constexpr (BLK) {
+      const int q = warp & 3;
+      const int row = q * 32 + lane;
+      const int ng = min(n0 + row, p.N - 1) / p.group_n;
+      float acc[MT];
+#pragma unroll
+      for (int j = 0; j < MT; ++j) acc[j] = 0.0f;
+      const int nsl = kb1 - kb0;
+      auto load_scales = [&](int sl, float& sw, float (&sa)[MT / 32]) {
+        const int kg = ((kb0 + sl) * kBlockKBytes) / p.group_k;
+        sw = __ldg(p.blk_sb + static_cast<int64_t>(kg) * p.sb0 + static_cast<int64_t>(ng) * p.sb1);
+#pragma unroll
+        for (int c = 0; c < MT / 32; ++c) {
+          const int m = c * 32 + lane;
+          sa[c] = m < p.M ? __ldg(p.blk_sa + static_cast<int64_t>(m) * p.sa0 + static_cast<int64_t>(kg) * p.sa1) : 0.0f;
+        }
+      };
+      float sw_n, sa_n[MT / 32];
+      load_scales(0, sw_n, sa_n);
+      for (int sl = 0; sl < nsl; ++sl) {
+        const int buf = sl & 1;
+        const float sw = sw_n;
+        float sa[MT / 32];
+#pragma unroll
+        for (int c = 0; c < MT / 32; ++c) sa[c] = sa_n[c] * sw;          // sA[m, kb] * sW[kb, n / group_n], per lane's token
+        if (sl + 1 < nsl) load_scales(sl + 1, sw_n, sa_n);
+        mbar_wait(&pfull[buf], (sl >> 1) & 1);
+        tc_fence_after();
+#pragma unroll
+        for (int c = 0; c < MT / 32; ++c) {
+          if (c * 32 < p.M) {
+            uint32_t r[32];
+            tmem_ld_32x32b_x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + buf * MT + c * 32, r);
+            tmem_ld_wait();
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+              acc[c * 32 + j] = fmaf(__uint_as_float(r[j]), __shfl_sync(0xffffffffu, sa[c], j), acc[c * 32 + j]);
+          }
+        }
+        tc_fence_before();
+        mbar_arrive(&pempty[buf]);
+      }
+      asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+      // every slice of this CTA has been consumed: the ring is drained, park the register tile in it
+#pragma unroll
+      for (int j = 0; j < MT; ++j)
+        if (j < p.M) park[j * 128 + row] = acc[j];
+    }
+  } else if (warp >= 4) {
     const int q = warp & 3;
     const int row = q * 32 + lane;
     mbar_wait(acc_bar, 0);
@@ -213,7 +291,7 @@ gemm_skinny_kernel(const SkinnyParams p, const __grid_constant__ CUtensorMap map
 #pragma unroll
     for (int t = 0; t < 4; ++t) {
       const bool ok = nc + t < p.N;
-      swv[t] = (p.b_scale_mode == 1) ? (ok ? __ldg(p.b_scale + nc + t) : 0.0f) : __ldg(p.b_scale);
+      swv[t] = BLK ? 1.0f : ((p.b_scale_mode == 1) ? (ok ? __ldg(p.b_scale + nc + t) : 0.0f) : __ldg(p.b_scale));
       bv[t] = 0.0f;
       if (p.bias && ok)
         bv[t] = (p.bias_dtype == VXK_F32)   ? __ldg(static_cast<const float*>(p.bias) + nc + t)
@@ -237,7 +315,7 @@ gemm_skinny_kernel(const SkinnyParams p, const __grid_constant__ CUtensorMap map
         if (s < p.splits) {
           acc[0] += part[s].x; acc[1] += part[s].y; acc[2] += part[s].z; acc[3] += part[s].w;
         }
-      const float sa = (p.a_scale_mode == 1) ? __ldg(p.a_scale + m) : sa_all;
+      const float sa = BLK ? 1.0f : ((p.a_scale_mode == 1) ? __ldg(p.a_scale + m) : sa_all);
       uint16_t h[4];
 #pragma unroll
       for (int t = 0; t < 4; ++t) {

@@ -379,10 +379,10 @@ static int run_pair_block_scaled(Tc2Params tp, const void* A, int64_t lda_bytes,
 }
 
 // Small-M FP8 GEMM (M <= 128): operands swapped, K split over a cluster.  See gemm_skinny.cuh.
-template <int MT>
+template <int MT, bool BLK = false>
 static int launch_skinny(SkinnyParams sp, const CUtensorMap& mw, const CUtensorMap& ma, int n_tiles, cudaStream_t st) {
   using L = SkinnySmem<MT>;
-  auto kernel = gemm_skinny_kernel<MT>;
+  auto kernel = gemm_skinny_kernel<MT, BLK>;
   static PerDeviceOnce once;
   const cudaError_t attr_err = once.get([&](PerDeviceOnce::Entry& x) {
     x.err = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotalBytes);
@@ -411,9 +411,15 @@ static int launch_skinny(SkinnyParams sp, const CUtensorMap& mw, const CUtensorM
   return check_launch("gemm_skinny");
 }
 
+struct SkinnyBlkScales { const float* sa; const float* sb; int64_t sa0, sa1, sb0, sb1; int group_k, group_n; };
+
 static int run_skinny_f8(const TcParams& tp, const void* A, const void* W, int64_t M, int64_t N, int64_t K,
-                         int64_t lda, int64_t ldw, cudaStream_t st) {
+                         int64_t lda, int64_t ldw, cudaStream_t st, const SkinnyBlkScales* blk = nullptr) {
   SkinnyParams sp{};
+  if (blk) {
+    sp.blk_sa = blk->sa; sp.blk_sb = blk->sb; sp.sa0 = blk->sa0; sp.sa1 = blk->sa1; sp.sb0 = blk->sb0; sp.sb1 = blk->sb1;
+    sp.group_k = blk->group_k; sp.group_n = blk->group_n;
+  }
   sp.D = tp.D; sp.a_scale = tp.a_scale; sp.b_scale = tp.b_scale; sp.bias = tp.bias;
   sp.M = (int)M; sp.N = (int)N; sp.ldd = tp.ldd;
   sp.a_scale_mode = tp.a_scale_mode; sp.b_scale_mode = tp.b_scale_mode; sp.out_dtype = tp.out_dtype;
@@ -441,6 +447,13 @@ static int run_skinny_f8(const TcParams& tp, const void* A, const void* W, int64
   int rc;
   if ((rc = make_map_2d_u8(&mw, W, K, N, ldw, kBlockKBytes, 128, true))) return rc;
   if ((rc = make_map_2d_u8(&ma, A, K, M, lda, kBlockKBytes, mt, true))) return rc;
+  if (blk) {
+    switch (mt) {
+      case 32: return launch_skinny<32, true>(sp, mw, ma, n_tiles, st);
+      case 64: return launch_skinny<64, true>(sp, mw, ma, n_tiles, st);
+      default: return launch_skinny<128, true>(sp, mw, ma, n_tiles, st);
+    }
+  }
   switch (mt) {
     case 32: return launch_skinny<32>(sp, mw, ma, n_tiles, st);
     case 64: return launch_skinny<64>(sp, mw, ma, n_tiles, st);
@@ -667,6 +680,14 @@ extern "C" int vxk_fp8_gemm(void* D, const void* A, const void* B, const void* a
     if ((rc = make_map_2d_u8(&ma, A, K, M, lda, kBlockKBytes, kBlockM, true))) return rc;
     if ((rc = make_map_2d_u8(&mb, B, K, N, b_stride_n, kBlockKBytes, bn, true))) return rc;
     return launch_tc_bn<KIND_F8>(bn, tp, ma, mb, msa, msb, st);
+  }
+  // fp32 block scales at M <= 128 (config 5 in the decode regime): the small-M kernel with per-slice promotion
+  static const int skinny_blk = env_int("VXK_SKINNY_BLK", 1);
+  if (operands_ok && a_scale_mode == 2 && scale_dtype == VXK_S_F32 && group_k % 128 == 0 && K % group_k == 0 &&
+      group_n > 0 && M <= 64 && K >= 512 && peers.n == 0 && skinny_blk) {   // (65..128 tokens measured slower than the general kernel)
+    SkinnyBlkScales bs{static_cast<const float*>(a_scale), static_cast<const float*>(b_scale), sa0, sa1, sb0, sb1,
+                       static_cast<int>(group_k), static_cast<int>(group_n)};
+    return run_skinny_f8(tp, A, B, M, N, K, lda, b_stride_n, st, &bs);
   }
   if (operands_ok && a_scale_mode == 2 && scale_dtype == VXK_S_F32 && group_k % 128 == 0 && group_n % 32 == 0 &&
       K % group_k == 0) {
