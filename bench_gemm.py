@@ -37,6 +37,7 @@ KERNEL_OF = {   # dominant kernel of each kind at large M (vllm_xpu_kernels_b200
     "fp8_w8a16": "gemm_w8a16_kernel (tcgen05 kind::f16, FP8 widened in the main loop)",
     "block_fp8": "gemm_tc2_blk_kernel<192> (tcgen05 kind::f8f6f4 per K slice + fp32 promotion)",
     "mxfp4_sf": "gemm_tc2_kernel<KIND_MXF4,192,*> via torch.ops._vxk.fp4_gemm_sf (pre-packed scale factors, no sf_pack launches)",
+    "block_fp8 (M <= 64)": "gemm_skinny_kernel<MT, BLK> (swap-AB, split-K over a cluster, per-slice promotion in registers)",
     "mxfp4 (M <= 128)": "gemm_skinny_mx4_kernel (swap-AB, split-K over a cluster, natural-layout scales re-tiled in the kernel)",
     "moe_bf16 / moe_fp8 / moe_mxfp4": "gemm_grouped_kernel<MT,kind,*> (tcgen05 kind::f16, swap-AB, device-side tile list; "
                                       "fp8 widened into shared memory, mxfp4 into tensor memory)",
@@ -188,15 +189,21 @@ def bench_gemms(dev, rank, world, pk, launches=100, warmup=10, m_tokens=8192, se
         for (K, N) in LLAMA70B_KN:
             for m in (1, 64):
                 rows4.append(time_case("mxfp4", m, K, N, dev, rank, world, pk, launches, warmup))
+    rows5d = []
     if "dsv3" in sets:
         for (K, N) in DSV3_KN:
             rows5.append(time_case("block_fp8", M, K, N, dev, rank, world, pk, launches, warmup))
+        # config 5 in the decode regime (block-scaled variant of the swap-AB split-K kernel)
+        for (K, N) in DSV3_KN:
+            for m in (1, 64):
+                rows5d.append(time_case("block_fp8", m, K, N, dev, rank, world, pk, launches, warmup))
     if "8b" in sets:
         for (K, N) in LLAMA8B_KN:
             for m in (1, 256, M):
                 rows3.append(time_case("fp8_w8a8", m, K, N, dev, rank, world, pk, launches, warmup))
     tc, fb = stats()
     return {"llama70b_m8192": rows70, "llama70b_mxfp4_decode": rows4, "dsv3_block_fp8_m8192": rows5,
+            "dsv3_block_fp8_decode": rows5d,
             "llama8b_w8a8_m_sweep": rows3,
             "kernels": KERNEL_OF, "tensor_core_calls": tc, "fallback_calls": fb,
             "peak_source": pk["src"] + " bf16 cuBLAS x2 (fp8) / x4 (fp4) / x1 (fp8_w8a16: bf16 MMA); "
