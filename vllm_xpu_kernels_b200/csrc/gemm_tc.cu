@@ -229,11 +229,12 @@ static int launch_tc2(Tc2Params tp, const CUtensorMap& ma, const CUtensorMap& mb
 template <int BLOCK_N, bool PIPE>
 static int launch_tc2_blk(Tc2BlkParams tp, const CUtensorMap& ma, const CUtensorMap& mb, cudaStream_t st) {
   using L = Tc2Smem<KIND_F8, BLOCK_N, 1>;
+  constexpr int kSmemBytes = L::kTotalBytes + 64;      // (room for a third pair of slice barriers)
   auto kernel = gemm_tc2_blk_kernel<BLOCK_N, PIPE>;
   static PerDeviceOnce once;
   const PerDeviceOnce::Entry cfg_once = once.get([&](PerDeviceOnce::Entry& x) {
-    x.err = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotalBytes);
-    if (x.err == cudaSuccess) x.aux = max_cluster_pairs(reinterpret_cast<const void*>(kernel), L::kTotalBytes);
+    x.err = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes);
+    if (x.err == cudaSuccess) x.aux = max_cluster_pairs(reinterpret_cast<const void*>(kernel), kSmemBytes);
   });
   const cudaError_t attr_err = cfg_once.err;
   const int pairs = cfg_once.aux;
@@ -245,7 +246,7 @@ static int launch_tc2_blk(Tc2BlkParams tp, const CUtensorMap& ma, const CUtensor
   tp.group_m = group_m < 1 ? 1 : group_m;
   const int tiles = tp.num_m_pairs * tp.num_n_blocks;
   const int grid = 2 * (tiles < pairs ? tiles : pairs);
-  kernel<<<grid, kTc2Threads, L::kTotalBytes, st>>>(tp, ma, mb);
+  kernel<<<grid, kTc2Threads, kSmemBytes, st>>>(tp, ma, mb);
   g_gemm_tc_calls.fetch_add(1, std::memory_order_relaxed);
   return check_launch("gemm_tc2_blk");
 }
@@ -693,7 +694,9 @@ extern "C" int vxk_fp8_gemm(void* D, const void* A, const void* B, const void* a
       K % group_k == 0) {
     // fp32 block scales: two-level accumulation (tensor core per K slice, CUDA cores across slices)
     static const int blk_pipe = env_int("VXK_BLK_PIPE", 1);
-    constexpr int BN = 192;
+    // tile width: 192 (two TMEM buffers) or 160 (three); the fused all-gather pushes 384-byte row segments: 192 only
+    static const int env_blk_bn = env_int("VXK_BLK_BN", 192);
+    const int BN = (env_blk_bn == 160 && peers.n == 0) ? 160 : 192;
     Tc2BlkParams t2{};
     t2.b = tp;
     t2.sa = static_cast<const float*>(a_scale);
@@ -705,7 +708,8 @@ extern "C" int vxk_fp8_gemm(void* D, const void* A, const void* B, const void* a
     t2.num_n_blocks = (int)((N + BN - 1) / BN);
     if ((rc = make_map_2d_u8(&ma, A, K, M, lda, kBlockKBytes, kBlockM, true))) return rc;
     if ((rc = make_map_2d_u8(&mb, B, K, N, b_stride_n, kBlockKBytes, BN / 2, true))) return rc;
-    return blk_pipe ? launch_tc2_blk<BN, true>(t2, ma, mb, st) : launch_tc2_blk<BN, false>(t2, ma, mb, st);
+    if (BN == 160) return launch_tc2_blk<160, true>(t2, ma, mb, st);
+    return blk_pipe ? launch_tc2_blk<192, true>(t2, ma, mb, st) : launch_tc2_blk<192, false>(t2, ma, mb, st);
   }
   if (operands_ok && a_scale_mode == 2 && scale_dtype == VXK_S_E8M0 && group_k % 32 == 0 && workspace &&
       workspace_bytes >= vxk_fp8_gemm_workspace_bytes(M, N, K, a_scale_mode, scale_dtype)) {

@@ -26,7 +26,10 @@
 // (256 x 128 tiles) were built and measured at 1200-1420 TFLOP/s (eight or sixteen promotion warps, register
 // double buffer) -- the 128-wide tile's MMA side alone reaches only 1515 TFLOP/s; 256-wide tiles leave no
 // registers for the staging buffers (128 accumulators per thread: 700 B of spills, 1860 TFLOP/s with 16-column
-// chunks).  192 x 2 is the measured optimum of this design space.
+// chunks).  Three 160-column buffers (256 x 160 tiles, columns split 96 + 64 over the two promotion warps of a lane
+// quarter; VXK_BLK_BN=160) take h off the critical path as intended but lose more on the MMA side (fewer flops per
+// operand byte) and on the 96 / 64 imbalance: 1427 vs 1756 TFLOP/s at 8192 x 36864 x 7168, slower on all six
+// DeepSeek-V3 shapes (profiles/r02_blk_analysis.txt).  192 x 2 is the measured optimum of this design space.
 // ref: fp8_gemm_w8a8.h:28-41,86-134 (block scale shapes), tests/test_fp8_gemm_onednn.py:270-358.
 #pragma once
 
@@ -57,9 +60,12 @@ gemm_tc2_blk_kernel(const Tc2BlkParams pp, const __grid_constant__ CUtensorMap m
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + S * L::kStageBytes);
   uint64_t* full_bar = bars;                 // leader CTA
   uint64_t* empty_bar = bars + S;            // per CTA
-  uint64_t* p_full_bar = bars + 2 * S;       // per CTA: partial product of one K slice is in TMEM buffer i
-  uint64_t* p_empty_bar = bars + 2 * S + 2;  // leader CTA: buffer i has been pulled into registers by all 16 warps
-  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(bars + 2 * S + 4);
+  // TMEM buffers that rotate per K slice: two 192-column ones, or THREE 160-column ones (a 256 x 160 tile): with three
+  // the hand-over latency h of the analysis above leaves the critical path (period max(m, d, (m + d + h) / 3))
+  constexpr int kNB = BLOCK_N <= 160 ? 3 : 2;
+  uint64_t* p_full_bar = bars + 2 * S;             // per CTA: partial product of one K slice is in TMEM buffer i
+  uint64_t* p_empty_bar = bars + 2 * S + kNB;      // leader CTA: buffer i has been pulled into registers by all 16 warps
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(bars + 2 * S + 2 * kNB);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t rank = cluster_ctarank();
@@ -74,7 +80,7 @@ gemm_tc2_blk_kernel(const Tc2BlkParams pp, const __grid_constant__ CUtensorMap m
       mbar_init(&full_bar[i], 1);
       mbar_init(&empty_bar[i], 1);
     }
-    for (int i = 0; i < 2; ++i) {
+    for (int i = 0; i < kNB; ++i) {
       mbar_init(&p_full_bar[i], 1);
       mbar_init(&p_empty_bar[i], 16);
     }
@@ -86,7 +92,7 @@ gemm_tc2_blk_kernel(const Tc2BlkParams pp, const __grid_constant__ CUtensorMap m
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr_smem;
   constexpr uint32_t kAccCols = BLOCK_N;
-  static_assert(2 * kAccCols <= kTmemCols, "TMEM budget");
+  static_assert(kNB * kAccCols <= kTmemCols, "TMEM budget");
 
   const int num_tiles = pp.num_m_pairs * pp.num_n_blocks;
   const int pair = blockIdx.x >> 1, num_pairs = gridDim.x >> 1;
@@ -124,8 +130,8 @@ gemm_tc2_blk_kernel(const Tc2BlkParams pp, const __grid_constant__ CUtensorMap m
       uint32_t g = 0;   // K slices issued so far (all tiles)
       for (int tile = pair; tile < num_tiles; tile += num_pairs) {
         for (int kb = 0; kb < KB; ++kb, ++g) {
-          const uint32_t buf = g & 1;
-          mbar_wait(&p_empty_bar[buf], ((g >> 1) & 1) ^ 1);
+          const uint32_t buf = g % kNB;
+          mbar_wait(&p_empty_bar[buf], ((g / kNB) & 1) ^ 1);
           mbar_wait(&full_bar[stage], phase);
           tc_fence_after();
           if (elect_one()) {
@@ -148,8 +154,10 @@ gemm_tc2_blk_kernel(const Tc2BlkParams pp, const __grid_constant__ CUtensorMap m
     // ===================== promotion + epilogue warps (both CTAs) =====================
     const int e = warp - 4;
     const int q = e & 3;                    // TMEM lane quarter
-    const int h = e >> 2;                   // column half of the tile
-    constexpr int kCols = BLOCK_N / 2;      // columns per thread
+    const int h = e >> 2;                   // column part of the tile: halves, or 96 + 64 of a 160-wide tile
+    auto promote = [&](auto nch_tag) {
+    constexpr int kCols = decltype(nch_tag)::value * 32;      // columns per thread
+    const int col_off = BLOCK_N == 160 ? h * 96 : h * kCols;
     constexpr int CW = 32;                  // tcgen05.ld chunk (columns)
     constexpr int kChunks = kCols / CW;
     constexpr int kSc = kCols / 32;         // 32-column scale blocks per thread
@@ -163,7 +171,7 @@ gemm_tc2_blk_kernel(const Tc2BlkParams pp, const __grid_constant__ CUtensorMap m
       int mt, nt;
       tile_coords(tile, pp.num_m_pairs, pp.num_n_blocks, pp.group_m, mt, nt);
       const int m = mt * (2 * kBlockM) + row_in_tile;
-      const int n_first = nt * BLOCK_N + h * kCols;
+      const int n_first = nt * BLOCK_N + col_off;
       const bool row_ok = m < p.M;
       const float* sa_row = pp.sa + static_cast<int64_t>(row_ok ? m : 0) * pp.sa0;
       // scale column groups of this thread's chunks (a 32-column chunk never straddles a group: group_n % 32 == 0)
@@ -188,11 +196,11 @@ gemm_tc2_blk_kernel(const Tc2BlkParams pp, const __grid_constant__ CUtensorMap m
       };
       RawScales s_next;
       load_scales(0, s_next);
-      const uint32_t t_lane = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + h * kCols;
+      const uint32_t t_lane = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + col_off;
       if (dbg_idle) {
         for (int kb = 0; kb < KB; ++kb, ++g) {
-          const uint32_t buf = g & 1;
-          mbar_wait(&p_full_bar[buf], (g >> 1) & 1);
+          const uint32_t buf = g % kNB;
+          mbar_wait(&p_full_bar[buf], (g / kNB) & 1);
           tc_fence_after();
           tc_fence_before();
           __syncwarp();
@@ -201,12 +209,12 @@ gemm_tc2_blk_kernel(const Tc2BlkParams pp, const __grid_constant__ CUtensorMap m
       } else if constexpr (!PIPE) {
         // all chunks of a slice at once: shortest hand-back latency, no overlap of ld and FMAs inside the warp
         for (int kb = 0; kb < KB; ++kb, ++g) {
-          const uint32_t buf = g & 1;
+          const uint32_t buf = g % kNB;
           float s[kChunks];
           asm volatile("" : "+f"(s_next.a));
 #pragma unroll
           for (int c = 0; c < kChunks; ++c) s[c] = s_next.a * s_next.b[c];
-          mbar_wait(&p_full_bar[buf], (g >> 1) & 1);
+          mbar_wait(&p_full_bar[buf], (g / kNB) & 1);
           tc_fence_after();
           uint32_t r[kChunks][32];
 #pragma unroll
@@ -228,12 +236,12 @@ gemm_tc2_blk_kernel(const Tc2BlkParams pp, const __grid_constant__ CUtensorMap m
         // (two rotating 32-register buffers; tcgen05.wait::ld has no finer granularity than "all").
         // A slice's TMEM buffer goes back to the MMA warp as soon as its last chunk has landed.
         uint32_t r[2][CW];
-        mbar_wait(&p_full_bar[g & 1], (g >> 1) & 1);
+        mbar_wait(&p_full_bar[g % kNB], (g / kNB) & 1);
         tc_fence_after();
-        tmem_ld_32x32b<CW>(t_lane + (g & 1) * kAccCols, r[0]);
+        tmem_ld_32x32b<CW>(t_lane + (g % kNB) * kAccCols, r[0]);
         auto slice = [&](auto kp_tag, int kb) {
           constexpr int KP = decltype(kp_tag)::value;      // parity of the slice index within the tile
-          const uint32_t buf = g & 1;
+          const uint32_t buf = g % kNB;
           float s[kSc];
           asm volatile("" : "+f"(s_next.a));
 #pragma unroll
@@ -258,9 +266,9 @@ gemm_tc2_blk_kernel(const Tc2BlkParams pp, const __grid_constant__ CUtensorMap m
               if (more) {
                 load_scales(kb + 1, s_next);
                 const uint32_t gn = g + 1;
-                if (__all_sync(0xffffffffu, mbar_try_wait(&p_full_bar[gn & 1], (gn >> 1) & 1))) {
+                if (__all_sync(0xffffffffu, mbar_try_wait(&p_full_bar[gn % kNB], (gn / kNB) & 1))) {
                   tc_fence_after();
-                  tmem_ld_32x32b<CW>(t_lane + (gn & 1) * kAccCols, r[cur ^ 1]);
+                  tmem_ld_32x32b<CW>(t_lane + (gn % kNB) * kAccCols, r[cur ^ 1]);
                   issued = true;
                 }
               }
@@ -270,9 +278,9 @@ gemm_tc2_blk_kernel(const Tc2BlkParams pp, const __grid_constant__ CUtensorMap m
               fma2(acc[c * CW + j], acc[c * CW + j + 1], __uint_as_float(r[cur][j]), __uint_as_float(r[cur][j + 1]), sc, sc);
             if (c + 1 == kChunks && more && !issued) {     // next slice was not ready: wait for it now
               const uint32_t gn = g + 1;
-              mbar_wait(&p_full_bar[gn & 1], (gn >> 1) & 1);
+              mbar_wait(&p_full_bar[gn % kNB], (gn / kNB) & 1);
               tc_fence_after();
-              tmem_ld_32x32b<CW>(t_lane + (gn & 1) * kAccCols, r[cur ^ 1]);
+              tmem_ld_32x32b<CW>(t_lane + (gn % kNB) * kAccCols, r[cur ^ 1]);
             }
           }
           ++g;
@@ -319,6 +327,13 @@ gemm_tc2_blk_kernel(const Tc2BlkParams pp, const __grid_constant__ CUtensorMap m
           }
         }
       }
+    }
+    };   // promote
+    if constexpr (BLOCK_N == 160) {
+      if (h == 0) promote(std::integral_constant<int, 3>{});
+      else promote(std::integral_constant<int, 2>{});
+    } else {
+      promote(std::integral_constant<int, BLOCK_N / 64>{});
     }
   }
 
