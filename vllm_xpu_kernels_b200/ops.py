@@ -58,7 +58,32 @@ def convert_fp8(dst_cache, src_cache, scale: float, kv_dtype: str = "fp8") -> No
     torch.ops._C_cache_ops.convert_fp8(dst_cache, src_cache, scale, kv_dtype)
 
 
-# ------------------------------------------------- allocation helpers (tests/ops)
+# ------------------------------------------------- allocation helpers
+# Same call signatures, defaults and output layouts as the reference's test-side helpers
+# (tests/ops/fp8_quant_op.py:135-276) so that its tests and callers run unchanged; the bodies are built on
+# the one scale allocator below.
+def _alloc_group_scales(rows_shape: tuple, n_groups: int, device, layout: str) -> torch.Tensor:
+    """fp32 scale tensor of logical shape rows_shape + (n_groups,).
+    layout "row": contiguous; "col": groups-major storage viewed back (stride 1 along rows);
+    "col_tma": like "col" with the row count padded to a multiple of 4 floats (16 bytes) per column, the pitch a
+    TMA descriptor over the scale columns needs."""
+    if layout == "row":
+        return torch.empty(rows_shape + (n_groups,), device=device, dtype=torch.float32)
+    m = rows_shape[-1]
+    if layout == "col":
+        return torch.empty(rows_shape[:-1] + (n_groups, m), device=device, dtype=torch.float32).transpose(-1, -2)
+    pitch = get_tma_aligned_size(m, 4)
+    batch = rows_shape[:-1]
+    strides = (1, pitch) if not batch else (pitch * n_groups, 1, pitch)
+    return torch.empty_strided(batch + (m, n_groups), strides, device=device, dtype=torch.float32)
+
+
+def get_tma_aligned_size(x: int, element_size: int) -> int:
+    """Smallest count >= x whose byte size is a multiple of 16 (tests/ops/fp8_quant_op.py:197-203)."""
+    per16 = 16 // element_size
+    return -(-x // per16) * per16
+
+
 def scaled_fp8_quant(
     input: torch.Tensor,
     scale: Optional[torch.Tensor] = None,
@@ -69,31 +94,26 @@ def scaled_fp8_quant(
     fp8_dtype: torch.dtype = torch.float8_e5m2,
     group_shape: tuple[int, int] | None = None,
 ) -> tuple[torch.Tensor, torch.Tensor]:
-    """tests/ops/fp8_quant_op.py:135-194."""
-    assert input.ndim == 2
-    shape: Union[tuple[int, int], torch.Size] = input.shape
-    if num_token_padding:
-        shape = (max(num_token_padding, input.shape[0]), shape[1])
-    if output is None:
-        output = torch.empty(shape, device=input.device, dtype=fp8_dtype)
-    else:
+    """FP8 quantisation of a [T, H] tensor: static when `scale` is given (per tensor, or per `group_shape`),
+    dynamic per token or per tensor otherwise.  Interface of tests/ops/fp8_quant_op.py:135-194."""
+    if input.ndim != 2:
+        raise AssertionError("scaled_fp8_quant takes a 2-D input")
+    rows = input.shape[0] if not num_token_padding else max(int(num_token_padding), input.shape[0])
+    if output is not None:
         assert num_token_padding is None, "padding not supported if output passed in"
         assert output.dtype == fp8_dtype
-    if scale is None:
-        if use_per_token_if_dynamic:
-            scale = torch.zeros((shape[0], 1), device=input.device, dtype=torch.float32)
-            dynamic_per_token_scaled_fp8_quant(output, input.contiguous(), scale, scale_ub)
-        else:
-            scale = torch.empty(1, device=input.device, dtype=torch.float32)
-            dynamic_scaled_fp8_quant(output, input, scale)
     else:
+        output = torch.empty((rows, input.shape[1]), device=input.device, dtype=fp8_dtype)
+    if scale is not None:
         static_scaled_fp8_quant(output, input, scale, group_shape)
+        return output, scale
+    if use_per_token_if_dynamic:
+        scale = torch.zeros((rows, 1), device=input.device, dtype=torch.float32)
+        dynamic_per_token_scaled_fp8_quant(output, input.contiguous(), scale, scale_ub)
+    else:
+        scale = torch.empty(1, device=input.device, dtype=torch.float32)
+        dynamic_scaled_fp8_quant(output, input, scale)
     return output, scale
-
-
-def get_tma_aligned_size(x: int, element_size: int) -> int:
-    alignment = 16 // element_size
-    return (x + alignment - 1) // alignment * alignment
 
 
 def per_token_group_quant_fp8(
@@ -106,30 +126,17 @@ def per_token_group_quant_fp8(
     tma_aligned_scales: bool = False,
     use_ue8m0: bool | None = None,
 ) -> tuple[torch.Tensor, torch.Tensor]:
-    """tests/ops/fp8_quant_op.py:206-276 (same scale allocation rules)."""
-    assert x.shape[-1] % group_size == 0
-    assert x.stride(-1) == 1, "`x` groups must be contiguous"
-    finfo = torch.finfo(dtype)
-    x_q = out_q if out_q is not None else torch.empty_like(x, dtype=dtype)
-    if column_major_scales:
-        if tma_aligned_scales:
-            m = x.shape[-2]
-            sf_k = x.shape[-1] // group_size
-            tma_m = get_tma_aligned_size(m, 4)
-            shape = x.shape[:-2] + (m, sf_k)
-            stride = (1, tma_m) if x.dim() == 2 else (tma_m * sf_k, 1, tma_m)
-            x_s = torch.empty_strided(shape, stride, device=x.device, dtype=torch.float32)
-        else:
-            shape = x.shape[:-2] + (x.shape[-1] // group_size, x.shape[-2])
-            x_s = torch.empty(shape, device=x.device, dtype=torch.float32).permute(-1, -2)
-    else:
-        shape = x.shape[:-1] + (x.shape[-1] // group_size,)
-        x_s = torch.empty(shape, device=x.device, dtype=torch.float32)
-    torch.ops._C.per_token_group_fp8_quant(x, x_q, x_s, group_size, eps, finfo.min, finfo.max,
-                                           bool(use_ue8m0), column_major_scales, tma_aligned_scales)
-    if use_ue8m0:
-        x_s = x_s.to(torch.float8_e8m0fnu)
-    return x_q, x_s
+    """1 x group_size FP8 quantisation along the last dimension; scales row-major, column-major or column-major with a
+    TMA-aligned pitch; UE8M0 scales come back as float8_e8m0fnu.  Interface of tests/ops/fp8_quant_op.py:206-276."""
+    if x.shape[-1] % group_size != 0 or x.stride(-1) != 1:
+        raise AssertionError("the last dimension must be contiguous and a multiple of group_size")
+    q = torch.empty_like(x, dtype=dtype) if out_q is None else out_q
+    layout = "row" if not column_major_scales else ("col_tma" if tma_aligned_scales else "col")
+    s = _alloc_group_scales(tuple(x.shape[:-1]), x.shape[-1] // group_size, x.device, layout)
+    lim = torch.finfo(dtype)
+    torch.ops._C.per_token_group_fp8_quant(x, q, s, group_size, eps, lim.min, lim.max, bool(use_ue8m0),
+                                           column_major_scales, tma_aligned_scales)
+    return q, (s.to(torch.float8_e8m0fnu) if use_ue8m0 else s)
 
 
 def per_token_group_quant_mxfp4(
@@ -142,10 +149,7 @@ def per_token_group_quant_mxfp4(
     assert x.ndim == 2 and x.shape[-1] % group_size == 0 and x.stride(-1) == 1
     M, N = x.shape
     out_q = torch.empty(M, N // 2, device=x.device, dtype=torch.uint8)
-    if column_major_scales:
-        out_s = torch.empty((N // group_size, M), device=x.device, dtype=torch.float32).permute(-1, -2)
-    else:
-        out_s = torch.empty(M, N // group_size, device=x.device, dtype=torch.float32)
+    out_s = _alloc_group_scales((M,), N // group_size, x.device, "col" if column_major_scales else "row")
     torch.ops._C.per_token_group_quant_mxfp4(x.contiguous(), out_q, out_s, group_size, eps)
     out_q = out_q.view(torch.float4_e2m1fn_x2)
     out_s = out_s.to(dtype=torch.float8_e8m0fnu, memory_format=torch.preserve_format)
@@ -166,10 +170,7 @@ def silu_and_mul_per_block_quant(
     hidden_size = input.shape[-1] // 2
     num_groups = hidden_size // group_size
     out = torch.empty((num_tokens, hidden_size), device=input.device, dtype=quant_dtype)
-    if is_scale_transposed:
-        scales = torch.empty((num_groups, num_tokens), device=input.device, dtype=torch.float32).t()
-    else:
-        scales = torch.empty((num_tokens, num_groups), device=input.device, dtype=torch.float32)
+    scales = _alloc_group_scales((num_tokens,), num_groups, input.device, "col" if is_scale_transposed else "row")
     torch.ops._C.silu_and_mul_per_block_quant(out, input, scales, group_size, scale_ub,
                                               is_scale_transposed, scale_ue8m0)
     return out, scales
@@ -201,10 +202,7 @@ def rms_norm_per_block_quant(x, weight, eps, group_size, quant_dtype, residual=N
     out = torch.empty(x.shape, dtype=quant_dtype, device=x.device)
     T = x.numel() // x.shape[-1]
     G = x.shape[-1] // group_size
-    if is_scale_transposed:
-        scales = torch.empty(G, T, dtype=torch.float32, device=x.device).t()
-    else:
-        scales = torch.empty(T, G, dtype=torch.float32, device=x.device)
+    scales = _alloc_group_scales((T,), G, x.device, "col" if is_scale_transposed else "row")
     torch.ops._C.rms_norm_per_block_quant(out, x, weight, scales, eps, None, residual, group_size,
                                           is_scale_transposed, scale_ue8m0)
     return out, scales
