@@ -161,7 +161,7 @@ def test_a2_strided_rows_and_errors(ops):
     ops.static_scaled_fp8_quant(out2, xs, s.to(DEV))
     ref = quant.static_scaled_fp8_quant(x.contiguous(), s, E4)
     assert torch.equal(u8(out2), u8(ref)) and torch.equal(u8(out), u8(ref))
-    with pytest.raises(RuntimeError, match="1D scale requires explicit group_shape"):
+    with pytest.raises(RuntimeError, match="1-D scale needs group_shape"):
         ops.static_scaled_fp8_quant(out, xs, torch.ones(16, device=DEV))
     with pytest.raises(RuntimeError, match="must be divisible"):
         ops.static_scaled_fp8_quant(out, xs, torch.ones(3, 2, device=DEV))

@@ -114,41 +114,34 @@ void static_scaled_fp8_quant(Tensor& out, const Tensor& input, const Tensor& sca
     group_m = num_tokens; group_n = hidden_size; ss_i = 0; ss_j = 0;
   } else if (scale.dim() == 1) {
     TORCH_CHECK(opt_group_shape.has_value(),
-                "1D scale requires explicit group_shape to disambiguate per-channel vs per-token "
-                "quantization. Use group_shape=(-1, 1) for per-channel or group_shape=(1, -1) for "
-                "per-token.");
+                "a 1-D scale needs group_shape: (1, -1) = one scale per token, (-1, 1) = one per channel");
     const auto [ogm, ogn] = opt_group_shape.value();
     group_m = ogm == -1 ? num_tokens : ogm;
     group_n = ogn == -1 ? hidden_size : ogn;
     TORCH_CHECK(group_m > 0 && group_n > 0, "invalid group_shape");
     const int64_t em = num_tokens / group_m, en = hidden_size / group_n;
-    TORCH_CHECK(scale.numel() == em * en, "1D scale length (", scale.numel(),
-                ") does not match expected size (", em * en, ") for group_shape (", ogm, ", ", ogn,
-                ") with input shape (", num_tokens, ", ", hidden_size, ")");
+    TORCH_CHECK(scale.numel() == em * en, "scale has ", scale.numel(), " elements, group_shape (", ogm, ", ", ogn,
+                ") over a [", num_tokens, ", ", hidden_size, "] input needs ", em * en);
     if (em == 1) { ss_i = 0; ss_j = scale.stride(0); }
     else if (en == 1) { ss_i = scale.stride(0); ss_j = 0; }
-    else TORCH_CHECK(false, "1D scale can only be used when one of the scale dimensions is 1. "
-                            "For 2D group scaling, use a 2D scale tensor.");
+    else TORCH_CHECK(false, "a 1-D scale covers per-token or per-channel groups only; pass a 2-D scale for 2-D groups");
   } else if (scale.dim() == 2) {
     const int64_t s0 = scale.size(0), s1 = scale.size(1);
-    TORCH_CHECK(s0 > 0 && num_tokens % s0 == 0, "num_tokens (", num_tokens,
-                ") must be divisible by scale.size(0) (", s0, ")");
-    TORCH_CHECK(s1 > 0 && hidden_size % s1 == 0, "hidden_size (", hidden_size,
-                ") must be divisible by scale.size(1) (", s1, ")");
+    TORCH_CHECK(s0 > 0 && num_tokens % s0 == 0, "rows of the input (", num_tokens, ") must be divisible by scale.size(0) = ", s0);
+    TORCH_CHECK(s1 > 0 && hidden_size % s1 == 0, "columns of the input (", hidden_size, ") must be divisible by scale.size(1) = ", s1);
     const int64_t igm = num_tokens / s0, ign = hidden_size / s1;
     if (opt_group_shape.has_value()) {
       const auto [ogm, ogn] = opt_group_shape.value();
       group_m = ogm == -1 ? num_tokens : ogm;
       group_n = ogn == -1 ? hidden_size : ogn;
-      TORCH_CHECK(group_m == igm && group_n == ign, "Explicit group_shape (", ogm, ", ", ogn,
-                  ") does not match inferred group shape (", igm, ", ", ign,
-                  ") from 2D scale tensor shape (", s0, ", ", s1, ")");
+      TORCH_CHECK(group_m == igm && group_n == ign, "group_shape (", ogm, ", ", ogn, ") contradicts the [", s0, ", ", s1,
+                  "] scale tensor, which implies groups of (", igm, ", ", ign, ")");
     } else {
       group_m = igm; group_n = ign;
     }
     ss_i = scale.stride(0); ss_j = scale.stride(1);
   } else {
-    TORCH_CHECK(false, "scale must be 0D, 1D, or 2D tensor, but got ", scale.dim(), "D");
+    TORCH_CHECK(false, "scale must have 0, 1 or 2 dimensions, got ", scale.dim());
   }
   const int64_t in_rs = input.dim() >= 2 ? input.stride(-2) : hidden_size;
   const int64_t out_rs = out.dim() >= 2 ? out.stride(-2) : hidden_size;
