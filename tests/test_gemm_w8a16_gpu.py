@@ -221,3 +221,37 @@ def test_w8a16_small_m_kernel(ops, lib, fp8, dtype, mode, mnk):
     tc1, fb1 = gemm_stats(lib)
     assert (tc1 - tc0, fb1 - fb0) == ((m + 127) // 128, 0)       # 129..256 tokens: two passes of 128
     close(out, og.fp8_gemm_w8a16_ref(x, wq.t(), s_ref, b))
+
+
+@pytest.mark.parametrize("fp8", [E4, E5])
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+@pytest.mark.parametrize("groups", [(128, 128), (64, 192), (256, 64), (192, 128)])      # (group_n, group_k)
+@pytest.mark.parametrize("mnk", [(257, 384, 768), (700, 1536, 1152), (1024, 768, 4224)])
+def test_w8a16_large_m_block_scales(ops, lib, fp8, dtype, groups, mnk):
+    """M > 256 with 2-D block scales: the swapped-operand kernel with the widened weight tile in tensor memory
+    folds the scale in while widening (one rounding to the activation type, like the small-M kernel).  Rectangular
+    groups, group_k a multiple of 64 only, partial 128-row weight tiles and partial 256-token tiles, bias."""
+    torch.manual_seed(11)
+    m, n, k = mnk
+    gn, gk = groups
+    if n % gn or k % gk:
+        pytest.skip("shape not divisible by the group")
+    x = torch.randn(m, k, dtype=dtype) / 10.0
+    w = torch.randn(n, k, dtype=torch.float32) / 10.0
+    w[: n // 2] *= 7.0                       # scales that differ a lot between blocks
+    b = torch.randn(n, dtype=dtype) / 4
+    wq, ws = og.fp8_block_quant_2d(w, gn, gk)
+    wq = wq if fp8 == E4 else wq.float().to(fp8)
+    sc = ws.t().contiguous()                 # [K / gk, N / gn]
+    tc0, fb0 = gemm_stats(lib)
+    out = ops.fp8_gemm_w8a16(x.to(DEV), wq.to(DEV).t(), sc.to(DEV), b.to(DEV))
+    tc1, fb1 = gemm_stats(lib)
+    assert (tc1 - tc0, fb1 - fb0) == (1, 0)
+    # against the exact oracle the rounding of the dequantised weights to bf16 / f16 shows: K terms of ~0.07 with a
+    # relative error of up to 2^-9 each (std ~0.005 at K = 4224, and 786 k outputs to take the maximum over)
+    close(out, og.fp8_gemm_w8a16_ref(x, wq.t(), sc, b), atol=6e-2, rtol=1e-2)
+    # the kernel's own statement: weights dequantised with ONE rounding to the activation type
+    # (tests/ops/fp8_quant_op.py:81-106), exact accumulation, one output rounding
+    w_deq = og.fp8_block_dequant_2d(wq, ws, gn, gk, dtype)
+    ref = (x.double() @ w_deq.double().t() + b.double()).to(dtype)
+    close(out, ref, atol=2e-3, rtol=8e-3)

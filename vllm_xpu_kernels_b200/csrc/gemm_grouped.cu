@@ -126,13 +126,17 @@ static int launch_gg_types(const GroupedParams& gp, const CUtensorMap& mw, const
 
 // Dense fp8_gemm_w8a16 at large M through the grouped kernel (one expert owning every row, weights W[N, K]
 // K-contiguous, widened operand in TMEM, 256-token tiles): see gemm_w8a16.cu for why.
-int run_w8a16_dense_tmem(void* D, const void* A, const void* W, const float* scale, int per_channel, const void* bias,
-                         int64_t M, int64_t N, int64_t K, int64_t lda, int64_t ldw, int64_t ldd, bool bf16, bool e5m2,
-                         cudaStream_t st) {
+int run_w8a16_dense_tmem(void* D, const void* A, const void* W, const float* scale, int scale_mode, int64_t group_k,
+                         int64_t group_n, int64_t sb0, int64_t sb1, const void* bias, int64_t M, int64_t N, int64_t K,
+                         int64_t lda, int64_t ldw, int64_t ldd, bool bf16, bool e5m2, cudaStream_t st) {
   const int mt = M <= 32 ? 32 : (M <= 64 ? 64 : (M <= 128 ? 128 : 256));
   const int block_k = mt <= 128 ? 128 : kGgBlockK;
   GroupedParams gp{};
-  gp.D = D; gp.bias = bias; gp.rows = nullptr; gp.w_scale = scale; gp.scale_per_channel = per_channel;
+  gp.D = D; gp.bias = bias; gp.rows = nullptr; gp.w_scale = scale; gp.scale_per_channel = scale_mode == 1;
+  if (scale_mode == 2) {   // 2-D block scales: folded into the widening
+    gp.blk_scale = scale; gp.w_scale = nullptr;
+    gp.group_k = static_cast<int>(group_k); gp.group_n = static_cast<int>(group_n); gp.sb0 = sb0; gp.sb1 = sb1;
+  }
   gp.total_m = static_cast<int>(M); gp.N = static_cast<int>(N); gp.K = static_cast<int>(K); gp.E = 1;
   gp.num_kb = static_cast<int>((K + block_k - 1) / block_k);
   gp.num_nt = static_cast<int>((N + 127) / 128);

@@ -59,6 +59,9 @@ struct GroupedParams {
   const uint8_t* w_sf;     // GW_MX4: [E, N, K / 32]
   const int32_t* rows;     // [E]; null: one expert owning all total_m rows (dense call)
   int scale_per_channel;   // GW_FP8T: w_scale is [E, N] (per output channel) instead of [E]
+  const float* blk_scale;  // GW_FP8T, dense call only: 2-D block scales, folded in while widening (w_scale unused);
+  int group_k, group_n;    //   scale of (k, n) = blk_scale[(k / group_k) * sb0 + (n / group_n) * sb1], group_k % 64 == 0
+  int64_t sb0, sb1;
   int total_m, N, K, E;
   int num_kb, num_nt;
   int64_t ldd;
@@ -358,7 +361,15 @@ gemm_grouped_kernel(const GroupedParams p, const __grid_constant__ CUtensorMap m
       int stage = 0, cs = 0;
       uint32_t phase = 0, cphase = 0;
       for (int idx = blockIdx.x; idx < num_tiles; idx += gridDim.x) {
+        const float* blk = nullptr;                // block-scaled dense call: this row's scale column
+        if (p.blk_scale) {
+          const GgTile t = gg_tile<MT>(tile_start, row_start, p.E, p.num_nt, idx);
+          blk = p.blk_scale + static_cast<int64_t>(min(t.n0 + row, p.N - 1) / p.group_n) * p.sb1;
+        }
         for (int kb = 0; kb < p.num_kb; ++kb) {
+          // the thread's 16 * kChunks codes lie inside one scale group (group_k % 64 == 0); fetched before the wait
+          float bs = 1.0f;
+          if (blk) bs = __ldg(blk + static_cast<int64_t>(min(kb * kBK + kChunks * j * 16, p.K - 1) / p.group_k) * p.sb0);
           mbar_wait(&full_bar[stage], phase);
           const uint32_t raw = smem_u32(stage_w(stage)) + row * kBK;
           uint32_t w[kChunks * 8];
@@ -366,7 +377,8 @@ gemm_grouped_kernel(const GroupedParams p, const __grid_constant__ CUtensorMap m
           for (int c = 0; c < kChunks; ++c) {
             const uint4 v = lds128(raw + (((kChunks * j + c) ^ sw) << 4));
             uint32_t t8[8];
-            widen16<BF16, E5M2, false>(v, 1.0f, t8);
+            if (blk) widen16<BF16, E5M2, true>(v, bs, t8);   // one rounding to the activation type, like gemm_w8a16.cuh
+            else widen16<BF16, E5M2, false>(v, 1.0f, t8);
 #pragma unroll
             for (int i = 0; i < 8; ++i) w[c * 8 + i] = t8[i];
           }
@@ -583,8 +595,9 @@ gemm_grouped_kernel(const GroupedParams p, const __grid_constant__ CUtensorMap m
       float sc = 1.0f, bv = 0.0f;
       if constexpr (WKIND == GW_FP8) sc = __ldg(p.w_scale + t.e);
       if constexpr (WKIND == GW_FP8T)
-        sc = p.scale_per_channel ? (n_ok ? __ldg(p.w_scale + static_cast<int64_t>(t.e) * p.N + n) : 0.0f)
-                                 : __ldg(p.w_scale + t.e);
+        sc = p.blk_scale ? 1.0f
+             : p.scale_per_channel ? (n_ok ? __ldg(p.w_scale + static_cast<int64_t>(t.e) * p.N + n) : 0.0f)
+                                   : __ldg(p.w_scale + t.e);
       if (p.bias && n_ok) {
         const int64_t bi = static_cast<int64_t>(t.e) * p.N + n;
         bv = BF16 ? __bfloat162float(static_cast<const __nv_bfloat16*>(p.bias)[bi])

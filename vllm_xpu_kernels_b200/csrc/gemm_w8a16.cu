@@ -7,9 +7,9 @@
 
 namespace vxk {
 
-int run_w8a16_dense_tmem(void* D, const void* A, const void* W, const float* scale, int per_channel, const void* bias,
-                         int64_t M, int64_t N, int64_t K, int64_t lda, int64_t ldw, int64_t ldd, bool bf16, bool e5m2,
-                         cudaStream_t st);
+int run_w8a16_dense_tmem(void* D, const void* A, const void* W, const float* scale, int scale_mode, int64_t group_k,
+                         int64_t group_n, int64_t sb0, int64_t sb1, const void* bias, int64_t M, int64_t N, int64_t K,
+                         int64_t lda, int64_t ldw, int64_t ldd, bool bf16, bool e5m2, cudaStream_t st);
 
 // ---- CUDA-core path: any strides, any K / N; 32 x 32 outputs per CTA, fp32 accumulation ----
 struct W16FallbackParams {
@@ -273,10 +273,11 @@ extern "C" int vxk_fp8_gemm_w8a16(void* D, const void* A, const void* B, const f
   // and 256 tokens as the N operand the same step moves 80 KB (156 B/clk).
   static const int dense_ta = [] { const char* e = getenv("VXK_W16_DENSE_TMEM_A"); return e ? atoi(e) : 1; }();
   const int want_bias_dtype = act_dtype == VXK_BF16 ? VXK_BF16 : VXK_F16;
-  if (dense_ta && b_scale_mode != 2 && K % 64 == 0 && (!bias || bias_dtype == want_bias_dtype) && ldd % 2 == 0 &&
-      N % 2 == 0 && (reinterpret_cast<uintptr_t>(D) & 3) == 0) {
-    const int rc = run_w8a16_dense_tmem(D, A, B, b_scale, b_scale_mode == 1, bias, M, N, K, lda, b_stride_n, ldd,
-                                        act_dtype == VXK_BF16, fp8_dtype == VXK_Q_E5M2, st);
+  // (VXK_W16_DENSE_TMEM_A=2 keeps block-scaled weights on the shared-memory kernel, for A/B timing)
+  const bool blk_ok = b_scale_mode != 2 || (group_k % 64 == 0 && dense_ta != 2);
+  if (dense_ta && blk_ok && K % 64 == 0 && (!bias || bias_dtype == want_bias_dtype) && ldd % 2 == 0 && N % 2 == 0 && (reinterpret_cast<uintptr_t>(D) & 3) == 0) {
+    const int rc = run_w8a16_dense_tmem(D, A, B, b_scale, b_scale_mode, group_k, group_n, sb0, sb1, bias, M, N, K, lda,
+                                        b_stride_n, ldd, act_dtype == VXK_BF16, fp8_dtype == VXK_Q_E5M2, st);
     return rc;
   }
 
