@@ -58,8 +58,14 @@ struct FlatParams {
 // bound on B200 rather than HBM bound unless the body is kept minimal: packed 16-bit multiply for
 // silu*up, constant-divisor and reciprocal-based exact divisions, compile-time segmented shuffles.
 // LL = log2(lanes per group) or -1 (runtime p.lanes_log2).
+// Register bound: 5 CTAs of 256 threads per SM (48 registers).  Left to itself ptxas gives the MXFP4 / f32
+// instantiations 79-86 registers (2-3 CTAs); 6 CTAs (40 registers) spills and measured 2-4 % slower than 5, 7 CTAs
+// 10-18 % slower (profiles/r02_flat_occupancy.txt).
+#ifndef VXK_FLAT_MIN_CTAS
+#define VXK_FLAT_MIN_CTAS 5
+#endif
 template <typename T, int Q, int PRO, int FMT, int FAST, int U, int LL>
-__global__ void __launch_bounds__(256) flat_quant_kernel(const FlatParams p) {
+__global__ void __launch_bounds__(256, VXK_FLAT_MIN_CTAS) flat_quant_kernel(const FlatParams p) {
   constexpr float kQMax = QTraits<Q>::kMax;
   constexpr bool kGated = PRO != PRO_NONE;
   constexpr int kOutVecBytes = (FMT == FMT_MXFP4) ? 4 : kVec;
@@ -435,13 +441,21 @@ static int launch_flat(FlatParams p, int64_t T_, int64_t H, int G, bool vec_ok, 
     while ((1 << p.lanes_log2) < lanes) ++p.lanes_log2;
     // column threads per row: the multiple of 32 (hence of `lanes`) that leaves the fewest idle
     // lanes in the last column block; short rows share a CTA (rpb rows per block)
+    // Among equally tight choices a divisor of 256 wins: 8-warp CTAs.  (Registers are handed out to CTAs in units
+    // of four warps, so a 7-warp CTA -- tx = 224, which H = 14336 would otherwise pick -- occupies the register file
+    // like an 8-warp one: 35 resident warps instead of 40, measured 4-5 % slower on the bench's dominant kernel,
+    // profiles/r02_flat_occupancy.txt.)
     int best_tx = 256;
     double best_idle = 2.0;
-    for (int tx = 256; tx >= 32; tx -= 32) {
+    static const int kTxOrder[8] = {256, 128, 64, 32, 224, 192, 160, 96};
+    for (int i = 0; i < 8; ++i) {
+      const int tx = kTxOrder[i];
       const int64_t cols = (static_cast<int64_t>(p.nvec) + tx * U - 1) / (tx * U) * (tx * U);
       const double idle = static_cast<double>(cols - p.nvec) / static_cast<double>(cols);
       if (idle < best_idle - 1e-9) { best_idle = idle; best_tx = tx; }
     }
+    static const int env_tx = [] { const char* e = getenv("VXK_FLAT_TX"); return e ? atoi(e) : 0; }();   // (A/B timing)
+    if (env_tx >= 32 && env_tx <= 256 && env_tx % 32 == 0) best_tx = env_tx;
     p.tx = best_tx;
     p.rpb = 256 / p.tx;
     p.ncb = (p.nvec + p.tx * U - 1) / (p.tx * U);
