@@ -21,7 +21,7 @@
 extern "C" {
 #endif
 
-#define VXK_ABI_VERSION 7
+#define VXK_ABI_VERSION 8
 
 typedef struct CUstream_st* vxk_stream_t; /* == cudaStream_t */
 
@@ -237,6 +237,24 @@ int vxk_fp4_gemm_allgather(void* const* peer_out, int n_peers, int self_rank, in
  * it the call still runs, on the single-CTA kernel.
  * ref: the per-call scratchpad of fp4_gemm_w4a4.h:159-162. */
 int64_t vxk_fp4_gemm_workspace_bytes(int64_t M, int64_t N, int64_t K);
+
+/* vxk_fp4_gemm for callers that may not allocate device memory (code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+ * Same operands, arithmetic and kernels as vxk_fp4_gemm; the scale-factor scratch is a file-scope
+ * device array inside the library (vxk_fp4_gemm_static_scratch_bytes() = 4 MiB, held by every GPU that loads the
+ * library until the process exits) instead of a caller buffer.  The call allocates nothing (no cudaMalloc /
+ * cudaFree, no allocating library routine).
+ *   Limit: vxk_fp4_gemm_workspace_bytes(M, N, K) + 256 must fit the array, e.g. M = 2048, N = 8192, K = 8192
+ *   (2.7 MB) does, M = 8192 with N = 28672 does not; larger problems return VXK_ERR_INVALID (message names the
+ *   sizes) -- use vxk_fp4_gemm with a workspace of your own there.
+ *   Sharing: every call on a device uses the same array.  Calls that follow each other on one stream are safe
+ *   (each call rewrites the whole region it reads; nothing needs to start at zero); calls that overlap on the GPU
+ *   (two streams, two threads) race on it and must not be issued. */
+int vxk_fp4_gemm_static_scratch(void* D, const void* A, const void* B, const void* a_scale,
+                                const void* b_scale, const void* bias, int64_t M, int64_t N, int64_t K,
+                                int64_t lda_bytes, int64_t ldb_bytes, int64_t ldd, int64_t sa0, int64_t sa1,
+                                int64_t sb0, int64_t sb1, int out_dtype, int bias_dtype, vxk_stream_t stream);
+int64_t vxk_fp4_gemm_static_scratch_bytes(void);
 
 /* ------------------------------------------------------- (f) next #2 ---
  * MX scale factors in the tensor core's own layout ("packed": the 512-byte chunks that

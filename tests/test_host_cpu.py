@@ -26,7 +26,7 @@ def test_c_abi_exports_every_declared_symbol():
     for n in names:
         assert hasattr(lib, n), f"{n} declared in include/vxk_b200.h but not exported"
     lib.vxk_abi_version.restype = ctypes.c_int
-    assert lib.vxk_abi_version() == 7
+    assert lib.vxk_abi_version() == 8
     lib.vxk_last_error.restype = ctypes.c_char_p
     assert isinstance(lib.vxk_last_error(), bytes)
 

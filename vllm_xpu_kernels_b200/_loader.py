@@ -9,7 +9,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "_lib", "libvxk_b200.so")
 SHIM_PATH = os.path.join(_HERE, "_lib", "_vxk_torch_ops.so")
 
-ABI_VERSION = 7   # == VXK_ABI_VERSION of include/vxk_b200.h
+ABI_VERSION = 8   # == VXK_ABI_VERSION of include/vxk_b200.h
 
 _lock = threading.Lock()
 _cdll = None

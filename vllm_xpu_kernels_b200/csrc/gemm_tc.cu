@@ -880,6 +880,59 @@ extern "C" int vxk_fp4_gemm(void* D, const void* A, const void* B, const void* a
                        out_dtype, bias_dtype, workspace, workspace_bytes, stream, nullptr, nullptr);
 }
 
+// ---- vxk_fp4_gemm_static_scratch: vxk_fp4_gemm for callers that may not allocate (include/vxk_b200.h) ----
+// The scale-factor re-packing scratch lives in a file-scope device array instead of a caller buffer.  Every device
+// that loads the library holds these 4 MiB until the process exits.  Nothing in it has to start at zero:
+// sf_pack_kernel / canon_sf_kernel rewrite every word of the region a call uses (zeros outside the tensor) before
+// the GEMM reads it, so the previous call's contents are never seen.  All calls on a device share the array: two
+// calls that overlap on the GPU (different streams) race.
+#define VXK_FP4_STATIC_SCRATCH_BYTES (4 << 20)
+static __device__ __align__(256) unsigned char g_fp4_static_scratch[VXK_FP4_STATIC_SCRATCH_BYTES];
+
+// Device address of the array on the current device.  In host code `g_fp4_static_scratch` is only the host-side
+// stand-in of the symbol; cudaGetSymbolAddress (once per device, with that device current) gives the address a
+// kernel can use.
+static int fp4_static_scratch_ptr(void** out) {
+  static std::mutex mu;
+  static void* ptr[64] = {nullptr};
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return fail(VXK_ERR_CUDA, "cudaGetDevice: %s", cudaGetErrorString(e));
+  if (dev < 0 || dev >= 64) return fail(VXK_ERR_UNSUPPORTED, "static scratch: device ordinal %d out of range", dev);
+  std::lock_guard<std::mutex> g(mu);
+  if (!ptr[dev]) {
+    void* p = nullptr;
+    e = cudaGetSymbolAddress(&p, g_fp4_static_scratch);
+    if (e != cudaSuccess || !p)
+      return fail(VXK_ERR_CUDA, "cudaGetSymbolAddress(static scratch) on device %d: %s", dev, cudaGetErrorString(e));
+    ptr[dev] = p;
+  }
+  *out = ptr[dev];
+  return VXK_OK;
+}
+
+extern "C" int64_t vxk_fp4_gemm_static_scratch_bytes(void) { return VXK_FP4_STATIC_SCRATCH_BYTES; }
+
+extern "C" int vxk_fp4_gemm_static_scratch(void* D, const void* A, const void* B, const void* a_scale,
+                                           const void* b_scale, const void* bias, int64_t M, int64_t N, int64_t K,
+                                           int64_t lda_bytes, int64_t ldb_bytes, int64_t ldd, int64_t sa0, int64_t sa1,
+                                           int64_t sb0, int64_t sb1, int out_dtype, int bias_dtype,
+                                           vxk_stream_t stream) {
+  VXK_REQUIRE(M >= 0 && N >= 0 && K >= 0, "negative shape");
+  const int64_t need = vxk_fp4_gemm_workspace_bytes(M, N, K);
+  if (need + 256 > VXK_FP4_STATIC_SCRATCH_BYTES)
+    return fail(VXK_ERR_INVALID,
+                "vxk_fp4_gemm_static_scratch: M = %lld, N = %lld, K = %lld needs %lld bytes of scale-factor scratch, the "
+                "static array holds %lld; call vxk_fp4_gemm with a caller-provided workspace",
+                (long long)M, (long long)N, (long long)K, (long long)(need + 256),
+                (long long)VXK_FP4_STATIC_SCRATCH_BYTES);
+  void* ws = nullptr;
+  const int rc = fp4_static_scratch_ptr(&ws);
+  if (rc) return rc;
+  return fp4_gemm_impl(D, A, B, a_scale, b_scale, bias, M, N, K, lda_bytes, ldb_bytes, ldd, sa0, sa1, sb0, sb1,
+                       out_dtype, bias_dtype, ws, VXK_FP4_STATIC_SCRATCH_BYTES, stream, nullptr, nullptr);
+}
+
 extern "C" int vxk_fp4_gemm_sf(void* D, const void* A, const void* B, const void* a_scale, const void* b_scale,
                                const void* a_scale_packed, const void* b_scale_packed, const void* bias, int64_t M,
                                int64_t N, int64_t K, int64_t lda_bytes, int64_t ldb_bytes, int64_t ldd, int64_t sa0,
