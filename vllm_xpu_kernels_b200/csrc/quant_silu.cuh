@@ -84,14 +84,35 @@ __device__ __forceinline__ void prologue(const RawV<T>& g, const RawV<T>& up, fl
                           __hmin2(*reinterpret_cast<const V*>(&gw[2]), *reinterpret_cast<const V*>(&gw[3])));
       deep = !__hbgt2(m, __float2bfloat162_rn(-87.25f));       // some gate <= -87.25 (or NaN)
     }
+    // (one branch per vector, not one per pair: the guard's BSSY / BRA / BSYNC triples were 5 % of all issued
+    // instructions of the silu + 1 x 128 FP8 kernel, profiles/r02b_silu_block.csv)
+    float sl[8];
+    if constexpr (FAST) {
+      if (__builtin_expect(deep, 0)) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const float2 f = Pair<T>::unpack(gw[i]);
+          sl[2 * i] = silu_slow(f.x);
+          sl[2 * i + 1] = silu_slow(f.y);
+        }
+      } else {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const float2 f = Pair<T>::unpack(gw[i]);
+          silu2_approx(f.x, f.y, sl[2 * i], sl[2 * i + 1]);
+        }
+      }
+    } else {
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const float2 f = Pair<T>::unpack(gw[i]);
+        sl[2 * i] = silu_f32<0>(f.x);
+        sl[2 * i + 1] = silu_f32<0>(f.y);
+      }
+    }
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
-      const float2 f = Pair<T>::unpack(gw[i]);
-      float s0, s1;
-      if constexpr (FAST) {
-        if (__builtin_expect(deep, 0)) { s0 = silu_slow(f.x); s1 = silu_slow(f.y); }
-        else silu2_approx(f.x, f.y, s0, s1);
-      } else { s0 = silu_f32<0>(f.x); s1 = silu_f32<0>(f.y); }
+      const float s0 = sl[2 * i], s1 = sl[2 * i + 1];
       const typename Pair<T>::V s2 = Pair<T>::pack(s0, s1);
       const typename Pair<T>::V y2 = __hmul2(s2, *reinterpret_cast<const typename Pair<T>::V*>(&uw[i]));
       yw[i] = *reinterpret_cast<const uint32_t*>(&y2);
