@@ -306,6 +306,49 @@ def test_a6_rms_norm_dynamic_per_token(ops, dtype, qd, T, H, add_res):
     _check_vs_torch_order(q, s, tq, ts, "a6 vs torch order", qd == torch.int8)
 
 
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("H", [1024, 4096])
+@pytest.mark.parametrize("eps", [1e-6, 1e-30])
+def test_a6_a9_variance_over_the_whole_input_range(ops, dtype, H, eps):
+    """The 16-bit static and MXFP4 kernels sum exact fp32 squares widened to fp64 by integer operations and fall back to
+    real conversions when that sum leaves its trusted window (quant_row_impl.cuh, widen_sq): one row per magnitude
+    from squares that flush in fp32 to squares that overflow it, all-zero rows, rows that mix the extremes,
+    and -0.0.  Same bar as every a6 / a7 test: bit-exact vs the exact-variance oracle."""
+    seed()
+    mags = ([1e-30, 1e-25, 1e-20, 1e-15, 1e-12, 1e-10, 1e-8, 1e-4, 1.0, 1e6, 1e15, 1e19, 3e19, 1e25]
+            if dtype == torch.bfloat16 else [1e-7, 1e-6, 1e-5, 1e-3, 1.0, 30.0, 1e3, 1e4])
+    rows = [torch.randn(H) * m for m in mags]
+    rows.append(torch.zeros(H))
+    z = torch.zeros(H); z[::2] = -0.0; z[5] = 1e-3 if dtype == torch.float16 else 1e-22
+    rows.append(z)
+    mix = torch.randn(H) * mags[0]; mix[H // 2:] = torch.randn(H - H // 2) * mags[-3]
+    rows.append(mix)
+    one = torch.zeros(H); one[7] = 1.0
+    rows.append(one)
+    x = torch.stack(rows).to(dtype)
+    w = torch.empty(H, dtype=dtype).normal_(mean=1.0, std=0.1)
+    q, s_ = ops.rms_norm_dynamic_per_token_quant(x.to(DEV), w.to(DEV), eps, E4, None, None)
+    rq, rs, _ = quant.rms_norm_dynamic_per_token_quant(x, w, eps, E4, None, None, exact_variance=True)
+    fin = torch.isfinite(rs)
+    assert torch.equal(s_.cpu()[fin], rs[fin]) and torch.equal(torch.isnan(s_.cpu()), torch.isnan(rs)), \
+        f"a6 scales differ in rows {(s_.cpu() != rs).nonzero().flatten().tolist()}"
+    assert torch.equal(u8(q)[fin], u8(rq)[fin])
+    q, s_ = ops.rms_norm_per_block_quant(x.to(DEV), w.to(DEV), eps, 128, E4, None)
+    rq, rs, _ = quant.rms_norm_per_block_quant(x, w, eps, 128, E4, None, exact_variance=True)
+    fin = torch.isfinite(rs).all(dim=1)
+    assert torch.equal(s_.cpu()[fin], rs[fin]), f"a7 scales differ in rows {(s_.cpu() != rs).any(1).nonzero().flatten().tolist()}"
+    assert torch.equal(u8(q)[fin], u8(rq)[fin])
+    q, s_ = ops.rms_norm_mxfp4_quant(x.to(DEV), w.to(DEV), eps, None)
+    rq, rs, _ = quant.rms_norm_mxfp4_quant(x, w, eps, None, exact_variance=True)
+    bad = (s_.cpu() != rs).any(1) | (u8(q) != rq).any(1)
+    assert not bad.any(), f"a8 differs in rows {bad.nonzero().flatten().tolist()}"
+    scale = torch.tensor(0.02, dtype=torch.float32)
+    q = ops.rms_norm_static_fp8_quant(x.to(DEV), w.to(DEV), scale.to(DEV), eps, None)
+    rq, _ = quant.rms_norm_static_fp8_quant(x, w, scale, eps, None, exact_variance=True)
+    bad = (u8(q) != u8(rq)).any(1)
+    assert not bad.any(), f"a9 differs in rows {bad.nonzero().flatten().tolist()}"
+
+
 def test_a6_scale_ub(ops):
     x, w, _ = _norm_inputs(83, 1024, torch.bfloat16, False)
     normed, _ = quant.rms_norm_f32(x, w, 1e-6, exact_variance=True)

@@ -180,6 +180,37 @@ __device__ __forceinline__ float mean_sq_f32(double sum, double inv_H, double H)
   return static_cast<float>(q);
 }
 
+// ---- exact sum of squares of 16-bit inputs without a conversion instruction ----------------------------
+// The square of a bf16 / f16 value has at most 16 / 22 significant bits, so `x * x` in fp32 is exact (unless
+// it leaves the normal fp32 range), and a finite non-negative fp32 bit pattern u, shifted into the fields of
+// a double -- high word u >> 3, low word u << 29 -- IS the double  value * 2^-896  (both formats code exponent
+// field 0 as "no hidden one", so zero and fp32 subnormals map exactly as well).  One packed FMUL2 per pair, one
+// shift and one DADD per element replace F2F.F64.F32 + DFMA: the conversion runs on the quarter-rate XU pipe,
+// which these kernels share with the output conversions (ncu, rms_norm + MXFP4: XU 32 %, math-pipe-throttle
+// and short-scoreboard stalls on it).  For bf16 the low word is always 0 for a normal square.  It costs half an
+// issue slot per element more than the conversions, so only the modes where it measured faster use it (kWidenSq).
+// The scaled sum is trusted when it is 0 (every square was 0 or flushed: the mean rounds to 0 either way) or
+// lies in [2^-955, 2^-768) = true sum in [2^-59, 2^128): below that, squares that fell into the fp32 subnormal
+// range (|x| < 2^-63, error <= 2^-150 each) could matter; at or above it some square was Inf / NaN (those
+// patterns widen to >= 2^-768).  Outside the window the caller re-does the row with real conversions.
+template <typename T>
+__device__ __forceinline__ double widen_sq(float sq) {
+  const uint32_t u = __float_as_uint(sq);
+  if constexpr (std::is_same<T, __nv_bfloat16>::value) return __hiloint2double(static_cast<int>(u >> 3), 0);
+  else return __hiloint2double(static_cast<int>(u >> 3), static_cast<int>(u << 29));
+}
+__device__ __forceinline__ bool widened_sum_ok(double s) {
+  return s == 0.0 || (s >= 0x1p-955 && s < 0x1p-768);
+}
+// mean_sq_f32 for a sum that carries the 2^-896 scale (power-of-two scaling commutes with every rounding
+// here: nothing in the window is subnormal)
+__device__ __forceinline__ float mean_sq_f32_widened(double sum, double inv_H, double H) {
+  const double q = sum * inv_H;
+  const uint32_t low = static_cast<uint32_t>(__double_as_longlong(q)) & 0x1fffffffu;
+  if (__builtin_expect(low - 0x0ffffffeu <= 4u, 0)) return static_cast<float>((sum / H) * 0x1p896);
+  return static_cast<float>(q * 0x1p896);
+}
+
 // Persistent CTAs (grid = min(T, resident CTAs)), each loops over rows.  A thread owns
 // VPT vectors of a row (tid + i * blockDim); the row lives in registers as fp32, so every
 // element is converted, normalised and scaled exactly once, and the NEXT row's 128-bit loads are
@@ -219,6 +250,10 @@ __global__ void __launch_bounds__(512) row_quant_kernel(const RowParams p, const
   if (!RMS) __syncthreads();
 
   constexpr bool kGrouped = MODE == MODE_GROUP || MODE == MODE_MXFP4;
+  // widen_sq() variance: measured per mode at 8192 x 4096 / 8192 bf16 (round 2): static 20.1 -> 19.1 / 36.9 -> 34.8 us,
+  // MXFP4 27.1 -> 26.6 / 50.4 -> 49.5 us; the per-token and 1 x G FP8 kernels sit exactly at their 128-register bound
+  // and lose to the extra live values (20.7 -> 21.3 us, 25.3 -> 27.5 us with spills), so they keep the conversions
+  constexpr bool kWidenSq = MODE == MODE_STATIC || MODE == MODE_MXFP4;
   static_assert(VG == 1 || kGrouped, "VG only applies to the per-group modes");
   static_assert(VPT % VG == 0, "whole runs per thread");
   // vector index of (thread, i), see above; VG == 1 without groups degenerates to tid + i * nthr
@@ -301,17 +336,38 @@ __global__ void __launch_bounds__(512) row_quant_kernel(const RowParams p, const
     if constexpr (RMS) {
       float var;
       if (p.exact_var) {
-        // fp64 sum of the (exact) squares: two accumulators, 1 conversion + 1 DFMA per element
-        double d0 = 0.0, d1 = 0.0;
+        bool have = false;
+        var = 0.0f;
+        if constexpr (sizeof(T) == 2 && kWidenSq) {
+          // exact fp32 squares widened with integer operations (see widen_sq)
+          double d0 = 0.0, d1 = 0.0;
 #pragma unroll
-        for (int i = 0; i < VPT; ++i)
+          for (int i = 0; i < VPT; ++i)
 #pragma unroll
-          for (int j = 0; j < 8; j += 2) {
-            const double a = static_cast<double>(v[i][j]), b = static_cast<double>(v[i][j + 1]);
-            d0 = fma(a, a, d0);
-            d1 = fma(b, b, d1);
-          }
-        var = mean_sq_f32(block_sum1_f64(d0 + d1, scratch64, slot), p.inv_H, static_cast<double>(p.H));
+            for (int j = 0; j < 8; j += 2) {
+              float a = v[i][j], b = v[i][j + 1];
+              mul2(a, b, a, b);
+              d0 += widen_sq<T>(a);
+              d1 += widen_sq<T>(b);
+            }
+          const double s = block_sum1_f64(d0 + d1, scratch64, slot);
+          have = widened_sum_ok(s);   // the same value in every thread: a CTA-uniform branch
+          if (have) var = mean_sq_f32_widened(s, p.inv_H, static_cast<double>(p.H));
+          else slot ^= 1;             // a second reduction follows: it must not reuse this one's scratch row
+        }
+        if (!have) {
+          // fp64 sum of the (exact) squares: two accumulators, 1 conversion + 1 DFMA per element
+          double d0 = 0.0, d1 = 0.0;
+#pragma unroll
+          for (int i = 0; i < VPT; ++i)
+#pragma unroll
+            for (int j = 0; j < 8; j += 2) {
+              const double a = static_cast<double>(v[i][j]), b = static_cast<double>(v[i][j + 1]);
+              d0 = fma(a, a, d0);
+              d1 = fma(b, b, d1);
+            }
+          var = mean_sq_f32(block_sum1_f64(d0 + d1, scratch64, slot), p.inv_H, static_cast<double>(p.H));
+        }
       } else {
         float s0 = 0.0f, s1 = 0.0f;
 #pragma unroll
@@ -378,7 +434,8 @@ __global__ void __launch_bounds__(512) row_quant_kernel(const RowParams p, const
         if (ok[i]) stg_stream(orow + voff[i], pack_q8<Q>(v[i]));
       }
     } else {  // MODE_GROUP / MODE_MXFP4: 1 x G groups; VG vectors per thread and 2^lanes_log2 lanes per group
-      const int lanes_log2 = p.lanes_log2;
+      // MXFP4 groups are 32 wide (4 vectors): the lane count follows from VG at compile time
+      const int lanes_log2 = MODE == MODE_MXFP4 ? (VG == 1 ? 2 : (VG == 2 ? 1 : 0)) : p.lanes_log2;
       const bool lead_lane = (tid & ((1 << lanes_log2) - 1)) == 0;
 #pragma unroll
       for (int gi = 0; gi < VPT / VG; ++gi) {
