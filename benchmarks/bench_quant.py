@@ -136,6 +136,7 @@ def main():
     ap.add_argument("--silu-fast", type=int, default=-1, help="-1 auto (default), 0 accurate, 1 approximate")
     ap.add_argument("--only", default=None, help="comma-separated op names")
     ap.add_argument("--T", type=int, default=None)
+    ap.add_argument("--H", default=None, help="comma-separated hidden sizes (overrides the per-op defaults)")
     ap.add_argument("--scale", type=float, default=1.0, help="multiply the random inputs (activation magnitude)")
     args = ap.parse_args()
     global SCALE
@@ -158,6 +159,8 @@ def main():
         Hs = ([4096] if args.quick else [4096, 8192]) if op in row_ops else ([14336] if args.quick else [14336, 28672])
         if op in cache_ops:
             Hs = [128, 512]
+        if args.H:
+            Hs = [int(h) for h in args.H.split(",")]
         for H in Hs:
             for T in (cache_Ts if op in cache_ops else Ts):
                 fns, nb = case(op, T, H)

@@ -700,7 +700,16 @@ int launch_row(const RowParams& p_in, int64_t T_rows, bool vec_ok, cudaStream_t 
   // per-token kernel 4 (no difference there)
   constexpr int kMaxVpt = 8;
   static const int env_vpt = [] { const char* e = getenv("VXK_ROW_VPT"); return e ? atoi(e) : 0; }();
-  const int want = env_vpt > 0 ? env_vpt : ((RMS && sizeof(T) == 2) ? 8 : 4);
+  int want = env_vpt > 0 ? env_vpt : ((RMS && sizeof(T) == 2) ? 8 : 4);
+  if (env_vpt <= 0 && want == 8 && nvec <= 640) {
+    // measured at T = 8192 (profiles/r02c_row_vpt_by_hidden.txt): up to H = 5120 the per-group kernels are faster
+    // with 4 vectors per thread and twice the warps (H = 2048: 14.9 -> 13.9 us 1x128, 16.2 -> 14.2 us MXFP4; 4096:
+    // 25.4 -> 24.2, 26.8 -> 26.1; 5120: 33.7 -> 31.0, 39.5 -> 34.8), and so is every mode when 8 vectors per thread
+    // would leave a partly filled last warp but 4 would not (H = 5120: 80 -> 96 threads with tail predicates
+    // against 160 full ones: per-token 31.3 -> 30.8, static 29.1 -> 25.6).  Longer rows keep 8.
+    const bool grouped = MODE == MODE_GROUP || MODE == MODE_MXFP4;
+    if (grouped || (nvec % 256 != 0 && nvec % 128 == 0)) want = 4;
+  }
   int vpt = 1;
   while (vpt < want && vpt < kMaxVpt && nvec > 32 * vpt) vpt *= 2;
   while ((nvec + vpt - 1) / vpt > 256 && vpt < 8) vpt *= 2;  // long rows: up to 8 x 512 threads
