@@ -226,10 +226,11 @@ DEEPSEEK = [(7168, 1536), (1536, 24576), (512, 32768), (16384, 7168), (7168, 368
 @pytest.mark.parametrize("per_channel", [True, False])
 @pytest.mark.parametrize("bias", [False, True])
 @pytest.mark.parametrize("nk", [(384, 512), (1000, 1040), (4096, 4096), (136, 7168), (6144, 640)])
-@pytest.mark.parametrize("m", [3, 33, 64, 65, 128, 129, 200, 256])
+@pytest.mark.parametrize("m", [3, 33, 64, 65, 128, 129, 200, 256, 257, 300, 384, 385, 511, 512])
 def test_fp8_gemm_skinny(ops, lib, fp8, per_channel, bias, nk, m):
     """Small-M kernel (gemm_skinny.cuh: operands swapped, K split over a cluster, DSMEM reduction): token
-    tiles 32 / 64 / 128 / 256, N and K tails, odd numbers of K slices per cluster rank, every scale mode.
+    tiles 32 / 64 / 128 / 256, two to four token tiles of 128 side by side (129 ... 512 tokens, partial last tile),
+    N and K tails, odd numbers of K slices per cluster rank, every scale mode.
     Same checker as tests/test_fp8_gemm_onednn.py:174-214 (dequantised matmul), atol = rtol = 1e-2."""
     torch.manual_seed(m * 7 + nk[0])
     n, k = nk

@@ -78,9 +78,20 @@ __device__ __forceinline__ uint32_t mapa_u32(uint32_t cta_addr, uint32_t rank) {
 // the cluster exactly like the plain kernel's TMEM tile.
 template <int MT, bool BLK = false>
 __global__ void __launch_bounds__(kSkinnyThreads, 1)
-gemm_skinny_kernel(const SkinnyParams p, const __grid_constant__ CUtensorMap map_w,
+gemm_skinny_kernel(const SkinnyParams p_in, const __grid_constant__ CUtensorMap map_w,
                    const __grid_constant__ CUtensorMap map_a) {
   static_assert(!BLK || MT <= 128, "block-scaled small-M kernel: two MT-column TMEM buffers, MT register accumulators");
+  // Token tiles (gridDim.z > 1, 256 < M <= 512): tile z owns tokens [z * MT, z * MT + MT); everything below sees its
+  // own tile as the whole problem (output, per-token scales and the block-scale grid shifted, M clipped), and the
+  // tiles of one weight tile run side by side, so the weight comes from HBM once and from L2 for the other tiles.
+  SkinnyParams p = p_in;
+  const int m0 = static_cast<int>(blockIdx.z) * MT;
+  if (m0 > 0) {
+    p.D = static_cast<uint16_t*>(p_in.D) + static_cast<int64_t>(m0) * p_in.ldd;
+    if (p_in.a_scale_mode == 1) p.a_scale = p_in.a_scale + m0;
+    if (BLK) p.blk_sa = p_in.blk_sa + static_cast<int64_t>(m0) * p_in.sa0;
+  }
+  p.M = min(MT, p_in.M - m0);
   using L = SkinnySmem<MT>;
   constexpr int S = L::kStages;
   constexpr int kSkinnyKS = L::kKS;
@@ -144,7 +155,7 @@ gemm_skinny_kernel(const SkinnyParams p, const __grid_constant__ CUtensorMap map
       const int ns = min(kSkinnyKS, kb1 - kb);
       uint8_t* st = smem + stg * L::kStageBytes;
       for (int s = 0; s < ns; ++s)
-        tma_load_2d(st + kSkinnyKS * L::kWSlice + s * L::kASlice, &map_a, &full_bar[stg], (kb + s) * kBlockKBytes, 0);
+        tma_load_2d(st + kSkinnyKS * L::kWSlice + s * L::kASlice, &map_a, &full_bar[stg], (kb + s) * kBlockKBytes, m0);
     };
     if (elect_one()) {
       for (int it = 0; it < pre; ++it) load_w(it, it);

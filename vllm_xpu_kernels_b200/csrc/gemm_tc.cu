@@ -381,7 +381,8 @@ static int run_pair_block_scaled(Tc2Params tp, const void* A, int64_t lda_bytes,
 
 // Small-M FP8 GEMM (M <= 128): operands swapped, K split over a cluster.  See gemm_skinny.cuh.
 template <int MT, bool BLK = false>
-static int launch_skinny(SkinnyParams sp, const CUtensorMap& mw, const CUtensorMap& ma, int n_tiles, cudaStream_t st) {
+static int launch_skinny(SkinnyParams sp, const CUtensorMap& mw, const CUtensorMap& ma, int n_tiles, cudaStream_t st,
+                         int m_tiles = 1) {
   using L = SkinnySmem<MT>;
   auto kernel = gemm_skinny_kernel<MT, BLK>;
   static PerDeviceOnce once;
@@ -391,7 +392,7 @@ static int launch_skinny(SkinnyParams sp, const CUtensorMap& mw, const CUtensorM
   if (attr_err != cudaSuccess)
     return fail(VXK_ERR_CUDA, "cudaFuncSetAttribute(smem=%d): %s", L::kTotalBytes, cudaGetErrorString(attr_err));
   cudaLaunchConfig_t cfg{};
-  cfg.gridDim = dim3(n_tiles, sp.splits, 1);
+  cfg.gridDim = dim3(n_tiles, sp.splits, m_tiles);
   cfg.blockDim = dim3(kSkinnyThreads);
   cfg.dynamicSmemBytes = L::kTotalBytes;
   cfg.stream = st;
@@ -412,6 +413,20 @@ static int launch_skinny(SkinnyParams sp, const CUtensorMap& mw, const CUtensorM
   return check_launch("gemm_skinny");
 }
 
+// Token tiles of 128 for the small-M FP8 kernel at 256 < M <= 512 (1 = not eligible).  The CTA-pair kernel
+// covers such a problem with M/256 x N/256 tiles -- 32 tiles on 64 SMs for 512 x 4096 -- and has no K split; the
+// small-M kernel's 128 x 128 tiles with the cluster K split fill the machine (profiles/r02c_skinny_token_tiles.txt).
+// VXK_SKINNY_MTILES=0 switches it off.
+static int skinny_token_tiles(int64_t M, int n_tiles) {
+  static const int on = env_int("VXK_SKINNY_MTILES", 1);
+  // measured (graph replays, Llama-3-8B shapes): up to 256 tokens the single 256-token tile is as fast or faster
+  // (13.5 vs 16.6 us at 129 x 6144 x 4096), and more than one wave of tiles loses to the CTA-pair kernel
+  // (512 x 6144 x 4096: 31.9 vs 20.4 us)
+  if (!on || M <= 256 || M > 512) return 1;
+  const int t = static_cast<int>((M + 127) / 128);
+  return n_tiles * t <= sm_count() ? t : 1;
+}
+
 struct SkinnyBlkScales { const float* sa; const float* sb; int64_t sa0, sa1, sb0, sb1; int group_k, group_n; };
 
 static int run_skinny_f8(const TcParams& tp, const void* A, const void* W, int64_t M, int64_t N, int64_t K,
@@ -429,10 +444,20 @@ static int run_skinny_f8(const TcParams& tp, const void* A, const void* W, int64
   const int n_tiles = (int)((N + 127) / 128);
   // K split: enough CTAs for one wave, every rank at least two ring stages, portable cluster size
   static const int env_splits = env_int("VXK_SKINNY_SPLITS", 0);
-  const int mt = M <= 32 ? 32 : (M <= 64 ? 64 : (M <= 128 ? 128 : 256));
+  // 256 < M <= 512: token tiles of 128 side by side (gridDim.z), see skinny_token_tiles(); one 256-token tile otherwise
+  int m_tiles = (!blk && M > 128) ? skinny_token_tiles(M, n_tiles) : 1;
+  int mt = M <= 32 ? 32 : (M <= 64 ? 64 : ((M <= 128 || m_tiles > 1) ? 128 : 256));
+  // two 256-token tiles instead of three or four 128-token ones while each can still split K over a cluster of two
+  // (fewer operand bytes per flop: 512 x 4096 x 14336 38.4 -> 33.1 us; without the split fewer CTAs lose:
+  // 384 x 6144 x 4096 17.3 -> 25.5 us).  VXK_SKINNY_MT256 = 0 / 1 forces the choice.
+  static const int env_mt256 = env_int("VXK_SKINNY_MT256", -1);
+  if (m_tiles > 1 && (env_mt256 >= 0 ? env_mt256 != 0 : n_tiles * 4 <= sm_count())) {
+    mt = 256;
+    m_tiles = static_cast<int>((M + 255) / 256);
+  }
   const int ks = mt <= 128 ? 2 : 1;
   static const int env_pow2 = env_int("VXK_SKINNY_POW2", 1);
-  int splits = sm_count() / n_tiles;
+  int splits = sm_count() / (n_tiles * m_tiles);
   if (splits > 8) splits = 8;
   if (env_splits > 0) splits = env_splits > 8 ? 8 : env_splits;
   const int max_by_k = sp.num_k_blocks / (2 * ks);
@@ -458,8 +483,8 @@ static int run_skinny_f8(const TcParams& tp, const void* A, const void* W, int64
   switch (mt) {
     case 32: return launch_skinny<32>(sp, mw, ma, n_tiles, st);
     case 64: return launch_skinny<64>(sp, mw, ma, n_tiles, st);
-    case 128: return launch_skinny<128>(sp, mw, ma, n_tiles, st);
-    default: return launch_skinny<256>(sp, mw, ma, n_tiles, st);
+    case 128: return launch_skinny<128>(sp, mw, ma, n_tiles, st, m_tiles);
+    default: return launch_skinny<256>(sp, mw, ma, n_tiles, st, m_tiles);
   }
 }
 
@@ -661,9 +686,12 @@ extern "C" int vxk_fp8_gemm(void* D, const void* A, const void* B, const void* a
   if (operands_ok && a_scale_mode != 2) {
     tp.a_scale = static_cast<const float*>(a_scale);
     tp.b_scale = static_cast<const float*>(b_scale);
-    static const int skinny_max_m = env_int("VXK_SKINNY_MAX_M", 256);
-    // 129..256 tokens: only while the 128-row weight tiles fit one wave (else the general kernels win)
-    if (peers.n == 0 && M <= skinny_max_m && M <= 256 && K >= 512 && (M <= 128 || (N + 127) / 128 <= sm_count()))
+    static const int skinny_max_m = env_int("VXK_SKINNY_MAX_M", 512);
+    // 129..256 tokens: only while the 128-row weight tiles fit one wave (else the general kernels win);
+    // 257..512 tokens: only as token tiles of 128 (skinny_token_tiles)
+    const int n_tiles128 = static_cast<int>((N + 127) / 128);
+    if (peers.n == 0 && M <= skinny_max_m && K >= 512 &&
+        (M <= 128 || (M <= 256 && n_tiles128 <= sm_count()) || (M <= 512 && skinny_token_tiles(M, n_tiles128) > 1)))
       return run_skinny_f8(tp, A, B, M, N, K, lda, b_stride_n, st);
     const int bn = single_cta_bn(M, N, 256);
     if (!force_single() && (prefer_pair(M, N, bn, 256) || peers.multicast)) {
