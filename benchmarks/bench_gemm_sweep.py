@@ -125,12 +125,15 @@ def main():
     ap.add_argument("--sets", default="llama8b_fp8,llama70b_mxfp4,dsv3_blockfp8")
     ap.add_argument("--Ms", default="1,16,64,256,1024,4096,8192")
     ap.add_argument("--json", default=None)
+    ap.add_argument("--shapes", default=None, help="restrict every set to these K:N pairs, e.g. 28672:8192,8192:10240")
     args = ap.parse_args()
     pk = peaks()
     out = []
     for kind in args.sets.split(","):
         peak_tf = (4.0 if kind == "llama70b_mxfp4" else 1.0 if kind == "llama8b_w8a16" else 2.0) * pk["bf16"]
         for (K, N) in SETS[kind]:
+            if args.shapes and f"{K}:{N}" not in args.shapes.split(","):
+                continue
             wbytes = K * N // (2 if kind == "llama70b_mxfp4" else 1)
             for M in [int(m) for m in args.Ms.split(",")]:
                 copies = max(1, min(8, int(300e6 // wbytes) + 1))

@@ -151,6 +151,53 @@ __global__ void sf_pack_kernel(uint32_t* out, int64_t rows, int64_t groups32, in
   }
 }
 
+// The same packing for the common case -- row-major E8M0 grids, one byte per 32-element group, 16-byte aligned rows,
+// K % 512 == 0 -- as a tiled transpose, BOTH operands in one launch.  A CTA owns one tile = 128 rows x 64 scale
+// bytes (2048 K elements = 16 output chunks): it reads the tile as 512 coalesced 16-byte loads (four lanes per row
+// segment, whole 32-byte sectors; sf_pack_kernel's 4-byte gathers use one eighth of every sector), parks it in shared
+// memory (row pitch 17 words: conflict-free both ways) and writes each 512-byte chunk as one warp-wide 16-byte store.
+// Blocks [0, a_tiles) pack operand A, the rest operand B.  ~6.4 us + 6.4 us + a launch gap -> one launch.
+struct SfPack2Op {
+  uint32_t* out;
+  const uint8_t* src;
+  int64_t rows, row_stride;
+  int nblk, tiles;
+};
+__global__ void __launch_bounds__(256) sf_pack2_kernel(SfPack2Op a, SfPack2Op b, int64_t groups32, int num_kb,
+                                                       int sf_words, int n_kq) {
+  __shared__ uint32_t tile[128 * 17];
+  const bool is_b = static_cast<int>(blockIdx.x) >= a.tiles;
+  const SfPack2Op& o = is_b ? b : a;
+  const int t = static_cast<int>(blockIdx.x) - (is_b ? a.tiles : 0);
+  const int blk = t / n_kq, kq = t % n_kq;
+  const int tid = threadIdx.x;
+#pragma unroll
+  for (int h = 0; h < 2; ++h) {
+    const int r = (tid >> 2) + h * 64, seg = tid & 3;
+    const int64_t row = static_cast<int64_t>(blk) * 128 + r;
+    const int64_t byte0 = static_cast<int64_t>(kq) * 64 + seg * 16;      // = first group of the segment
+    uint4 v = make_uint4(0u, 0u, 0u, 0u);
+    if (row < o.rows && byte0 < groups32) v = __ldg(reinterpret_cast<const uint4*>(o.src + row * o.row_stride + byte0));
+    uint32_t* d = tile + r * 17 + seg * 4;
+    d[0] = v.x; d[1] = v.y; d[2] = v.z; d[3] = v.w;
+  }
+  __syncthreads();
+  const int chunks = num_kb * sf_words;      // 512-byte chunks per 128-row block along K
+#pragma unroll
+  for (int h = 0; h < 2; ++h) {
+    const int lane = tid & 31, j = (tid >> 5) + h * 8;
+    const int64_t jg = static_cast<int64_t>(kq) * 16 + j;                // chunk index along K = kb * sf_words + w
+    if (jg < chunks) {
+      const int64_t kb = jg / sf_words;
+      const int w = static_cast<int>(jg % sf_words);
+      const uint4 v = make_uint4(tile[lane * 17 + j], tile[(32 + lane) * 17 + j], tile[(64 + lane) * 17 + j],
+                                 tile[(96 + lane) * 17 + j]);
+      uint32_t* dst = o.out + (((kb * o.nblk + blk) * sf_words + w) << 7) + lane * 4;
+      *reinterpret_cast<uint4*>(dst) = v;
+    }
+  }
+}
+
 static std::atomic<uint64_t> g_sf_pack_calls{0};   // scale re-packing launches (tests: the packed entry points issue none)
 
 struct SfPack {
@@ -349,13 +396,30 @@ static int run_pair_block_scaled(Tc2Params tp, const void* A, int64_t lda_bytes,
   const int a_words = a_kps == 1 && a_k_stride == 1 && a_row_stride % 4 == 0 && reinterpret_cast<uintptr_t>(a_scale) % 4 == 0;
   const int b_words = b_kps == 1 && b_k_stride == 1 && b_row_stride % 4 == 0 && reinterpret_cast<uintptr_t>(b_scale) % 4 == 0;
   int rc;
-  if (!a_packed) {
+  // both grids in the plain row-major form: one tiled launch (sf_pack2_kernel)
+  static const int env_pack2 = env_int("VXK_SF_PACK2", 1);
+  auto plain = [&](const uint8_t* p, int words, int64_t row_div, int64_t row_stride) {
+    return words && row_div == 1 && row_stride % 16 == 0 && reinterpret_cast<uintptr_t>(p) % 16 == 0 && groups32 % 16 == 0;
+  };
+  const bool a_fast = !a_packed && plain(a_scale, a_words, 1, a_row_stride);
+  const bool b_fast = !b_packed && plain(b_scale, b_words, b_row_div, b_row_stride);
+  bool a_done = a_packed != nullptr, b_done = b_packed != nullptr;
+  if (env_pack2 && (a_fast || a_done) && (b_fast || b_done) && (a_fast || b_fast)) {
+    const int n_kq = (sp.num_kb * sp.sf_words + 15) / 16;
+    SfPack2Op oa{const_cast<uint32_t*>(sfa), a_scale, M, a_row_stride, sp.a_blocks, a_fast ? sp.a_blocks * n_kq : 0};
+    SfPack2Op ob{const_cast<uint32_t*>(sfb), b_scale, N, b_row_stride, sp.b_blocks, b_fast ? sp.b_blocks * n_kq : 0};
+    sf_pack2_kernel<<<oa.tiles + ob.tiles, 256, 0, st>>>(oa, ob, groups32, sp.num_kb, sp.sf_words, n_kq);
+    if ((rc = check_launch("sf_pack2"))) return rc;
+    g_sf_pack_calls.fetch_add(1, std::memory_order_relaxed);
+    a_done = b_done = true;
+  }
+  if (!a_done) {
     sf_pack_kernel<<<blocks, 256, 0, st>>>(const_cast<uint32_t*>(sfa), M, groups32, sp.num_kb, sp.a_blocks, sp.sf_words,
                                            a_scale, 1, a_row_stride, a_kps, a_k_stride, a_words);
     if ((rc = check_launch("sf_pack_a"))) return rc;
     g_sf_pack_calls.fetch_add(1, std::memory_order_relaxed);
   }
-  if (!b_packed) {
+  if (!b_done) {
     sf_pack_kernel<<<blocks, 256, 0, st>>>(const_cast<uint32_t*>(sfb), N, groups32, sp.num_kb, sp.b_blocks, sp.sf_words,
                                            b_scale, b_row_div, b_row_stride, b_kps, b_k_stride, b_words);
     if ((rc = check_launch("sf_pack_b"))) return rc;
