@@ -503,9 +503,10 @@ def test_ops_on_second_device_after_first(ops):
 
 @pytest.mark.parametrize("k", [1024, 1280, 4096, 8192])
 @pytest.mark.parametrize("n", [128, 1000, 4096])
-@pytest.mark.parametrize("m", [1, 7, 33, 64, 100, 128])
+@pytest.mark.parametrize("m", [1, 7, 33, 64, 100, 128, 129, 200, 256, 257, 385, 512])
 def test_mxfp4_skinny_decode_kernel(ops, lib, m, n, k):
-    """M <= 128: the swap-AB split-K MXFP4 kernel (gemm_skinny_mx4.cuh) straight from the natural scale tensors;
+    """M <= 128, and 129 ... 512 tokens as two to four 128-token tiles side by side: the swap-AB split-K MXFP4 kernel
+    (gemm_skinny_mx4.cuh) straight from the natural scale tensors;
     ragged N, K slices that do not fill the last ring stage (1280 = 5 x 256), bias, both output types."""
     torch.manual_seed(m * 131 + n + k)
     x = torch.randn(m, k, dtype=torch.bfloat16, device=DEV)

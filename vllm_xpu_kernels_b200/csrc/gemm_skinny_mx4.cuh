@@ -57,9 +57,14 @@ struct SkinnyMx4Smem {
 
 template <int MT>
 __global__ void __launch_bounds__(kSkinnyThreads, 1)
-gemm_skinny_mx4_kernel(const SkinnyMx4Params p, const __grid_constant__ CUtensorMap map_w,
+gemm_skinny_mx4_kernel(const SkinnyMx4Params p_in, const __grid_constant__ CUtensorMap map_w,
                        const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_sfw,
                        const __grid_constant__ CUtensorMap map_sfa) {
+  // token tiles (gridDim.z > 1, 128 < M <= 512): tile z owns tokens [z * MT, z * MT + MT), as in gemm_skinny_kernel
+  SkinnyMx4Params p = p_in;
+  const int m0 = static_cast<int>(blockIdx.z) * MT;
+  p.D = static_cast<uint16_t*>(p_in.D) + static_cast<int64_t>(m0) * p_in.ldd;
+  p.M = min(MT, p_in.M - m0);
   using L = SkinnyMx4Smem<MT>;
   constexpr int S = L::kStages;
   constexpr int KS = L::kKS;
@@ -125,8 +130,8 @@ gemm_skinny_mx4_kernel(const SkinnyMx4Params p, const __grid_constant__ CUtensor
       const int ns = min(KS, kb1 - kb);
       uint8_t* st = smem + stg * L::kStageBytes;
       for (int s = 0; s < ns; ++s)
-        tma_load_2d(st + L::kOffA + s * L::kASlice, &map_a, &full_bar[stg], (kb + s) * kBlockKBytes, 0);
-      tma_load_2d(st + L::kOffRawA, &map_sfa, &full_bar[stg], kb * 8, 0);
+        tma_load_2d(st + L::kOffA + s * L::kASlice, &map_a, &full_bar[stg], (kb + s) * kBlockKBytes, m0);
+      tma_load_2d(st + L::kOffRawA, &map_sfa, &full_bar[stg], kb * 8, m0);
     };
     if (elect_one()) {
       for (int it = 0; it < pre; ++it) load_w(it, it);

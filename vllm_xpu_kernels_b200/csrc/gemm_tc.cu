@@ -555,7 +555,7 @@ static int run_skinny_f8(const TcParams& tp, const void* A, const void* W, int64
 // Small-M MXFP4 GEMM (M <= 128).  See gemm_skinny_mx4.cuh.
 template <int MT>
 static int launch_skinny_mx4(SkinnyMx4Params sp, const CUtensorMap& mw, const CUtensorMap& ma, const CUtensorMap& msw,
-                             const CUtensorMap& msa, int n_tiles, cudaStream_t st) {
+                             const CUtensorMap& msa, int n_tiles, cudaStream_t st, int m_tiles = 1) {
   using L = SkinnyMx4Smem<MT>;
   auto kernel = gemm_skinny_mx4_kernel<MT>;
   static PerDeviceOnce once;
@@ -565,7 +565,7 @@ static int launch_skinny_mx4(SkinnyMx4Params sp, const CUtensorMap& mw, const CU
   if (attr_err != cudaSuccess)
     return fail(VXK_ERR_CUDA, "cudaFuncSetAttribute(smem=%d): %s", L::kTotalBytes, cudaGetErrorString(attr_err));
   cudaLaunchConfig_t cfg{};
-  cfg.gridDim = dim3(n_tiles, sp.splits, 1);
+  cfg.gridDim = dim3(n_tiles, sp.splits, m_tiles);
   cfg.blockDim = dim3(kSkinnyThreads);
   cfg.dynamicSmemBytes = L::kTotalBytes;
   cfg.stream = st;
@@ -595,8 +595,9 @@ static int run_skinny_mx4(const TcParams& tp, const void* A, const void* W, cons
   const int n_tiles = (int)((N + 127) / 128);
   static const int env_splits = env_int("VXK_SKINNY_SPLITS", 0);
   const int mt = M <= 32 ? 32 : (M <= 64 ? 64 : 128);
+  const int m_tiles = static_cast<int>((M + mt - 1) / mt);   // > 1 only for 128 < M <= 512 (skinny_mx4_token_tiles)
   constexpr int ks = 2;
-  int splits = sm_count() / n_tiles;
+  int splits = sm_count() / (n_tiles * m_tiles);
   if (splits > 8) splits = 8;
   if (env_splits > 0) splits = env_splits > 8 ? 8 : env_splits;
   const int max_by_k = sp.num_k_blocks / (2 * ks);
@@ -617,7 +618,7 @@ static int run_skinny_mx4(const TcParams& tp, const void* A, const void* W, cons
   switch (mt) {
     case 32: return launch_skinny_mx4<32>(sp, mw, ma, msw, msa, n_tiles, st);
     case 64: return launch_skinny_mx4<64>(sp, mw, ma, msw, msa, n_tiles, st);
-    default: return launch_skinny_mx4<128>(sp, mw, ma, msw, msa, n_tiles, st);
+    default: return launch_skinny_mx4<128>(sp, mw, ma, msw, msa, n_tiles, st, m_tiles);
   }
 }
 
@@ -928,7 +929,12 @@ static int fp4_gemm_impl(void* D, const void* A, const void* B, const void* a_sc
   // decode regime: swap-AB split-K kernel straight from the caller's scale tensors
   static const int skinny_mx4 = env_int("VXK_SKINNY_MX4", 1);
   // (65..128 tokens: only while the 128-row weight tiles fit one wave -- measured, profiles/r02_mxfp4_smallm.txt)
-  if (skinny_mx4 && peers.n == 0 && K >= 1024 && scales_direct && (M <= 64 || (M <= 128 && (N + 127) / 128 <= sm_count())))
+  // 129..512 tokens: two to four 128-token tiles side by side (gridDim.z) while they fit one wave
+  static const int skinny_mx4_max_m = env_int("VXK_SKINNY_MX4_MAX_M", 512);
+  const int64_t n_tiles128 = (N + 127) / 128;
+  if (skinny_mx4 && peers.n == 0 && K >= 1024 && scales_direct &&
+      (M <= 64 || (M <= 128 && n_tiles128 <= sm_count()) ||
+       (M <= 512 && M <= skinny_mx4_max_m && n_tiles128 * ((M + 127) / 128) <= sm_count())))
     return run_skinny_mx4(tp, A, B, a_scale, b_scale, M, N, K, lda_bytes, ldb_bytes, sa0, sb0, st);
   const bool ws_ok = (a_packed && b_packed) || (workspace && workspace_bytes >= vxk_fp4_gemm_workspace_bytes(M, N, K));
   if (!force_single() && (prefer_pair(M, N, bn, 192) || peers.n > 0) && ws_ok) {
