@@ -66,12 +66,12 @@ def test_fused_equals_the_two_ops(ops, mid, fp8, per_channel, bias, m, inter, k)
     q, s = ops.fp8_gemm_silu_mul_quant(A, W.t(), sA, sW, bd, mid)
     assert launches() == n0 + 1, "one kernel launch"
     torch.cuda.synchronize()
-    if m > 256:
+    if m > 512:
         # fp8_gemm accumulates K in one chain here, like the fused kernel: bit for bit
         assert torch.equal(s, ref_s)
         assert torch.equal(q.view(torch.uint8), ref_q.view(torch.uint8))
     else:
-        # M <= 256: fp8_gemm runs its split-K small-M kernel, whose fp32 partial sums are added in another order;
+        # M <= 512: fp8_gemm may run its split-K small-M kernel, whose fp32 partial sums are added in another order;
         # the rare last-bit differences of the 16-bit intermediate move a few codes by one step
         torch.testing.assert_close(s, ref_s, rtol=1e-2, atol=0)
         assert (q.view(torch.uint8) != ref_q.view(torch.uint8)).float().mean().item() < 5e-3

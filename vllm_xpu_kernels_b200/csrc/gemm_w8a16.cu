@@ -136,7 +136,7 @@ static int launch_w16_skinny_impl(const W16SkinnyParams& sp, const CUtensorMap& 
   if (attr_err != cudaSuccess)
     return fail(VXK_ERR_CUDA, "cudaFuncSetAttribute(smem=%d): %s", L::kTotalBytes, cudaGetErrorString(attr_err));
   cudaLaunchConfig_t cfg{};
-  cfg.gridDim = dim3(n_tiles, sp.splits, 1);
+  cfg.gridDim = dim3(n_tiles, sp.splits, sp.m_tiles > 1 ? sp.m_tiles : 1);
   cfg.blockDim = dim3(kW16SkThreads);
   cfg.dynamicSmemBytes = L::kTotalBytes;
   cfg.stream = st;
@@ -185,7 +185,7 @@ static int run_w16_skinny(W16SkinnyParams sp, const void* A, const void* W, int6
   sp.num_k_blocks = (int)(K / kW16SkBlockK);
   // K split: enough CTAs for one wave, every rank at least two raw stages, cluster sizes 1 / 2 / 4 / 8
   static const int env_splits = [] { const char* e = getenv("VXK_W16_SPLITS"); return e ? atoi(e) : 0; }();
-  int splits = sm_count() / n_tiles;
+  int splits = sm_count() / (n_tiles * (sp.m_tiles > 1 ? sp.m_tiles : 1));
   if (splits > 8) splits = 8;
   if (env_splits > 0) splits = env_splits > 8 ? 8 : env_splits;
   if (splits > sp.num_k_blocks / 2) splits = sp.num_k_blocks / 2;
@@ -200,7 +200,7 @@ static int run_w16_skinny(W16SkinnyParams sp, const void* A, const void* W, int6
   // widening, and the extra requests only add contention.  Kept as a switch, off by default.
   static const int env_pf = [] { const char* e = getenv("VXK_W16_PREFETCH"); return e ? atoi(e) : 0; }();
   sp.prefetch = env_pf;
-  const int mt = M <= 32 ? 32 : (M <= 64 ? 64 : 128);
+  const int mt = M <= 32 ? 32 : (M <= 64 ? 64 : 128);   // M > 128 only as sp.m_tiles tiles of 128
   CUtensorMap mw, ma;
   int rc;
   if ((rc = make_map_2d_u8(&mw, W, K, N, ldw, kW16SkBlockK, 128, true))) return rc;
@@ -249,15 +249,23 @@ extern "C" int vxk_fp8_gemm_w8a16(void* D, const void* A, const void* B, const f
   // streamed twice, which still beats the general kernel's thin in-flight window at this M while the weight
   // tiles fit one wave (measured: 26 vs 37 us at N = K = 4096, but 138 vs 94 us at N = 28672).
   static const int skinny_max_m = [] { const char* e = getenv("VXK_W16_SKINNY_MAX_M"); return e ? atoi(e) : 256; }();
-  if (M <= skinny_max_m && M <= 256 && (M <= 128 || (N + 127) / 128 <= sm_count()) && K % kW16SkBlockK == 0 &&
-      K >= 512 && (b_scale_mode != 2 || group_k % kW16SkBlockK == 0)) {
-    for (int64_t m0 = 0; m0 < M; m0 += 128) {
-      const int64_t mc = M - m0 < 128 ? M - m0 : 128;
+  static const int tiles_on = [] { const char* e = getenv("VXK_W16_MTILES"); return e ? atoi(e) : 1; }();
+  const bool w16_tiles_fit = tiles_on && M <= 512 && ((N + 127) / 128) * ((M + 127) / 128) <= sm_count();
+  if (((M <= skinny_max_m && M <= 256 && (M <= 128 || (N + 127) / 128 <= sm_count())) ||
+       (M > 256 && M <= 2 * skinny_max_m && w16_tiles_fit)) &&
+      K % kW16SkBlockK == 0 && K >= 512 && (b_scale_mode != 2 || group_k % kW16SkBlockK == 0)) {
+    // token tiles side by side in one launch while they fit one wave (the weight comes from HBM once and from L2
+    // for the other tiles, and no launch waits for the previous one); else the sequential passes below
+    const int64_t tiles = (M + 127) / 128;
+    const bool side_by_side = tiles > 1 && w16_tiles_fit;
+    for (int64_t m0 = 0; m0 < M; m0 += side_by_side ? M : 128) {
+      const int64_t mc = side_by_side ? M : (M - m0 < 128 ? M - m0 : 128);
       W16SkinnyParams sp{};
       sp.D = static_cast<uint16_t*>(D) + m0 * ldd; sp.b_scale = b_scale; sp.bias = bias; sp.M = (int)mc; sp.N = (int)N;
       sp.ldd = ldd; sp.b_scale_mode = b_scale_mode; sp.out_dtype = act_dtype; sp.bias_dtype = bias_dtype;
       sp.sb0 = sb0; sp.sb1 = sb1;
       sp.group_k = b_scale_mode == 2 ? (int)group_k : 1; sp.group_n = b_scale_mode == 2 ? (int)group_n : 1;
+      sp.m_tiles = side_by_side ? static_cast<int>(tiles) : 1;
       const int rc = run_w16_skinny(sp, static_cast<const uint16_t*>(A) + m0 * lda, B, mc, N, K, lda, b_stride_n,
                                     act_dtype == VXK_BF16, fp8_dtype == VXK_Q_E5M2, st);
       if (rc) return rc;

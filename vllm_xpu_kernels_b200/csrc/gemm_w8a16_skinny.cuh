@@ -45,6 +45,7 @@ struct W16SkinnyParams {
   int kb_per_split;
   int splits;
   int prefetch;           // raw stages requested into L2 ahead of the ring (cp.async.bulk.prefetch.tensor)
+  int m_tiles;            // token tiles of MT side by side in gridDim.z (0 / 1: one tile)
 };
 
 // TMA prefetch of one box into L2: no shared memory, no barrier -- it only starts the HBM read early
@@ -78,8 +79,13 @@ struct W16SkinnySmem {
 
 template <int MT, bool BF16, bool E5M2, bool SCALED, bool TA = false>
 __global__ void __launch_bounds__(kW16SkThreads, 1)
-gemm_w8a16_skinny_kernel(const W16SkinnyParams p, const __grid_constant__ CUtensorMap map_w,
+gemm_w8a16_skinny_kernel(const W16SkinnyParams p_in, const __grid_constant__ CUtensorMap map_w,
                          const __grid_constant__ CUtensorMap map_a) {
+  // token tiles (gridDim.z > 1, 128 < M <= 512): tile z owns tokens [z * MT, z * MT + MT), as in gemm_skinny_kernel
+  W16SkinnyParams p = p_in;
+  const int m0 = static_cast<int>(blockIdx.z) * MT;
+  p.D = static_cast<uint16_t*>(p_in.D) + static_cast<int64_t>(m0) * p_in.ldd;
+  p.M = min(MT, p_in.M - m0);
   using L = W16SkinnySmem<MT, TA>;
   constexpr uint32_t kASlotCol = 256;        // TA: operand slots in TMEM columns [256, 512)
   constexpr int S = L::kStages;
@@ -135,8 +141,8 @@ gemm_w8a16_skinny_kernel(const W16SkinnyParams p, const __grid_constant__ CUtens
     };
     auto load_a = [&](int it, int stg) {
       uint8_t* st = smem + stg * L::kRawStage + L::kRawW;
-      tma_load_2d(st, &map_a, &full_bar[stg], (kb0 + it) * 256, 0);                 // byte coordinates
-      tma_load_2d(st + L::kABox, &map_a, &full_bar[stg], (kb0 + it) * 256 + 128, 0);
+      tma_load_2d(st, &map_a, &full_bar[stg], (kb0 + it) * 256, m0);                // byte coordinates
+      tma_load_2d(st + L::kABox, &map_a, &full_bar[stg], (kb0 + it) * 256 + 128, m0);
     };
     // Optional (p.prefetch > 0, off by default -- measured slower at every depth): request the weight stream
     // into L2 `prefetch` stages ahead of the ring, so that the ring's own loads hit L2.
