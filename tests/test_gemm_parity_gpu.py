@@ -555,12 +555,13 @@ def test_weight_written_right_before_small_m_gemm(ops, lib):
 
 
 @pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
-@pytest.mark.parametrize("m", [1, 3, 17, 33, 64])
+@pytest.mark.parametrize("m", [1, 3, 17, 33, 64, 65, 128, 130, 200, 256])
 @pytest.mark.parametrize("nk,gk,gn", [((1536, 7168), 128, 128), ((7168, 2048), 128, 128), ((576, 1024), 128, 64),
                                       ((1000, 1536), 256, 8), ((384, 1024), 512, 128), ((24576, 1536), 128, 128)])
 @pytest.mark.parametrize("bias,col_major_sa", [(False, False), (True, True)])
 def test_block_fp8_small_m_kernel(ops, lib, dtype, m, nk, gk, gn, bias, col_major_sa):
-    """fp32 block scales at M <= 64 (BASELINE config 5 in the decode regime): gemm_skinny_kernel<MT, BLK> -- swap-AB,
+    """fp32 block scales at M <= 64 (BASELINE config 5 in the decode regime), and 65 ... 256 tokens as 64-token tiles
+    side by side where they fit one wave (else the general kernels): gemm_skinny_kernel<MT, BLK> -- swap-AB,
     cluster split-K, per-slice promotion.  DeepSeek shapes, N tails (576, 1000), group_k 128 / 256 / 512, group_n
     8 ... 128, row- and column-major activation scales, bias; float64 oracle, atol = rtol = 1e-2; deterministic."""
     n, k = nk

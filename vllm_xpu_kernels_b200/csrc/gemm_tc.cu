@@ -491,6 +491,16 @@ static int skinny_token_tiles(int64_t M, int n_tiles) {
   return n_tiles * t <= sm_count() ? t : 1;
 }
 
+// fp32-block small-M kernel: 64-token tiles side by side for 64 < M <= 256 (VXK_SKINNY_BLK_MAX_M, default 256)
+static int skinny_blk_token_tiles(int64_t M, int n_tiles) {
+  static const int max_m = env_int("VXK_SKINNY_BLK_MAX_M", 256);
+  if (M <= 64 || M > max_m || M > 256) return 1;
+  const int t = static_cast<int>((M + 63) / 64);
+  // only while every tile can still split K over a cluster of two (measured, DeepSeek-V3 shapes: 65 x 1536 x 7168
+  // 25.8 -> 10.9 us, 256 x 1536 x 7168 28.3 -> 18.2 us; without the split 128 x 7168 x 16384 64.2 -> 76.9 us)
+  return n_tiles * t * 2 <= sm_count() ? t : 1;
+}
+
 struct SkinnyBlkScales { const float* sa; const float* sb; int64_t sa0, sa1, sb0, sb1; int group_k, group_n; };
 
 static int run_skinny_f8(const TcParams& tp, const void* A, const void* W, int64_t M, int64_t N, int64_t K,
@@ -511,11 +521,12 @@ static int run_skinny_f8(const TcParams& tp, const void* A, const void* W, int64
   // 256 < M <= 512: token tiles of 128 side by side (gridDim.z), see skinny_token_tiles(); one 256-token tile otherwise
   int m_tiles = (!blk && M > 128) ? skinny_token_tiles(M, n_tiles) : 1;
   int mt = M <= 32 ? 32 : (M <= 64 ? 64 : ((M <= 128 || m_tiles > 1) ? 128 : 256));
+  if (blk && M > 64) { mt = 64; m_tiles = skinny_blk_token_tiles(M, n_tiles); }
   // two 256-token tiles instead of three or four 128-token ones while each can still split K over a cluster of two
   // (fewer operand bytes per flop: 512 x 4096 x 14336 38.4 -> 33.1 us; without the split fewer CTAs lose:
   // 384 x 6144 x 4096 17.3 -> 25.5 us).  VXK_SKINNY_MT256 = 0 / 1 forces the choice.
   static const int env_mt256 = env_int("VXK_SKINNY_MT256", -1);
-  if (m_tiles > 1 && (env_mt256 >= 0 ? env_mt256 != 0 : n_tiles * 4 <= sm_count())) {
+  if (!blk && m_tiles > 1 && (env_mt256 >= 0 ? env_mt256 != 0 : n_tiles * 4 <= sm_count())) {
     mt = 256;
     m_tiles = static_cast<int>((M + 255) / 256);
   }
@@ -540,7 +551,7 @@ static int run_skinny_f8(const TcParams& tp, const void* A, const void* W, int64
   if (blk) {
     switch (mt) {
       case 32: return launch_skinny<32, true>(sp, mw, ma, n_tiles, st);
-      case 64: return launch_skinny<64, true>(sp, mw, ma, n_tiles, st);
+      case 64: return launch_skinny<64, true>(sp, mw, ma, n_tiles, st, m_tiles);
       default: return launch_skinny<128, true>(sp, mw, ma, n_tiles, st);
     }
   }
@@ -778,7 +789,10 @@ extern "C" int vxk_fp8_gemm(void* D, const void* A, const void* B, const void* a
   // fp32 block scales at M <= 128 (config 5 in the decode regime): the small-M kernel with per-slice promotion
   static const int skinny_blk = env_int("VXK_SKINNY_BLK", 1);
   if (operands_ok && a_scale_mode == 2 && scale_dtype == VXK_S_F32 && group_k % 128 == 0 && K % group_k == 0 &&
-      group_n > 0 && M <= 64 && K >= 512 && peers.n == 0 && skinny_blk) {   // (65..128 tokens measured slower than the general kernel)
+      group_n > 0 && K >= 512 && peers.n == 0 && skinny_blk &&
+      (M <= 64 || skinny_blk_token_tiles(M, static_cast<int>((N + 127) / 128)) > 1)) {
+    // (a 128-token tile of this kernel measured slower than the general kernel; 65..256 tokens run as 64-token tiles
+    //  side by side while they fit one wave)
     SkinnyBlkScales bs{static_cast<const float*>(a_scale), static_cast<const float*>(b_scale), sa0, sa1, sb0, sb1,
                        static_cast<int>(group_k), static_cast<int>(group_n)};
     return run_skinny_f8(tp, A, B, M, N, K, lda, b_stride_n, st, &bs);
