@@ -9,6 +9,14 @@ import torch.distributed as dist
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 
+# The fused kernels accumulate K in ONE chain per output tile.  Up to 512 tokens the unfused ops would by default run
+# their split-K small-M kernels (token tiles side by side), whose fp32 partial sums are added in another order: equal
+# to output rounding, not bit for bit.  The bit-for-bit comparison below is against the same-chain kernels, so the
+# token-tile dispatch is switched off for this process (read once, at the first call).
+os.environ.setdefault("VXK_SKINNY_MTILES", "0")
+os.environ.setdefault("VXK_SKINNY_MX4_MAX_M", "128")
+os.environ.setdefault("VXK_SKINNY_BLK_MAX_M", "64")
+
 
 def main():
     rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
