@@ -346,7 +346,13 @@ static bool prefer_pair(int64_t M, int64_t N, int bn1, int bn2) {
   const int64_t sms = sm_count();
   const int64_t t1 = ((M + 127) / 128) * ((N + bn1 - 1) / bn1);
   const int64_t t2 = ((M + 255) / 256) * ((N + bn2 - 1) / bn2);
-  const double c1 = static_cast<double>((t1 + sms - 1) / sms) * 128.0 * bn1 * (bn1 >= 256 ? 1.20 : 1.35);
+  // the block-scaled single-CTA kernels (192-wide pair tiles as the alternative) lose more than this model's 1.35
+  // against the pair kernel once K is deep: MXFP4 384 x 8192 x 28672 ran 87 us single against 68 us as a pair, 384 x
+  // 8192 x 8192 29 vs 26 us, everything else measured within 3 % (profiles/r02c_pair_bias.txt) -> their single-CTA
+  // cost is weighted 1.5 x.  VXK_GEMM_PAIR_BIAS overrides the weight for every kind.
+  static const double env_bias = [] { const char* e = getenv("VXK_GEMM_PAIR_BIAS"); return e ? atof(e) : 0.0; }();
+  const double bias = env_bias > 0.0 ? env_bias : (bn2 == 192 ? 1.5 : 1.0);
+  const double c1 = static_cast<double>((t1 + sms - 1) / sms) * 128.0 * bn1 * (bn1 >= 256 ? 1.20 : 1.35) * bias;
   const double c2 = static_cast<double>((t2 + sms / 2 - 1) / (sms / 2)) * 128.0 * bn2;
   return c2 <= c1;
 }
